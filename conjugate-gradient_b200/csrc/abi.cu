@@ -1,0 +1,663 @@
+// abi.cu -- the C ABI of libcgb200.so.
+//
+// Part 1: the reference's operator API (include/mv_ops.h; reference mv_ops.h:26-42) and its
+//         solver entry point conj_grad (reference cg.c:24,88), symbol for symbol.  Host structs
+//         in, host structs out; the arithmetic runs in the kernels of kernels.cu.
+// Part 2: the cgb200_* extensions (include/cgb200.h).
+//
+// There is no CPU implementation of any arithmetic in this file: without a usable CUDA device
+// every arithmetic entry point fails (-1 / -1.0) and cgb200_last_error() says so.
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "../../include/cgb200.h"
+#include "solver.h"
+
+using namespace cgb;
+
+namespace {
+
+#define CU_OK(call)                                                              \
+  do {                                                                           \
+    cudaError_t e__ = (call);                                                    \
+    if (e__ != cudaSuccess) {                                                    \
+      set_error(std::string(#call) + ": " + cudaGetErrorString(e__));            \
+      return -1;                                                                 \
+    }                                                                            \
+  } while (0)
+
+std::mutex g_tab_mu;
+int g_mode = CGB200_EAGER;
+
+// ---- device mirrors of caller structs (keyed by struct address) -----------------------------
+
+struct MatrixEntry {
+  System* sys = nullptr;
+  const double* values = nullptr;
+  const int* cols = nullptr;
+  const int* rowptr = nullptr;
+  int size = 0, nnz = 0;
+  uint64_t fp = 0;
+};
+
+struct VectorEntry {
+  double* d = nullptr;
+  int cap = 0;
+  int n = 0;
+  bool dev_valid = false;   // device copy holds the current values
+  bool host_valid = false;  // host array holds the current values
+};
+
+std::unordered_map<const void*, MatrixEntry> g_mats;
+std::unordered_map<const void*, VectorEntry> g_vecs;
+
+// eager-mode scratch vectors
+double* g_scratch[3] = {nullptr, nullptr, nullptr};
+size_t g_scratch_cap[3] = {0, 0, 0};
+
+int scratch(int slot, size_t n, double** out) {
+  if (g_scratch_cap[slot] < n + 2) {
+    if (g_scratch[slot]) cudaFree(g_scratch[slot]);
+    g_scratch[slot] = nullptr;
+    g_scratch_cap[slot] = 0;
+    CU_OK(cudaMalloc(&g_scratch[slot], (n + 2) * sizeof(double)));
+    g_scratch_cap[slot] = n + 2;
+  }
+  *out = g_scratch[slot];
+  return 0;
+}
+
+// Sampled fingerprint of a matrix's host arrays: catches a caller that rebuilt or edited the
+// matrix behind an unchanged struct address (not a proof; cgb200_invalidate() is the contract).
+uint64_t mix(uint64_t h, uint64_t v) {
+  h ^= v + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
+  return h;
+}
+uint64_t fingerprint(const struct __mv_sparse* A) {
+  uint64_t h = 1469598103934665603ull;
+  const long long nnz = A->nnz, n = A->size;
+  const long long step_v = nnz > 2048 ? nnz / 2048 : 1;
+  for (long long k = 0; k < nnz; k += step_v) {
+    uint64_t bits;
+    memcpy(&bits, &A->values[k], 8);
+    h = mix(h, bits);
+    if (A->col_indices) h = mix(h, (uint64_t)(uint32_t)A->col_indices[k]);
+  }
+  if (nnz > 0) {
+    uint64_t bits;
+    memcpy(&bits, &A->values[nnz - 1], 8);
+    h = mix(h, bits);
+  }
+  const long long step_r = n > 1024 ? n / 1024 : 1;
+  for (long long i = 0; i <= n; i += step_r) h = mix(h, (uint64_t)(uint32_t)A->row_ptr[i]);
+  h = mix(h, (uint64_t)(uint32_t)A->row_ptr[n]);
+  return h;
+}
+
+bool is_vector(const struct __mv_sparse* v) { return v->col_indices == NULL && v->row_ptr == NULL; }
+
+// Device system for a host CSR struct, uploaded on first use and whenever the struct changed.
+System* matrix_system(struct __mv_sparse* A) {
+  if (!A->row_ptr || !A->values || (!A->col_indices && A->nnz > 0)) {
+    set_error("matrix struct lacks CSR arrays");
+    return nullptr;
+  }
+  if (ctx().world > 1) {
+    set_error("host-struct entry points are single-rank; use the cgb200_system_* API when distributed");
+    return nullptr;
+  }
+  const uint64_t fp = fingerprint(A);
+  auto it = g_mats.find(A);
+  if (it != g_mats.end()) {
+    MatrixEntry& e = it->second;
+    if (e.values == A->values && e.cols == A->col_indices && e.rowptr == A->row_ptr &&
+        e.size == A->size && e.nnz == A->nnz && e.fp == fp)
+      return e.sys;
+    delete e.sys;
+    g_mats.erase(it);
+  }
+  System* sys = system_from_csr(A->size, 0, A->size, A->row_ptr, A->col_indices, A->values, nullptr);
+  if (!sys) return nullptr;
+  MatrixEntry e;
+  e.sys = sys;
+  e.values = A->values;
+  e.cols = A->col_indices;
+  e.rowptr = A->row_ptr;
+  e.size = A->size;
+  e.nnz = A->nnz;
+  e.fp = fp;
+  g_mats[A] = e;
+  return sys;
+}
+
+void drop_mirror(const void* obj) {
+  auto im = g_mats.find(obj);
+  if (im != g_mats.end()) {
+    delete im->second.sys;
+    g_mats.erase(im);
+  }
+  auto iv = g_vecs.find(obj);
+  if (iv != g_vecs.end()) {
+    cudaFree(iv->second.d);
+    g_vecs.erase(iv);
+  }
+}
+
+int ensure_vec_capacity(VectorEntry& e, int n) {
+  if (e.cap < n || !e.d) {
+    if (e.d) cudaFree(e.d);
+    e.d = nullptr;
+    e.cap = 0;
+    CU_OK(cudaMalloc(&e.d, ((size_t)n + 2) * sizeof(double)));
+    e.cap = n;
+  }
+  e.n = n;
+  return 0;
+}
+
+// Device pointer holding the current values of an input vector.
+int dev_input(struct __mv_sparse* v, int slot, const double** out) {
+  Ctx& c = ctx();
+  const int n = v->size;
+  if (g_mode == CGB200_RESIDENT) {
+    VectorEntry& e = g_vecs[v];
+    if (e.dev_valid && e.n == n) {
+      *out = e.d;
+      return 0;
+    }
+    if (ensure_vec_capacity(e, n)) return -1;
+    if (n > 0)
+      CU_OK(cudaMemcpyAsync(e.d, v->values, sizeof(double) * n, cudaMemcpyHostToDevice, c.stream));
+    e.dev_valid = true;
+    e.host_valid = true;
+    *out = e.d;
+    return 0;
+  }
+  double* d;
+  if (scratch(slot, n, &d)) return -1;
+  if (n > 0)
+    CU_OK(cudaMemcpyAsync(d, v->values, sizeof(double) * n, cudaMemcpyHostToDevice, c.stream));
+  *out = d;
+  return 0;
+}
+
+// The reference's allocate-or-reuse rule for outputs (mv_ops.c:141-152 and its twins).
+int prepare_out(struct __mv_sparse** out, int size, int nnz) {
+  if (*out == NULL) {
+    *out = (struct __mv_sparse*)calloc(1, sizeof(struct __mv_sparse));
+    if (!*out) return -1;
+    (*out)->values = (double*)calloc(size > 0 ? size : 1, sizeof(double));
+    (*out)->col_indices = NULL;
+    (*out)->row_ptr = NULL;
+  } else {
+    (*out)->values = (double*)realloc((*out)->values, sizeof(double) * (size > 0 ? size : 1));
+  }
+  if (!(*out)->values) {
+    set_error("host allocation failed");
+    return -1;
+  }
+  (*out)->size = size;
+  (*out)->nnz = nnz;
+  return 0;
+}
+
+// Device pointer an op writes its result to (may coincide with an input mirror: in-place).
+int dev_output(struct __mv_sparse* o, int slot, double** out) {
+  const int n = o->size;
+  if (g_mode == CGB200_RESIDENT) {
+    VectorEntry& e = g_vecs[o];
+    if (e.cap < n || !e.d) {
+      // growing must keep nothing: the op overwrites all n elements
+      if (ensure_vec_capacity(e, n)) return -1;
+    }
+    e.n = n;
+    *out = e.d;
+    return 0;
+  }
+  return scratch(slot, n, out);
+}
+
+// Publishes an op's result: eager -> copy to the host array now; resident -> mark the mirror.
+int finish_output(struct __mv_sparse* o, double* d) {
+  Ctx& c = ctx();
+  if (g_mode == CGB200_RESIDENT) {
+    VectorEntry& e = g_vecs[o];
+    e.dev_valid = true;
+    e.host_valid = false;
+    return 0;
+  }
+  if (o->size > 0)
+    CU_OK(cudaMemcpyAsync(o->values, d, sizeof(double) * o->size, cudaMemcpyDeviceToHost, c.stream));
+  CU_OK(cudaStreamSynchronize(c.stream));
+  return 0;
+}
+
+int sync_to_host(struct __mv_sparse* o) {
+  auto it = g_vecs.find(o);
+  if (it == g_vecs.end()) return 0;
+  VectorEntry& e = it->second;
+  if (e.dev_valid && !e.host_valid && e.n == o->size && o->values) {
+    Ctx& c = ctx();
+    if (e.n > 0)
+      CU_OK(cudaMemcpyAsync(o->values, e.d, sizeof(double) * e.n, cudaMemcpyDeviceToHost, c.stream));
+    CU_OK(cudaStreamSynchronize(c.stream));
+    e.host_valid = true;
+  }
+  return 0;
+}
+
+int ewise(int op, double sca, struct __mv_sparse* a, struct __mv_sparse* b, struct __mv_sparse** out) {
+  if (!a || (op != 0 && !b) || !out) return -1;
+  if (op != 0 && a->size != b->size) return -1;
+  if (ensure_init(-1)) return -1;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  Ctx& c = ctx();
+  const int n = a->size, nnz = a->nnz;
+  // inputs first: *out may alias an input whose host array prepare_out() is about to realloc
+  const double *da = nullptr, *db = nullptr;
+  if (dev_input(a, 0, &da)) return -1;
+  if (op != 0 && dev_input(b, 1, &db)) return -1;
+  if (g_mode == CGB200_EAGER) CU_OK(cudaStreamSynchronize(c.stream));
+  if (prepare_out(out, n, nnz)) return -1;
+  double* dout = nullptr;
+  if (dev_output(*out, 2, &dout)) return -1;
+  if (g_mode == CGB200_RESIDENT) {  // dev_output may have re-allocated an aliased mirror
+    if (*out == a) da = dout;
+    if (op != 0 && *out == b) db = dout;
+  }
+  CU_OK(launch_ewise(op, sca, da, db, dout, n, c.stream));
+  return finish_output(*out, dout);
+}
+
+int solve_host(struct __mv_sparse* A, struct __mv_sparse* b, struct __mv_sparse** x,
+               const SolveOpts& o, SolveResult* res) {
+  if (!A || !b || !x) {
+    set_error("NULL argument");
+    return -1;
+  }
+  if (A->size != b->size) {
+    set_error("A and b sizes differ");
+    return -1;
+  }
+  if (ensure_init(-1)) return -1;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  Ctx& c = ctx();
+  System* sys = matrix_system(A);
+  if (!sys) return -1;
+  if (sync_to_host(b)) return -1;
+  const int n = b->size;
+  if (n > 0) CU_OK(cudaMemcpyAsync(sys->b, b->values, sizeof(double) * n, cudaMemcpyHostToDevice, c.stream));
+  if (system_solve(sys, o, res)) return -1;
+  // the reference hands back a freshly allocated vector (cg.c:104,138)
+  struct __mv_sparse* xv = (struct __mv_sparse*)calloc(1, sizeof(struct __mv_sparse));
+  if (!xv) return -1;
+  xv->size = n;
+  xv->nnz = n;
+  xv->values = (double*)calloc(n > 0 ? n : 1, sizeof(double));
+  if (!xv->values) {
+    free(xv);
+    return -1;
+  }
+  if (n > 0 && system_get_x(sys, xv->values)) {
+    free(xv->values);
+    free(xv);
+    return -1;
+  }
+  *x = xv;
+  return 0;
+}
+
+}  // namespace
+
+// =============================================================================================
+// Part 1: the reference surface
+// =============================================================================================
+
+extern "C" {
+
+struct __mv_sparse* new_mv_struct(void) {
+  return (struct __mv_sparse*)calloc(1, sizeof(struct __mv_sparse));
+}
+
+struct __mv_sparse* new_mv_struct_with_size(int size) {
+  struct __mv_sparse* v = new_mv_struct();
+  if (!v) return NULL;
+  v->size = size;
+  v->nnz = size;
+  v->values = (double*)calloc(size > 0 ? size : 1, sizeof(double));
+  return v;
+}
+
+void free_mv_struct(struct __mv_sparse* obj) {
+  if (!obj) return;
+  {
+    std::lock_guard<std::mutex> lk(g_tab_mu);
+    drop_mirror(obj);
+  }
+  free(obj);  // arrays stay with the caller, as in the reference (mv_ops.c:41)
+}
+
+struct __mv_sparse* mv_deep_copy(struct __mv_sparse* orig) {
+  if (!orig) return NULL;
+  {
+    std::lock_guard<std::mutex> lk(g_tab_mu);
+    if (sync_to_host(orig)) return NULL;
+  }
+  struct __mv_sparse* cp = new_mv_struct();
+  if (!cp) return NULL;
+  cp->size = orig->size;
+  cp->nnz = orig->nnz;
+  const size_t nv = orig->nnz > 0 ? (size_t)orig->nnz : 1;
+  cp->values = (double*)calloc(nv, sizeof(double));
+  if (orig->values && orig->nnz > 0) memcpy(cp->values, orig->values, sizeof(double) * orig->nnz);
+  if (orig->col_indices) {
+    cp->col_indices = (int*)calloc(nv, sizeof(int));
+    if (orig->nnz > 0) memcpy(cp->col_indices, orig->col_indices, sizeof(int) * orig->nnz);
+  }
+  if (orig->row_ptr) {
+    cp->row_ptr = (int*)calloc((size_t)orig->size + 1, sizeof(int));
+    memcpy(cp->row_ptr, orig->row_ptr, sizeof(int) * ((size_t)orig->size + 1));
+  }
+  return cp;
+}
+
+void print_sparse(struct __mv_sparse* obj) {
+  printf("Sparse Object:\n");
+  if (!obj) {
+    printf("\tObject is NULL\n");
+    return;
+  }
+  {
+    std::lock_guard<std::mutex> lk(g_tab_mu);
+    sync_to_host(obj);
+  }
+  printf("\tSize: %d\n", obj->size);
+  printf("\tNNZ: %d\n", obj->nnz);
+  printf("\tValues: %p\n", (void*)obj->values);
+  for (int i = 0; i < obj->nnz; i++) printf("\t%f\n", obj->values[i]);
+}
+
+int mat_get_row(struct __mv_sparse* mat_A, int row_id, double* p_row) {
+  if (!mat_A || !p_row) return -1;
+  if (!mat_A->row_ptr || row_id < 0 || row_id >= mat_A->size) return -1;
+  memset(p_row, 0, sizeof(double) * (size_t)mat_A->size);
+  for (int k = mat_A->row_ptr[row_id]; k < mat_A->row_ptr[row_id + 1]; ++k) {
+    const int c = mat_A->col_indices[k];
+    if (c >= 0 && c < mat_A->size) p_row[c] = mat_A->values[k];
+  }
+  return 0;
+}
+
+double dot_product(struct __mv_sparse* vec_a, struct __mv_sparse* vec_b) {
+  if (!vec_a || !vec_b) return -1.0;
+  if (vec_a->size != vec_b->size) return -1.0;
+  if (ensure_init(-1)) return -1.0;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  Ctx& c = ctx();
+  const double *da = nullptr, *db = nullptr;
+  if (dev_input(vec_a, 0, &da)) return -1.0;
+  if (vec_b == vec_a)
+    db = da;
+  else if (dev_input(vec_b, 1, &db))
+    return -1.0;
+  double* dres = (double*)c.d_scratch;
+  if (launch_dot(da, db, vec_a->size, c.partials, &c.d_state->ticket[0], dres, c.stream) !=
+          cudaSuccess ||
+      cudaMemcpyAsync(c.h_scratch, dres, sizeof(double), cudaMemcpyDeviceToHost, c.stream) !=
+          cudaSuccess ||
+      cudaStreamSynchronize(c.stream) != cudaSuccess) {
+    set_error(std::string("dot_product: ") + cudaGetErrorString(cudaGetLastError()));
+    return -1.0;
+  }
+  return *(double*)c.h_scratch;
+}
+
+int sv_mult(double s, struct __mv_sparse* vec_a, struct __mv_sparse** out) {
+  return ewise(0, s, vec_a, NULL, out);
+}
+
+int vec_add(struct __mv_sparse* vec_a, struct __mv_sparse* vec_b, struct __mv_sparse** out) {
+  return ewise(1, 0.0, vec_a, vec_b, out);
+}
+
+int vec_sub(struct __mv_sparse* vec_a, struct __mv_sparse* vec_b, struct __mv_sparse** out) {
+  return ewise(2, 0.0, vec_a, vec_b, out);
+}
+
+int mv_mult(struct __mv_sparse* mat_A, struct __mv_sparse* vec_b, struct __mv_sparse** out) {
+  if (!mat_A || !vec_b || !out) return -1;
+  if (mat_A->size != vec_b->size) return -1;
+  if (ensure_init(-1)) return -1;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  Ctx& c = ctx();
+  System* sys = matrix_system(mat_A);
+  if (!sys) return -1;
+  const int n = mat_A->size;
+  const double* db = nullptr;
+  if (dev_input(vec_b, 0, &db)) return -1;
+  if (g_mode == CGB200_EAGER) CU_OK(cudaStreamSynchronize(c.stream));
+  if (prepare_out(out, n, vec_b->nnz)) return -1;
+  if (n == 0) return 0;
+  if (system_matvec_dev(sys, db, nullptr)) return -1;
+  double* dout = nullptr;
+  if (dev_output(*out, 2, &dout)) return -1;
+  CU_OK(cudaMemcpyAsync(dout, sys->s, sizeof(double) * n, cudaMemcpyDeviceToDevice, c.stream));
+  return finish_output(*out, dout);
+}
+
+int conj_grad(int max_iter, struct __mv_sparse* mat_A, struct __mv_sparse* vec_b,
+              struct __mv_sparse** x) {
+  SolveOpts o;
+  o.max_iter = max_iter;
+  o.tol = 0.0;
+  o.variant = CGB200_CLASSIC;
+  SolveResult r;
+  return solve_host(mat_A, vec_b, x, o, &r);
+}
+
+// =============================================================================================
+// Part 2: extensions
+// =============================================================================================
+
+int cgb200_init(int device) { return ensure_init(device); }
+
+void cgb200_shutdown(void) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  for (auto& kv : g_mats) delete kv.second.sys;
+  g_mats.clear();
+  for (auto& kv : g_vecs) cudaFree(kv.second.d);
+  g_vecs.clear();
+  for (int i = 0; i < 3; ++i) {
+    if (g_scratch[i]) cudaFree(g_scratch[i]);
+    g_scratch[i] = nullptr;
+    g_scratch_cap[i] = 0;
+  }
+  shutdown();
+}
+
+const char* cgb200_last_error(void) { return last_error(); }
+long long cgb200_launch_count(void) { return launch_count(); }
+
+int cgb200_device_available(void) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n > 0 ? 1 : 0;
+}
+
+int cgb200_set_mode(int mode) {
+  if (mode != CGB200_EAGER && mode != CGB200_RESIDENT) return -1;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  if (mode == CGB200_EAGER && g_mode == CGB200_RESIDENT) {
+    // leaving resident mode: nothing may stay newer on the device than on the host
+    for (auto& kv : g_vecs) {
+      struct __mv_sparse* o = (struct __mv_sparse*)kv.first;
+      if (kv.second.dev_valid && !kv.second.host_valid) sync_to_host(o);
+      kv.second.dev_valid = false;
+    }
+  }
+  g_mode = mode;
+  return 0;
+}
+
+int cgb200_to_device(struct __mv_sparse* obj) {
+  if (!obj) return -1;
+  if (ensure_init(-1)) return -1;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  if (!is_vector(obj)) return matrix_system(obj) ? 0 : -1;
+  VectorEntry& e = g_vecs[obj];
+  if (ensure_vec_capacity(e, obj->size)) return -1;
+  if (obj->size > 0)
+    CU_OK(cudaMemcpyAsync(e.d, obj->values, sizeof(double) * obj->size, cudaMemcpyHostToDevice,
+                          ctx().stream));
+  CU_OK(cudaStreamSynchronize(ctx().stream));
+  e.dev_valid = true;
+  e.host_valid = true;
+  return 0;
+}
+
+int cgb200_to_host(struct __mv_sparse* obj) {
+  if (!obj) return -1;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  return sync_to_host(obj);
+}
+
+int cgb200_invalidate(struct __mv_sparse* obj) {
+  if (!obj) return -1;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  drop_mirror(obj);
+  return 0;
+}
+
+void cgb200_free_all(struct __mv_sparse* obj) {
+  if (!obj) return;
+  {
+    std::lock_guard<std::mutex> lk(g_tab_mu);
+    drop_mirror(obj);
+  }
+  free(obj->values);
+  free(obj->col_indices);
+  free(obj->row_ptr);
+  free(obj);
+}
+
+static void fill_result(const SolveResult& r, cgb200_result* res) {
+  if (!res) return;
+  res->iterations = r.iterations;
+  res->status = r.status;
+  res->rr = r.rr;
+  res->bb = r.bb;
+  res->relres = r.relres;
+  res->seconds = r.seconds;
+  res->bytes_per_iter = r.bytes_per_iter;
+  res->path = r.path;
+  res->world = r.world;
+  res->kernel_launches = r.kernel_launches;
+}
+
+static SolveOpts to_opts(const cgb200_opts* o) {
+  SolveOpts s;
+  if (o) {
+    s.max_iter = o->max_iter;
+    s.tol = o->tol;
+    s.variant = o->variant;
+    s.check_every = o->check_every;
+  }
+  return s;
+}
+
+int cgb200_solve(struct __mv_sparse* A, struct __mv_sparse* b, struct __mv_sparse** x,
+                 const cgb200_opts* opts, cgb200_result* res) {
+  SolveResult r;
+  memset(&r, 0, sizeof(r));
+  const int rc = solve_host(A, b, x, to_opts(opts), &r);
+  if (rc == 0) fill_result(r, res);
+  return rc;
+}
+
+cgb200_system* cgb200_system_lap(int nx, int ny, int nz, int z0, int nzl, uint64_t bseed) {
+  return (cgb200_system*)system_lap(nx, ny, nz, z0, nzl, bseed);
+}
+
+cgb200_system* cgb200_system_dense(int n, int row0, int nrows, uint64_t aseed, uint64_t bseed) {
+  return (cgb200_system*)system_dense(n, row0, nrows, aseed, bseed);
+}
+
+cgb200_system* cgb200_system_from_csr(long long n_global, long long row0, int nrows,
+                                      const int* row_ptr, const int* cols, const double* vals,
+                                      const double* b) {
+  return (cgb200_system*)system_from_csr(n_global, row0, nrows, row_ptr, cols, vals, b);
+}
+
+void cgb200_system_free(cgb200_system* sys) {
+  if (!sys) return;
+  cudaStreamSynchronize(ctx().stream);
+  delete (System*)sys;
+}
+
+int cgb200_system_set_rhs(cgb200_system* sys, const double* b_host) {
+  if (!sys || !b_host) return -1;
+  return system_set_rhs((System*)sys, b_host);
+}
+
+int cgb200_system_gen_rhs(cgb200_system* sys, uint64_t bseed) {
+  if (!sys) return -1;
+  return system_gen_rhs((System*)sys, bseed);
+}
+
+int cgb200_system_get_x(cgb200_system* sys, double* x_host) {
+  if (!sys || !x_host) return -1;
+  return system_get_x((System*)sys, x_host);
+}
+
+int cgb200_system_solve(cgb200_system* sys, const cgb200_opts* opts, cgb200_result* res) {
+  SolveResult r;
+  memset(&r, 0, sizeof(r));
+  const int rc = system_solve((System*)sys, to_opts(opts), &r);
+  if (rc == 0) fill_result(r, res);
+  return rc;
+}
+
+int cgb200_system_matvec(cgb200_system* sys, const double* v_host, double* s_host) {
+  if (!sys || !v_host || !s_host) return -1;
+  return system_matvec((System*)sys, v_host, s_host);
+}
+
+int cgb200_system_true_relres(cgb200_system* sys, double* relres) {
+  if (!sys || !relres) return -1;
+  return system_true_relres((System*)sys, relres);
+}
+
+int cgb200_system_time_kernel(cgb200_system* sys, int which, int reps, double* ms) {
+  if (!sys || !ms || reps < 1 || which < 1 || which > 3) return -1;
+  return system_time_kernel((System*)sys, which, reps, ms);
+}
+
+int cgb200_system_bytes(cgb200_system* sys, double* iter_bytes, double* k1_bytes) {
+  if (!sys) return -1;
+  if (iter_bytes) *iter_bytes = ((System*)sys)->iter_bytes();
+  if (k1_bytes) *k1_bytes = ((System*)sys)->k1_bytes();
+  return 0;
+}
+
+long long cgb200_system_rows(cgb200_system* sys) { return sys ? ((System*)sys)->nloc : -1; }
+long long cgb200_system_nnz(cgb200_system* sys) { return sys ? ((System*)sys)->A.nnz : -1; }
+
+int cgb200_dist_unique_id(void* id128) { return id128 ? dist_unique_id(id128) : -1; }
+int cgb200_dist_init(int rank, int world, const void* id128) {
+  if (world > 1 && !id128) return -1;
+  return dist_init(rank, world, id128);
+}
+int cgb200_dist_finalize(void) { return dist_finalize(); }
+int cgb200_dist_rank(void) { return ctx().rank; }
+int cgb200_dist_world(void) { return ctx().world; }
+
+}  // extern "C"

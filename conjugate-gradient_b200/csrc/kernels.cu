@@ -1,0 +1,845 @@
+// kernels.cu -- hand-written sm_100a kernels of the conjugate-gradient path.
+//
+// Reference functions replaced (all of mv_ops.c's arithmetic and the body of cg.c's loop):
+//   k_spmv_stream     mv_mult + mat_get_row on CSR     mv_ops.c:160-201, 99-113   (fused with p.s)
+//   k_gemv_rows       mv_mult on full rows (nnz==n^2)  mv_ops.c:160-201           (fused with p.s)
+//   k_update_xr       sv_mult, vec_add, sv_mult, vec_sub, dot_product   cg.c:115-123,129
+//   k_update_p        sv_mult, vec_add                 cg.c:131-132
+//   k_init            new_mv_struct_with_size, 2x mv_deep_copy, dot     cg.c:104-108
+//   k_dot/k_scale/k_add/k_sub   the standalone operators of mv_ops.h    mv_ops.c:117-259
+//
+// All kernels are HBM-bound streaming kernels; no tensor cores (GEMV/SpMV is not a dense
+// contraction).  Grids are persistent multiples of the SM count; reductions are deterministic.
+// Arithmetic in the vector updates and the CSR row sums is deliberately unfused (separate
+// multiply and add, __dmul_rn/__dadd_rn) because the reference is built without FMA contraction
+// (Makefile:2, x86-64 -g): s = A p is then bit-identical to the reference and only the dot
+// products differ (by summation order).
+#include "kernels.h"
+
+#include <stdio.h>
+
+#include "device_utils.cuh"
+
+namespace cgb {
+
+static int g_launches = 0;
+long long launch_count() { return g_launches; }
+void add_launches(long long n) { g_launches += (int)n; }
+
+// ---------------------------------------------------------------------------------------------
+// K1-sparse: CSR "stream" SpMV fused with p.s
+//
+// A tile is R consecutive rows (one thread per row).  The tile's slice of values[], col_indices[]
+// and row_ptr[] is contiguous in memory, so one elected thread moves it into shared memory with
+// three 1-D bulk async copies (TMA, UBLKCP) that complete on an mbarrier; STAGES tiles are in
+// flight per CTA so outstanding bytes cost no registers.  Each thread then walks its own row out
+// of shared memory in ascending column order (the reference's order) and gathers p[col] through
+// the read-only path with an L2 evict-last policy, while the matrix streams with evict-first so it
+// does not push p out of L2.  Tiles are dealt round-robin to a persistent grid so that all CTAs
+// sweep the matrix as one front and the gathered window of p (two grid planes for a 7-point
+// stencil) stays L2-resident: HBM sees p once.
+//
+// Rows longer than the stage capacity are handled by splitting the tile's nnz span in chunks of
+// CAP entries; a row simply keeps accumulating across chunks (still ascending order).
+// ---------------------------------------------------------------------------------------------
+
+template <int R, int CAP, int STAGES>
+struct SpmvSmem {
+  static constexpr int RPN = R + 4;  // row_ptr entries copied per tile (R+1 rounded up to 16 B)
+  static constexpr size_t vals_bytes = (size_t)STAGES * CAP * 8;
+  static constexpr size_t cols_bytes = (size_t)STAGES * CAP * 4;
+  static constexpr size_t rp_bytes = (size_t)STAGES * RPN * 4;
+  static constexpr size_t bar_bytes = (size_t)STAGES * 8;
+  static constexpr size_t total = vals_bytes + cols_bytes + rp_bytes + bar_bytes + 16;
+};
+
+struct TileRange {
+  int begin0, end0;  // first range of tiles  [begin0, end0)
+  int begin1, end1;  // optional second range [begin1, end1)
+};
+
+__device__ __forceinline__ int vtile_to_tile(const TileRange& tr, int v) {
+  const int n0 = tr.end0 - tr.begin0;
+  return v < n0 ? tr.begin0 + v : tr.begin1 + (v - n0);
+}
+
+template <int R, int CAP, int STAGES>
+__global__ void __launch_bounds__(R)
+k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
+              const int* __restrict__ rowptr, int nrows, const double* __restrict__ pg,
+              const double* __restrict__ pown, double* __restrict__ s, TileRange tr,
+              double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
+              int mode) {
+  using SM = SpmvSmem<R, CAP, STAGES>;
+  if (mode != SPMV_PLAIN && S->done) return;
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double* sm_vals = reinterpret_cast<double*>(smem_raw);
+  int* sm_cols = reinterpret_cast<int*>(smem_raw + SM::vals_bytes);
+  int* sm_rp = reinterpret_cast<int*>(smem_raw + SM::vals_bytes + SM::cols_bytes);
+  uint64_t* bars =
+      reinterpret_cast<uint64_t*>(smem_raw + SM::vals_bytes + SM::cols_bytes + SM::rp_bytes);
+
+  const int tid = threadIdx.x;
+  const int nvt = (tr.end0 - tr.begin0) + (tr.end1 - tr.begin1);  // virtual tiles in this launch
+  const uint64_t pol_stream = policy_evict_first();
+  const uint64_t pol_keep = policy_evict_last();
+
+  if (tid == 0) {
+    for (int i = 0; i < STAGES; ++i) mbar_init(&bars[i], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  // ---- producer cursor (meaningful in thread 0 only) ----
+  int p_vt = blockIdx.x;  // virtual tile being issued
+  int p_chunk = 0, p_nchunks = 0, p_lo = 0, p_hi = 0;
+  int p_item = 0;  // items issued so far by this CTA
+  auto p_load_bounds = [&]() {
+    if (p_vt < nvt) {
+      const int t = vtile_to_tile(tr, p_vt);
+      const int r0 = t * R;
+      const int r1 = min(r0 + R, nrows);
+      p_lo = __ldg(rowptr + r0) & ~3;
+      p_hi = (__ldg(rowptr + r1) + 3) & ~3;
+      p_nchunks = max(1, (p_hi - p_lo + CAP - 1) / CAP);
+      p_chunk = 0;
+    }
+  };
+  auto p_issue = [&]() {  // issue the item under the cursor, advance the cursor
+    if (p_vt >= nvt) return;
+    const int stage = p_item % STAGES;
+    const int c0 = p_lo + p_chunk * CAP;
+    const int cnt = min(CAP, p_hi - c0);
+    const uint32_t bytes = (uint32_t)cnt * 12u + (p_chunk == 0 ? (uint32_t)SM::RPN * 4u : 0u);
+    mbar_expect_tx(&bars[stage], bytes);
+    if (cnt > 0) {
+      bulk_g2s(sm_vals + (size_t)stage * CAP, vals + c0, (uint32_t)cnt * 8u, &bars[stage],
+               pol_stream);
+      bulk_g2s(sm_cols + (size_t)stage * CAP, cols + c0, (uint32_t)cnt * 4u, &bars[stage],
+               pol_stream);
+    }
+    if (p_chunk == 0) {
+      const int t = vtile_to_tile(tr, p_vt);
+      bulk_g2s(sm_rp + (size_t)stage * SM::RPN, rowptr + (size_t)t * R, (uint32_t)SM::RPN * 4u,
+               &bars[stage], pol_stream);
+    }
+    ++p_item;
+    if (++p_chunk == p_nchunks) {
+      p_vt += gridDim.x;
+      p_load_bounds();
+    }
+  };
+
+  if (tid == 0) {
+    p_load_bounds();
+#pragma unroll 1
+    for (int i = 0; i < STAGES - 1; ++i) p_issue();
+  }
+
+  // ---- consumer ----
+  double dot = 0.0;
+  int item = 0;
+#pragma unroll 1
+  for (int vt = blockIdx.x; vt < nvt; vt += gridDim.x) {
+    const int t = vtile_to_tile(tr, vt);
+    const int row = t * R + tid;
+    const int rows_valid = min(R, nrows - t * R);
+    int rs = 0, re = 0, lo = 0, nchunks = 1;
+    double acc = 0.0;
+#pragma unroll 1
+    for (int chunk = 0; chunk < nchunks; ++chunk, ++item) {
+      if (tid == 0) p_issue();  // refills the stage freed by the previous item
+      const int stage = item % STAGES;
+      mbar_wait(&bars[stage], (uint32_t)(item / STAGES) & 1u);
+      const double* v_s = sm_vals + (size_t)stage * CAP;
+      const int* c_s = sm_cols + (size_t)stage * CAP;
+      if (chunk == 0) {
+        const int* rp_s = sm_rp + (size_t)stage * SM::RPN;
+        lo = rp_s[0] & ~3;
+        const int hi = (rp_s[rows_valid] + 3) & ~3;
+        nchunks = max(1, (hi - lo + CAP - 1) / CAP);
+        if (tid < rows_valid) {
+          rs = rp_s[tid];
+          re = rp_s[tid + 1];
+        }
+      }
+      const int c0 = lo + chunk * CAP;
+      int k = max(rs - c0, 0);
+      const int k1 = min(re - c0, CAP);
+      while (k < k1) {
+        double v[8], pv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const bool ok = (k + j) < k1;
+          const int kk = ok ? (k + j) : k;
+          v[j] = v_s[kk];
+          pv[j] = ld_keep(pg + c_s[kk], pol_keep);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if ((k + j) < k1) acc = __dadd_rn(acc, __dmul_rn(v[j], pv[j]));
+        k += 8;
+      }
+      __syncthreads();  // every thread is done with this stage
+    }
+    if (tid < rows_valid) {
+      s[row] = acc;
+      if (mode != SPMV_PLAIN) dot += pown[row] * acc;
+    }
+  }
+
+  if (mode == SPMV_PLAIN) return;
+  if (mode == SPMV_PARTIAL_ONLY) {
+    // first half of a split launch (interior rows): leave the partial for the finishing launch
+    __shared__ double smp[R / 32];
+    const double t = block_sum<R>(dot, smp);
+    if (tid == 0) partials[blockIdx.x] = t;  // caller passes partials + SPMV_EXTRA_OFFSET
+    return;
+  }
+  double total;
+  if (grid_sum<R>(dot, partials, ticket, total)) {
+    // `partials` may carry extra slots written by a preceding PARTIAL_ONLY launch
+    const int extra = mode >> 8;
+    for (int i = 0; i < extra; ++i) total += __ldcg(partials + SPMV_EXTRA_OFFSET + i);
+    if ((mode & 0xff) == SPMV_FINISH_LOCAL)
+      S->local = total;
+    else
+      finish_ps(S, total);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1-dense: row-block GEMV over values[] only, fused with p.s
+//
+// When every CSR row is full (nnz == n*n, row_ptr[i] == i*n) values[] is a row-major dense
+// matrix and col_indices carries no information: stream 8 B/entry instead of 12.  A CTA owns
+// RB rows at a time; its threads stride across the columns with 256-bit loads, so each p chunk
+// (L1/L2 resident) is reused for RB rows of A and RB independent wide loads are in flight per
+// thread.  Row groups are dealt round-robin to a persistent grid.
+// ---------------------------------------------------------------------------------------------
+
+template <int THREADS, int RB, int VEC>
+__global__ void __launch_bounds__(THREADS)
+k_gemv_rows(const double* __restrict__ A, long long ld, int nrows, int ncols,
+            const double* __restrict__ pg, const double* __restrict__ pown,
+            double* __restrict__ s, double* __restrict__ partials,
+            unsigned int* __restrict__ ticket, CgState* S, int mode) {
+  if (mode != SPMV_PLAIN && S->done) return;
+  __shared__ double sm_red[RB][THREADS / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint64_t pol_stream = policy_evict_first();
+  const int ngroups = (nrows + RB - 1) / RB;
+  double dot = 0.0;
+
+#pragma unroll 1
+  for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
+    const int row0 = g * RB;
+    const double* rowp[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) rowp[r] = A + (long long)min(row0 + r, nrows - 1) * ld;
+    double acc[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) acc[r] = 0.0;
+
+    if constexpr (VEC == 4) {
+#pragma unroll 2
+      for (int c = tid * 4; c < ncols; c += THREADS * 4) {
+        const double4_t pv = *reinterpret_cast<const double4_t*>(pg + c);
+        double4_t a[RB];
+#pragma unroll
+        for (int r = 0; r < RB; ++r) a[r] = ld_stream4(rowp[r] + c);
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+          acc[r] = fma(a[r].x, pv.x, acc[r]);
+          acc[r] = fma(a[r].y, pv.y, acc[r]);
+          acc[r] = fma(a[r].z, pv.z, acc[r]);
+          acc[r] = fma(a[r].w, pv.w, acc[r]);
+        }
+      }
+    } else if constexpr (VEC == 2) {
+#pragma unroll 2
+      for (int c = tid * 2; c < ncols; c += THREADS * 2) {
+        const double2 pv = *reinterpret_cast<const double2*>(pg + c);
+        double2 a[RB];
+#pragma unroll
+        for (int r = 0; r < RB; ++r) a[r] = ld_stream2(rowp[r] + c, pol_stream);
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+          acc[r] = fma(a[r].x, pv.x, acc[r]);
+          acc[r] = fma(a[r].y, pv.y, acc[r]);
+        }
+      }
+    } else {
+#pragma unroll 4
+      for (int c = tid; c < ncols; c += THREADS) {
+        const double pv = pg[c];
+#pragma unroll
+        for (int r = 0; r < RB; ++r) acc[r] = fma(__ldg(rowp[r] + c), pv, acc[r]);
+      }
+    }
+
+#pragma unroll
+    for (int r = 0; r < RB; ++r) acc[r] = warp_sum(acc[r]);
+    __syncthreads();
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < RB; ++r) sm_red[r][warp] = acc[r];
+    }
+    __syncthreads();
+    if (tid < RB && row0 + tid < nrows) {
+      double t = 0.0;
+#pragma unroll
+      for (int w = 0; w < THREADS / 32; ++w) t += sm_red[tid][w];
+      s[row0 + tid] = t;
+      if (mode != SPMV_PLAIN) dot += pown[row0 + tid] * t;
+    }
+  }
+
+  if (mode == SPMV_PLAIN) return;
+  double total;
+  if (grid_sum<THREADS>(dot, partials, ticket, total)) {
+    if ((mode & 0xff) == SPMV_FINISH_LOCAL)
+      S->local = total;
+    else
+      finish_ps(S, total);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Streaming vector kernels.  128-bit accesses, UNROLL independent loads per array in flight.
+// The tail (n odd) is handled by one thread.
+// ---------------------------------------------------------------------------------------------
+
+constexpr int VT = 512;   // threads per CTA for the vector kernels
+constexpr int VU = 4;     // unroll
+
+// number of double2 elements the vector path may cover: all of them when every pointer is 16-byte
+// aligned, none otherwise (the scalar loop then covers the whole range)
+__device__ __forceinline__ long long vec_pairs(long long n, const void* a, const void* b,
+                                               const void* c, const void* d) {
+  const uintptr_t m = (uintptr_t)a | (uintptr_t)b | (uintptr_t)c | (uintptr_t)d;
+  return (m & 15) ? 0 : (n >> 1);
+}
+
+__device__ __forceinline__ double2 ld2(const double* p) {
+  return *reinterpret_cast<const double2*>(p);
+}
+__device__ __forceinline__ void st2(double* p, double2 v) { *reinterpret_cast<double2*>(p) = v; }
+
+// K2: x += alpha p ; r -= alpha s ; partial r.r           (cg.c:115-123 and the dot of cg.c:129)
+__global__ void __launch_bounds__(VT)
+k_update_xr(double* __restrict__ x, double* __restrict__ r, const double* __restrict__ p,
+            const double* __restrict__ s, long long n, double* __restrict__ partials,
+            unsigned int* __restrict__ ticket, CgState* S, int finish_local) {
+  if (S->done) return;
+  const double alpha = S->alpha;
+  const long long n2 = vec_pairs(n, x, r, p, s);
+  const long long stride = (long long)gridDim.x * VT;
+  double acc = 0.0;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * VU) {
+    double2 xv[VU], rv[VU], pv[VU], sv[VU];
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        xv[u] = ld2(x + 2 * j);
+        pv[u] = ld2(p + 2 * j);
+        rv[u] = ld2(r + 2 * j);
+        sv[u] = ld2(s + 2 * j);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        xv[u].x = __dadd_rn(xv[u].x, __dmul_rn(alpha, pv[u].x));
+        xv[u].y = __dadd_rn(xv[u].y, __dmul_rn(alpha, pv[u].y));
+        rv[u].x = __dsub_rn(rv[u].x, __dmul_rn(alpha, sv[u].x));
+        rv[u].y = __dsub_rn(rv[u].y, __dmul_rn(alpha, sv[u].y));
+        st2(x + 2 * j, xv[u]);
+        st2(r + 2 * j, rv[u]);
+        acc = fma(rv[u].x, rv[u].x, acc);
+        acc = fma(rv[u].y, rv[u].y, acc);
+      }
+    }
+  }
+  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride) {
+    const double xn = __dadd_rn(x[j], __dmul_rn(alpha, p[j]));
+    const double rn = __dsub_rn(r[j], __dmul_rn(alpha, s[j]));
+    x[j] = xn;
+    r[j] = rn;
+    acc = fma(rn, rn, acc);
+  }
+  double total;
+  if (grid_sum<VT>(acc, partials, ticket, total)) {
+    if (finish_local)
+      S->local = total;
+    else
+      finish_rr(S, total);
+  }
+}
+
+// K3: p = r + beta p                                                            (cg.c:131-132)
+__global__ void __launch_bounds__(VT)
+k_update_p(double* __restrict__ p, const double* __restrict__ r, long long n, const CgState* S) {
+  if (S->done) return;
+  const double beta = S->beta;
+  const long long n2 = vec_pairs(n, p, r, nullptr, nullptr);
+  const long long stride = (long long)gridDim.x * VT;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * VU) {
+    double2 rv[VU], pv[VU];
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        rv[u] = ld2(r + 2 * j);
+        pv[u] = ld2(p + 2 * j);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        pv[u].x = __dadd_rn(rv[u].x, __dmul_rn(beta, pv[u].x));
+        pv[u].y = __dadd_rn(rv[u].y, __dmul_rn(beta, pv[u].y));
+        st2(p + 2 * j, pv[u]);
+      }
+    }
+  }
+  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride)
+    p[j] = __dadd_rn(r[j], __dmul_rn(beta, p[j]));
+}
+
+// Loop entry: x = 0, r = b, p = b, partial b.b                                  (cg.c:104-108)
+__global__ void __launch_bounds__(VT)
+k_init(double* __restrict__ x, double* __restrict__ r, double* __restrict__ p,
+       const double* __restrict__ b, long long n, double* __restrict__ partials,
+       unsigned int* __restrict__ ticket, CgState* S, int finish_local) {
+  const long long stride = (long long)gridDim.x * VT;
+  double acc = 0.0;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n; i += stride) {
+    const double v = b[i];
+    x[i] = 0.0;
+    r[i] = v;
+    p[i] = v;
+    acc = fma(v, v, acc);
+  }
+  double total;
+  if (grid_sum<VT>(acc, partials, ticket, total)) {
+    if (finish_local)
+      S->local = total;
+    else
+      finish_init(S, total);
+  }
+}
+
+// One-thread bookkeeping kernels used after a cross-GPU sum of S->local.
+__global__ void k_finish(CgState* S, int which) {
+  if (which == FIN_INIT) {
+    finish_init(S, S->local);
+  } else if (S->done) {
+    return;
+  } else if (which == FIN_PS) {
+    finish_ps(S, S->local);
+  } else {
+    finish_rr(S, S->local);
+  }
+}
+
+// Standalone operators of mv_ops.h ------------------------------------------------------------
+
+// dot_product (mv_ops.c:117-132): result left in *out (device)
+__global__ void __launch_bounds__(VT)
+k_dot(const double* __restrict__ a, const double* __restrict__ b, long long n,
+      double* __restrict__ partials, unsigned int* __restrict__ ticket, double* __restrict__ out) {
+  const long long n2 = vec_pairs(n, a, b, nullptr, nullptr);
+  const long long stride = (long long)gridDim.x * VT;
+  double acc = 0.0;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * VU) {
+    double2 av[VU], bv[VU];
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        av[u] = ld2(a + 2 * j);
+        bv[u] = ld2(b + 2 * j);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        acc = fma(av[u].x, bv[u].x, acc);
+        acc = fma(av[u].y, bv[u].y, acc);
+      }
+    }
+  }
+  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride)
+    acc = fma(a[j], b[j], acc);
+  double total;
+  if (grid_sum<VT>(acc, partials, ticket, total)) *out = total;
+}
+
+// op: 0 = scale (out = sca*a; mv_ops.c:134-158), 1 = add (203-230), 2 = sub (232-259).
+// out may alias a or b (element-wise, each element read before it is written).
+template <int OP>
+__global__ void __launch_bounds__(VT)
+k_ewise(double sca, const double* a, const double* b, double* out, long long n) {
+  const long long n2 = vec_pairs(n, a, OP != 0 ? b : nullptr, out, nullptr);
+  const long long stride = (long long)gridDim.x * VT;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * VU) {
+    double2 av[VU], bv[VU];
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        av[u] = ld2(a + 2 * j);
+        if (OP != 0) bv[u] = ld2(b + 2 * j);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        double2 o;
+        if (OP == 0) {
+          o.x = __dmul_rn(sca, av[u].x);
+          o.y = __dmul_rn(sca, av[u].y);
+        } else if (OP == 1) {
+          o.x = __dadd_rn(av[u].x, bv[u].x);
+          o.y = __dadd_rn(av[u].y, bv[u].y);
+        } else {
+          o.x = __dsub_rn(av[u].x, bv[u].x);
+          o.y = __dsub_rn(av[u].y, bv[u].y);
+        }
+        st2(out + 2 * j, o);
+      }
+    }
+  }
+  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride)
+    out[j] = OP == 0 ? __dmul_rn(sca, a[j]) : OP == 1 ? __dadd_rn(a[j], b[j]) : __dsub_rn(a[j], b[j]);
+}
+
+// r = b - s and partial sums of r.r and b.b (independent true-residual check)
+__global__ void __launch_bounds__(VT)
+k_resid_norms(const double* __restrict__ b, const double* __restrict__ s, long long n,
+              double* __restrict__ partials, unsigned int* __restrict__ ticket,
+              double* __restrict__ out2) {
+  const long long stride = (long long)gridDim.x * VT;
+  double num = 0.0, den = 0.0;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n; i += stride) {
+    const double d = b[i] - s[i];
+    num = fma(d, d, num);
+    den = fma(b[i], b[i], den);
+  }
+  double total;
+  if (grid_sum<VT>(num, partials, ticket, total)) out2[0] = total;
+  if (grid_sum<VT>(den, partials + gridDim.x, ticket + 1, total)) out2[1] = total;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Matrix analysis / generators (set-up, not on the iteration loop)
+// ---------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ unsigned long long splitmix64(unsigned long long z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+__device__ __forceinline__ double uniform_pm_half(unsigned long long seed, unsigned long long ctr) {
+  const unsigned long long h = splitmix64(splitmix64(seed) ^ (ctr * 0xD1342543DE82EF95ull + 1ull));
+  return (double)(h >> 11) * (1.0 / 9007199254740992.0) - 0.5;
+}
+
+__global__ void k_gen_rhs(double* b, long long row0, long long n, unsigned long long seed) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    b[i] = uniform_pm_half(seed, (unsigned long long)(row0 + i));
+}
+
+// Stored entries in rows [0, row) of the Dirichlet 5/7-point operator on nx*ny*nz, natural order.
+__device__ __forceinline__ long long lap_nnz_before(long long row, long long nx, long long ny,
+                                                    long long nz) {
+  const long long pl = nx * ny;
+  const long long L = row / nx, xx = row % nx;
+  const long long P = row / pl, q = row % pl;
+  long long missing = 0;
+  missing += L + (xx > 0 ? 1 : 0);                                   // x == 0      (no -x)
+  missing += L;                                                      // x == nx-1   (no +x)
+  missing += P * nx + (q < nx ? q : nx);                             // y == 0
+  missing += P * nx + (q > (ny - 1) * nx ? q - (ny - 1) * nx : 0);   // y == ny-1
+  missing += row < pl ? row : pl;                                    // z == 0
+  missing += row > (nz - 1) * pl ? row - (nz - 1) * pl : 0;          // z == nz-1
+  return 7 * row - missing;
+}
+
+// Local rows [row0, row0+nloc) of the operator; columns are written already shifted by
+// -col_shift (the local gather index space).
+__global__ void k_gen_lap(int nx, int ny, int nz, long long row0, int nloc, long long col_shift,
+                          int* __restrict__ rowptr, int* __restrict__ cols,
+                          double* __restrict__ vals) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long pl = (long long)nx * ny;
+  const double diag = nz == 1 ? 4.0 : 6.0;
+  const long long base = lap_nnz_before(row0, nx, ny, nz);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i <= nloc; i += stride) {
+    const long long row = row0 + i;
+    long long k = lap_nnz_before(row, nx, ny, nz) - base;
+    rowptr[i] = (int)k;
+    if (i == nloc) break;
+    const int xx = (int)(row % nx), yy = (int)((row / nx) % ny), zz = (int)(row / pl);
+    if (zz > 0) { cols[k] = (int)(row - pl - col_shift); vals[k++] = -1.0; }
+    if (yy > 0) { cols[k] = (int)(row - nx - col_shift); vals[k++] = -1.0; }
+    if (xx > 0) { cols[k] = (int)(row - 1 - col_shift); vals[k++] = -1.0; }
+    cols[k] = (int)(row - col_shift); vals[k++] = diag;
+    if (xx < nx - 1) { cols[k] = (int)(row + 1 - col_shift); vals[k++] = -1.0; }
+    if (yy < ny - 1) { cols[k] = (int)(row + nx - col_shift); vals[k++] = -1.0; }
+    if (zz < nz - 1) { cols[k] = (int)(row + pl - col_shift); vals[k++] = -1.0; }
+  }
+}
+
+// Rows [row0, row0+nloc) of the dense SPD test matrix, values only (row-major, ld = n).
+__global__ void k_gen_dense(int n, int row0, int nloc, unsigned long long seed,
+                            double* __restrict__ vals) {
+  const long long total = (long long)nloc * n;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+    const long long i = row0 + e / n, j = e % n;
+    const long long lo = i < j ? i : j, hi = i < j ? j : i;
+    vals[e] = (i == j) ? 0.5 * n + 1.0
+                       : uniform_pm_half(seed, (unsigned long long)lo * (unsigned long long)n +
+                                                   (unsigned long long)hi);
+  }
+}
+
+// min / max column index over all stored entries (halo discovery) and the "every row is full"
+// test (row_ptr[i] == i*ncols).  out[0] = min col, out[1] = max col, out[2] = #rows not full.
+__global__ void k_analyze(const int* __restrict__ rowptr, const int* __restrict__ cols, int nrows,
+                          long long nnz, int ncols, int* __restrict__ out) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  int mn = 0x7fffffff, mx = -0x7fffffff - 1, bad = 0;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += stride) {
+    const int c = cols[i];
+    mn = min(mn, c);
+    mx = max(mx, c);
+  }
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i <= nrows; i += stride)
+    if ((long long)rowptr[i] != i * (long long)ncols) ++bad;
+  for (int o = 16; o > 0; o >>= 1) {
+    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    bad += __shfl_xor_sync(0xffffffffu, bad, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMin(out + 0, mn);
+    atomicMax(out + 1, mx);
+    if (bad) atomicAdd(out + 2, bad);
+  }
+}
+
+__global__ void k_shift_cols(int* __restrict__ cols, long long nnz, int shift) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += stride)
+    cols[i] -= shift;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Launch wrappers
+// ---------------------------------------------------------------------------------------------
+
+static int g_sms = 0;
+int sm_count() {
+  if (!g_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sms <= 0) g_sms = 148;
+  }
+  return g_sms;
+}
+
+static inline int vec_grid(long long n) {
+  const long long want = (n / 2 + (long long)VT * VU - 1) / ((long long)VT * VU);
+  const long long cap = (long long)sm_count() * 4;
+  long long g = want < cap ? want : cap;
+  return (int)(g < 1 ? 1 : g);
+}
+
+int max_partials() { return 8192; }
+
+// SpMV tile configuration (one instantiation; see DESIGN.md for the sizing argument)
+constexpr int SP_R = 256;
+constexpr int SP_CAP = 2048;
+constexpr int SP_STAGES = 4;
+using SpSM = SpmvSmem<SP_R, SP_CAP, SP_STAGES>;
+
+int spmv_rows_per_tile() { return SP_R; }
+
+static int spmv_blocks_per_sm() {
+  static int bps = 0;
+  if (!bps) {
+    cudaFuncSetAttribute(k_spmv_stream<SP_R, SP_CAP, SP_STAGES>,
+                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SpSM::total);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_stream<SP_R, SP_CAP, SP_STAGES>,
+                                                  SP_R, SpSM::total);
+    if (bps < 1) bps = 1;
+  }
+  return bps;
+}
+
+cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, double* s,
+                        int tile_begin0, int tile_end0, int tile_begin1, int tile_end1,
+                        double* partials, unsigned int* ticket, CgState* S, int mode,
+                        cudaStream_t st) {
+  TileRange tr{tile_begin0, tile_end0, tile_begin1, tile_end1};
+  const int nvt = (tile_end0 - tile_begin0) + (tile_end1 - tile_begin1);
+  if (nvt <= 0) return cudaSuccess;
+  const int bps = spmv_blocks_per_sm();
+  int grid = sm_count() * bps;
+  if (grid > nvt) grid = nvt;
+  k_spmv_stream<SP_R, SP_CAP, SP_STAGES><<<grid, SP_R, SpSM::total, st>>>(
+      A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s, tr, partials, ticket, S, mode);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+int spmv_grid_for(int ntiles) {
+  int grid = sm_count() * spmv_blocks_per_sm();
+  return grid > ntiles ? ntiles : grid;
+}
+
+constexpr int GV_T = 256;
+constexpr int GV_RB = 4;
+
+template <int VEC>
+static cudaError_t launch_gemv_vec(const double* A, long long ld, int nrows, int ncols,
+                                   const double* pg, const double* pown, double* s,
+                                   double* partials, unsigned int* ticket, CgState* S, int mode,
+                                   cudaStream_t st) {
+  static int bps = 0;
+  if (!bps) {
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_gemv_rows<GV_T, GV_RB, VEC>, GV_T, 0);
+    if (bps < 1) bps = 1;
+  }
+  const int ngroups = (nrows + GV_RB - 1) / GV_RB;
+  int grid = sm_count() * bps;
+  if (grid > ngroups) grid = ngroups;
+  if (grid > max_partials()) grid = max_partials();
+  k_gemv_rows<GV_T, GV_RB, VEC><<<grid, GV_T, 0, st>>>(A, ld, nrows, ncols, pg, pown, s, partials,
+                                                      ticket, S, mode);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_gemv(const double* A, long long ld, int nrows, int ncols, const double* pg,
+                        const double* pown, double* s, double* partials, unsigned int* ticket,
+                        CgState* S, int mode, cudaStream_t st) {
+  const bool al32 = ((uintptr_t)A % 32 == 0) && ((uintptr_t)pg % 32 == 0);
+  const bool al16 = ((uintptr_t)A % 16 == 0) && ((uintptr_t)pg % 16 == 0);
+  if (ld % 4 == 0 && ncols % 4 == 0 && al32)
+    return launch_gemv_vec<4>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, st);
+  if (ld % 2 == 0 && ncols % 2 == 0 && al16)
+    return launch_gemv_vec<2>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, st);
+  return launch_gemv_vec<1>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, st);
+}
+
+cudaError_t launch_update_xr(double* x, double* r, const double* p, const double* s, long long n,
+                             double* partials, unsigned int* ticket, CgState* S, int finish_local,
+                             cudaStream_t st) {
+  k_update_xr<<<vec_grid(n), VT, 0, st>>>(x, r, p, s, n, partials, ticket, S, finish_local);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_update_p(double* p, const double* r, long long n, const CgState* S,
+                            cudaStream_t st) {
+  k_update_p<<<vec_grid(n), VT, 0, st>>>(p, r, n, S);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_init(double* x, double* r, double* p, const double* b, long long n,
+                        double* partials, unsigned int* ticket, CgState* S, int finish_local,
+                        cudaStream_t st) {
+  k_init<<<vec_grid(n), VT, 0, st>>>(x, r, p, b, n, partials, ticket, S, finish_local);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_finish(CgState* S, int which, cudaStream_t st) {
+  k_finish<<<1, 1, 0, st>>>(S, which);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_dot(const double* a, const double* b, long long n, double* partials,
+                       unsigned int* ticket, double* out, cudaStream_t st) {
+  k_dot<<<vec_grid(n), VT, 0, st>>>(a, b, n, partials, ticket, out);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_ewise(int op, double sca, const double* a, const double* b, double* out,
+                         long long n, cudaStream_t st) {
+  const int g = vec_grid(n);
+  if (op == 0)
+    k_ewise<0><<<g, VT, 0, st>>>(sca, a, b, out, n);
+  else if (op == 1)
+    k_ewise<1><<<g, VT, 0, st>>>(sca, a, b, out, n);
+  else
+    k_ewise<2><<<g, VT, 0, st>>>(sca, a, b, out, n);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_resid_norms(const double* b, const double* s, long long n, double* partials,
+                               unsigned int* ticket, double* out2, cudaStream_t st) {
+  int g = vec_grid(n);
+  if (g > max_partials() / 2) g = max_partials() / 2;
+  k_resid_norms<<<g, VT, 0, st>>>(b, s, n, partials, ticket, out2);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_gen_rhs(double* b, long long row0, long long n, unsigned long long seed,
+                           cudaStream_t st) {
+  k_gen_rhs<<<sm_count() * 4, 256, 0, st>>>(b, row0, n, seed);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_gen_lap(int nx, int ny, int nz, long long row0, int nloc, long long col_shift,
+                           int* rowptr, int* cols, double* vals, cudaStream_t st) {
+  k_gen_lap<<<sm_count() * 8, 256, 0, st>>>(nx, ny, nz, row0, nloc, col_shift, rowptr, cols, vals);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_gen_dense(int n, int row0, int nloc, unsigned long long seed, double* vals,
+                             cudaStream_t st) {
+  k_gen_dense<<<sm_count() * 8, 256, 0, st>>>(n, row0, nloc, seed, vals);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_analyze(const int* rowptr, const int* cols, int nrows, long long nnz, int ncols,
+                           int* out3, cudaStream_t st) {
+  static const int init[3] = {0x7fffffff, -0x7fffffff - 1, 0};
+  cudaError_t e = cudaMemcpyAsync(out3, init, sizeof(init), cudaMemcpyHostToDevice, st);
+  if (e != cudaSuccess) return e;
+  k_analyze<<<sm_count() * 4, 256, 0, st>>>(rowptr, cols, nrows, nnz, ncols, out3);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_shift_cols(int* cols, long long nnz, int shift, cudaStream_t st) {
+  if (shift == 0) return cudaSuccess;
+  k_shift_cols<<<sm_count() * 4, 256, 0, st>>>(cols, nnz, shift);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+}  // namespace cgb

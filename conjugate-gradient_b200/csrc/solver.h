@@ -1,0 +1,105 @@
+// solver.h -- host-side objects of libcgb200: the process context, device-resident systems and
+// the solve entry points used by the C ABI (abi.cu).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <math.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+#include "state.h"
+
+namespace cgb {
+
+struct Ctx {
+  bool ready = false;
+  int device = 0;
+  cudaStream_t stream = nullptr;       // every kernel of the path runs here
+  cudaStream_t comm_stream = nullptr;  // halo exchange, overlapped with interior tiles
+  double* partials = nullptr;          // grid-reduction partials for the standalone operators
+  CgState* d_state = nullptr;          // scratch state for the standalone operators
+  CgState* h_state = nullptr;          // pinned: [0],[1] poll slots, [2] upload, [3] final
+  void* d_scratch = nullptr;           // 64 B
+  void* h_scratch = nullptr;           // 64 B pinned
+  cudaEvent_t poll_ev[2] = {nullptr, nullptr};
+  cudaEvent_t t0 = nullptr, t1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
+  // multi-GPU
+  int rank = 0, world = 1;
+  void* comm = nullptr;  // ncclComm_t
+};
+
+Ctx& ctx();
+int ensure_init(int device);
+void shutdown();
+void set_error(const std::string& m);
+const char* last_error();
+
+int dist_unique_id(void* id128);
+int dist_init(int rank, int world, const void* id128);
+int dist_finalize();
+
+// One row block [row0, row0 + nloc) of the system and everything the loop needs for it.
+struct System {
+  long long n_global = 0;
+  long long row0 = 0;
+  int nloc = 0;
+  bool dense = false;  // values[] is a row-major nloc x n_global block, no index arrays
+  CsrDev A;
+
+  // gather space of the matvec: p_ext = [ lower halo | owned rows | upper halo ] (neighbour mode)
+  // or the whole global vector (single rank, all-gather mode)
+  double* p_ext = nullptr;
+  double* p_own = nullptr;  // p_ext + off
+  long long off = 0, ext_len = 0;
+  int h_lo = 0, h_hi = 0;
+  bool allgather = false;
+  int world = 1, rank = 0;
+  std::vector<long long> part_row0;
+  std::vector<int> part_nloc, part_hlo, part_hhi;
+
+  // tiles [tb_lo, tb_hi) touch owned columns only; the rest wait for the halo
+  int ntiles = 0, tb_lo = 0, tb_hi = 0;
+
+  double *b = nullptr, *x = nullptr, *r = nullptr, *s = nullptr;
+  CgState* state = nullptr;
+  double* partials = nullptr;
+  std::map<int, cudaGraphExec_t> graphs;  // iterations per graph -> instantiated graph
+
+  double iter_bytes() const;  // contract bytes per iteration: A + 88 n
+  double k1_bytes() const;    // share of the matvec kernel: A + 16 n
+  ~System();
+};
+
+struct SolveOpts {
+  int max_iter = 0;
+  double tol = 0.0;
+  int variant = 0;
+  int check_every = 0;
+};
+
+struct SolveResult {
+  int iterations;
+  int status;
+  double rr, bb, relres, seconds, bytes_per_iter;
+  int path, world;
+  long long kernel_launches;
+};
+
+System* system_lap(int nx, int ny, int nz, int z0, int nzl, unsigned long long bseed);
+System* system_dense(int n, int row0, int nrows, unsigned long long aseed, unsigned long long bseed);
+System* system_from_csr(long long n_global, long long row0, int nrows, const int* row_ptr,
+                        const int* cols, const double* vals, const double* b);
+int classify_tiles(System* S);
+int system_solve(System* S, const SolveOpts& o, SolveResult* res);
+int system_set_rhs(System* S, const double* b_host);
+int system_gen_rhs(System* S, unsigned long long seed);
+int system_get_x(System* S, double* x_host);
+int system_matvec(System* S, const double* v_host, double* s_host);
+int system_matvec_dev(System* S, const double* v_dev, double* s_host_or_null);
+int system_true_relres(System* S, double* relres);
+int system_time_kernel(System* S, int which, int reps, double* ms_out);
+
+}  // namespace cgb

@@ -1,0 +1,125 @@
+/* cgb200.h -- extensions of libcgb200.so beyond the reference's mv_ops.h / conj_grad surface.
+ *
+ * None of these symbols is required by a drop-in caller of mv_ops.h.  They expose what the
+ * reference does not have: a tolerance stop, device-resident systems (so large matrices never
+ * pass through host structs), row-block partitioning across GPUs, and measurement hooks.
+ * Plain C ABI: pointers and sizes only.
+ */
+#ifndef CGB200_H
+#define CGB200_H
+
+#include <stdint.h>
+
+#include "mv_ops.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status of a solve ------------------------------------------------------------------- */
+#define CGB200_RUNNING 0
+#define CGB200_MAXITER 1   /* ran the fixed count (the reference's only exit, cg.c:125-127) */
+#define CGB200_CONVERGED 2 /* r.r <= tol^2 * b.b */
+#define CGB200_BREAKDOWN 3 /* p.Ap not positive and finite: stopped, last finite x kept */
+#define CGB200_EXACT 4     /* r.r == 0: stopped where the reference would compute 0/0 = NaN */
+
+/* ---- recurrence variants ------------------------------------------------------------------ */
+#define CGB200_CLASSIC 0          /* Hestenes-Stiefel, the reference's recurrence (default) */
+#define CGB200_SINGLE_REDUCTION 1 /* Chronopoulos-Gear: one fused reduction per iteration */
+
+/* ---- operator-API residency modes --------------------------------------------------------- */
+#define CGB200_EAGER 0    /* every op uploads its inputs and downloads its output (default) */
+#define CGB200_RESIDENT 1 /* outputs stay on the device until cgb200_to_host()/print/get_row */
+
+typedef struct cgb200_opts {
+  int max_iter;    /* reference semantics: M performs M+1 matvecs and x/r updates */
+  double tol;      /* stop when ||r||/||b|| <= tol; 0 = fixed count (reference behaviour) */
+  int variant;     /* CGB200_CLASSIC | CGB200_SINGLE_REDUCTION */
+  int check_every; /* iterations per graph launch / host poll of the stop flag; 0 = default */
+  int reserved;
+} cgb200_opts;
+
+typedef struct cgb200_result {
+  int iterations; /* x updates performed (matvecs) */
+  int status;     /* CGB200_MAXITER ... */
+  double rr;      /* final recursive r.r */
+  double bb;      /* b.b */
+  double relres;  /* sqrt(rr/bb) */
+  double seconds; /* device time of the loop (CUDA events on the solve stream) */
+  double bytes_per_iter; /* contract bytes this rank moves per iteration */
+  int path;       /* 0 = CSR stream SpMV, 1 = dense row-block GEMV */
+  int world;      /* ranks that took part */
+  long long kernel_launches; /* kernels launched by this solve (graph nodes included) */
+} cgb200_result;
+
+/* ---- process-wide context ----------------------------------------------------------------- */
+
+/* Binds the library to a CUDA device (default: LOCAL_RANK, else 0).  Optional: the first call
+ * that needs the device initialises lazily.  0 / -1. */
+int cgb200_init(int device);
+void cgb200_shutdown(void);
+/* Message of the last failure on the calling process ("" if none). */
+const char *cgb200_last_error(void);
+/* Kernels launched by the library so far in this process (graph launches count their nodes). */
+long long cgb200_launch_count(void);
+/* 1 when a CUDA device is usable, 0 otherwise (never touches the oracle or any CPU path). */
+int cgb200_device_available(void);
+
+/* ---- operator-API residency (struct address -> device mirror table) ------------------------ */
+int cgb200_set_mode(int mode);
+int cgb200_to_device(struct __mv_sparse *obj); /* upload now; the mirror becomes valid */
+int cgb200_to_host(struct __mv_sparse *obj);   /* bring values back if the device copy is newer */
+int cgb200_invalidate(struct __mv_sparse *obj); /* caller changed host arrays in place */
+void cgb200_free_all(struct __mv_sparse *obj);  /* struct + its host arrays + device mirror */
+
+/* ---- solve on host structs with options ---------------------------------------------------- */
+/* conj_grad(M, A, b, &x) == cgb200_solve with {max_iter = M, tol = 0, CGB200_CLASSIC}. */
+int cgb200_solve(struct __mv_sparse *A, struct __mv_sparse *b, struct __mv_sparse **x,
+                 const cgb200_opts *opts, cgb200_result *res);
+
+/* ---- device-resident systems (one row block of A, b, x and the work vectors) -------------- */
+typedef struct cgb200_system cgb200_system;
+
+/* Rows [z0*nx*ny, (z0+nzl)*nx*ny) of the Dirichlet 5-point (nz == 1) or 7-point Laplacian on an
+ * nx*ny*nz grid, natural ordering, generated on the device as CSR; b_i = U(-1/2,1/2)(bseed, i). */
+cgb200_system *cgb200_system_lap(int nx, int ny, int nz, int z0, int nzl, uint64_t bseed);
+/* Rows [row0, row0+nrows) of the dense SPD test matrix, values only. */
+cgb200_system *cgb200_system_dense(int n, int row0, int nrows, uint64_t aseed, uint64_t bseed);
+/* Rows [row0, row0+nrows) of a CSR matrix held in host arrays: row_ptr[nrows+1] local (starts at
+ * 0), cols global, b local.  A full-row matrix (row_ptr[i] == i*n_global) takes the dense path. */
+cgb200_system *cgb200_system_from_csr(long long n_global, long long row0, int nrows,
+                                      const int *row_ptr, const int *cols, const double *vals,
+                                      const double *b);
+void cgb200_system_free(cgb200_system *sys);
+int cgb200_system_set_rhs(cgb200_system *sys, const double *b_host);   /* H2D, nrows doubles */
+int cgb200_system_gen_rhs(cgb200_system *sys, uint64_t bseed);         /* on the device */
+int cgb200_system_get_x(cgb200_system *sys, double *x_host);           /* D2H, nrows doubles */
+int cgb200_system_solve(cgb200_system *sys, const cgb200_opts *opts, cgb200_result *res);
+/* s = A v for a host vector v[n_local] (single rank) -> s_host; exercises the loop's matvec
+ * kernel alone (mode PLAIN). */
+int cgb200_system_matvec(cgb200_system *sys, const double *v_host, double *s_host);
+/* ||b - A x|| / ||b|| recomputed from scratch on the device (all ranks get the global value). */
+int cgb200_system_true_relres(cgb200_system *sys, double *relres);
+/* Average device time (ms, CUDA events on the launching stream) of `reps` back-to-back launches
+ * of one kernel of the loop on this system's buffers.  which: 1 = matvec+dot (K1),
+ * 2 = x/r update + r.r (K2), 3 = direction update (K3). */
+int cgb200_system_time_kernel(cgb200_system *sys, int which, int reps, double *ms);
+/* Contract bytes per iteration for this rank and the share of the matvec kernel. */
+int cgb200_system_bytes(cgb200_system *sys, double *iter_bytes, double *k1_bytes);
+long long cgb200_system_rows(cgb200_system *sys);
+long long cgb200_system_nnz(cgb200_system *sys);
+
+/* ---- multi-GPU: one process per GPU, NCCL over NVLink -------------------------------------- */
+/* Rank 0 obtains a 128-byte NCCL unique id and ships it to the other ranks by any means
+ * (torch.distributed broadcast in bench.py, a pipe in the cg driver). */
+int cgb200_dist_unique_id(void *id128);
+int cgb200_dist_init(int rank, int world, const void *id128);
+int cgb200_dist_finalize(void);
+int cgb200_dist_rank(void);
+int cgb200_dist_world(void);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* CGB200_H */
