@@ -152,6 +152,9 @@ def lib():
     L.cgb200_system_true_relres.argtypes = [C.c_void_p, c_double_p]
     L.cgb200_system_time_kernel.argtypes = [C.c_void_p, C.c_int, C.c_int, c_double_p]
     L.cgb200_system_bytes.argtypes = [C.c_void_p, c_double_p, c_double_p]
+    L.cgb200_system_download.argtypes = [C.c_void_p, c_double_p, c_int_p, c_int_p]
+    L.cgb200_system_get_b.argtypes = [C.c_void_p, c_double_p]
+    L.cgb200_timer_stop.argtypes = [c_double_p]
     L.cgb200_system_rows.restype = C.c_longlong
     L.cgb200_system_rows.argtypes = [C.c_void_p]
     L.cgb200_system_nnz.restype = C.c_longlong

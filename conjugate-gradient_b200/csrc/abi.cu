@@ -641,6 +641,19 @@ int cgb200_system_time_kernel(cgb200_system* sys, int which, int reps, double* m
   return system_time_kernel((System*)sys, which, reps, ms);
 }
 
+int cgb200_system_download(cgb200_system* sys, double* vals, int* cols, int* row_ptr) {
+  if (!sys) return -1;
+  return system_download((System*)sys, vals, cols, row_ptr);
+}
+
+int cgb200_system_get_b(cgb200_system* sys, double* b_host) {
+  if (!sys || !b_host) return -1;
+  return system_get_b((System*)sys, b_host);
+}
+
+int cgb200_timer_start(void) { return ensure_init(-1) ? -1 : timer_start(); }
+int cgb200_timer_stop(double* ms) { return ms ? timer_stop(ms) : -1; }
+
 int cgb200_system_bytes(cgb200_system* sys, double* iter_bytes, double* k1_bytes) {
   if (!sys) return -1;
   if (iter_bytes) *iter_bytes = ((System*)sys)->iter_bytes();

@@ -17,6 +17,7 @@
 #include "kernels.h"
 
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "device_utils.cuh"
 
@@ -29,15 +30,17 @@ void add_launches(long long n) { g_launches += (int)n; }
 // ---------------------------------------------------------------------------------------------
 // K1-sparse: CSR "stream" SpMV fused with p.s
 //
-// A tile is R consecutive rows (one thread per row).  The tile's slice of values[], col_indices[]
-// and row_ptr[] is contiguous in memory, so one elected thread moves it into shared memory with
-// three 1-D bulk async copies (TMA, UBLKCP) that complete on an mbarrier; STAGES tiles are in
-// flight per CTA so outstanding bytes cost no registers.  Each thread then walks its own row out
-// of shared memory in ascending column order (the reference's order) and gathers p[col] through
-// the read-only path with an L2 evict-last policy, while the matrix streams with evict-first so it
-// does not push p out of L2.  Tiles are dealt round-robin to a persistent grid so that all CTAs
-// sweep the matrix as one front and the gathered window of p (two grid planes for a 7-point
-// stencil) stays L2-resident: HBM sees p once.
+// A tile is R consecutive rows (one consumer thread per row).  The tile's slice of values[],
+// col_indices[] and row_ptr[] is contiguous in memory, so a dedicated producer warp moves it into
+// shared memory with three 1-D bulk async copies (TMA, UBLKCP) that complete on a "full"
+// mbarrier; STAGES tiles are in flight per CTA, so outstanding bytes cost no registers.  Each
+// consumer thread walks its own row out of shared memory in ascending column order (the
+// reference's order, mv_ops.c:106-110,192-194) and gathers p[col] through the read-only path with
+// an L2 evict-last policy, while the matrix streams with evict-first so it does not push p out of
+// L2.  A consumer warp releases a stage by arriving on its "empty" mbarrier; there is no
+// CTA-wide barrier in the steady state, warps drift freely across tiles.  Tiles are dealt
+// round-robin to a persistent grid so that all CTAs sweep the matrix as one front and the
+// gathered window of p (two grid planes for a 7-point stencil) stays L2-resident: HBM sees p once.
 //
 // Rows longer than the stage capacity are handled by splitting the tile's nnz span in chunks of
 // CAP entries; a row simply keeps accumulating across chunks (still ascending order).
@@ -49,7 +52,7 @@ struct SpmvSmem {
   static constexpr size_t vals_bytes = (size_t)STAGES * CAP * 8;
   static constexpr size_t cols_bytes = (size_t)STAGES * CAP * 4;
   static constexpr size_t rp_bytes = (size_t)STAGES * RPN * 4;
-  static constexpr size_t bar_bytes = (size_t)STAGES * 8;
+  static constexpr size_t bar_bytes = (size_t)STAGES * 16;
   static constexpr size_t total = vals_bytes + cols_bytes + rp_bytes + bar_bytes + 16;
 };
 
@@ -64,141 +67,151 @@ __device__ __forceinline__ int vtile_to_tile(const TileRange& tr, int v) {
 }
 
 template <int R, int CAP, int STAGES>
-__global__ void __launch_bounds__(R)
+__global__ void __launch_bounds__(R + 32)
 k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
               const int* __restrict__ rowptr, int nrows, const double* __restrict__ pg,
               const double* __restrict__ pown, double* __restrict__ s, TileRange tr,
               double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
-              int mode) {
+              int mode, int hint) {
   using SM = SpmvSmem<R, CAP, STAGES>;
+  constexpr int THREADS = R + 32;
+  constexpr int CWARPS = R / 32;
   if (mode != SPMV_PLAIN && S->done) return;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double* sm_vals = reinterpret_cast<double*>(smem_raw);
   int* sm_cols = reinterpret_cast<int*>(smem_raw + SM::vals_bytes);
   int* sm_rp = reinterpret_cast<int*>(smem_raw + SM::vals_bytes + SM::cols_bytes);
-  uint64_t* bars =
+  uint64_t* full =
       reinterpret_cast<uint64_t*>(smem_raw + SM::vals_bytes + SM::cols_bytes + SM::rp_bytes);
+  uint64_t* empty = full + STAGES;
 
   const int tid = threadIdx.x;
   const int nvt = (tr.end0 - tr.begin0) + (tr.end1 - tr.begin1);  // virtual tiles in this launch
-  const uint64_t pol_stream = policy_evict_first();
-  const uint64_t pol_keep = policy_evict_last();
 
   if (tid == 0) {
-    for (int i = 0; i < STAGES; ++i) mbar_init(&bars[i], 1);
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], CWARPS);
+    }
     mbar_fence_init();
   }
   __syncthreads();
 
-  // ---- producer cursor (meaningful in thread 0 only) ----
-  int p_vt = blockIdx.x;  // virtual tile being issued
-  int p_chunk = 0, p_nchunks = 0, p_lo = 0, p_hi = 0;
-  int p_item = 0;  // items issued so far by this CTA
-  auto p_load_bounds = [&]() {
-    if (p_vt < nvt) {
-      const int t = vtile_to_tile(tr, p_vt);
-      const int r0 = t * R;
-      const int r1 = min(r0 + R, nrows);
-      p_lo = __ldg(rowptr + r0) & ~3;
-      p_hi = (__ldg(rowptr + r1) + 3) & ~3;
-      p_nchunks = max(1, (p_hi - p_lo + CAP - 1) / CAP);
-      p_chunk = 0;
-    }
-  };
-  auto p_issue = [&]() {  // issue the item under the cursor, advance the cursor
-    if (p_vt >= nvt) return;
-    const int stage = p_item % STAGES;
-    const int c0 = p_lo + p_chunk * CAP;
-    const int cnt = min(CAP, p_hi - c0);
-    const uint32_t bytes = (uint32_t)cnt * 12u + (p_chunk == 0 ? (uint32_t)SM::RPN * 4u : 0u);
-    mbar_expect_tx(&bars[stage], bytes);
-    if (cnt > 0) {
-      bulk_g2s(sm_vals + (size_t)stage * CAP, vals + c0, (uint32_t)cnt * 8u, &bars[stage],
-               pol_stream);
-      bulk_g2s(sm_cols + (size_t)stage * CAP, cols + c0, (uint32_t)cnt * 4u, &bars[stage],
-               pol_stream);
-    }
-    if (p_chunk == 0) {
-      const int t = vtile_to_tile(tr, p_vt);
-      bulk_g2s(sm_rp + (size_t)stage * SM::RPN, rowptr + (size_t)t * R, (uint32_t)SM::RPN * 4u,
-               &bars[stage], pol_stream);
-    }
-    ++p_item;
-    if (++p_chunk == p_nchunks) {
-      p_vt += gridDim.x;
-      p_load_bounds();
-    }
-  };
-
-  if (tid == 0) {
-    p_load_bounds();
-#pragma unroll 1
-    for (int i = 0; i < STAGES - 1; ++i) p_issue();
-  }
-
-  // ---- consumer ----
   double dot = 0.0;
-  int item = 0;
+
+  if (tid >= R) {
+    // ------------------------------ producer warp ------------------------------
+    if (tid == R) {
+      const uint64_t pol_stream = policy_evict_first();
+      int item = 0;
+      // bounds of the next tile are fetched one tile ahead so their latency is never exposed
+      int vt = blockIdx.x;
+      int nlo = 0, nhi = 0;
+      if (vt < nvt) {
+        const int t = vtile_to_tile(tr, vt);
+        nlo = __ldg(rowptr + t * R);
+        nhi = __ldg(rowptr + min(t * R + R, nrows));
+      }
 #pragma unroll 1
-  for (int vt = blockIdx.x; vt < nvt; vt += gridDim.x) {
-    const int t = vtile_to_tile(tr, vt);
-    const int row = t * R + tid;
-    const int rows_valid = min(R, nrows - t * R);
-    int rs = 0, re = 0, lo = 0, nchunks = 1;
-    double acc = 0.0;
+      for (; vt < nvt; vt += gridDim.x) {
+        const int t = vtile_to_tile(tr, vt);
+        const int lo = nlo & ~3, hi = (nhi + 3) & ~3;
+        const int vt2 = vt + gridDim.x;
+        if (vt2 < nvt) {
+          const int t2 = vtile_to_tile(tr, vt2);
+          nlo = __ldg(rowptr + t2 * R);
+          nhi = __ldg(rowptr + min(t2 * R + R, nrows));
+        }
+        const int nchunks = max(1, (hi - lo + CAP - 1) / CAP);
 #pragma unroll 1
-    for (int chunk = 0; chunk < nchunks; ++chunk, ++item) {
-      if (tid == 0) p_issue();  // refills the stage freed by the previous item
-      const int stage = item % STAGES;
-      mbar_wait(&bars[stage], (uint32_t)(item / STAGES) & 1u);
-      const double* v_s = sm_vals + (size_t)stage * CAP;
-      const int* c_s = sm_cols + (size_t)stage * CAP;
-      if (chunk == 0) {
-        const int* rp_s = sm_rp + (size_t)stage * SM::RPN;
-        lo = rp_s[0] & ~3;
-        const int hi = (rp_s[rows_valid] + 3) & ~3;
-        nchunks = max(1, (hi - lo + CAP - 1) / CAP);
-        if (tid < rows_valid) {
-          rs = rp_s[tid];
-          re = rp_s[tid + 1];
+        for (int chunk = 0; chunk < nchunks; ++chunk, ++item) {
+          const int stage = item % STAGES;
+          if (item >= STAGES) mbar_wait(&empty[stage], ((uint32_t)(item / STAGES) & 1u) ^ 1u);
+          const int c0 = lo + chunk * CAP;
+          const int cnt = min(CAP, hi - c0);
+          const uint32_t bytes = (uint32_t)cnt * 12u + (chunk == 0 ? (uint32_t)SM::RPN * 4u : 0u);
+          mbar_expect_tx(&full[stage], bytes);
+          if (cnt > 0) {
+            bulk_g2s(sm_vals + (size_t)stage * CAP, vals + c0, (uint32_t)cnt * 8u, &full[stage],
+                     pol_stream);
+            bulk_g2s(sm_cols + (size_t)stage * CAP, cols + c0, (uint32_t)cnt * 4u, &full[stage],
+                     pol_stream);
+          }
+          if (chunk == 0)
+            bulk_g2s(sm_rp + (size_t)stage * SM::RPN, rowptr + (size_t)t * R,
+                     (uint32_t)SM::RPN * 4u, &full[stage], pol_stream);
         }
       }
-      const int c0 = lo + chunk * CAP;
-      int k = max(rs - c0, 0);
-      const int k1 = min(re - c0, CAP);
-      while (k < k1) {
-        double v[8], pv[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const bool ok = (k + j) < k1;
-          const int kk = ok ? (k + j) : k;
-          v[j] = v_s[kk];
-          pv[j] = ld_keep(pg + c_s[kk], pol_keep);
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if ((k + j) < k1) acc = __dadd_rn(acc, __dmul_rn(v[j], pv[j]));
-        k += 8;
-      }
-      __syncthreads();  // every thread is done with this stage
     }
-    if (tid < rows_valid) {
-      s[row] = acc;
-      if (mode != SPMV_PLAIN) dot += pown[row] * acc;
+  } else {
+    // ------------------------------ consumer warps ------------------------------
+    const uint64_t pol_keep = hint ? policy_evict_last() : policy_evict_normal();
+    const int lane = tid & 31;
+    int item = 0;
+#pragma unroll 1
+    for (int vt = blockIdx.x; vt < nvt; vt += gridDim.x) {
+      const int t = vtile_to_tile(tr, vt);
+      const int row = t * R + tid;
+      const int rows_valid = min(R, nrows - t * R);
+      int rs = 0, re = 0, lo = 0, nchunks = 1;
+      double acc = 0.0;
+#pragma unroll 1
+      for (int chunk = 0; chunk < nchunks; ++chunk, ++item) {
+        const int stage = item % STAGES;
+        mbar_wait(&full[stage], (uint32_t)(item / STAGES) & 1u);
+        const double* v_s = sm_vals + (size_t)stage * CAP;
+        const int* c_s = sm_cols + (size_t)stage * CAP;
+        if (chunk == 0) {
+          const int* rp_s = sm_rp + (size_t)stage * SM::RPN;
+          lo = rp_s[0] & ~3;
+          const int hi = (rp_s[rows_valid] + 3) & ~3;
+          nchunks = max(1, (hi - lo + CAP - 1) / CAP);
+          if (tid < rows_valid) {
+            rs = rp_s[tid];
+            re = rp_s[tid + 1];
+          }
+        }
+        const int c0 = lo + chunk * CAP;
+        int k = max(rs - c0, 0);
+        const int k1 = min(re - c0, CAP);
+        while (k < k1) {
+          double v[8], pv[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const bool ok = (k + j) < k1;
+            v[j] = 0.0;
+            pv[j] = 0.0;
+            if (ok) {
+              v[j] = v_s[k + j];
+              pv[j] = ld_keep(pg + c_s[k + j], pol_keep);
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if ((k + j) < k1) acc = __dadd_rn(acc, __dmul_rn(v[j], pv[j]));
+          k += 8;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[stage]);  // this warp is done with the stage
+      }
+      if (tid < rows_valid) {
+        s[row] = acc;
+        if (mode != SPMV_PLAIN) dot += pown[row] * acc;
+      }
     }
   }
 
   if (mode == SPMV_PLAIN) return;
   if (mode == SPMV_PARTIAL_ONLY) {
     // first half of a split launch (interior rows): leave the partial for the finishing launch
-    __shared__ double smp[R / 32];
-    const double t = block_sum<R>(dot, smp);
+    __shared__ double smp[THREADS / 32];
+    const double t = block_sum<THREADS>(dot, smp);
     if (tid == 0) partials[blockIdx.x] = t;  // caller passes partials + SPMV_EXTRA_OFFSET
     return;
   }
   double total;
-  if (grid_sum<R>(dot, partials, ticket, total)) {
+  if (grid_sum<THREADS>(dot, partials, ticket, total)) {
     // `partials` may carry extra slots written by a preceding PARTIAL_ONLY launch
     const int extra = mode >> 8;
     for (int i = 0; i < extra; ++i) total += __ldcg(partials + SPMV_EXTRA_OFFSET + i);
@@ -670,24 +683,74 @@ static inline int vec_grid(long long n) {
 
 int max_partials() { return 8192; }
 
-// SpMV tile configuration (one instantiation; see DESIGN.md for the sizing argument)
-constexpr int SP_R = 256;
-constexpr int SP_CAP = 2048;
-constexpr int SP_STAGES = 4;
-using SpSM = SpmvSmem<SP_R, SP_CAP, SP_STAGES>;
+// SpMV tile configurations.  One is chosen per process (CGB200_SPMV_CFG, default 0); DESIGN.md
+// records the sweep that picked the default.
+struct SpmvCfg {
+  int R, CAP, STAGES;
+  size_t smem;
+  const void* fn;
+  void (*launch)(int grid, cudaStream_t st, const CsrDev& A, const double* pg, const double* pown,
+                 double* s, TileRange tr, double* partials, unsigned int* ticket, CgState* S,
+                 int mode, int hint);
+};
 
-int spmv_rows_per_tile() { return SP_R; }
+template <int R, int CAP, int STAGES>
+static void spmv_launch_t(int grid, cudaStream_t st, const CsrDev& A, const double* pg,
+                          const double* pown, double* s, TileRange tr, double* partials,
+                          unsigned int* ticket, CgState* S, int mode, int hint) {
+  k_spmv_stream<R, CAP, STAGES><<<grid, R + 32, SpmvSmem<R, CAP, STAGES>::total, st>>>(
+      A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s, tr, partials, ticket, S, mode, hint);
+}
 
-static int spmv_blocks_per_sm() {
-  static int bps = 0;
-  if (!bps) {
-    cudaFuncSetAttribute(k_spmv_stream<SP_R, SP_CAP, SP_STAGES>,
-                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SpSM::total);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_stream<SP_R, SP_CAP, SP_STAGES>,
-                                                  SP_R, SpSM::total);
-    if (bps < 1) bps = 1;
+#define SPMV_CFG(R, CAP, ST)                                                        \
+  SpmvCfg {                                                                         \
+    R, CAP, ST, SpmvSmem<R, CAP, ST>::total, (const void*)k_spmv_stream<R, CAP, ST>, \
+        spmv_launch_t<R, CAP, ST>                                                   \
   }
-  return bps;
+
+static const SpmvCfg g_spmv_cfgs[] = {
+    SPMV_CFG(512, 3584, 2),  // 0  default: 2 CTAs/SM x 16 consumer warps, double-buffered, 7 nnz/row
+    SPMV_CFG(256, 2048, 2),  // 1
+    SPMV_CFG(256, 2048, 4),  // 2
+    SPMV_CFG(128, 1024, 4),  // 3
+    SPMV_CFG(128, 1024, 3),  // 4
+    SPMV_CFG(256, 2048, 3),  // 5
+    SPMV_CFG(512, 4096, 3),  // 6
+    SPMV_CFG(512, 4096, 2),  // 7
+    SPMV_CFG(384, 2688, 2),  // 8
+    SPMV_CFG(608, 4256, 2),  // 9
+    SPMV_CFG(480, 3840, 1),  // 10
+    SPMV_CFG(992, 7936, 1),  // 11
+    SPMV_CFG(576, 4032, 2),  // 12
+};
+
+static int g_spmv_cfg = -1, g_spmv_bps = 0, g_spmv_hint = 1;
+
+static const SpmvCfg& spmv_cfg() {
+  if (g_spmv_cfg < 0) {
+    const char* e = getenv("CGB200_SPMV_CFG");
+    int i = e ? atoi(e) : 0;
+    const int ncfg = (int)(sizeof(g_spmv_cfgs) / sizeof(g_spmv_cfgs[0]));
+    if (i < 0 || i >= ncfg) i = 0;
+    g_spmv_cfg = i;
+    const char* h = getenv("CGB200_SPMV_HINT");
+    if (h) g_spmv_hint = atoi(h);
+    const SpmvCfg& c = g_spmv_cfgs[i];
+    cudaFuncSetAttribute(c.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c.smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_spmv_bps, c.fn, c.R + 32, c.smem);
+    if (g_spmv_bps < 1) g_spmv_bps = 1;
+    const char* b = getenv("CGB200_SPMV_BPS");
+    if (b && atoi(b) > 0 && atoi(b) < g_spmv_bps) g_spmv_bps = atoi(b);
+  }
+  return g_spmv_cfgs[g_spmv_cfg];
+}
+
+int spmv_rows_per_tile() { return spmv_cfg().R; }
+
+int spmv_grid_for(int ntiles) {
+  spmv_cfg();
+  int grid = sm_count() * g_spmv_bps;
+  return grid > ntiles ? ntiles : grid;
 }
 
 cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, double* s,
@@ -697,18 +760,10 @@ cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, d
   TileRange tr{tile_begin0, tile_end0, tile_begin1, tile_end1};
   const int nvt = (tile_end0 - tile_begin0) + (tile_end1 - tile_begin1);
   if (nvt <= 0) return cudaSuccess;
-  const int bps = spmv_blocks_per_sm();
-  int grid = sm_count() * bps;
-  if (grid > nvt) grid = nvt;
-  k_spmv_stream<SP_R, SP_CAP, SP_STAGES><<<grid, SP_R, SpSM::total, st>>>(
-      A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s, tr, partials, ticket, S, mode);
+  const SpmvCfg& c = spmv_cfg();
+  c.launch(spmv_grid_for(nvt), st, A, pg, pown, s, tr, partials, ticket, S, mode, g_spmv_hint);
   ++g_launches;
   return cudaGetLastError();
-}
-
-int spmv_grid_for(int ntiles) {
-  int grid = sm_count() * spmv_blocks_per_sm();
-  return grid > ntiles ? ntiles : grid;
 }
 
 constexpr int GV_T = 256;

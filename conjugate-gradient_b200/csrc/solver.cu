@@ -641,20 +641,20 @@ static int enqueue_exchange_end(System* S) {
 }
 
 // K1 in the given mode on the loop's vectors (or on `pg`/`pown` overrides for PLAIN matvecs).
-static int enqueue_matvec(System* S, int mode_single, bool split_ok) {
+static int enqueue_matvec(System* S, int mode_single, bool split_ok, bool do_exchange = true) {
   Ctx& c = g_ctx;
   CgState* st = S->state;
   if (S->dense) {
-    if (enqueue_exchange_begin(S)) return -1;
+    if (do_exchange && enqueue_exchange_begin(S)) return -1;
     CUDA_OK(launch_gemv(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext, S->p_own,
                         S->s, S->partials, &st->ticket[0], st, mode_single, c.stream));
     return 0;
   }
-  const bool split = split_ok && S->world > 1 && !S->allgather && S->tb_hi > S->tb_lo &&
-                     (S->tb_lo > 0 || S->tb_hi < S->ntiles);
-  if (enqueue_exchange_begin(S)) return -1;
+  const bool split = do_exchange && split_ok && S->world > 1 && !S->allgather &&
+                     S->tb_hi > S->tb_lo && (S->tb_lo > 0 || S->tb_hi < S->ntiles);
+  if (do_exchange && enqueue_exchange_begin(S)) return -1;
   if (!split) {
-    if (enqueue_exchange_end(S)) return -1;
+    if (do_exchange && enqueue_exchange_end(S)) return -1;
     CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, S->s, 0, S->ntiles, 0, 0, S->partials,
                         &st->ticket[0], st, mode_single, c.stream));
     return 0;
@@ -889,12 +889,70 @@ int system_true_relres(System* S, double* relres) {
   return 0;
 }
 
-int system_time_kernel(System* S, int which, int reps, double* ms_out) {
+// Copies the matrix block back to host arrays (any of them may be NULL).  Columns are returned as
+// GLOBAL indices.  For a dense block cols/row_ptr are synthesised (row_ptr[i] = i*n, col = j).
+int system_download(System* S, double* vals, int* cols, int* row_ptr) {
   Ctx& c = g_ctx;
-  if (S->world > 1 && which == 1) {
-    set_error("time_kernel(K1) is a single-rank measurement");
+  const long long nnz = S->A.nnz;
+  if (vals && nnz > 0)
+    CUDA_OK(cudaMemcpyAsync(vals, S->A.vals, sizeof(double) * nnz, cudaMemcpyDeviceToHost, c.stream));
+  if (S->dense) {
+    CUDA_OK(cudaStreamSynchronize(c.stream));
+    const long long n = S->n_global;
+    if (row_ptr)
+      for (long long i = 0; i <= S->nloc; ++i) row_ptr[i] = (int)(i * n);
+    if (cols)
+      for (long long i = 0; i < S->nloc; ++i)
+        for (long long j = 0; j < n; ++j) cols[i * n + j] = (int)j;
+    return 0;
+  }
+  if (cols && nnz > 0)
+    CUDA_OK(cudaMemcpyAsync(cols, S->A.cols, sizeof(int) * nnz, cudaMemcpyDeviceToHost, c.stream));
+  if (row_ptr)
+    CUDA_OK(cudaMemcpyAsync(row_ptr, S->A.rowptr, sizeof(int) * ((size_t)S->nloc + 1),
+                            cudaMemcpyDeviceToHost, c.stream));
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  const long long shift = (S->world == 1 || S->allgather) ? 0 : S->row0 - S->off;
+  if (cols && shift != 0)
+    for (long long k = 0; k < nnz; ++k) cols[k] += (int)shift;
+  return 0;
+}
+
+int system_get_b(System* S, double* b_host) {
+  Ctx& c = g_ctx;
+  CUDA_OK(cudaMemcpyAsync(b_host, S->b, sizeof(double) * S->nloc, cudaMemcpyDeviceToHost, c.stream));
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  return 0;
+}
+
+// Device timer on the solve stream (bench harness: brackets K steps with one event pair).
+int timer_start() {
+  Ctx& c = g_ctx;
+  if (!c.t2) {
+    CUDA_OK(cudaEventCreate(&c.t2));
+    CUDA_OK(cudaEventCreate(&c.t3));
+  }
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  CUDA_OK(cudaEventRecord(c.t2, c.stream));
+  return 0;
+}
+
+int timer_stop(double* ms_out) {
+  Ctx& c = g_ctx;
+  if (!c.t2) {
+    set_error("timer_stop without timer_start");
     return -1;
   }
+  CUDA_OK(cudaEventRecord(c.t3, c.stream));
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  float ms = 0.f;
+  CUDA_OK(cudaEventElapsedTime(&ms, c.t2, c.t3));
+  *ms_out = ms;
+  return 0;
+}
+
+int system_time_kernel(System* S, int which, int reps, double* ms_out) {
+  Ctx& c = g_ctx;
   // a benign state: alpha = beta = 0 keeps x, r, p finite however often the kernels run
   CgState* h = &c.h_state[2];
   memset(h, 0, sizeof(CgState));
@@ -903,7 +961,7 @@ int system_time_kernel(System* S, int which, int reps, double* ms_out) {
   CUDA_OK(cudaMemcpyAsync(S->state, h, sizeof(CgState), cudaMemcpyHostToDevice, c.stream));
   auto one = [&]() -> int {
     if (which == 1) {
-      if (enqueue_matvec(S, SPMV_FINISH_LOCAL, false)) return -1;
+      if (enqueue_matvec(S, SPMV_FINISH_LOCAL, false, false)) return -1;  // local kernel only
     } else if (which == 2) {
       CUDA_OK(launch_update_xr(S->x, S->r, S->p_own, S->s, S->nloc, S->partials,
                                &S->state->ticket[1], S->state, 1, c.stream));

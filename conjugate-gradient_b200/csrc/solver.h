@@ -25,7 +25,8 @@ struct Ctx {
   void* d_scratch = nullptr;           // 64 B
   void* h_scratch = nullptr;           // 64 B pinned
   cudaEvent_t poll_ev[2] = {nullptr, nullptr};
-  cudaEvent_t t0 = nullptr, t1 = nullptr, ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t t0 = nullptr, t1 = nullptr, t2 = nullptr, t3 = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   // multi-GPU
   int rank = 0, world = 1;
   void* comm = nullptr;  // ncclComm_t
@@ -101,5 +102,9 @@ int system_matvec(System* S, const double* v_host, double* s_host);
 int system_matvec_dev(System* S, const double* v_dev, double* s_host_or_null);
 int system_true_relres(System* S, double* relres);
 int system_time_kernel(System* S, int which, int reps, double* ms_out);
+int system_download(System* S, double* vals, int* cols, int* row_ptr);
+int system_get_b(System* S, double* b_host);
+int timer_start();
+int timer_stop(double* ms_out);
 
 }  // namespace cgb

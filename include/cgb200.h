@@ -106,6 +106,14 @@ int cgb200_system_true_relres(cgb200_system *sys, double *relres);
 int cgb200_system_time_kernel(cgb200_system *sys, int which, int reps, double *ms);
 /* Contract bytes per iteration for this rank and the share of the matvec kernel. */
 int cgb200_system_bytes(cgb200_system *sys, double *iter_bytes, double *k1_bytes);
+/* Copies the matrix block to host arrays (any may be NULL): vals[nnz], cols[nnz] (global column
+ * indices), row_ptr[rows+1] (local, from 0).  Lets a device-generated system be handed to code
+ * that wants the reference's host structs (the cg driver's --gen, bench.py's end-to-end leg). */
+int cgb200_system_download(cgb200_system *sys, double *vals, int *cols, int *row_ptr);
+int cgb200_system_get_b(cgb200_system *sys, double *b_host);
+/* One CUDA-event pair on the library's solve stream: start, run any calls, stop -> elapsed ms. */
+int cgb200_timer_start(void);
+int cgb200_timer_stop(double *ms);
 long long cgb200_system_rows(cgb200_system *sys);
 long long cgb200_system_nnz(cgb200_system *sys);
 

@@ -67,6 +67,8 @@ def oracle():
     L.oracle_lap_nnz.argtypes = [C.c_int, C.c_int, C.c_int]
     L.oracle_gen_lap.argtypes = [C.c_int, C.c_int, C.c_int, c_int_p, c_int_p, c_double_p]
     L.oracle_gen_dense.argtypes = [C.c_int, C.c_uint64, c_int_p, c_int_p, c_double_p]
+    L.oracle_gen_banded.restype = C.c_int64
+    L.oracle_gen_banded.argtypes = [C.c_int, C.c_int, C.c_uint64, c_int_p, c_int_p, c_double_p]
     L.oracle_spmv.argtypes = [C.c_int, c_int_p, c_int_p, c_double_p, c_double_p, c_double_p]
     L.oracle_dot.restype = C.c_double
     L.oracle_dot.argtypes = [C.c_int, c_double_p, c_double_p]
@@ -176,19 +178,11 @@ def banded(n, half_bw, seed=3, bseed=7):
     """Symmetric banded SPD, strictly diagonally dominant, irreducible (bleed-free for the
     reference's mat_get_row): off-diagonals U(-1/2,1/2) by (min,max) pair, diagonal = bw + 1."""
     O = oracle()
-    rp = [0]
-    ci = []
-    va = []
-    for i in range(n):
-        lo, hi = max(0, i - half_bw), min(n - 1, i + half_bw)
-        for j in range(lo, hi + 1):
-            ci.append(j)
-            if i == j:
-                va.append(half_bw + 1.0)
-            else:
-                a, b_ = (i, j) if i < j else (j, i)
-                va.append(O.oracle_uniform(seed, a * n + b_))
-        rp.append(len(ci))
+    nnz = O.oracle_gen_banded(n, half_bw, seed, None, None, None)
+    rp = np.empty(n + 1, dtype=np.int32)
+    ci = np.empty(nnz, dtype=np.int32)
+    va = np.empty(nnz, dtype=np.float64)
+    O.oracle_gen_banded(n, half_bw, seed, iptr(rp), iptr(ci), dptr(va))
     return System(rp, ci, va, rhs(n, bseed), name=f"banded_{n}_{half_bw}")
 
 
