@@ -1,0 +1,581 @@
+#!/usr/bin/env python
+"""bench.py -- CG iterations/second of the hot path on N B200s, beside the reference's CPU build.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one CG iteration (one matvec + the two fused vector updates: one pass of the hot path
+over the whole system).  The headline workload is BASELINE.json configs[1]: dense SPD n = 32768,
+fp64, values-only GEMV path; with N > 1 the same system is row-block partitioned over the ranks
+(strong scaling: search direction all-gathered, two scalar all-reduces per iteration).  Because
+that matrix is strictly diagonally dominant CG converges to 1e-10 in a handful of iterations, so
+K steps are run as back-to-back solves of J iterations each with a fresh right-hand side
+(J = iterations a tolerance-1e-10 solve needs, measured in the warm-up), see DESIGN.md.
+
+Prints ONE JSON line (rank 0).  Keys beyond the base contract: roofline, cpu_baseline, e2e,
+clocks, gpu_launches, workloads (the other BASELINE configs measured in the same run).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "cg_iterations_per_second"
+UNIT = "it/s"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def traffic_from_profiles(kernel):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(kernel)
+    except Exception:
+        return None
+
+
+# -------------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# -------------------------------------------------------------------------------------------------
+
+
+class ClockSampler:
+    FIELDS = (
+        "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+        "clocks_event_reasons.sw_power_cap"
+    )
+
+    def __init__(self, gpu_index):
+        self.samples = []  # (t, sm, max, power, [flags])
+        self.proc = None
+        self.thread = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.FIELDS}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True,
+            )
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception as e:  # no nvidia-smi: report that instead of inventing clocks
+            log("clock sampler unavailable:", e)
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            p = [x.strip() for x in line.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                self.samples.append((time.time(), float(p[0]), float(p[1]), float(p[2]), p[3:7]))
+            except ValueError:
+                pass
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, t0, t1):
+        inside = [s for s in self.samples if t0 <= s[0] <= t1]
+        window = "timed region"
+        if not inside:
+            inside = [s for s in self.samples if s[0] <= t1 + 0.2][-5:]
+            window = "nearest samples (timed region shorter than the sampling period)"
+        if not inside:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "window": "none"}
+        sm = sorted(s[1] for s in inside)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[4][i].lower().startswith("active") for s in inside)]
+        return {
+            "sm_mhz": sm[len(sm) // 2], "sm_max_mhz": inside[0][2], "reasons": reasons,
+            "power_w_max": max(s[3] for s in inside), "samples": len(inside), "window": window,
+        }
+
+
+# -------------------------------------------------------------------------------------------------
+# workloads
+# -------------------------------------------------------------------------------------------------
+
+
+def make_system(pkg, name, rank, world):
+    """This rank's row block of the named workload, generated on the device."""
+    if name == "dense32768":
+        n = 32768
+        assert n % world == 0
+        nl = n // world
+        return pkg.DeviceSystem.dense(n, rank * nl, nl), {"kind": "dense", "n": n, "scaling": "strong"}
+    if name == "lap2d4096":
+        assert world == 1
+        return pkg.DeviceSystem.lap(4096, 4096, 1), {"kind": "lap2d", "n": 4096 * 4096, "scaling": "strong"}
+    if name == "lap3d512":
+        nz = 512
+        assert nz % world == 0
+        nzl = nz // world
+        return pkg.DeviceSystem.lap(512, 512, nz, rank * nzl, nzl), {"kind": "lap3d", "n": 512 ** 3, "scaling": "strong"}
+    if name == "lap3d384w":
+        nz = 384 * world
+        return pkg.DeviceSystem.lap(384, 384, nz, rank * 384, 384), {"kind": "lap3d", "n": 384 * 384 * nz, "scaling": "weak"}
+    raise SystemExit(f"unknown workload {name}")
+
+
+class Runner:
+    """Runs exactly K CG iterations of a workload as the reference's loop would be used."""
+
+    def __init__(self, pkg, d, info):
+        self.pkg, self.d, self.info = pkg, d, info
+        self.J = None      # iterations per solve (dense: to 1e-10; stencils: all K in one solve)
+        self.seed = 1000
+
+    def calibrate(self):
+        if self.info["kind"] == "dense":
+            r = self.d.solve(200, tol=1e-10)
+            assert r.status == self.pkg.CONVERGED, f"dense warm-up did not converge: status {r.status}"
+            self.J = r.iterations
+        return self.J
+
+    def run(self, K):
+        """K iterations; returns the number actually performed (must equal K)."""
+        done = 0
+        if self.J is None:
+            r = self.d.solve(K - 1)
+            return r.iterations
+        while done < K:
+            j = min(self.J, K - done)
+            self.seed += 1
+            self.d.gen_rhs(self.seed)     # fresh right-hand side, generated on the device
+            r = self.d.solve(j - 1)
+            done += r.iterations
+            if r.iterations != j:
+                raise RuntimeError(f"solve stopped early: {r.iterations} of {j} (status {r.status})")
+        return done
+
+
+def dist_sync(world):
+    import torch
+
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(v, world):
+    if world == 1:
+        return v
+    import torch
+    import torch.distributed as dist
+
+    t = torch.tensor([v], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def timed_steps(pkg, runner, K, W, world, sampler=None):
+    L = pkg.lib()
+    runner.calibrate()
+    w_done = runner.run(max(W, 3))
+    dist_sync(world)
+    l0 = L.cgb200_launch_count()
+    t0 = time.time()
+    assert L.cgb200_timer_start() == 0, pkg.last_error()
+    done = runner.run(K)
+    ms = C.c_double(0.0)
+    assert L.cgb200_timer_stop(C.byref(ms)) == 0, pkg.last_error()
+    t1 = time.time()
+    launches = L.cgb200_launch_count() - l0
+    dist_sync(world)
+    assert done == K, (done, K)
+    ms_max = max_over_ranks(ms.value, world)
+    return {"ms": ms_max, "steps": done, "warmup": w_done, "launches": int(launches), "t0": t0, "t1": t1}
+
+
+def roofline_for(pkg, d, peak, peak_src, kernel_name):
+    it_b, k1_b = d.bytes()
+    t1 = d.time_kernel(1, 30)
+    ach = k1_b / (t1 * 1e-3) / 1e9
+    return {
+        "bound": "hbm", "kernel": kernel_name, "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
+        "frac": round(ach / peak, 4), "traffic": traffic_from_profiles(kernel_name),
+        "algorithmic_bytes_per_launch": k1_b, "avg_launch_ms": round(t1, 5),
+        "peak_source": peak_src,
+        "how": "CUDA events on the library's solve stream around 30 back-to-back launches of the matvec kernel (this rank's block), after 3 warm-ups",
+    }
+
+
+# -------------------------------------------------------------------------------------------------
+# end-to-end through the reference-facing C ABI with host buffers
+# -------------------------------------------------------------------------------------------------
+
+
+def e2e_host_structs(pkg, d, info, J, solves=8):
+    """N = 1: cgb200_solve(A, b, &x) on struct __mv_sparse host arrays (pinned), every solve copying
+    its right-hand side host->device and its solution device->host.  A is uploaded by the first
+    call (reported as cold) and stays resident while its struct is unchanged."""
+    import numpy as np
+    import torch
+
+    L = pkg.lib()
+    n, nnz = d.rows, d.nnz
+    vals = torch.empty(nnz, dtype=torch.float64, pin_memory=True)
+    cols = torch.empty(nnz, dtype=torch.int32)
+    rp = torch.empty(n + 1, dtype=torch.int32)
+    bh = torch.empty(n, dtype=torch.float64, pin_memory=True)
+    vnp, cnp, rnp, bnp = vals.numpy(), cols.numpy(), rp.numpy(), bh.numpy()
+    assert L.cgb200_system_download(d.h, vnp.ctypes.data_as(pkg.c_double_p), cnp.ctypes.data_as(pkg.c_int_p),
+                                    rnp.ctypes.data_as(pkg.c_int_p)) == 0, pkg.last_error()
+    assert L.cgb200_system_get_b(d.h, bnp.ctypes.data_as(pkg.c_double_p)) == 0
+    A = pkg.MvSparse(n, nnz, vnp.ctypes.data_as(pkg.c_double_p), cnp.ctypes.data_as(pkg.c_int_p),
+                     rnp.ctypes.data_as(pkg.c_int_p))
+    b = pkg.MvSparse(n, n, bnp.ctypes.data_as(pkg.c_double_p), None, None)
+    o = pkg.Opts(200, 1e-10, 0, 0, 0) if info["kind"] == "dense" else pkg.Opts(J - 1, 0.0, 0, 0, 0)
+    res = pkg.Result()
+
+    def one():
+        xp = pkg.MvSparseP()
+        rc = L.cgb200_solve(C.byref(A), C.byref(b), C.byref(xp), C.byref(o), C.byref(res))
+        assert rc == 0, pkg.last_error()
+        chk = float(xp.contents.values[0])
+        L.cgb200_free_all(xp)
+        return res.iterations, chk
+
+    t = time.perf_counter()
+    it_cold, _ = one()                       # uploads A (8 B/nnz on the dense path) + b
+    cold_s = time.perf_counter() - t
+    rng = np.random.default_rng(3)
+    bs = [rng.random(n) - 0.5 for _ in range(solves)]
+    iters = 0
+    t = time.perf_counter()
+    for i in range(solves):
+        bnp[:] = bs[i]                       # caller refreshes b in place; A untouched
+        it, _ = one()
+        iters += it
+    warm_s = time.perf_counter() - t
+    L.cgb200_invalidate(C.byref(A))
+    a_bytes = 8 * nnz if info["kind"] == "dense" else 12 * nnz + 4 * (n + 1)
+    per_solve_iters = iters / solves
+    return {
+        "value": round(iters / warm_s, 2), "unit": UNIT,
+        "h2d_bytes_per_step": round(8 * n / per_solve_iters, 1),
+        "d2h_bytes_per_step": round(8 * n / per_solve_iters, 1),
+        "api": "cgb200_solve(struct __mv_sparse* A, b, &x) == conj_grad with tol 1e-10; host arrays pinned",
+        "solves": solves, "iterations_per_solve": per_solve_iters,
+        "per_solve": {"h2d_bytes": 8 * n, "d2h_bytes": 8 * n, "ms": round(warm_s / solves * 1e3, 3)},
+        "cold_first_call": {"value": round(it_cold / cold_s, 3), "unit": UNIT, "seconds": round(cold_s, 3),
+                            "h2d_bytes": a_bytes + 8 * n, "note": "includes uploading A"},
+        "note": "A stays device-resident between calls while its struct is unchanged (fingerprinted); every solve copies b in and x out",
+    }
+
+
+def e2e_row_blocks(pkg, name, rank, world, J, solves=8):
+    """N > 1: each rank hands its row block as host CSR arrays to cgb200_system_from_csr, then per
+    solve copies its slice of b in and its slice of x out."""
+    import numpy as np
+    import torch
+
+    L = pkg.lib()
+    d, info = make_system(pkg, name, rank, world)
+    n, nnz = d.rows, d.nnz
+    vals = torch.empty(nnz, dtype=torch.float64, pin_memory=True).numpy()
+    cols = np.empty(nnz, dtype=np.int32)
+    rp = np.empty(n + 1, dtype=np.int32)
+    bh = torch.empty(n, dtype=torch.float64, pin_memory=True).numpy()
+    xh = torch.empty(n, dtype=torch.float64, pin_memory=True).numpy()
+    assert L.cgb200_system_download(d.h, vals.ctypes.data_as(pkg.c_double_p), cols.ctypes.data_as(pkg.c_int_p),
+                                    rp.ctypes.data_as(pkg.c_int_p)) == 0, pkg.last_error()
+    assert L.cgb200_system_get_b(d.h, bh.ctypes.data_as(pkg.c_double_p)) == 0
+    row0 = rank * n
+    d.free()
+    dist_sync(world)
+    t = time.perf_counter()
+    h = pkg.DeviceSystem.from_csr(info["n"], row0, rp, cols, vals, bh)
+    dist_sync(world)
+    cold_s = time.perf_counter() - t
+    tol, mi = (1e-10, 200) if info["kind"] == "dense" else (0.0, J - 1)
+    h.solve(mi, tol=tol)
+    rng = np.random.default_rng(3 + rank)
+    bs = [rng.random(n) - 0.5 for _ in range(solves)]
+    dist_sync(world)
+    iters = 0
+    t = time.perf_counter()
+    for i in range(solves):
+        bh[:] = bs[i]
+        h.set_rhs(bh)
+        r = h.solve(mi, tol=tol)
+        assert L.cgb200_system_get_x(h.h, xh.ctypes.data_as(pkg.c_double_p)) == 0
+        iters += r.iterations
+    dist_sync(world)
+    warm_s = max_over_ranks(time.perf_counter() - t, world)
+    h.free()
+    per_solve_iters = iters / solves
+    return {
+        "value": round(iters / warm_s, 2), "unit": UNIT,
+        "h2d_bytes_per_step": round(8 * n * world / per_solve_iters, 1),
+        "d2h_bytes_per_step": round(8 * n * world / per_solve_iters, 1),
+        "api": "cgb200_system_from_csr(host row block) + set_rhs / solve / get_x per solve, all ranks; host arrays pinned",
+        "solves": solves, "iterations_per_solve": per_solve_iters,
+        "cold_upload_seconds": round(cold_s, 3),
+    }
+
+
+# -------------------------------------------------------------------------------------------------
+# CPU legs (the only places that execute oracle/)
+# -------------------------------------------------------------------------------------------------
+
+
+def cpu_reference_run(workload, budget_s, want_steps, host_arrays=None):
+    """Times the reference's own CPU implementation on the host cores.
+
+    oracle/_ref/libcgref.so (the UNMODIFIED reference, gcc -g as its Makefile builds it) when
+    present, else the oracle port.  The reference is single-threaded, cores = 1.
+    Returns (cpu_baseline dict, steps_run, seconds)."""
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers as H
+
+    assert workload == "dense32768", "the reference arm is defined on the headline workload"
+    n = 32768
+    if host_arrays is None:
+        log("[cpu] generating dense n=32768 CSR on the host (oracle generator)...")
+        s = H.dense(n)
+        rp, ci, va, b = s.row_ptr, s.cols, s.vals, s.b
+    else:
+        rp, ci, va, b = host_arrays
+    have_ref = H.have_ref()
+    kind = "reference" if have_ref else "port"
+
+    def run(max_iter):
+        t = time.perf_counter()
+        if have_ref:
+            R = H.ref()
+            A = H.MvSparse(n, len(va), H.dptr(va), H.iptr(ci), H.iptr(rp))
+            bv = H.MvSparse(n, n, H.dptr(b), None, None)
+            xp = H.MvSparseP()
+            assert R.conj_grad(max_iter, C.byref(A), C.byref(bv), C.byref(xp)) == 0
+            x0 = float(xp.contents.values[0])
+        else:
+            x = np.empty(n)
+            H.oracle().oracle_conj_grad(n, H.iptr(rp), H.iptr(ci), H.dptr(va), H.dptr(b), max_iter, 0.0, 1,
+                                        H.dptr(x), None, None)
+            x0 = float(x[0])
+        return time.perf_counter() - t, x0
+
+    t1, _ = run(0)  # one iteration: calibration and warm-up
+    m = int(max(1, min(want_steps, budget_s // max(t1, 1e-3))))
+    m = min(m, 5)   # fixed-count CG on this matrix is past convergence after ~6 iterations
+    tm, _ = run(m - 1)
+    val = m / tm
+    cb = {
+        "value": round(val, 5), "unit": UNIT, "cores": 1, "kind": kind,
+        "sample": f"{m} iteration(s) (max_iter={m - 1}) of {'the unmodified reference conj_grad (oracle/_ref, gcc -g as its Makefile)' if have_ref else 'the oracle port (oracle/cg_oracle.c, -O2)'} on the full dense n=32768 CSR system, after a 1-iteration warm-up ({t1:.1f} s)",
+        "seconds": round(tm, 2),
+    }
+    return cb, m, tm
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cb, m, tm = cpu_reference_run(args.workload, budget_s=100.0, want_steps=args.steps)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": m, "warmup": 1, "ms_per_step": round(tm / m * 1e3, 2), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.workload, 1),
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference's own CPU implementation on the box's host cores; steps bounded to keep the run within minutes",
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(name, world):
+    cfgs = {
+        "dense32768": {"workload": "dense SPD n=32768 fp64 (diagonally dominant, synthetic), CG to rel. residual 1e-10 (BASELINE configs[1])",
+                       "n": 32768, "nnz": 32768 ** 2, "matvec": "values-only row-block GEMV", "partition": f"row blocks x{world}",
+                       "l2": "inputs larger than L2 (8.6 GB matrix streamed every iteration)"},
+        "lap2d4096": {"workload": "2D 5-point Poisson 4096x4096 CSR fp64 (BASELINE configs[2])", "n": 4096 ** 2,
+                      "matvec": "CSR stream SpMV", "l2": "inputs larger than L2 (2.5 GB per iteration)"},
+        "lap3d512": {"workload": "3D 7-point Laplacian 512^3 CSR fp64 (BASELINE configs[3])", "n": 512 ** 3,
+                     "matvec": "CSR stream SpMV", "partition": f"z-slabs x{world}, halo exchange", "l2": "inputs larger than L2"},
+        "lap3d384w": {"workload": "3D 7-point Laplacian 384^3 per GPU, weak scaling (BASELINE configs[4])",
+                      "n": 384 ** 3 * world, "matvec": "CSR stream SpMV", "partition": f"z-slabs x{world}, halo exchange",
+                      "l2": "inputs larger than L2"},
+    }
+    return cfgs[name]
+
+
+# -------------------------------------------------------------------------------------------------
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--workload", default="dense32768")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the other BASELINE configs")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-leg", action="store_true", help="internal: print the cpu_baseline object only")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    if args.cpu_leg:
+        cb, _, _ = cpu_reference_run(args.workload, budget_s=20.0, want_steps=2)
+        print(json.dumps(cb), flush=True)
+        return 0
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run --nproc-per-node N")
+        args.gpus = world
+
+    import torch
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    import __graft_entry__ as g
+
+    pkg = g.load_package()
+    L = pkg.lib()
+    assert L.cgb200_init(local_rank) == 0, pkg.last_error()
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        idbuf = (C.c_ubyte * 128)()
+        if rank == 0:
+            assert L.cgb200_dist_unique_id(idbuf) == 0, pkg.last_error()
+        t = torch.tensor(list(bytes(idbuf)), dtype=torch.uint8, device="cuda")
+        dist.broadcast(t, 0)
+        raw = bytes(t.cpu().tolist())
+        idbuf = (C.c_ubyte * 128).from_buffer_copy(raw)
+        assert L.cgb200_dist_init(rank, world, idbuf) == 0, pkg.last_error()
+
+    peak, peak_src = measured_peak()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    time.sleep(0.3)
+
+    # ---- headline ----
+    d, info = make_system(pkg, args.workload, rank, world)
+    runner = Runner(pkg, d, info)
+    tm = timed_steps(pkg, runner, args.steps, args.warmup, world)
+    clocks = sampler.summary(tm["t0"], tm["t1"]) if sampler else None
+    it_b, k1_b = d.bytes()
+    value = tm["steps"] / (tm["ms"] * 1e-3)
+    kname = "k_gemv_rows" if info["kind"] == "dense" else "k_spmv_stream"
+    roof = roofline_for(pkg, d, peak, peak_src, kname)
+    iter_gbs = it_b / (tm["ms"] / tm["steps"] * 1e-3) / 1e9
+    true_rr = d.true_relres() if info["kind"] != "dense" else None
+    line = {
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": tm["steps"],
+        "warmup": tm["warmup"], "ms_per_step": round(tm["ms"] / tm["steps"], 5), "higher_is_better": True,
+        "scaling": info["scaling"], "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": dict(workload_config(args.workload, world), iterations_per_solve=runner.J),
+        "roofline": roof,
+        "iteration": {"contract_bytes_per_rank": it_b, "achieved_gbs_per_gpu": round(iter_gbs, 1),
+                      "frac_of_peak": round(iter_gbs / peak, 4),
+                      "note": "contract bytes/iteration (SURVEY 8d: A + 88 n) / device time per iteration, per GPU"},
+        "gpu_launches": tm["launches"],
+        "clocks": clocks,
+    }
+    J = runner.J
+    d.free()
+
+    # ---- end to end with host buffers ----
+    if not args.no_e2e:
+        try:
+            if world == 1:
+                d2, info2 = make_system(pkg, args.workload, 0, 1)
+                J2 = J if J else 50
+                line["e2e"] = e2e_host_structs(pkg, d2, info2, J2)
+                host_arrays = None
+                d2.free()
+            else:
+                line["e2e"] = e2e_row_blocks(pkg, args.workload, rank, world, J if J else 50)
+        except Exception as e:  # an honest gap beats a crashed bench line
+            line["e2e"] = {"value": None, "unit": UNIT, "error": repr(e)}
+
+    # ---- the other BASELINE configs, same run ----
+    if not args.no_extras:
+        extras = {}
+        names = ["lap2d4096", "lap3d512"] if world == 1 else ["lap3d512", "lap3d384w"]
+        for nm in names:
+            if nm == args.workload:
+                continue
+            try:
+                dx, ix = make_system(pkg, nm, rank, world)
+                rx = Runner(pkg, dx, ix)
+                k = 300 if nm == "lap2d4096" else 100
+                tx = timed_steps(pkg, rx, k, 5, world)
+                ib, _ = dx.bytes()
+                gbs = ib / (tx["ms"] / tx["steps"] * 1e-3) / 1e9
+                ex = {"value": round(tx["steps"] / (tx["ms"] * 1e-3), 2), "unit": UNIT, "steps": tx["steps"],
+                      "ms_per_step": round(tx["ms"] / tx["steps"], 5), "scaling": ix["scaling"],
+                      "achieved_gbs_per_gpu": round(gbs, 1), "frac_of_peak": round(gbs / peak, 4),
+                      "config": workload_config(nm, world)}
+                ex["roofline"] = roofline_for(pkg, dx, peak, peak_src, "k_spmv_stream")
+                extras[nm] = ex
+                dx.free()
+            except Exception as e:
+                extras[nm] = {"error": repr(e)}
+        line["workloads"] = extras
+
+    if sampler:
+        sampler.stop()
+
+    # ---- CPU baseline (rank 0, N = 1 only; the one leg that runs oracle/) ----
+    if world == 1 and not args.no_cpu and args.workload == "dense32768":
+        try:
+            # a fresh process that never loads libcgb200.so: the reference must run its own operators
+            out = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-leg", "--workload", args.workload],
+                                 stdout=subprocess.PIPE, text=True, timeout=900)
+            line["cpu_baseline"] = json.loads(out.stdout.strip().splitlines()[-1])
+        except Exception as e:
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "error": repr(e)}
+
+    if world > 1:
+        import torch.distributed as dist
+
+        L.cgb200_dist_finalize()
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -100,7 +100,7 @@ def lib():
             f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
             "(there is no CPU fallback)"
         )
-    L = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+    L = C.CDLL(LIB_PATH, mode=C.RTLD_LOCAL)
     # --- reference surface ---
     L.new_mv_struct.restype = MvSparseP
     L.new_mv_struct.argtypes = []
@@ -159,6 +159,7 @@ def lib():
     L.cgb200_system_rows.argtypes = [C.c_void_p]
     L.cgb200_system_nnz.restype = C.c_longlong
     L.cgb200_system_nnz.argtypes = [C.c_void_p]
+    L.cgb200_plan_partition.argtypes = [C.c_int, C.c_int, C.c_longlong, C.POINTER(C.c_longlong), C.c_int, C.POINTER(C.c_longlong)]
     L.cgb200_dist_unique_id.argtypes = [C.c_void_p]
     L.cgb200_dist_init.argtypes = [C.c_int, C.c_int, C.c_void_p]
     _lib = L

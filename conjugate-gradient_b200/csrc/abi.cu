@@ -14,6 +14,7 @@
 
 #include <mutex>
 #include <unordered_map>
+#include <vector>
 
 #include "../../include/cgb200.h"
 #include "solver.h"
@@ -663,6 +664,31 @@ int cgb200_system_bytes(cgb200_system* sys, double* iter_bytes, double* k1_bytes
 
 long long cgb200_system_rows(cgb200_system* sys) { return sys ? ((System*)sys)->nloc : -1; }
 long long cgb200_system_nnz(cgb200_system* sys) { return sys ? ((System*)sys)->A.nnz : -1; }
+
+int cgb200_plan_partition(int world, int rank, long long n_global, const long long* info4,
+                          int dense, long long* out10) {
+  if (!info4 || !out10 || world < 1) return -1;
+  std::vector<PartInfo> parts(world);
+  for (int g = 0; g < world; ++g)
+    parts[g] = PartInfo{info4[4 * g], info4[4 * g + 1], info4[4 * g + 2], info4[4 * g + 3]};
+  Plan p;
+  const char* err = nullptr;
+  if (plan_partition(world, rank, n_global, parts.data(), dense, &p, &err)) {
+    set_error(err ? err : "plan_partition failed");
+    return -1;
+  }
+  out10[0] = p.allgather;
+  out10[1] = p.h_lo;
+  out10[2] = p.h_hi;
+  out10[3] = p.off;
+  out10[4] = p.ext_len;
+  out10[5] = p.col_shift;
+  out10[6] = p.send_lo;
+  out10[7] = p.send_hi;
+  out10[8] = p.recv_lo;
+  out10[9] = p.recv_hi;
+  return 0;
+}
 
 int cgb200_dist_unique_id(void* id128) { return id128 ? dist_unique_id(id128) : -1; }
 int cgb200_dist_init(int rank, int world, const void* id128) {

@@ -240,7 +240,6 @@ static int allgather_i64(const long long* mine, int count, std::vector<long long
 // Systems
 // ---------------------------------------------------------------------------------------------
 
-static inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 System::~System() {
   for (auto& kv : graphs)
@@ -281,54 +280,33 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
   Ctx& c = g_ctx;
   S->world = c.world;
   S->rank = c.rank;
-  const long long row1 = S->row0 + S->nloc;
-  long long h_lo = std::max(0LL, S->row0 - mincol);
-  long long h_hi = std::max(0LL, maxcol - (row1 - 1));
-  if (S->dense) {
-    h_lo = S->row0;
-    h_hi = S->n_global - row1;
-  }
-
-  // every rank learns every rank's (row0, nloc, h_lo, h_hi)
-  long long mine[4] = {S->row0, (long long)S->nloc, h_lo, h_hi};
+  // every rank learns every rank's (row0, nloc, mincol, maxcol); the plan is pure host logic
+  long long mine[4] = {S->row0, (long long)S->nloc, mincol, maxcol};
   std::vector<long long> all;
   if (allgather_i64(mine, 4, all)) return -1;
-  S->part_row0.resize(c.world);
-  S->part_nloc.resize(c.world);
-  S->part_hlo.resize(c.world);
-  S->part_hhi.resize(c.world);
-  bool wide = S->dense;
-  for (int g = 0; g < c.world; ++g) {
-    S->part_row0[g] = all[4 * g + 0];
-    S->part_nloc[g] = (int)all[4 * g + 1];
-    S->part_hlo[g] = (int)std::min<long long>(all[4 * g + 2], 0x7fffffff);
-    S->part_hhi[g] = (int)std::min<long long>(all[4 * g + 3], 0x7fffffff);
-    if (g > 0 && all[4 * g + 2] > all[4 * (g - 1) + 1]) wide = true;
-    if (g + 1 < c.world && all[4 * g + 3] > all[4 * (g + 1) + 1]) wide = true;
-    if (g == 0 && all[4 * g + 2] > 0) wide = true;             // columns below row 0?!
-    if (g == c.world - 1 && all[4 * g + 3] > 0 && !S->dense) wide = true;
-  }
-  if (c.world == 1) wide = false;
-  S->allgather = (c.world > 1) && wide;
-
-  long long col_shift;  // global column -> index in p_ext
-  if (c.world == 1 || S->allgather) {
-    // the gather space is the whole vector
-    S->h_lo = S->h_hi = 0;
-    S->off = (long long)S->row0;
-    S->ext_len = S->n_global;
-    col_shift = 0;
-  } else {
-    S->h_lo = (int)h_lo;
-    S->h_hi = (int)h_hi;
-    S->off = (long long)round_up((size_t)h_lo, 16);  // keep the owned block 128-byte aligned
-    S->ext_len = S->off + S->nloc + h_hi;
-    col_shift = S->row0 - S->off;
-  }
-  if (c.world == 1 && S->row0 != 0) {
-    set_error("single-rank system must start at row 0");
+  std::vector<PartInfo> parts(c.world);
+  for (int g = 0; g < c.world; ++g)
+    parts[g] = PartInfo{all[4 * g + 0], all[4 * g + 1], all[4 * g + 2], all[4 * g + 3]};
+  Plan plan;
+  const char* perr = nullptr;
+  if (plan_partition(c.world, c.rank, S->n_global, parts.data(), S->dense ? 1 : 0, &plan, &perr)) {
+    set_error(std::string("partition plan: ") + (perr ? perr : "?"));
     return -1;
   }
+  S->part_row0.resize(c.world);
+  S->part_nloc.resize(c.world);
+  for (int g = 0; g < c.world; ++g) {
+    S->part_row0[g] = parts[g].row0;
+    S->part_nloc[g] = (int)parts[g].nloc;
+  }
+  S->allgather = (c.world > 1) && plan.allgather;
+  S->h_lo = plan.h_lo;
+  S->h_hi = plan.h_hi;
+  S->send_lo = plan.send_lo;
+  S->send_hi = plan.send_hi;
+  S->off = plan.off;
+  S->ext_len = plan.ext_len;
+  const long long col_shift = plan.col_shift;  // global column -> index in p_ext
 
   const size_t nl = (size_t)S->nloc;
   CUDA_OK(cudaMalloc(&S->b, (nl + 16) * sizeof(double)));
@@ -612,7 +590,7 @@ static int enqueue_exchange_begin(System* S) {
   const int me = S->rank;
   NCCL_OK(g_nccl.GroupStart());
   if (me > 0) {
-    const int send_cnt = S->part_hhi[me - 1];  // my first rows are the lower rank's upper halo
+    const int send_cnt = S->send_lo;  // my first rows are the lower rank's upper halo
     if (send_cnt > 0)
       NCCL_OK(g_nccl.Send(S->p_own, (size_t)send_cnt, ncclDouble, me - 1, comm, c.comm_stream));
     if (S->h_lo > 0)
@@ -620,7 +598,7 @@ static int enqueue_exchange_begin(System* S) {
                           c.comm_stream));
   }
   if (me + 1 < S->world) {
-    const int send_cnt = S->part_hlo[me + 1];  // my last rows are the upper rank's lower halo
+    const int send_cnt = S->send_hi;  // my last rows are the upper rank's lower halo
     if (send_cnt > 0)
       NCCL_OK(g_nccl.Send(S->p_own + S->nloc - send_cnt, (size_t)send_cnt, ncclDouble, me + 1,
                           comm, c.comm_stream));

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "kernels.h"
+#include "partition.h"
 #include "state.h"
 
 namespace cgb {
@@ -59,7 +60,8 @@ struct System {
   bool allgather = false;
   int world = 1, rank = 0;
   std::vector<long long> part_row0;
-  std::vector<int> part_nloc, part_hlo, part_hhi;
+  std::vector<int> part_nloc;
+  int send_lo = 0, send_hi = 0;  // rows sent to rank-1 / rank+1 in neighbour mode
 
   // tiles [tb_lo, tb_hi) touch owned columns only; the rest wait for the halo
   int ntiles = 0, tb_lo = 0, tb_hi = 0;

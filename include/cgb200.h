@@ -120,6 +120,12 @@ long long cgb200_system_nnz(cgb200_system *sys);
 /* ---- multi-GPU: one process per GPU, NCCL over NVLink -------------------------------------- */
 /* Rank 0 obtains a 128-byte NCCL unique id and ships it to the other ranks by any means
  * (torch.distributed broadcast in bench.py, a pipe in the cg driver). */
+/* Host-only planning of the row-block decomposition (csrc/partition.h).  info4 holds, per rank,
+ * {row0, nloc, mincol, maxcol} (global column span of that rank's rows).  out10 receives
+ * {allgather, h_lo, h_hi, off, ext_len, col_shift, send_lo, send_hi, recv_lo, recv_hi}.
+ * Needs no device. */
+int cgb200_plan_partition(int world, int rank, long long n_global, const long long *info4,
+                          int dense, long long *out10);
 int cgb200_dist_unique_id(void *id128);
 int cgb200_dist_init(int rank, int world, const void *id128);
 int cgb200_dist_finalize(void);

@@ -105,7 +105,7 @@ def ref():
     global _ref
     if _ref is not None:
         return _ref
-    L = C.CDLL(REF_SO)
+    L = C.CDLL(REF_SO, mode=C.RTLD_LOCAL)
     L.new_mv_struct.restype = MvSparseP
     L.new_mv_struct_with_size.restype = MvSparseP
     L.new_mv_struct_with_size.argtypes = [C.c_int]

@@ -1,0 +1,140 @@
+"""CPU: libcgb200.so loads without a GPU and exports every symbol include/*.h declare; the
+host-only parts of the reference surface behave like the reference; arithmetic entry points fail
+loudly (no CPU fallback) when there is no device."""
+import ctypes as C
+import io
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import helpers as H
+
+ROOT = H.ROOT
+
+
+def declared_functions(header):
+    txt = open(os.path.join(ROOT, "include", header)).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    names = re.findall(r"\b([A-Za-z_][A-Za-z0-9_]*)\s*\([^;{]*\)\s*;", txt)
+    return sorted(set(n for n in names if n not in ("defined",)))
+
+
+def test_headers_declare_the_reference_surface():
+    fns = declared_functions("mv_ops.h")
+    # reference mv_ops.h:26-42 + cg.c:24
+    for n in ["new_mv_struct", "new_mv_struct_with_size", "free_mv_struct", "mv_deep_copy", "print_sparse",
+              "mat_get_row", "dot_product", "sv_mult", "mv_mult", "vec_add", "vec_sub", "conj_grad"]:
+        assert n in fns
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    L = pkg.lib()
+    out = subprocess.run(["nm", "-D", "--defined-only", pkg.LIB_PATH], stdout=subprocess.PIPE, text=True, check=True).stdout
+    exported = {ln.split()[-1] for ln in out.splitlines() if " T " in ln}
+    for hdr in ("mv_ops.h", "cgb200.h"):
+        for fn in declared_functions(hdr):
+            assert fn in exported, f"{fn} declared in include/{hdr} but not exported"
+            getattr(L, fn)
+
+
+def test_struct_layout_is_the_reference_abi(pkg):
+    # mv_ops.h:17-23 on LP64: int, int, double*, int*, int* = 32 bytes
+    assert C.sizeof(pkg.MvSparse) == 32
+    assert pkg.MvSparse.values.offset == 8 and pkg.MvSparse.col_indices.offset == 16 and pkg.MvSparse.row_ptr.offset == 24
+
+
+def test_lifecycle_is_host_side_and_matches_reference_behaviour(pkg):
+    L = pkg.lib()
+    v = L.new_mv_struct_with_size(5)
+    assert v.contents.size == 5 and v.contents.nnz == 5
+    assert not v.contents.col_indices and not v.contents.row_ptr
+    assert np.array_equal(np.ctypeslib.as_array(v.contents.values, shape=(5,)), np.zeros(5))
+    z = L.new_mv_struct()
+    assert z.contents.size == 0 and not z.contents.values
+    s = H.lap(4, 3)
+    A = pkg.MvSparse(s.n, s.nnz, H.dptr(s.vals), H.iptr(s.cols), H.iptr(s.row_ptr))
+    cp = L.mv_deep_copy(C.byref(A))
+    assert cp.contents.size == s.n and cp.contents.nnz == s.nnz
+    assert np.array_equal(np.ctypeslib.as_array(cp.contents.values, shape=(s.nnz,)), s.vals)
+    assert np.array_equal(np.ctypeslib.as_array(cp.contents.col_indices, shape=(s.nnz,)), s.cols)
+    assert np.array_equal(np.ctypeslib.as_array(cp.contents.row_ptr, shape=(s.n + 1,)), s.row_ptr)
+    assert C.addressof(cp.contents.values.contents) != s.vals.ctypes.data
+    assert not L.mv_deep_copy(None)
+    L.cgb200_free_all(cp)
+    L.free_mv_struct(z)
+    L.free_mv_struct(None)
+
+
+def test_mat_get_row(pkg):
+    L = pkg.lib()
+    s = H.lap(4, 3)
+    A = pkg.MvSparse(s.n, s.nnz, H.dptr(s.vals), H.iptr(s.cols), H.iptr(s.row_ptr))
+    row = np.full(s.n, 7.0)
+    for i in range(s.n):
+        assert L.mat_get_row(C.byref(A), i, H.dptr(row)) == 0
+        want = np.zeros(s.n)
+        want[s.cols[s.row_ptr[i]:s.row_ptr[i + 1]]] = s.vals[s.row_ptr[i]:s.row_ptr[i + 1]]
+        assert np.array_equal(row, want)
+    assert L.mat_get_row(None, 0, H.dptr(row)) == -1            # mv_ops.c:103-104
+    assert L.mat_get_row(C.byref(A), 0, None) == -1
+    # unlike the reference's scan a diagonal matrix does not bleed into the next row
+    n = 4
+    rp = np.arange(n + 1, dtype=np.int32)
+    ci = np.arange(n, dtype=np.int32)
+    va = np.array([1.0, 2.0, 3.0, 4.0])
+    D = pkg.MvSparse(n, n, H.dptr(va), H.iptr(ci), H.iptr(rp))
+    r = np.empty(n)
+    assert L.mat_get_row(C.byref(D), 0, H.dptr(r)) == 0
+    assert np.array_equal(r, [1, 0, 0, 0])
+
+
+def test_argument_errors_need_no_device(pkg):
+    L = pkg.lib()
+    a, b = H.rhs(8, 1), H.rhs(9, 2)
+    va = pkg.MvSparse(8, 8, H.dptr(a), None, None)
+    vb = pkg.MvSparse(9, 9, H.dptr(b), None, None)
+    out = pkg.MvSparseP()
+    assert L.vec_add(C.byref(va), C.byref(vb), C.byref(out)) == -1
+    assert L.vec_sub(None, C.byref(vb), C.byref(out)) == -1
+    assert L.sv_mult(2.0, None, C.byref(out)) == -1
+    assert L.dot_product(C.byref(va), C.byref(vb)) == -1.0
+    assert L.dot_product(None, None) == -1.0
+    assert L.mv_mult(None, C.byref(va), C.byref(out)) == -1
+    assert L.conj_grad(3, None, C.byref(va), C.byref(out)) == -1
+
+
+def test_no_cpu_fallback(pkg):
+    """Without a device the arithmetic fails loudly; with one this test has nothing to prove."""
+    L = pkg.lib()
+    if L.cgb200_device_available():
+        pytest.skip("a CUDA device is present")
+    a = H.rhs(8, 1)
+    va = pkg.MvSparse(8, 8, H.dptr(a), None, None)
+    out = pkg.MvSparseP()
+    assert L.sv_mult(2.0, C.byref(va), C.byref(out)) == -1
+    assert "no CPU fallback" in pkg.last_error()
+    assert L.dot_product(C.byref(va), C.byref(va)) == -1.0
+    s = H.tridiag4()
+    A = pkg.MvSparse(s.n, s.nnz, H.dptr(s.vals), H.iptr(s.cols), H.iptr(s.row_ptr))
+    b = pkg.MvSparse(s.n, s.n, H.dptr(s.b), None, None)
+    assert L.conj_grad(1, C.byref(A), C.byref(b), C.byref(out)) == -1
+    with pytest.raises(pkg.CgError):
+        pkg.DeviceSystem.lap(8, 8)
+
+
+def test_product_sources_never_touch_the_oracle():
+    """The product path may not import, link or execute anything under oracle/ (tier rule 3)."""
+    pk = os.path.join(ROOT, "conjugate-gradient_b200")
+    bad = []
+    for dp, _, fns in os.walk(pk):
+        for fn in fns:
+            if fn.endswith((".cu", ".cuh", ".h", ".c", ".cpp", ".py", "Makefile")):
+                txt = open(os.path.join(dp, fn), errors="ignore").read()
+                if re.search(r"oracle/|liboracle|cg_oracle|libcgref", txt):
+                    bad.append(os.path.join(dp, fn))
+    assert not bad, bad
+    ldd = subprocess.run(["ldd", os.path.join(pk, "libcgb200.so")], stdout=subprocess.PIPE, text=True).stdout
+    assert "oracle" not in ldd and "cgref" not in ldd
