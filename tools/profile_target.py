@@ -1,0 +1,23 @@
+"""Small fixed workload for ncu captures: a few CG iterations of one BASELINE config on 1 GPU.
+usage: profile_target.py {dense|lap2d|lap3d512|lap3d384} [iterations]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as g
+
+pkg = g.load_package()
+L = pkg.lib()
+assert L.cgb200_init(-1) == 0, pkg.last_error()
+w = sys.argv[1]
+iters = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+d = {
+    "dense": lambda: pkg.DeviceSystem.dense(32768),
+    "lap2d": lambda: pkg.DeviceSystem.lap(4096, 4096, 1),
+    "lap3d512": lambda: pkg.DeviceSystem.lap(512, 512, 512),
+    "lap3d384": lambda: pkg.DeviceSystem.lap(384, 384, 384),
+}[w]()
+r = d.solve(iters - 1, check_every=iters)
+print(w, "iterations", r.iterations, "status", r.status, "relres", r.relres, "ms/iter", r.seconds * 1e3 / max(r.iterations, 1))
+d.free()
