@@ -43,11 +43,15 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def traffic_from_profiles(kernel):
-    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+def traffic_from_profiles(kernel, workload, world):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture of this very
+    launch shape (same workload, 1 GPU), or None."""
+    if world != 1:
+        return None
+    key = {"dense32768": "dense", "lap3d512": "lap3d512", "lap2d4096": "lap2d"}.get(workload)
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get(kernel)
+            return json.load(f)["_by_workload"][key][kernel]
     except Exception:
         return None
 
@@ -212,13 +216,13 @@ def timed_steps(pkg, runner, K, W, world, sampler=None):
     return {"ms": ms_max, "steps": done, "warmup": w_done, "launches": int(launches), "t0": t0, "t1": t1}
 
 
-def roofline_for(pkg, d, peak, peak_src, kernel_name):
+def roofline_for(pkg, d, peak, peak_src, kernel_name, workload, world):
     it_b, k1_b = d.bytes()
     t1 = d.time_kernel(1, 30)
     ach = k1_b / (t1 * 1e-3) / 1e9
     return {
         "bound": "hbm", "kernel": kernel_name, "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
-        "frac": round(ach / peak, 4), "traffic": traffic_from_profiles(kernel_name),
+        "frac": round(ach / peak, 4), "traffic": traffic_from_profiles(kernel_name, workload, world),
         "algorithmic_bytes_per_launch": k1_b, "avg_launch_ms": round(t1, 5),
         "peak_source": peak_src,
         "how": "CUDA events on the library's solve stream around 30 back-to-back launches of the matvec kernel (this rank's block), after 3 warm-ups",
@@ -496,7 +500,7 @@ def main():
     it_b, k1_b = d.bytes()
     value = tm["steps"] / (tm["ms"] * 1e-3)
     kname = "k_gemv_rows" if info["kind"] == "dense" else "k_spmv_stream"
-    roof = roofline_for(pkg, d, peak, peak_src, kname)
+    roof = roofline_for(pkg, d, peak, peak_src, kname, args.workload, world)
     iter_gbs = it_b / (tm["ms"] / tm["steps"] * 1e-3) / 1e9
     true_rr = d.true_relres() if info["kind"] != "dense" else None
     line = {
@@ -546,7 +550,7 @@ def main():
                       "ms_per_step": round(tx["ms"] / tx["steps"], 5), "scaling": ix["scaling"],
                       "achieved_gbs_per_gpu": round(gbs, 1), "frac_of_peak": round(gbs / peak, 4),
                       "config": workload_config(nm, world)}
-                ex["roofline"] = roofline_for(pkg, dx, peak, peak_src, "k_spmv_stream")
+                ex["roofline"] = roofline_for(pkg, dx, peak, peak_src, "k_spmv_stream", nm, world)
                 extras[nm] = ex
                 dx.free()
             except Exception as e:

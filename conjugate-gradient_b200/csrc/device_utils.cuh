@@ -155,7 +155,9 @@ __device__ __forceinline__ double block_sum(double v, double* sm) {
 // that last block only, with the grand total in `total`; the ticket is reset for the next launch.
 template <int THREADS>
 __device__ __forceinline__ bool grid_sum(double v, double* __restrict__ partials,
-                                         unsigned int* __restrict__ ticket, double& total) {
+                                         unsigned int* __restrict__ ticket, double& total,
+                                         const double* __restrict__ extra = nullptr,
+                                         int n_extra = 0) {
   __shared__ double sm[THREADS / 32];
   __shared__ int is_last;
   double t = block_sum<THREADS>(v, sm);
@@ -170,6 +172,8 @@ __device__ __forceinline__ bool grid_sum(double v, double* __restrict__ partials
   __threadfence();
   double acc = 0.0;
   for (int i = threadIdx.x; i < (int)gridDim.x; i += THREADS) acc += __ldcg(partials + i);
+  // partials left by a preceding launch of the same reduction (split matvec), same fixed order
+  for (int i = threadIdx.x; i < n_extra; i += THREADS) acc += __ldcg(extra + i);
   total = block_sum<THREADS>(acc, sm);
   if (threadIdx.x == 0) {
     *ticket = 0u;

@@ -210,11 +210,9 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
     if (tid == 0) partials[blockIdx.x] = t;  // caller passes partials + SPMV_EXTRA_OFFSET
     return;
   }
+  // `partials` may carry extra slots written by a preceding PARTIAL_ONLY launch
   double total;
-  if (grid_sum<THREADS>(dot, partials, ticket, total)) {
-    // `partials` may carry extra slots written by a preceding PARTIAL_ONLY launch
-    const int extra = mode >> 8;
-    for (int i = 0; i < extra; ++i) total += __ldcg(partials + SPMV_EXTRA_OFFSET + i);
+  if (grid_sum<THREADS>(dot, partials, ticket, total, partials + SPMV_EXTRA_OFFSET, mode >> 8)) {
     if ((mode & 0xff) == SPMV_FINISH_LOCAL)
       S->local = total;
     else

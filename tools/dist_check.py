@@ -1,0 +1,123 @@
+"""Multi-rank parity check, launched as
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/dist_check.py
+Every rank builds its row block through the C ABI, the ranks solve together (NCCL), rank 0 gathers x
+and compares with the CPU oracle on the whole system (tests/helpers.py; checker only)."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import __graft_entry__ as g
+import helpers as H
+
+rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(lr)
+pkg = g.load_package()
+L = pkg.lib()
+assert L.cgb200_init(lr) == 0, pkg.last_error()
+dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+idbuf = (C.c_ubyte * 128)()
+if rank == 0:
+    assert L.cgb200_dist_unique_id(idbuf) == 0, pkg.last_error()
+t = torch.tensor(list(bytes(idbuf)), dtype=torch.uint8, device="cuda")
+dist.broadcast(t, 0)
+idbuf = (C.c_ubyte * 128).from_buffer_copy(bytes(t.cpu().tolist()))
+assert L.cgb200_dist_init(rank, world, idbuf) == 0, pkg.last_error()
+
+
+def gather_x(d, n, counts):
+    xl = torch.from_numpy(d.x()).cuda()
+    parts = [torch.empty(c, dtype=torch.float64, device="cuda") for c in counts]
+    # uneven sizes: one broadcast per rank
+    for r_ in range(world):
+        buf = xl if r_ == rank else parts[r_]
+        dist.broadcast(buf, r_)
+        parts[r_] = buf
+    return torch.cat(parts).cpu().numpy()
+
+
+def blocks(n, align=1):
+    base = (n // world) // align * align
+    cnt = [base] * world
+    cnt[-1] = n - base * (world - 1)
+    return cnt
+
+
+ok = True
+
+
+def report(name, cond, detail):
+    global ok
+    ok = ok and bool(cond)
+    if rank == 0:
+        print(("PASS " if cond else "FAIL ") + name + " " + detail, flush=True)
+
+
+# 1) device-generated 3D Laplacian, z-slabs, fixed count vs oracle; halo overlap path
+nx, ny, nz = 48, 40, 8 * world
+s = H.lap(nx, ny, nz)
+nzl = nz // world
+d = pkg.DeviceSystem.lap(nx, ny, nz, rank * nzl, nzl)
+r = d.solve(60)
+x = gather_x(d, s.n, [nx * ny * nzl] * world)
+xo, it, _, _ = H.oracle_cg(s, 60)
+rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+report("lap3d fixed-count", r.iterations == it and rel <= 1e-8, f"iters {r.iterations}/{it} rel {rel:.2e} world {r.world}")
+r = d.solve(100000, tol=1e-10)
+xo, it, _, st = H.oracle_cg(s, 100000, tol=1e-10, guard=1)
+x = gather_x(d, s.n, [nx * ny * nzl] * world)
+tr = d.true_relres()
+rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+report("lap3d tolerance", abs(r.iterations - it) <= 2 and tr <= 1.05e-10 and rel <= 1e-8,
+       f"iters {r.iterations}/{it} true relres {tr:.2e} rel {rel:.2e}")
+d.free()
+
+# 2) bigger slab so interior and boundary tiles both exist (tile = 512 rows)
+nx, ny, nz = 64, 64, 16 * world
+nzl = nz // world
+d = pkg.DeviceSystem.lap(nx, ny, nz, rank * nzl, nzl)
+s = H.lap(nx, ny, nz)
+r = d.solve(40)
+x = gather_x(d, s.n, [nx * ny * nzl] * world)
+xo, it, _, _ = H.oracle_cg(s, 40)
+rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+report("lap3d split-launch", r.iterations == it and rel <= 1e-8, f"rel {rel:.2e}")
+d.free()
+
+# 3) dense, all-gather mode
+n = 1024 * world
+s = H.dense(n)
+nl = n // world
+d = pkg.DeviceSystem.dense(n, rank * nl, nl)
+r = d.solve(200, tol=1e-10)
+x = gather_x(d, n, [nl] * world)
+xo, it, _, _ = H.oracle_cg(s, 200, tol=1e-10, guard=1)
+rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+report("dense all-gather", abs(r.iterations - it) <= 2 and rel <= 1e-8, f"iters {r.iterations}/{it} rel {rel:.2e}")
+d.free()
+
+# 4) host CSR row blocks, uneven, banded (neighbour mode) and wide band (all-gather fallback)
+for hb, name in ((7, "banded neighbour"), (900, "banded wide")):
+    s = H.banded(3001, hb)
+    cnt = blocks(s.n)
+    row0 = sum(cnt[:rank])
+    nl = cnt[rank]
+    rp = s.row_ptr[row0:row0 + nl + 1]
+    d = pkg.DeviceSystem.from_csr(s.n, row0, rp - rp[0], s.cols[rp[0]:rp[-1]], s.vals[rp[0]:rp[-1]], s.b[row0:row0 + nl])
+    r = d.solve(15)
+    x = gather_x(d, s.n, cnt)
+    xo, it, _, _ = H.oracle_cg(s, 15)
+    rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+    report("from_csr " + name, r.iterations == it and rel <= 1e-8, f"rel {rel:.2e}")
+    d.free()
+
+L.cgb200_dist_finalize()
+dist.barrier()
+dist.destroy_process_group()
+sys.exit(0 if ok else 1)
