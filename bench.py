@@ -147,14 +147,14 @@ def make_system(pkg, name, rank, world):
 class Runner:
     """Runs exactly K CG iterations of a workload as the reference's loop would be used."""
 
-    def __init__(self, pkg, d, info):
-        self.pkg, self.d, self.info = pkg, d, info
+    def __init__(self, pkg, d, info, variant=0):
+        self.pkg, self.d, self.info, self.variant = pkg, d, info, variant
         self.J = None      # iterations per solve (dense: to 1e-10; stencils: all K in one solve)
         self.seed = 1000
 
     def calibrate(self):
         if self.info["kind"] == "dense":
-            r = self.d.solve(200, tol=1e-10)
+            r = self.d.solve(200, tol=1e-10, variant=self.variant)
             assert r.status == self.pkg.CONVERGED, f"dense warm-up did not converge: status {r.status}"
             self.J = r.iterations
         return self.J
@@ -163,13 +163,13 @@ class Runner:
         """K iterations; returns the number actually performed (must equal K)."""
         done = 0
         if self.J is None:
-            r = self.d.solve(K - 1)
+            r = self.d.solve(K - 1, variant=self.variant)
             return r.iterations
         while done < K:
             j = min(self.J, K - done)
             self.seed += 1
             self.d.gen_rhs(self.seed)     # fresh right-hand side, generated on the device
-            r = self.d.solve(j - 1)
+            r = self.d.solve(j - 1, variant=self.variant)
             done += r.iterations
             if r.iterations != j:
                 raise RuntimeError(f"solve stopped early: {r.iterations} of {j} (status {r.status})")
@@ -445,6 +445,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--workload", default="dense32768")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--variant", default="classic", choices=["classic", "single-reduction"],
+                    help="recurrence of the headline run (the reference's classic one by default)")
     ap.add_argument("--no-extras", action="store_true", help="skip the other BASELINE configs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
@@ -493,8 +495,10 @@ def main():
     time.sleep(0.3)
 
     # ---- headline ----
+    variant = 1 if args.variant == "single-reduction" else 0
     d, info = make_system(pkg, args.workload, rank, world)
-    runner = Runner(pkg, d, info)
+    comm = "single" if world == 1 else ("p2p" if L.cgb200_system_comm_is_p2p(d.h) else "nccl")
+    runner = Runner(pkg, d, info, variant)
     tm = timed_steps(pkg, runner, args.steps, args.warmup, world)
     clocks = sampler.summary(tm["t0"], tm["t1"]) if sampler else None
     it_b, k1_b = d.bytes()
@@ -507,7 +511,8 @@ def main():
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": tm["steps"],
         "warmup": tm["warmup"], "ms_per_step": round(tm["ms"] / tm["steps"], 5), "higher_is_better": True,
         "scaling": info["scaling"], "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": dict(workload_config(args.workload, world), iterations_per_solve=runner.J),
+        "config": dict(workload_config(args.workload, world), iterations_per_solve=runner.J,
+                       variant=args.variant, comm=comm),
         "roofline": roof,
         "iteration": {"contract_bytes_per_rank": it_b, "achieved_gbs_per_gpu": round(iter_gbs, 1),
                       "frac_of_peak": round(iter_gbs / peak, 4),
@@ -516,6 +521,15 @@ def main():
         "clocks": clocks,
     }
     J = runner.J
+    # the other recurrence on the same system, same K (explains, does not replace, the headline)
+    try:
+        other = Runner(pkg, d, info, 1 - variant)
+        to = timed_steps(pkg, other, args.steps, args.warmup, world)
+        line["other_variant"] = {"variant": "classic" if variant else "single-reduction",
+                                 "value": round(to["steps"] / (to["ms"] * 1e-3), 2), "unit": UNIT,
+                                 "ms_per_step": round(to["ms"] / to["steps"], 5), "gpu_launches": to["launches"]}
+    except Exception as e:
+        line["other_variant"] = {"error": repr(e)}
     d.free()
 
     # ---- end to end with host buffers ----
@@ -541,7 +555,7 @@ def main():
                 continue
             try:
                 dx, ix = make_system(pkg, nm, rank, world)
-                rx = Runner(pkg, dx, ix)
+                rx = Runner(pkg, dx, ix, variant)
                 k = 300 if nm == "lap2d4096" else 100
                 tx = timed_steps(pkg, rx, k, 5, world)
                 ib, _ = dx.bytes()
@@ -551,6 +565,11 @@ def main():
                       "achieved_gbs_per_gpu": round(gbs, 1), "frac_of_peak": round(gbs / peak, 4),
                       "config": workload_config(nm, world)}
                 ex["roofline"] = roofline_for(pkg, dx, peak, peak_src, "k_spmv_stream", nm, world)
+                ry = Runner(pkg, dx, ix, 1 - variant)
+                ty = timed_steps(pkg, ry, k, 5, world)
+                ex["other_variant"] = {"variant": "classic" if variant else "single-reduction",
+                                       "value": round(ty["steps"] / (ty["ms"] * 1e-3), 2),
+                                       "ms_per_step": round(ty["ms"] / ty["steps"], 5)}
                 extras[nm] = ex
                 dx.free()
             except Exception as e:

@@ -66,7 +66,7 @@ class Result(C.Structure):
     ]
 
 
-RUNNING, MAXITER, CONVERGED, BREAKDOWN, EXACT = 0, 1, 2, 3, 4
+RUNNING, MAXITER, CONVERGED, BREAKDOWN, EXACT, COMM_TIMEOUT = 0, 1, 2, 3, 4, 5
 CLASSIC, SINGLE_REDUCTION = 0, 1
 EAGER, RESIDENT = 0, 1
 
@@ -160,8 +160,11 @@ def lib():
     L.cgb200_system_nnz.restype = C.c_longlong
     L.cgb200_system_nnz.argtypes = [C.c_void_p]
     L.cgb200_plan_partition.argtypes = [C.c_int, C.c_int, C.c_longlong, C.POINTER(C.c_longlong), C.c_int, C.POINTER(C.c_longlong)]
+    L.cgb200_plan_push.argtypes = [C.c_int, C.c_int, C.c_longlong, C.POINTER(C.c_longlong), C.c_int, C.POINTER(C.c_longlong)]
     L.cgb200_dist_unique_id.argtypes = [C.c_void_p]
     L.cgb200_dist_init.argtypes = [C.c_int, C.c_int, C.c_void_p]
+    L.cgb200_dist_comm_mode.restype = C.c_char_p
+    L.cgb200_system_comm_is_p2p.argtypes = [C.c_void_p]
     _lib = L
     return L
 

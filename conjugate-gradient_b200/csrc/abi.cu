@@ -638,7 +638,7 @@ int cgb200_system_true_relres(cgb200_system* sys, double* relres) {
 }
 
 int cgb200_system_time_kernel(cgb200_system* sys, int which, int reps, double* ms) {
-  if (!sys || !ms || reps < 1 || which < 1 || which > 3) return -1;
+  if (!sys || !ms || reps < 1 || which < 1 || which > 5) return -1;
   return system_time_kernel((System*)sys, which, reps, ms);
 }
 
@@ -690,6 +690,31 @@ int cgb200_plan_partition(int world, int rank, long long n_global, const long lo
   return 0;
 }
 
+int cgb200_plan_push(int world, int rank, long long n_global, const long long* info4, int dense,
+                     long long* out) {
+  if (!info4 || !out || world < 1 || world > 8) return -1;
+  std::vector<PartInfo> parts(world);
+  for (int g = 0; g < world; ++g)
+    parts[g] = PartInfo{info4[4 * g], info4[4 * g + 1], info4[4 * g + 2], info4[4 * g + 3]};
+  PushPlan pp;
+  const char* err = nullptr;
+  if (plan_push(world, rank, n_global, parts.data(), dense, &pp, &err)) {
+    set_error(err ? err : "plan_push failed");
+    return -1;
+  }
+  out[0] = pp.npush;
+  for (int t = 0; t < 8; ++t) {
+    const bool on = t < pp.npush;
+    out[1 + 4 * t + 0] = on ? pp.push[t].peer : -1;
+    out[1 + 4 * t + 1] = on ? pp.push[t].begin : 0;
+    out[1 + 4 * t + 2] = on ? pp.push[t].end : 0;
+    out[1 + 4 * t + 3] = on ? pp.push[t].dst_index : 0;
+  }
+  out[33] = pp.nwait;
+  for (int i = 0; i < 8; ++i) out[34 + i] = i < pp.nwait ? pp.wait_src[i] : -1;
+  return 0;
+}
+
 int cgb200_dist_unique_id(void* id128) { return id128 ? dist_unique_id(id128) : -1; }
 int cgb200_dist_init(int rank, int world, const void* id128) {
   if (world > 1 && !id128) return -1;
@@ -698,5 +723,8 @@ int cgb200_dist_init(int rank, int world, const void* id128) {
 int cgb200_dist_finalize(void) { return dist_finalize(); }
 int cgb200_dist_rank(void) { return ctx().rank; }
 int cgb200_dist_world(void) { return ctx().world; }
+int cgb200_dist_barrier(void) { return dist_barrier(); }
+const char* cgb200_dist_comm_mode(void) { return comm_mode_name(); }
+int cgb200_system_comm_is_p2p(cgb200_system* sys) { return sys && ((System*)sys)->p2p ? 1 : 0; }
 
 }  // extern "C"

@@ -7,6 +7,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "comm.h"
+#include "kernels.h"
 #include "state.h"
 
 namespace cgb {
@@ -149,20 +151,29 @@ __device__ __forceinline__ double block_sum(double v, double* sm) {
   return t;
 }
 
-// Single-pass grid reduction: every block publishes one partial, takes a ticket, and the block
-// that draws the last ticket sums all partials in index order (fixed order for a fixed grid, so
-// results are run-to-run reproducible; no floating-point atomics).  Returns true in thread 0 of
-// that last block only, with the grand total in `total`; the ticket is reset for the next launch.
-template <int THREADS>
-__device__ __forceinline__ bool grid_sum(double v, double* __restrict__ partials,
-                                         unsigned int* __restrict__ ticket, double& total,
-                                         const double* __restrict__ extra = nullptr,
-                                         int n_extra = 0) {
+// Single-pass grid reduction of NV values at once: every block publishes one partial per value,
+// takes a ticket, and the block that draws the last ticket sums all partials in index order
+// (fixed order for a fixed grid, so results are run-to-run reproducible; no floating-point
+// atomics).  Returns a block-uniform "this is the last block"; the grand totals are left in v[]
+// of thread 0 of that block, and the ticket is reset for the next launch.  Value k's partials live
+// at partials + k * PART_STRIDE; `extra` (same layout) holds n_extra partials left by a preceding
+// launch of the same reduction (split matvec), folded in in the same fixed order.
+constexpr int PART_STRIDE = 8192;
+constexpr int MAX_GRID = 4096;
+
+template <int THREADS, int NV>
+__device__ __forceinline__ bool grid_reduce(double (&v)[NV], double* __restrict__ partials,
+                                            unsigned int* __restrict__ ticket,
+                                            const double* __restrict__ extra = nullptr,
+                                            int n_extra = 0) {
   __shared__ double sm[THREADS / 32];
   __shared__ int is_last;
-  double t = block_sum<THREADS>(v, sm);
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const double t = block_sum<THREADS>(v[k], sm);
+    if (threadIdx.x == 0) partials[k * PART_STRIDE + blockIdx.x] = t;
+  }
   if (threadIdx.x == 0) {
-    partials[blockIdx.x] = t;
     __threadfence();
     unsigned int tk = atomicAdd(ticket, 1u);
     is_last = (tk == gridDim.x - 1);
@@ -170,22 +181,183 @@ __device__ __forceinline__ bool grid_sum(double v, double* __restrict__ partials
   __syncthreads();
   if (!is_last) return false;
   __threadfence();
-  double acc = 0.0;
-  for (int i = threadIdx.x; i < (int)gridDim.x; i += THREADS) acc += __ldcg(partials + i);
-  // partials left by a preceding launch of the same reduction (split matvec), same fixed order
-  for (int i = threadIdx.x; i < n_extra; i += THREADS) acc += __ldcg(extra + i);
-  total = block_sum<THREADS>(acc, sm);
-  if (threadIdx.x == 0) {
-    *ticket = 0u;
-    return true;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += THREADS)
+      acc += __ldcg(partials + k * PART_STRIDE + i);
+    for (int i = threadIdx.x; i < n_extra; i += THREADS) acc += __ldcg(extra + k * PART_STRIDE + i);
+    v[k] = block_sum<THREADS>(acc, sm);
   }
-  return false;
+  if (threadIdx.x == 0) *ticket = 0u;
+  return true;
+}
+
+// One-value convenience form used by the standalone operators: true in thread 0 of the last block.
+template <int THREADS>
+__device__ __forceinline__ bool grid_sum(double v, double* __restrict__ partials,
+                                         unsigned int* __restrict__ ticket, double& total) {
+  double a[1] = {v};
+  const bool last = grid_reduce<THREADS, 1>(a, partials, ticket);
+  total = a[0];
+  return last && threadIdx.x == 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Peer-memory exchange (comm.h): system-scope accesses, the in-kernel cross-GPU sum, the
+// gather-vector push and the wait on its flags.
+// ---------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ double ld_relaxed_sys(const double* p) {
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_sys(double* p, double v) {
+  asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+// Gathered operand in a boundary tile: the halo was written by a peer while this kernel may
+// already have been running, so go to L2 (the coherence point for peer writes), never L1.
+__device__ __forceinline__ double ld_l2(const double* p) {
+  double v;
+  asm volatile("ld.relaxed.gpu.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+constexpr unsigned long long PEER_TIMEOUT_NS = 4000000000ull;  // a hung peer must not hang this GPU
+
+// Spins until *flag satisfies (exact ? == want : >= want).  false on time-out.
+__device__ __forceinline__ bool spin_until(const unsigned long long* flag, unsigned long long want,
+                                           bool exact) {
+  unsigned long long t0 = 0;
+  for (unsigned int it = 0;; ++it) {
+    const unsigned long long f = ld_acquire_sys(flag);
+    if (exact ? f == want : f >= want) return true;
+    if ((it & 255u) == 255u) {
+      const unsigned long long now = global_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > PEER_TIMEOUT_NS) return false;
+    }
+  }
+}
+
+__device__ __forceinline__ void comm_failed(CgState* S) {
+  S->done = 1;
+  S->status = CGB200_ST_COMM;
+}
+
+// Sum of (t0, t1) over all ranks, formed inside the calling kernel.  Called by every thread of
+// ONE block per GPU (the last block of a fused reduction) with the local totals valid in thread
+// 0; thread g < world stores this rank's pair into rank g's mailbox and then collects rank g's
+// pair from the local mailbox; thread 0 adds the G pairs in rank order, so every rank obtains the
+// same bits and takes the same branches.  Slots are indexed by the reduction number modulo 4: a
+// peer can be at most one reduction ahead (it needs this rank's next contribution to go further).
+template <int THREADS>
+__device__ __forceinline__ bool peer_allreduce(const PeerComm& cm, CgState* S, double& t0,
+                                               double& t1) {
+  static_assert(THREADS >= MAX_RANKS, "block too small");
+  __shared__ double sh[2 * MAX_RANKS + 2];
+  __shared__ unsigned long long sh_epoch;
+  __shared__ int sh_fail;
+  if (threadIdx.x == 0) {
+    const unsigned long long e = cm.local->red_epoch + 1;
+    cm.local->red_epoch = e;
+    sh_epoch = e;
+    sh[2 * MAX_RANKS] = t0;
+    sh[2 * MAX_RANKS + 1] = t1;
+    sh_fail = 0;
+  }
+  __syncthreads();
+  const unsigned long long e = sh_epoch;
+  const int slot = (int)(e & 3ull);
+  if ((int)threadIdx.x < cm.world) {
+    const int g = threadIdx.x;
+    RedSlot* dst = &cm.mbox[g]->red[slot][cm.rank];
+    st_relaxed_sys(&dst->v[0], sh[2 * MAX_RANKS]);
+    st_relaxed_sys(&dst->v[1], sh[2 * MAX_RANKS + 1]);
+    st_release_sys(&dst->epoch, e);  // orders the two value stores before the flag
+    const RedSlot* src = &cm.mbox[cm.rank]->red[slot][g];
+    if (spin_until(&src->epoch, e, true)) {
+      sh[2 * g] = ld_relaxed_sys(&src->v[0]);
+      sh[2 * g + 1] = ld_relaxed_sys(&src->v[1]);
+    } else {
+      sh_fail = 1;
+    }
+  }
+  __syncthreads();
+  const bool ok = sh_fail == 0;
+  if (threadIdx.x == 0) {
+    if (ok) {
+      double a = 0.0, b = 0.0;
+      for (int g = 0; g < cm.world; ++g) {
+        a += sh[2 * g];
+        b += sh[2 * g + 1];
+      }
+      t0 = a;
+      t1 = b;
+    } else {
+      comm_failed(S);
+    }
+  }
+  return ok;
+}
+
+// Element j of the owned block of the gather vector has just been computed: store it into the
+// halo slots of every peer that gathers it.
+__device__ __forceinline__ void push_elem(const PeerComm& cm, long long j, double v) {
+  for (int t = 0; t < cm.npush; ++t)
+    if (j >= cm.push[t].begin && j < cm.push[t].end) cm.push[t].dst[j - cm.push[t].begin] = v;
+}
+
+// Called by every thread of every CTA of a kernel that used push_elem(), after its last store:
+// the CTA that draws the last ticket knows all remote stores of the grid have been fenced and
+// raises this rank's flag in each target's mailbox.
+__device__ __forceinline__ void push_finish(const PeerComm& cm) {
+  if (cm.npush <= 0) return;
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(&cm.local->push_ticket, 1u);
+    if (tk == gridDim.x - 1) {
+      cm.local->push_ticket = 0u;
+      __threadfence_system();
+      const unsigned long long e = cm.local->push_epoch + 1;
+      cm.local->push_epoch = e;
+      for (int t = 0; t < cm.npush; ++t)
+        st_release_sys(&cm.mbox[cm.push[t].peer]->halo_flag[cm.rank], e);
+    }
+  }
+}
+
+// One thread: wait until every source this rank gathers from has completed as many pushes as
+// this rank has (the ranks push in lockstep, once before every matvec).
+__device__ __forceinline__ void wait_halo(const PeerComm& cm, CgState* S) {
+  if (cm.nwait <= 0) return;
+  const unsigned long long e = *(volatile unsigned long long*)&cm.local->push_epoch;
+  for (int i = 0; i < cm.nwait; ++i)
+    if (!spin_until(&cm.mbox[cm.rank]->halo_flag[cm.wait_src[i]], e, false)) {
+      comm_failed(S);
+      return;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
 // Scalar bookkeeping of the loop (reference cg.c:113,125-134), run by exactly one thread per
-// iteration: either the last block of the fused kernel (one GPU) or a one-thread kernel after the
-// cross-GPU sum.
+// iteration: the last block of the fused kernel (after the in-kernel cross-GPU sum when several
+// GPUs take part), or a one-thread kernel after an NCCL sum.
 // ---------------------------------------------------------------------------------------------
 
 // After p.s is known (reference cg.c:113).  Breakdown policy: the reference divides regardless
@@ -230,10 +402,80 @@ __device__ __forceinline__ void finish_init(CgState* S, double bb) {
   S->ps = 0.0;
   S->done = 0;
   S->status = CGB200_ST_RUNNING;
+  S->sr_first = 1;
   if (bb == 0.0) {  // b = 0: x = 0 is the solution; the reference would return NaN
     S->done = 1;
     S->status = CGB200_ST_EXACT;
   }
+}
+
+// Single-reduction variant (Chronopoulos-Gear): after w = A r, with rw = r.w and rr = r.r from the
+// same fused reduction.  The first call (loop entry, r = b) only forms alpha_0 = rr / rw; later
+// calls close the x update that preceded them: stop tests as in finish_rr, then
+//   beta = rr / rr_old,   alpha = rr / (rw - beta * rr / alpha_old).
+__device__ __forceinline__ void finish_sr(CgState* S, double rw, double rr) {
+  S->ps = rw;
+  if (S->sr_first) {
+    S->sr_first = 0;
+    if (rr == 0.0) {
+      S->done = 1;
+      S->status = CGB200_ST_EXACT;
+    } else if (!(rw > 0.0) || isinf(rw)) {
+      S->done = 1;
+      S->status = CGB200_ST_BREAKDOWN;
+    } else {
+      S->alpha = rr / rw;
+      S->beta = 0.0;
+    }
+    S->rr = rr;
+    return;
+  }
+  const int k = S->iter;
+  S->iter = k + 1;
+  if (S->thresh > 0.0 && rr <= S->thresh) {
+    S->done = 1;
+    S->status = CGB200_ST_CONVERGED;
+  } else if (k >= S->max_iter) {
+    S->done = 1;
+    S->status = CGB200_ST_MAXITER;
+  } else if (rr == 0.0) {
+    S->done = 1;
+    S->status = CGB200_ST_EXACT;
+  } else {
+    const double beta = rr / S->rr;
+    const double denom = rw - beta * rr / S->alpha;
+    if (!(denom > 0.0) || isinf(denom)) {
+      S->done = 1;
+      S->status = CGB200_ST_BREAKDOWN;
+    } else {
+      S->beta = beta;
+      S->alpha = rr / denom;
+    }
+  }
+  S->rr = rr;
+}
+
+__device__ __forceinline__ void apply_finish(CgState* S, int fin, double t0, double t1) {
+  if (fin == FIN_INIT) finish_init(S, t0);
+  else if (fin == FIN_PS) finish_ps(S, t0);
+  else if (fin == FIN_RR) finish_rr(S, t0);
+  else if (fin == FIN_SR) finish_sr(S, t0, t1);
+}
+
+// Block-wide epilogue of a fused reduction, run by the last block only (totals in thread 0).
+template <int THREADS>
+__device__ __forceinline__ void finish_block(CgState* S, const PeerComm& cm, int fin, double t0,
+                                             double t1) {
+  if (fin == FIN_LOCAL) {  // NCCL mode / kernel timing: leave the local sums for the caller
+    if (threadIdx.x == 0) {
+      S->local[0] = t0;
+      S->local[1] = t1;
+    }
+    return;
+  }
+  bool ok = true;
+  if (cm.world > 1) ok = peer_allreduce<THREADS>(cm, S, t0, t1);
+  if (ok && threadIdx.x == 0) apply_finish(S, fin, t0, t1);
 }
 
 }  // namespace cgb

@@ -19,6 +19,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <algorithm>
+
 #include "device_utils.cuh"
 
 namespace cgb {
@@ -56,27 +58,56 @@ struct SpmvSmem {
   static constexpr size_t total = vals_bytes + cols_bytes + rp_bytes + bar_bytes + 16;
 };
 
-struct TileRange {
-  int begin0, end0;  // first range of tiles  [begin0, end0)
-  int begin1, end1;  // optional second range [begin1, end1)
-};
-
+// Up to three runs of tiles, visited in this order.  With several GPUs run 0 holds the interior
+// tiles (columns inside the owned block) and runs 1-2 the boundary tiles that gather halo values.
 __device__ __forceinline__ int vtile_to_tile(const TileRange& tr, int v) {
-  const int n0 = tr.end0 - tr.begin0;
-  return v < n0 ? tr.begin0 + v : tr.begin1 + (v - n0);
+  const int n0 = tr.e[0] - tr.b[0];
+  if (v < n0) return tr.b[0] + v;
+  v -= n0;
+  const int n1 = tr.e[1] - tr.b[1];
+  return v < n1 ? tr.b[1] + v : tr.b[2] + (v - n1);
+}
+
+// One row's share of a staged chunk: entries [k, k1) of the stage, ascending column order.
+// COHERENT = the gathered values may have been written by a peer GPU during this kernel.
+template <bool COHERENT>
+__device__ __forceinline__ double walk_row(const double* __restrict__ v_s,
+                                           const int* __restrict__ c_s, int k, const int k1,
+                                           const double* __restrict__ pg, const uint64_t pol,
+                                           double acc) {
+  while (k < k1) {
+    double v[8], pv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const bool ok = (k + j) < k1;
+      v[j] = 0.0;
+      pv[j] = 0.0;
+      if (ok) {
+        v[j] = v_s[k + j];
+        pv[j] = COHERENT ? ld_l2(pg + c_s[k + j]) : ld_keep(pg + c_s[k + j], pol);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if ((k + j) < k1) acc = __dadd_rn(acc, __dmul_rn(v[j], pv[j]));
+    k += 8;
+  }
+  return acc;
 }
 
 template <int R, int CAP, int STAGES>
 __global__ void __launch_bounds__(R + 32)
 k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
               const int* __restrict__ rowptr, int nrows, const double* __restrict__ pg,
-              const double* __restrict__ pown, double* __restrict__ s, TileRange tr,
-              double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
-              int mode, int hint) {
+              const double* __restrict__ pown, double* __restrict__ s, const TileRange tr,
+              const int wait_from, double* __restrict__ partials,
+              unsigned int* __restrict__ ticket, CgState* S, const int mode, const int hint,
+              const __grid_constant__ PeerComm cm) {
   using SM = SpmvSmem<R, CAP, STAGES>;
   constexpr int THREADS = R + 32;
   constexpr int CWARPS = R / 32;
-  if (mode != SPMV_PLAIN && S->done) return;
+  const int fin = mode & MV_FIN_MASK;
+  if (fin != FIN_NONE && S->done) return;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double* sm_vals = reinterpret_cast<double*>(smem_raw);
@@ -87,7 +118,7 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
   uint64_t* empty = full + STAGES;
 
   const int tid = threadIdx.x;
-  const int nvt = (tr.end0 - tr.begin0) + (tr.end1 - tr.begin1);  // virtual tiles in this launch
+  const int nvt = (tr.e[0] - tr.b[0]) + (tr.e[1] - tr.b[1]) + (tr.e[2] - tr.b[2]);
 
   if (tid == 0) {
     for (int i = 0; i < STAGES; ++i) {
@@ -98,13 +129,14 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
   }
   __syncthreads();
 
-  double dot = 0.0;
+  double dot = 0.0, dot2 = 0.0;
 
   if (tid >= R) {
     // ------------------------------ producer warp ------------------------------
     if (tid == R) {
       const uint64_t pol_stream = policy_evict_first();
       int item = 0;
+      bool waited = false;
       // bounds of the next tile are fetched one tile ahead so their latency is never exposed
       int vt = blockIdx.x;
       int nlo = 0, nhi = 0;
@@ -115,6 +147,12 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
       }
 #pragma unroll 1
       for (; vt < nvt; vt += gridDim.x) {
+        if (vt >= wait_from && !waited) {
+          // first boundary tile of this CTA: the peers' rows of the gather vector must have
+          // landed.  The consumers are ordered behind this through the stage's full barrier.
+          wait_halo(cm, S);
+          waited = true;
+        }
         const int t = vtile_to_tile(tr, vt);
         const int lo = nlo & ~3, hi = (nhi + 3) & ~3;
         const int vt2 = vt + gridDim.x;
@@ -154,6 +192,7 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
       const int t = vtile_to_tile(tr, vt);
       const int row = t * R + tid;
       const int rows_valid = min(R, nrows - t * R);
+      const bool boundary = vt >= wait_from;
       int rs = 0, re = 0, lo = 0, nchunks = 1;
       double acc = 0.0;
 #pragma unroll 1
@@ -173,51 +212,52 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
           }
         }
         const int c0 = lo + chunk * CAP;
-        int k = max(rs - c0, 0);
+        const int k = max(rs - c0, 0);
         const int k1 = min(re - c0, CAP);
-        while (k < k1) {
-          double v[8], pv[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const bool ok = (k + j) < k1;
-            v[j] = 0.0;
-            pv[j] = 0.0;
-            if (ok) {
-              v[j] = v_s[k + j];
-              pv[j] = ld_keep(pg + c_s[k + j], pol_keep);
-            }
-          }
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if ((k + j) < k1) acc = __dadd_rn(acc, __dmul_rn(v[j], pv[j]));
-          k += 8;
-        }
+        if (boundary)
+          acc = walk_row<true>(v_s, c_s, k, k1, pg, pol_keep, acc);
+        else
+          acc = walk_row<false>(v_s, c_s, k, k1, pg, pol_keep, acc);
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[stage]);  // this warp is done with the stage
       }
       if (tid < rows_valid) {
         s[row] = acc;
-        if (mode != SPMV_PLAIN) dot += pown[row] * acc;
+        if (fin != FIN_NONE) {
+          const double g = pown[row];
+          dot += g * acc;
+          if (mode & MV_DUAL) dot2 += g * g;
+        }
       }
     }
   }
 
-  if (mode == SPMV_PLAIN) return;
-  if (mode == SPMV_PARTIAL_ONLY) {
-    // first half of a split launch (interior rows): leave the partial for the finishing launch
+  if (fin == FIN_NONE) return;
+  const int nv = (mode & MV_DUAL) ? 2 : 1;
+  if (mode & MV_PARTIAL) {
+    // first half of a split launch (interior rows): leave the partials for the finishing launch
+    // (the caller passes partials + MV_EXTRA_OFFSET)
     __shared__ double smp[THREADS / 32];
     const double t = block_sum<THREADS>(dot, smp);
-    if (tid == 0) partials[blockIdx.x] = t;  // caller passes partials + SPMV_EXTRA_OFFSET
+    if (tid == 0) partials[blockIdx.x] = t;
+    if (nv == 2) {
+      const double t2 = block_sum<THREADS>(dot2, smp);
+      if (tid == 0) partials[PART_STRIDE + blockIdx.x] = t2;
+    }
     return;
   }
-  // `partials` may carry extra slots written by a preceding PARTIAL_ONLY launch
-  double total;
-  if (grid_sum<THREADS>(dot, partials, ticket, total, partials + SPMV_EXTRA_OFFSET, mode >> 8)) {
-    if ((mode & 0xff) == SPMV_FINISH_LOCAL)
-      S->local = total;
-    else
-      finish_ps(S, total);
+  // `partials` may carry extra slots written by a preceding MV_PARTIAL launch
+  double v[2] = {dot, dot2};
+  bool last;
+  if (nv == 2) {
+    last = grid_reduce<THREADS, 2>(v, partials, ticket, partials + MV_EXTRA_OFFSET, mode >> 8);
+  } else {
+    double v1[1] = {dot};
+    last = grid_reduce<THREADS, 1>(v1, partials, ticket, partials + MV_EXTRA_OFFSET, mode >> 8);
+    v[0] = v1[0];
+    v[1] = 0.0;
   }
+  if (last) finish_block<THREADS>(S, cm, fin, v[0], v[1]);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -235,13 +275,19 @@ __global__ void __launch_bounds__(THREADS)
 k_gemv_rows(const double* __restrict__ A, long long ld, int nrows, int ncols,
             const double* __restrict__ pg, const double* __restrict__ pown,
             double* __restrict__ s, double* __restrict__ partials,
-            unsigned int* __restrict__ ticket, CgState* S, int mode) {
-  if (mode != SPMV_PLAIN && S->done) return;
+            unsigned int* __restrict__ ticket, CgState* S, const int mode, const int wait,
+            const __grid_constant__ PeerComm cm) {
+  const int fin = mode & MV_FIN_MASK;
+  if (fin != FIN_NONE && S->done) return;
   __shared__ double sm_red[RB][THREADS / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (wait) {  // the peers' slices of the gather vector must have landed (all-gather mode)
+    if (tid == 0) wait_halo(cm, S);
+    __syncthreads();
+  }
   const uint64_t pol_stream = policy_evict_first();
   const int ngroups = (nrows + RB - 1) / RB;
-  double dot = 0.0;
+  double dot = 0.0, dot2 = 0.0;
 
 #pragma unroll 1
   for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
@@ -303,18 +349,26 @@ k_gemv_rows(const double* __restrict__ A, long long ld, int nrows, int ncols,
 #pragma unroll
       for (int w = 0; w < THREADS / 32; ++w) t += sm_red[tid][w];
       s[row0 + tid] = t;
-      if (mode != SPMV_PLAIN) dot += pown[row0 + tid] * t;
+      if (fin != FIN_NONE) {
+        const double g = pown[row0 + tid];
+        dot += g * t;
+        if (mode & MV_DUAL) dot2 += g * g;
+      }
     }
   }
 
-  if (mode == SPMV_PLAIN) return;
-  double total;
-  if (grid_sum<THREADS>(dot, partials, ticket, total)) {
-    if ((mode & 0xff) == SPMV_FINISH_LOCAL)
-      S->local = total;
-    else
-      finish_ps(S, total);
+  if (fin == FIN_NONE) return;
+  double v[2] = {dot, dot2};
+  bool last;
+  if (mode & MV_DUAL) {
+    last = grid_reduce<THREADS, 2>(v, partials, ticket);
+  } else {
+    double v1[1] = {dot};
+    last = grid_reduce<THREADS, 1>(v1, partials, ticket);
+    v[0] = v1[0];
+    v[1] = 0.0;
   }
+  if (last) finish_block<THREADS>(S, cm, fin, v[0], v[1]);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -342,7 +396,8 @@ __device__ __forceinline__ void st2(double* p, double2 v) { *reinterpret_cast<do
 __global__ void __launch_bounds__(VT)
 k_update_xr(double* __restrict__ x, double* __restrict__ r, const double* __restrict__ p,
             const double* __restrict__ s, long long n, double* __restrict__ partials,
-            unsigned int* __restrict__ ticket, CgState* S, int finish_local) {
+            unsigned int* __restrict__ ticket, CgState* S, const int fin,
+            const __grid_constant__ PeerComm cm) {
   if (S->done) return;
   const double alpha = S->alpha;
   const long long n2 = vec_pairs(n, x, r, p, s);
@@ -382,20 +437,18 @@ k_update_xr(double* __restrict__ x, double* __restrict__ r, const double* __rest
     r[j] = rn;
     acc = fma(rn, rn, acc);
   }
-  double total;
-  if (grid_sum<VT>(acc, partials, ticket, total)) {
-    if (finish_local)
-      S->local = total;
-    else
-      finish_rr(S, total);
-  }
+  double v[1] = {acc};
+  if (grid_reduce<VT, 1>(v, partials, ticket)) finish_block<VT>(S, cm, fin, v[0], 0.0);
 }
 
-// K3: p = r + beta p                                                            (cg.c:131-132)
+// K3: p = r + beta p, and the rows of p a peer GPU gathers go straight into its halo slots
+// (cg.c:131-132)
 __global__ void __launch_bounds__(VT)
-k_update_p(double* __restrict__ p, const double* __restrict__ r, long long n, const CgState* S) {
+k_update_p(double* __restrict__ p, const double* __restrict__ r, long long n, const CgState* S,
+           const __grid_constant__ PeerComm cm) {
   if (S->done) return;
   const double beta = S->beta;
+  const bool pushing = cm.npush > 0;
   const long long n2 = vec_pairs(n, p, r, nullptr, nullptr);
   const long long stride = (long long)gridDim.x * VT;
   for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * VU) {
@@ -415,47 +468,128 @@ k_update_p(double* __restrict__ p, const double* __restrict__ r, long long n, co
         pv[u].x = __dadd_rn(rv[u].x, __dmul_rn(beta, pv[u].x));
         pv[u].y = __dadd_rn(rv[u].y, __dmul_rn(beta, pv[u].y));
         st2(p + 2 * j, pv[u]);
+        if (pushing) {
+          push_elem(cm, 2 * j, pv[u].x);
+          push_elem(cm, 2 * j + 1, pv[u].y);
+        }
       }
     }
   }
-  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride)
-    p[j] = __dadd_rn(r[j], __dmul_rn(beta, p[j]));
+  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride) {
+    const double pn = __dadd_rn(r[j], __dmul_rn(beta, p[j]));
+    p[j] = pn;
+    if (pushing) push_elem(cm, j, pn);
+  }
+  push_finish(cm);
 }
 
-// Loop entry: x = 0, r = b, p = b, partial b.b                                  (cg.c:104-108)
+// Single-reduction variant, the whole vector update in one pass (g = residual, held in the gather
+// vector; d = search direction; s = A d; w = A g):
+//   d = g + beta d ; s = w + beta s ; x += alpha d ; g -= alpha s ; push the new g to the peers
+__global__ void __launch_bounds__(VT)
+k_update_sr(double* __restrict__ x, double* __restrict__ g, double* __restrict__ d,
+            double* __restrict__ s, const double* __restrict__ w, long long n, const CgState* S,
+            const __grid_constant__ PeerComm cm) {
+  if (S->done) return;
+  const double alpha = S->alpha, beta = S->beta;
+  const bool pushing = cm.npush > 0;
+  const uintptr_t al = (uintptr_t)x | (uintptr_t)g | (uintptr_t)d | (uintptr_t)s | (uintptr_t)w;
+  const long long n2 = (al & 15) ? 0 : (n >> 1);
+  const long long stride = (long long)gridDim.x * VT;
+  constexpr int U = 2;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * U) {
+    double2 xv[U], gv[U], dv[U], sv[U], wv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        gv[u] = ld2(g + 2 * j);
+        dv[u] = ld2(d + 2 * j);
+        wv[u] = ld2(w + 2 * j);
+        sv[u] = ld2(s + 2 * j);
+        xv[u] = ld2(x + 2 * j);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        dv[u].x = __dadd_rn(gv[u].x, __dmul_rn(beta, dv[u].x));
+        dv[u].y = __dadd_rn(gv[u].y, __dmul_rn(beta, dv[u].y));
+        sv[u].x = __dadd_rn(wv[u].x, __dmul_rn(beta, sv[u].x));
+        sv[u].y = __dadd_rn(wv[u].y, __dmul_rn(beta, sv[u].y));
+        xv[u].x = __dadd_rn(xv[u].x, __dmul_rn(alpha, dv[u].x));
+        xv[u].y = __dadd_rn(xv[u].y, __dmul_rn(alpha, dv[u].y));
+        gv[u].x = __dsub_rn(gv[u].x, __dmul_rn(alpha, sv[u].x));
+        gv[u].y = __dsub_rn(gv[u].y, __dmul_rn(alpha, sv[u].y));
+        st2(d + 2 * j, dv[u]);
+        st2(s + 2 * j, sv[u]);
+        st2(x + 2 * j, xv[u]);
+        st2(g + 2 * j, gv[u]);
+        if (pushing) {
+          push_elem(cm, 2 * j, gv[u].x);
+          push_elem(cm, 2 * j + 1, gv[u].y);
+        }
+      }
+    }
+  }
+  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride) {
+    const double dn = __dadd_rn(g[j], __dmul_rn(beta, d[j]));
+    const double sn = __dadd_rn(w[j], __dmul_rn(beta, s[j]));
+    const double xn = __dadd_rn(x[j], __dmul_rn(alpha, dn));
+    const double gn = __dsub_rn(g[j], __dmul_rn(alpha, sn));
+    d[j] = dn;
+    s[j] = sn;
+    x[j] = xn;
+    g[j] = gn;
+    if (pushing) push_elem(cm, j, gn);
+  }
+  push_finish(cm);
+}
+
+// Loop entry: x = 0, r = b, p = b, partial b.b (cg.c:104-108); p is pushed to the peers.
+// Single-reduction variant (sr): the gather vector p holds the residual b, the direction buffer r
+// and s start at zero (the first update then forms d = g, s = w with beta = 0).
 __global__ void __launch_bounds__(VT)
 k_init(double* __restrict__ x, double* __restrict__ r, double* __restrict__ p,
-       const double* __restrict__ b, long long n, double* __restrict__ partials,
-       unsigned int* __restrict__ ticket, CgState* S, int finish_local) {
+       double* __restrict__ s, const double* __restrict__ b, long long n, const int sr,
+       double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S, const int fin,
+       const __grid_constant__ PeerComm cm) {
   const long long stride = (long long)gridDim.x * VT;
+  const bool pushing = cm.npush > 0;
   double acc = 0.0;
   for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n; i += stride) {
     const double v = b[i];
     x[i] = 0.0;
-    r[i] = v;
+    r[i] = sr ? 0.0 : v;
+    if (sr) s[i] = 0.0;
     p[i] = v;
+    if (pushing) push_elem(cm, i, v);
     acc = fma(v, v, acc);
   }
-  double total;
-  if (grid_sum<VT>(acc, partials, ticket, total)) {
-    if (finish_local)
-      S->local = total;
-    else
-      finish_init(S, total);
-  }
+  push_finish(cm);
+  double v[1] = {acc};
+  if (grid_reduce<VT, 1>(v, partials, ticket)) finish_block<VT>(S, cm, fin, v[0], 0.0);
 }
 
-// One-thread bookkeeping kernels used after a cross-GPU sum of S->local.
-__global__ void k_finish(CgState* S, int which) {
-  if (which == FIN_INIT) {
-    finish_init(S, S->local);
-  } else if (S->done) {
-    return;
-  } else if (which == FIN_PS) {
-    finish_ps(S, S->local);
-  } else {
-    finish_rr(S, S->local);
+// Stand-alone push of the owned block's boundary rows (operator-API matvecs, residual checks):
+// the loop itself never launches this, its vector kernels push as they write.
+__global__ void __launch_bounds__(VT)
+k_push(const double* __restrict__ p, const __grid_constant__ PeerComm cm) {
+  const long long stride = (long long)gridDim.x * VT;
+  for (int t = 0; t < cm.npush; ++t) {
+    const long long b0 = cm.push[t].begin, cnt = cm.push[t].end - b0;
+    double* dst = cm.push[t].dst;
+    for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < cnt; i += stride)
+      dst[i] = p[b0 + i];
   }
+  push_finish(cm);
+}
+
+// One-thread bookkeeping kernel used after an NCCL sum of S->local (NCCL mode only).
+__global__ void k_finish(CgState* S, int which) {
+  if (which != FIN_INIT && S->done) return;
+  apply_finish(S, which, S->local[0], S->local[1]);
 }
 
 // Standalone operators of mv_ops.h ------------------------------------------------------------
@@ -679,7 +813,7 @@ static inline int vec_grid(long long n) {
   return (int)(g < 1 ? 1 : g);
 }
 
-int max_partials() { return 8192; }
+int max_partials() { return PART_STRIDE; }
 
 // SpMV tile configurations.  One is chosen per process (CGB200_SPMV_CFG, default 0); DESIGN.md
 // records the sweep that picked the default.
@@ -688,16 +822,18 @@ struct SpmvCfg {
   size_t smem;
   const void* fn;
   void (*launch)(int grid, cudaStream_t st, const CsrDev& A, const double* pg, const double* pown,
-                 double* s, TileRange tr, double* partials, unsigned int* ticket, CgState* S,
-                 int mode, int hint);
+                 double* s, const TileRange& tr, int wait_from, double* partials,
+                 unsigned int* ticket, CgState* S, int mode, int hint, const PeerComm& cm);
 };
 
 template <int R, int CAP, int STAGES>
 static void spmv_launch_t(int grid, cudaStream_t st, const CsrDev& A, const double* pg,
-                          const double* pown, double* s, TileRange tr, double* partials,
-                          unsigned int* ticket, CgState* S, int mode, int hint) {
+                          const double* pown, double* s, const TileRange& tr, int wait_from,
+                          double* partials, unsigned int* ticket, CgState* S, int mode, int hint,
+                          const PeerComm& cm) {
   k_spmv_stream<R, CAP, STAGES><<<grid, R + 32, SpmvSmem<R, CAP, STAGES>::total, st>>>(
-      A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s, tr, partials, ticket, S, mode, hint);
+      A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s, tr, wait_from, partials, ticket, S, mode,
+      hint, cm);
 }
 
 #define SPMV_CFG(R, CAP, ST)                                                        \
@@ -748,18 +884,19 @@ int spmv_rows_per_tile() { return spmv_cfg().R; }
 int spmv_grid_for(int ntiles) {
   spmv_cfg();
   int grid = sm_count() * g_spmv_bps;
+  if (grid > MAX_GRID) grid = MAX_GRID;
   return grid > ntiles ? ntiles : grid;
 }
 
 cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, double* s,
-                        int tile_begin0, int tile_end0, int tile_begin1, int tile_end1,
-                        double* partials, unsigned int* ticket, CgState* S, int mode,
+                        const TileRange& tr, int wait_from, double* partials,
+                        unsigned int* ticket, CgState* S, int mode, const PeerComm& cm,
                         cudaStream_t st) {
-  TileRange tr{tile_begin0, tile_end0, tile_begin1, tile_end1};
-  const int nvt = (tile_end0 - tile_begin0) + (tile_end1 - tile_begin1);
+  const int nvt = (tr.e[0] - tr.b[0]) + (tr.e[1] - tr.b[1]) + (tr.e[2] - tr.b[2]);
   if (nvt <= 0) return cudaSuccess;
   const SpmvCfg& c = spmv_cfg();
-  c.launch(spmv_grid_for(nvt), st, A, pg, pown, s, tr, partials, ticket, S, mode, g_spmv_hint);
+  c.launch(spmv_grid_for(nvt), st, A, pg, pown, s, tr, wait_from, partials, ticket, S, mode,
+           g_spmv_hint, cm);
   ++g_launches;
   return cudaGetLastError();
 }
@@ -771,7 +908,7 @@ template <int VEC>
 static cudaError_t launch_gemv_vec(const double* A, long long ld, int nrows, int ncols,
                                    const double* pg, const double* pown, double* s,
                                    double* partials, unsigned int* ticket, CgState* S, int mode,
-                                   cudaStream_t st) {
+                                   int wait, const PeerComm& cm, cudaStream_t st) {
   static int bps = 0;
   if (!bps) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_gemv_rows<GV_T, GV_RB, VEC>, GV_T, 0);
@@ -780,44 +917,64 @@ static cudaError_t launch_gemv_vec(const double* A, long long ld, int nrows, int
   const int ngroups = (nrows + GV_RB - 1) / GV_RB;
   int grid = sm_count() * bps;
   if (grid > ngroups) grid = ngroups;
-  if (grid > max_partials()) grid = max_partials();
+  if (grid > MAX_GRID) grid = MAX_GRID;
   k_gemv_rows<GV_T, GV_RB, VEC><<<grid, GV_T, 0, st>>>(A, ld, nrows, ncols, pg, pown, s, partials,
-                                                      ticket, S, mode);
+                                                      ticket, S, mode, wait, cm);
   ++g_launches;
   return cudaGetLastError();
 }
 
 cudaError_t launch_gemv(const double* A, long long ld, int nrows, int ncols, const double* pg,
                         const double* pown, double* s, double* partials, unsigned int* ticket,
-                        CgState* S, int mode, cudaStream_t st) {
+                        CgState* S, int mode, int wait, const PeerComm& cm, cudaStream_t st) {
   const bool al32 = ((uintptr_t)A % 32 == 0) && ((uintptr_t)pg % 32 == 0);
   const bool al16 = ((uintptr_t)A % 16 == 0) && ((uintptr_t)pg % 16 == 0);
   if (ld % 4 == 0 && ncols % 4 == 0 && al32)
-    return launch_gemv_vec<4>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, st);
+    return launch_gemv_vec<4>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, wait,
+                              cm, st);
   if (ld % 2 == 0 && ncols % 2 == 0 && al16)
-    return launch_gemv_vec<2>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, st);
-  return launch_gemv_vec<1>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, st);
+    return launch_gemv_vec<2>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, wait,
+                              cm, st);
+  return launch_gemv_vec<1>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, wait, cm,
+                            st);
 }
 
 cudaError_t launch_update_xr(double* x, double* r, const double* p, const double* s, long long n,
-                             double* partials, unsigned int* ticket, CgState* S, int finish_local,
-                             cudaStream_t st) {
-  k_update_xr<<<vec_grid(n), VT, 0, st>>>(x, r, p, s, n, partials, ticket, S, finish_local);
+                             double* partials, unsigned int* ticket, CgState* S, int fin,
+                             const PeerComm& cm, cudaStream_t st) {
+  k_update_xr<<<vec_grid(n), VT, 0, st>>>(x, r, p, s, n, partials, ticket, S, fin, cm);
   ++g_launches;
   return cudaGetLastError();
 }
 
 cudaError_t launch_update_p(double* p, const double* r, long long n, const CgState* S,
-                            cudaStream_t st) {
-  k_update_p<<<vec_grid(n), VT, 0, st>>>(p, r, n, S);
+                            const PeerComm& cm, cudaStream_t st) {
+  k_update_p<<<vec_grid(n), VT, 0, st>>>(p, r, n, S, cm);
   ++g_launches;
   return cudaGetLastError();
 }
 
-cudaError_t launch_init(double* x, double* r, double* p, const double* b, long long n,
-                        double* partials, unsigned int* ticket, CgState* S, int finish_local,
-                        cudaStream_t st) {
-  k_init<<<vec_grid(n), VT, 0, st>>>(x, r, p, b, n, partials, ticket, S, finish_local);
+cudaError_t launch_update_sr(double* x, double* g, double* d, double* s, const double* w,
+                             long long n, const CgState* S, const PeerComm& cm, cudaStream_t st) {
+  k_update_sr<<<vec_grid(n), VT, 0, st>>>(x, g, d, s, w, n, S, cm);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_init(double* x, double* r, double* p, double* s, const double* b, long long n,
+                        int sr, double* partials, unsigned int* ticket, CgState* S, int fin,
+                        const PeerComm& cm, cudaStream_t st) {
+  k_init<<<vec_grid(n), VT, 0, st>>>(x, r, p, s, b, n, sr, partials, ticket, S, fin, cm);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_push(const double* p, const PeerComm& cm, cudaStream_t st) {
+  if (cm.npush <= 0) return cudaSuccess;
+  long long most = 1;
+  for (int t = 0; t < cm.npush; ++t)
+    most = std::max(most, cm.push[t].end - cm.push[t].begin);
+  k_push<<<vec_grid(2 * most), VT, 0, st>>>(p, cm);
   ++g_launches;
   return cudaGetLastError();
 }

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "comm.h"
 #include "state.h"
 
 namespace cgb {
@@ -18,18 +19,26 @@ struct CsrDev {
   long long nnz = 0;
 };
 
-// `mode` of the matvec kernels
-enum : int {
-  SPMV_PLAIN = 0,         // s = A p only (mv_mult of the operator API)
-  SPMV_FINISH = 1,        // + p.s, grid-reduced, finish_ps() on this GPU
-  SPMV_FINISH_LOCAL = 2,  // + p.s, grid-reduced into S->local (a cross-GPU sum follows)
-  SPMV_PARTIAL_ONLY = 3,  // + p.s, per-CTA partials only (first half of a split launch)
-};
-// a finishing launch adds `extra` partials left at partials[SPMV_EXTRA_OFFSET ..] by a preceding
-// SPMV_PARTIAL_ONLY launch: mode = base | (extra << 8)
-constexpr int SPMV_EXTRA_OFFSET = 4096;
+// `mode` of the matvec kernels: a finish kind (what the last CTA does with the fused dot
+// products) in the low bits plus flags.
+//   FIN_NONE   s = A p only (mv_mult of the operator API)
+//   FIN_PS     + p.s   -> alpha = rr / ps                      (classic recurrence, cg.c:113)
+//   FIN_SR     + r.w and r.r (MV_DUAL) -> alpha, beta          (single-reduction variant)
+//   FIN_LOCAL  + the sums are left in S->local for the caller (NCCL mode, kernel timing)
+// FIN_INIT / FIN_RR are the finish kinds of the vector kernels.
+enum : int { FIN_NONE = 0, FIN_INIT = 1, FIN_PS = 2, FIN_RR = 3, FIN_SR = 4, FIN_LOCAL = 5 };
+constexpr int MV_FIN_MASK = 0x0f;
+constexpr int MV_PARTIAL = 0x10;  // publish per-CTA partials only (first half of a split launch)
+constexpr int MV_DUAL = 0x20;     // also reduce the square of the gathered vector's owned block
+// a finishing launch adds `extra` partials left at partials[MV_EXTRA_OFFSET ..] by a preceding
+// MV_PARTIAL launch: mode |= extra << 8
+constexpr int MV_EXTRA_OFFSET = 4096;
+constexpr int NO_WAIT = 0x7fffffff;
 
-enum : int { FIN_INIT = 0, FIN_PS = 1, FIN_RR = 2 };
+// Up to three runs of tiles [b[i], e[i]), visited in this order by the stream SpMV.
+struct TileRange {
+  int b[3], e[3];
+};
 
 int sm_count();
 int max_partials();
@@ -39,20 +48,23 @@ long long launch_count();
 void add_launches(long long n);
 
 cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, double* s,
-                        int tile_begin0, int tile_end0, int tile_begin1, int tile_end1,
-                        double* partials, unsigned int* ticket, CgState* S, int mode,
+                        const TileRange& tr, int wait_from, double* partials,
+                        unsigned int* ticket, CgState* S, int mode, const PeerComm& cm,
                         cudaStream_t st);
 cudaError_t launch_gemv(const double* A, long long ld, int nrows, int ncols, const double* pg,
                         const double* pown, double* s, double* partials, unsigned int* ticket,
-                        CgState* S, int mode, cudaStream_t st);
+                        CgState* S, int mode, int wait, const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_update_xr(double* x, double* r, const double* p, const double* s, long long n,
-                             double* partials, unsigned int* ticket, CgState* S, int finish_local,
-                             cudaStream_t st);
+                             double* partials, unsigned int* ticket, CgState* S, int fin,
+                             const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_update_p(double* p, const double* r, long long n, const CgState* S,
-                            cudaStream_t st);
-cudaError_t launch_init(double* x, double* r, double* p, const double* b, long long n,
-                        double* partials, unsigned int* ticket, CgState* S, int finish_local,
-                        cudaStream_t st);
+                            const PeerComm& cm, cudaStream_t st);
+cudaError_t launch_update_sr(double* x, double* g, double* d, double* s, const double* w,
+                             long long n, const CgState* S, const PeerComm& cm, cudaStream_t st);
+cudaError_t launch_init(double* x, double* r, double* p, double* s, const double* b, long long n,
+                        int sr, double* partials, unsigned int* ticket, CgState* S, int fin,
+                        const PeerComm& cm, cudaStream_t st);
+cudaError_t launch_push(const double* p, const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_finish(CgState* S, int which, cudaStream_t st);
 cudaError_t launch_dot(const double* a, const double* b, long long n, double* partials,
                        unsigned int* ticket, double* out, cudaStream_t st);

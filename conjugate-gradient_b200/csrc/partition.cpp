@@ -72,4 +72,43 @@ int plan_partition(int world, int rank, long long n_global, const PartInfo* part
   return 0;
 }
 
+int plan_push(int world, int rank, long long n_global, const PartInfo* parts, int dense,
+              PushPlan* out, const char** err) {
+  if (world > 8) {
+    if (err) *err = "peer-memory mode supports at most 8 ranks";
+    return -1;
+  }
+  Plan plans[8] = {};
+  for (int g = 0; g < world; ++g)
+    if (plan_partition(world, g, n_global, parts, dense, &plans[g], err)) return -1;
+  PushPlan pp = {};
+  const Plan& me = plans[rank];
+  const long long nloc = parts[rank].nloc;
+  if (world == 1) {
+    *out = pp;
+    return 0;
+  }
+  if (me.allgather) {
+    // every peer holds the whole vector: my block sits at my global row offset in each of them
+    for (int q = 0; q < world; ++q) {
+      if (q == rank) continue;
+      pp.push[pp.npush++] = PushItem{q, 0, nloc, parts[rank].row0};
+      pp.wait_src[pp.nwait++] = q;
+    }
+  } else {
+    if (rank > 0 && me.send_lo > 0) {  // my first rows are the lower rank's upper halo
+      const Plan& q = plans[rank - 1];
+      pp.push[pp.npush++] = PushItem{rank - 1, 0, me.send_lo, q.off + parts[rank - 1].nloc};
+    }
+    if (rank + 1 < world && me.send_hi > 0) {  // my last rows are the upper rank's lower halo
+      const Plan& q = plans[rank + 1];
+      pp.push[pp.npush++] = PushItem{rank + 1, nloc - me.send_hi, nloc, q.off - q.h_lo};
+    }
+    if (me.h_lo > 0) pp.wait_src[pp.nwait++] = rank - 1;
+    if (me.h_hi > 0) pp.wait_src[pp.nwait++] = rank + 1;
+  }
+  *out = pp;
+  return 0;
+}
+
 }  // namespace cgb

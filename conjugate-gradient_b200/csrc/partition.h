@@ -32,4 +32,25 @@ struct Plan {
 int plan_partition(int world, int rank, long long n_global, const PartInfo* parts, int dense,
                    Plan* out, const char** err);
 
+// Peer-memory mode (comm.h): who stores which of its rows where.  Rank `rank` stores rows
+// [begin, end) of its owned block at index dst_index.. of rank `peer`'s gather vector p_ext, and
+// must see a completion flag from every rank in wait_src before gathering outside its own block.
+struct PushItem {
+  int peer;
+  long long begin, end;   // local row range of the sender
+  long long dst_index;    // first index in the receiver's p_ext
+};
+
+struct PushPlan {
+  int npush;
+  PushItem push[8];
+  int nwait;
+  int wait_src[8];
+};
+
+// Derived from plan_partition() of every rank (each rank can evaluate every rank's plan, so the
+// layout never has to be communicated).  world <= 8.  0 / -1 like plan_partition.
+int plan_push(int world, int rank, long long n_global, const PartInfo* parts, int dense,
+              PushPlan* out, const char** err);
+
 }  // namespace cgb

@@ -145,6 +145,8 @@ int ensure_init(int device) {
   CUDA_OK(cudaEventCreate(&c.t1));
   CUDA_OK(cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming));
   CUDA_OK(cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming));
+  const char* cmode = getenv("CGB200_COMM");
+  c.comm_mode = (cmode && strcmp(cmode, "nccl") == 0) ? 0 : 1;
   c.ready = true;
   return 0;
 }
@@ -236,6 +238,42 @@ static int allgather_i64(const long long* mine, int count, std::vector<long long
   return 0;
 }
 
+// host-side all-gather of `bytes` bytes per rank through a device bounce buffer (set-up only)
+static int allgather_bytes(const void* mine, int bytes, std::vector<unsigned char>& all) {
+  Ctx& c = g_ctx;
+  all.assign((size_t)bytes * c.world, 0);
+  if (c.world == 1) {
+    memcpy(all.data(), mine, bytes);
+    return 0;
+  }
+  unsigned char* d = nullptr;
+  CUDA_OK(cudaMalloc(&d, (size_t)bytes * c.world));
+  CUDA_OK(cudaMemcpyAsync(d + (size_t)c.rank * bytes, mine, bytes, cudaMemcpyHostToDevice, c.stream));
+  NCCL_OK(g_nccl.AllGather(d + (size_t)c.rank * bytes, d, (size_t)bytes, ncclInt8,
+                           (ncclComm_t)c.comm, c.stream));
+  CUDA_OK(cudaMemcpyAsync(all.data(), d, (size_t)bytes * c.world, cudaMemcpyDeviceToHost, c.stream));
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  cudaFree(d);
+  return 0;
+}
+
+// All ranks have finished everything queued on their solve streams.
+int dist_barrier() {
+  Ctx& c = g_ctx;
+  if (c.world <= 1 || !c.comm) return 0;
+  CUDA_OK(cudaMemsetAsync(c.d_scratch, 0, 8, c.stream));
+  NCCL_OK(g_nccl.AllReduce(c.d_scratch, c.d_scratch, 1, ncclInt32, ncclSum, (ncclComm_t)c.comm,
+                           c.stream));
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  return 0;
+}
+
+const char* comm_mode_name() {
+  Ctx& c = g_ctx;
+  if (c.world <= 1) return "single";
+  return c.comm_mode == 1 ? "p2p" : "nccl";
+}
+
 // ---------------------------------------------------------------------------------------------
 // Systems
 // ---------------------------------------------------------------------------------------------
@@ -244,6 +282,13 @@ static int allgather_i64(const long long* mine, int count, std::vector<long long
 System::~System() {
   for (auto& kv : graphs)
     if (kv.second) cudaGraphExecDestroy(kv.second);
+  if (p2p) {
+    // unmap the peers, and do not release what they may still have mapped before they did too
+    cudaStreamSynchronize(g_ctx.stream);
+    for (int g = 0; g < MAX_RANKS; ++g)
+      if (peer_base[g]) cudaIpcCloseMemHandle(peer_base[g]);
+    dist_barrier();
+  }
   cudaFree(A.vals);
   cudaFree(A.cols);
   cudaFree(A.rowptr);
@@ -251,7 +296,11 @@ System::~System() {
   cudaFree(x);
   cudaFree(r);
   cudaFree(s);
-  cudaFree(p_ext);
+  cudaFree(w);
+  if (comm_buf)
+    cudaFree(comm_buf);  // p_ext lives inside it
+  else
+    cudaFree(p_ext);
   cudaFree(state);
   cudaFree(partials);
 }
@@ -270,6 +319,84 @@ static int alloc_matrix(System* S, long long nnz, bool with_index) {
     CUDA_OK(cudaMalloc(&S->A.rowptr, rpad * sizeof(int)));
     CUDA_OK(cudaMemsetAsync(S->A.rowptr, 0, rpad * sizeof(int), g_ctx.stream));
   }
+  return 0;
+}
+
+// Maps every peer's exported allocation and describes who pushes what to whom (comm.h).  Every
+// rank evaluates every rank's plan (pure host logic), so no layout has to be communicated beyond
+// the IPC handles.  If any rank cannot export or map, all ranks fall back to NCCL together.
+static int setup_peer_comm(System* S, const std::vector<PartInfo>& parts) {
+  Ctx& c = g_ctx;
+  const int G = c.world, me = c.rank;
+  CUDA_OK(cudaStreamSynchronize(c.stream));  // the zero-fill is complete before anyone can map it
+  struct Msg {
+    cudaIpcMemHandle_t h;
+    int ok;
+    int pad;
+  } mine;
+  memset(&mine, 0, sizeof(mine));
+  cudaError_t e = cudaIpcGetMemHandle(&mine.h, S->comm_buf);
+  mine.ok = (e == cudaSuccess);
+  if (!mine.ok) cudaGetLastError();
+  std::vector<unsigned char> all;
+  if (allgather_bytes(&mine, (int)sizeof(Msg), all)) return -1;
+  const Msg* msgs = (const Msg*)all.data();
+  bool ok = true;
+  for (int g = 0; g < G; ++g) ok = ok && msgs[g].ok;
+  int opened = 1;
+  if (ok) {
+    for (int g = 0; g < G && opened; ++g) {
+      if (g == me) continue;
+      void* ptr = nullptr;
+      e = cudaIpcOpenMemHandle(&ptr, msgs[g].h, cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        opened = 0;
+      } else {
+        S->peer_base[g] = ptr;
+      }
+    }
+  } else {
+    opened = 0;
+  }
+  std::vector<unsigned char> all2;
+  if (allgather_bytes(&opened, (int)sizeof(int), all2)) return -1;
+  for (int g = 0; g < G; ++g) ok = ok && ((const int*)all2.data())[g] != 0;
+  if (!ok) {  // together: NCCL between the kernels instead
+    for (int g = 0; g < G; ++g)
+      if (S->peer_base[g]) {
+        cudaIpcCloseMemHandle(S->peer_base[g]);
+        S->peer_base[g] = nullptr;
+      }
+    if (getenv("CGB200_VERBOSE")) fprintf(stderr, "[cgb200] rank %d: CUDA IPC unavailable, using NCCL\n", me);
+    S->p2p = false;
+    return 0;
+  }
+
+  PushPlan pp;
+  const char* perr = nullptr;
+  if (plan_push(G, me, S->n_global, parts.data(), S->dense ? 1 : 0, &pp, &perr)) {
+    set_error(std::string("push plan: ") + (perr ? perr : "?"));
+    return -1;
+  }
+  auto base_of = [&](int g) { return g == me ? (char*)S->comm_buf : (char*)S->peer_base[g]; };
+
+  PeerComm cm;
+  memset(&cm, 0, sizeof(cm));
+  cm.world = G;
+  cm.rank = me;
+  for (int g = 0; g < G; ++g) cm.mbox[g] = (Mailbox*)base_of(g);
+  cm.local = (CommLocal*)((char*)S->comm_buf + COMM_LOCAL_OFFSET);
+  cm.npush = pp.npush;
+  for (int t = 0; t < pp.npush; ++t) {
+    double* pext = (double*)(base_of(pp.push[t].peer) + COMM_PEXT_OFFSET);
+    cm.push[t] = PushTarget{pext + pp.push[t].dst_index, pp.push[t].begin, pp.push[t].end,
+                            pp.push[t].peer, 0};
+  }
+  cm.nwait = pp.nwait;
+  for (int i = 0; i < pp.nwait; ++i) cm.wait_src[i] = pp.wait_src[i];
+  S->cm = cm;
+  S->p2p = true;
   return 0;
 }
 
@@ -313,13 +440,26 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
   CUDA_OK(cudaMalloc(&S->x, (nl + 16) * sizeof(double)));
   CUDA_OK(cudaMalloc(&S->r, (nl + 16) * sizeof(double)));
   CUDA_OK(cudaMalloc(&S->s, (nl + 16) * sizeof(double)));
-  CUDA_OK(cudaMalloc(&S->p_ext, ((size_t)S->ext_len + 16) * sizeof(double)));
-  CUDA_OK(cudaMemsetAsync(S->p_ext, 0, ((size_t)S->ext_len + 16) * sizeof(double), c.stream));
+  S->cm_off.world = 1;
+  S->cm = S->cm_off;
+  if (c.world > 1 && c.comm_mode == 1 && c.world <= MAX_RANKS) {
+    // one exported allocation: [Mailbox | CommLocal | p_ext]; a multiple of 2 MiB so that it is
+    // never a sub-allocation of a block shared with other buffers
+    size_t bytes = COMM_PEXT_OFFSET + ((size_t)S->ext_len + 16) * sizeof(double);
+    bytes = (bytes + (2u << 20) - 1) / (2u << 20) * (2u << 20);
+    CUDA_OK(cudaMalloc(&S->comm_buf, bytes));
+    CUDA_OK(cudaMemsetAsync(S->comm_buf, 0, bytes, c.stream));
+    S->p_ext = (double*)((char*)S->comm_buf + COMM_PEXT_OFFSET);
+  } else {
+    CUDA_OK(cudaMalloc(&S->p_ext, ((size_t)S->ext_len + 16) * sizeof(double)));
+    CUDA_OK(cudaMemsetAsync(S->p_ext, 0, ((size_t)S->ext_len + 16) * sizeof(double), c.stream));
+  }
   CUDA_OK(cudaMemsetAsync(S->x, 0, (nl + 16) * sizeof(double), c.stream));
   CUDA_OK(cudaMalloc(&S->state, sizeof(CgState)));
   CUDA_OK(cudaMemsetAsync(S->state, 0, sizeof(CgState), c.stream));
   CUDA_OK(cudaMalloc(&S->partials, sizeof(double) * max_partials() * 2));
   S->p_own = S->p_ext + S->off;
+  if (S->comm_buf && setup_peer_comm(S, parts)) return -1;
 
   if (!S->dense) {
     if (cols_are_global && col_shift != 0) {
@@ -618,62 +758,111 @@ static int enqueue_exchange_end(System* S) {
   return 0;
 }
 
-// K1 in the given mode on the loop's vectors (or on `pg`/`pown` overrides for PLAIN matvecs).
-static int enqueue_matvec(System* S, int mode_single, bool split_ok, bool do_exchange = true) {
+static const PeerComm& comm_of(const System* S) { return S->p2p ? S->cm : S->cm_off; }
+
+// K1: out = A * (gather vector), optionally fused with the dot products of the loop.
+//   fin      FIN_NONE (plain product), FIN_PS, FIN_SR, or FIN_LOCAL (sums left in state->local)
+//   dual     also reduce the square of the gathered vector's owned block (single-reduction)
+//   exchange the gather vector's halo / remote blocks take part: in peer-memory mode they were
+//            pushed by the kernel that wrote the vector and this kernel waits for the flags at
+//            its first boundary tile; in NCCL mode the exchange is enqueued here.
+static int enqueue_matvec(System* S, double* out, int fin, bool dual, bool exchange) {
   Ctx& c = g_ctx;
   CgState* st = S->state;
+  const PeerComm& cm = comm_of(S);
+  const bool multi = S->world > 1 && exchange;
+  int mode = fin | (dual ? MV_DUAL : 0);
   if (S->dense) {
-    if (do_exchange && enqueue_exchange_begin(S)) return -1;
-    CUDA_OK(launch_gemv(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext, S->p_own,
-                        S->s, S->partials, &st->ticket[0], st, mode_single, c.stream));
+    if (multi && !S->p2p && enqueue_exchange_begin(S)) return -1;
+    CUDA_OK(launch_gemv(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext, S->p_own, out,
+                        S->partials, &st->ticket[0], st, mode, (multi && S->p2p) ? 1 : 0, cm,
+                        c.stream));
     return 0;
   }
-  const bool split = do_exchange && split_ok && S->world > 1 && !S->allgather &&
-                     S->tb_hi > S->tb_lo && (S->tb_lo > 0 || S->tb_hi < S->ntiles);
-  if (do_exchange && enqueue_exchange_begin(S)) return -1;
+  const TileRange all_tiles = {{0, 0, 0}, {S->ntiles, 0, 0}};
+  if (!multi) {
+    CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, out, all_tiles, NO_WAIT, S->partials,
+                        &st->ticket[0], st, mode, cm, c.stream));
+    return 0;
+  }
+  const bool has_interior = !S->allgather && S->tb_hi > S->tb_lo;
+  if (S->p2p) {
+    // one launch: interior tiles first, the boundary tiles behind the wait on the peers' flags
+    TileRange tr = all_tiles;
+    int wait_from = cm.nwait > 0 ? 0 : NO_WAIT;
+    if (has_interior) {
+      tr = TileRange{{S->tb_lo, 0, S->tb_hi}, {S->tb_hi, S->tb_lo, S->ntiles}};
+      if (cm.nwait > 0) wait_from = S->tb_hi - S->tb_lo;
+    }
+    CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, out, tr, wait_from, S->partials,
+                        &st->ticket[0], st, mode, cm, c.stream));
+    return 0;
+  }
+  // NCCL mode
+  const bool split = has_interior && (S->tb_lo > 0 || S->tb_hi < S->ntiles);
+  if (enqueue_exchange_begin(S)) return -1;
   if (!split) {
-    if (do_exchange && enqueue_exchange_end(S)) return -1;
-    CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, S->s, 0, S->ntiles, 0, 0, S->partials,
-                        &st->ticket[0], st, mode_single, c.stream));
+    if (enqueue_exchange_end(S)) return -1;
+    CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, out, all_tiles, NO_WAIT, S->partials,
+                        &st->ticket[0], st, mode, cm, c.stream));
     return 0;
   }
   // interior tiles while the halo is in flight, then the boundary tiles finish the reduction
-  const int n_int = S->tb_hi - S->tb_lo;
-  const int g_int = spmv_grid_for(n_int);
-  const int int_mode = (mode_single == SPMV_PLAIN) ? SPMV_PLAIN : SPMV_PARTIAL_ONLY;
-  CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, S->s, S->tb_lo, S->tb_hi, 0, 0,
-                      S->partials + SPMV_EXTRA_OFFSET, &st->ticket[0], st, int_mode, c.stream));
+  const TileRange interior = {{S->tb_lo, 0, 0}, {S->tb_hi, 0, 0}};
+  const TileRange boundary = {{0, S->tb_hi, 0}, {S->tb_lo, S->ntiles, 0}};
+  const int g_int = spmv_grid_for(S->tb_hi - S->tb_lo);
+  const int int_mode = (fin == FIN_NONE) ? mode : (mode | MV_PARTIAL);
+  CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, out, interior, NO_WAIT,
+                      S->partials + MV_EXTRA_OFFSET, &st->ticket[0], st, int_mode, cm, c.stream));
   if (enqueue_exchange_end(S)) return -1;
-  const int fin_mode = (mode_single == SPMV_PLAIN) ? SPMV_PLAIN : (mode_single | (g_int << 8));
-  CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, S->s, 0, S->tb_lo, S->tb_hi, S->ntiles,
-                      S->partials, &st->ticket[0], st, fin_mode, c.stream));
+  const int fin_mode = (fin == FIN_NONE) ? mode : (mode | (g_int << 8));
+  CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, out, boundary, NO_WAIT, S->partials,
+                      &st->ticket[0], st, fin_mode, cm, c.stream));
   return 0;
 }
 
-static int enqueue_iteration(System* S) {
+// NCCL mode only: cross-GPU sum of state->local[0..count) and the one-thread bookkeeping kernel.
+static int enqueue_nccl_finish(System* S, int count, int which) {
+  Ctx& c = g_ctx;
+  if (allreduce_sum_f64(&S->state->local[0], (size_t)count, c.stream)) return -1;
+  CUDA_OK(launch_finish(S->state, which, c.stream));
+  return 0;
+}
+
+static int ensure_w(System* S) {
+  if (S->w) return 0;
+  CUDA_OK(cudaMalloc(&S->w, ((size_t)S->nloc + 16) * sizeof(double)));
+  CUDA_OK(cudaMemsetAsync(S->w, 0, ((size_t)S->nloc + 16) * sizeof(double), g_ctx.stream));
+  return 0;
+}
+
+// Classic recurrence (the reference's, cg.c:110-135): K1, K2, K3.
+// Single-reduction recurrence: one fused vector update, then K1 with both dot products.
+static int enqueue_iteration(System* S, int variant) {
   Ctx& c = g_ctx;
   CgState* st = S->state;
-  const bool multi = S->world > 1;
-  if (enqueue_matvec(S, multi ? SPMV_FINISH_LOCAL : SPMV_FINISH, true)) return -1;
-  if (multi) {
-    if (allreduce_sum_f64(&st->local, 1, c.stream)) return -1;
-    CUDA_OK(launch_finish(st, FIN_PS, c.stream));
+  const PeerComm& cm = comm_of(S);
+  const bool nccl = S->world > 1 && !S->p2p;
+  if (variant == 1) {
+    CUDA_OK(launch_update_sr(S->x, S->p_own, S->r, S->s, S->w, S->nloc, st, cm, c.stream));
+    if (enqueue_matvec(S, S->w, nccl ? FIN_LOCAL : FIN_SR, true, true)) return -1;
+    if (nccl && enqueue_nccl_finish(S, 2, FIN_SR)) return -1;
+    return 0;
   }
+  if (enqueue_matvec(S, S->s, nccl ? FIN_LOCAL : FIN_PS, false, true)) return -1;
+  if (nccl && enqueue_nccl_finish(S, 1, FIN_PS)) return -1;
   CUDA_OK(launch_update_xr(S->x, S->r, S->p_own, S->s, S->nloc, S->partials, &st->ticket[1], st,
-                           multi ? 1 : 0, c.stream));
-  if (multi) {
-    if (allreduce_sum_f64(&st->local, 1, c.stream)) return -1;
-    CUDA_OK(launch_finish(st, FIN_RR, c.stream));
-  }
-  CUDA_OK(launch_update_p(S->p_own, S->r, S->nloc, st, c.stream));
+                           nccl ? FIN_LOCAL : FIN_RR, cm, c.stream));
+  if (nccl && enqueue_nccl_finish(S, 1, FIN_RR)) return -1;
+  CUDA_OK(launch_update_p(S->p_own, S->r, S->nloc, st, cm, c.stream));
   return 0;
 }
 
 // Kernel nodes per captured iteration (for the launch counter)
-static int kernels_per_iteration(const System* S) {
-  int k = 3;
-  if (S->world > 1) {
-    k += 2;  // bookkeeping kernels
+static int kernels_per_iteration(const System* S, int variant) {
+  int k = variant == 1 ? 2 : 3;
+  if (S->world > 1 && !S->p2p) {
+    k += variant == 1 ? 1 : 2;  // bookkeeping kernels
     if (!S->dense && !S->allgather && S->tb_hi > S->tb_lo &&
         (S->tb_lo > 0 || S->tb_hi < S->ntiles))
       k += 1;  // split K1
@@ -681,9 +870,10 @@ static int kernels_per_iteration(const System* S) {
   return k;
 }
 
-static int get_graph(System* S, int iters, cudaGraphExec_t* out) {
+static int get_graph(System* S, int iters, int variant, cudaGraphExec_t* out) {
   Ctx& c = g_ctx;
-  auto it = S->graphs.find(iters);
+  const int key = 2 * iters + variant;
+  auto it = S->graphs.find(key);
   if (it != S->graphs.end()) {
     *out = it->second;
     return 0;
@@ -692,7 +882,7 @@ static int get_graph(System* S, int iters, cudaGraphExec_t* out) {
   cudaGraph_t graph = nullptr;
   CUDA_OK(cudaStreamBeginCapture(c.stream, cudaStreamCaptureModeThreadLocal));
   int rc = 0;
-  for (int i = 0; i < iters && rc == 0; ++i) rc = enqueue_iteration(S);
+  for (int i = 0; i < iters && rc == 0; ++i) rc = enqueue_iteration(S, variant);
   cudaError_t e = cudaStreamEndCapture(c.stream, &graph);
   add_launches(before - launch_count());  // capture is not execution
   if (rc) {
@@ -710,7 +900,7 @@ static int get_graph(System* S, int iters, cudaGraphExec_t* out) {
     set_error(std::string("graph instantiate: ") + cudaGetErrorString(e));
     return -1;
   }
-  S->graphs[iters] = exec;
+  S->graphs[key] = exec;
   *out = exec;
   return 0;
 }
@@ -732,12 +922,15 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
     set_error("system_solve: NULL system");
     return -1;
   }
-  if (o.variant != 0) {
-    set_error("system_solve: only the classic recurrence is built in this version");
+  if (o.variant != 0 && o.variant != 1) {
+    set_error("system_solve: variant must be CGB200_CLASSIC or CGB200_SINGLE_REDUCTION");
     return -1;
   }
   CUDA_OK(cudaSetDevice(c.device));
+  const int variant = o.variant;
   const bool multi = S->world > 1;
+  const bool nccl = multi && !S->p2p;
+  const PeerComm& cm = comm_of(S);
   const long long launches0 = launch_count();
   const int max_iter = o.max_iter < 0 ? 0 : o.max_iter;
 
@@ -746,6 +939,7 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
   memset(h, 0, sizeof(CgState));
   h->tol = o.tol > 0.0 ? o.tol : 0.0;
   h->max_iter = max_iter;
+  h->variant = variant;
   CUDA_OK(cudaMemcpyAsync(S->state, h, sizeof(CgState), cudaMemcpyHostToDevice, c.stream));
 
   if (S->nloc == 0 && !multi) {
@@ -756,21 +950,23 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
     }
     return 0;
   }
+  if (variant == 1 && ensure_w(S)) return -1;
 
   // loop entry: x = 0, r = p = b, rr = bb = b.b                         (cg.c:104-108)
-  CUDA_OK(launch_init(S->x, S->r, S->p_own, S->b, S->nloc, S->partials, &S->state->ticket[2],
-                      S->state, multi ? 1 : 0, c.stream));
-  if (multi) {
-    if (allreduce_sum_f64(&S->state->local, 1, c.stream)) return -1;
-    CUDA_OK(launch_finish(S->state, FIN_INIT, c.stream));
+  CUDA_OK(launch_init(S->x, S->r, S->p_own, S->s, S->b, S->nloc, variant == 1 ? 1 : 0, S->partials,
+                      &S->state->ticket[2], S->state, nccl ? FIN_LOCAL : FIN_INIT, cm, c.stream));
+  if (nccl && enqueue_nccl_finish(S, 1, FIN_INIT)) return -1;
+  if (variant == 1) {  // w = A r, alpha_0 = r.r / r.w
+    if (enqueue_matvec(S, S->w, nccl ? FIN_LOCAL : FIN_SR, true, true)) return -1;
+    if (nccl && enqueue_nccl_finish(S, 2, FIN_SR)) return -1;
   }
 
   const long long total_updates = (long long)max_iter + 1;
   int batch = o.check_every > 0 ? o.check_every : 32;
   if (batch > total_updates) batch = (int)total_updates;
   cudaGraphExec_t exec = nullptr;
-  if (get_graph(S, batch, &exec)) return -1;
-  const int kpi = kernels_per_iteration(S);
+  if (get_graph(S, batch, variant, &exec)) return -1;
+  const int kpi = kernels_per_iteration(S, variant);
 
   CUDA_OK(cudaEventRecord(c.t0, c.stream));
   long long enq = 0;
@@ -808,6 +1004,10 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
     res->world = S->world;
     res->kernel_launches = launch_count() - launches0;
   }
+  if (f.status == CGB200_ST_COMM) {
+    set_error("system_solve: a peer-memory exchange between GPUs timed out");
+    return -1;
+  }
   return 0;
 }
 
@@ -837,11 +1037,15 @@ int system_matvec_dev(System* S, const double* v_dev, double* s_host_or_null) {
   if (v_dev != S->p_own)
     CUDA_OK(cudaMemcpyAsync(S->p_own, v_dev, sizeof(double) * S->nloc, cudaMemcpyDeviceToDevice,
                             c.stream));
-  if (enqueue_matvec(S, SPMV_PLAIN, true)) return -1;
+  if (S->world > 1 && S->p2p) CUDA_OK(launch_push(S->p_own, S->cm, c.stream));
+  if (enqueue_matvec(S, S->s, FIN_NONE, false, true)) return -1;
   if (s_host_or_null)
     CUDA_OK(cudaMemcpyAsync(s_host_or_null, S->s, sizeof(double) * S->nloc, cudaMemcpyDeviceToHost,
                             c.stream));
   CUDA_OK(cudaStreamSynchronize(c.stream));
+  // no reduction follows a plain product, so nothing else keeps a fast rank from pushing its next
+  // vector into halo slots a slow rank is still reading
+  if (S->world > 1 && S->p2p && dist_barrier()) return -1;
   return 0;
 }
 
@@ -937,14 +1141,20 @@ int system_time_kernel(System* S, int which, int reps, double* ms_out) {
   h->rr = 1.0;
   h->max_iter = 0x7fffffff;
   CUDA_OK(cudaMemcpyAsync(S->state, h, sizeof(CgState), cudaMemcpyHostToDevice, c.stream));
+  if (which >= 4 && ensure_w(S)) return -1;
   auto one = [&]() -> int {
-    if (which == 1) {
-      if (enqueue_matvec(S, SPMV_FINISH_LOCAL, false, false)) return -1;  // local kernel only
+    if (which == 1) {  // local kernel only: no exchange, sums left in state->local
+      if (enqueue_matvec(S, S->s, FIN_LOCAL, false, false)) return -1;
     } else if (which == 2) {
       CUDA_OK(launch_update_xr(S->x, S->r, S->p_own, S->s, S->nloc, S->partials,
-                               &S->state->ticket[1], S->state, 1, c.stream));
+                               &S->state->ticket[1], S->state, FIN_LOCAL, S->cm_off, c.stream));
+    } else if (which == 3) {
+      CUDA_OK(launch_update_p(S->p_own, S->r, S->nloc, S->state, S->cm_off, c.stream));
+    } else if (which == 4) {
+      CUDA_OK(launch_update_sr(S->x, S->p_own, S->r, S->s, S->w, S->nloc, S->state, S->cm_off,
+                               c.stream));
     } else {
-      CUDA_OK(launch_update_p(S->p_own, S->r, S->nloc, S->state, c.stream));
+      if (enqueue_matvec(S, S->w, FIN_LOCAL, true, false)) return -1;
     }
     return 0;
   };

@@ -9,6 +9,7 @@
 #include <string>
 #include <vector>
 
+#include "comm.h"
 #include "kernels.h"
 #include "partition.h"
 #include "state.h"
@@ -31,6 +32,9 @@ struct Ctx {
   // multi-GPU
   int rank = 0, world = 1;
   void* comm = nullptr;  // ncclComm_t
+  // how the GPUs talk inside the loop: 1 = peer memory over NVLink (kernels store into each
+  // other's buffers, comm.h), 0 = NCCL calls between the kernels.  CGB200_COMM=p2p|nccl.
+  int comm_mode = 1;
 };
 
 Ctx& ctx();
@@ -42,6 +46,8 @@ const char* last_error();
 int dist_unique_id(void* id128);
 int dist_init(int rank, int world, const void* id128);
 int dist_finalize();
+int dist_barrier();
+const char* comm_mode_name();
 
 // One row block [row0, row0 + nloc) of the system and everything the loop needs for it.
 struct System {
@@ -67,9 +73,18 @@ struct System {
   int ntiles = 0, tb_lo = 0, tb_hi = 0;
 
   double *b = nullptr, *x = nullptr, *r = nullptr, *s = nullptr;
+  double* w = nullptr;  // single-reduction variant only: w = A r (allocated on first use)
   CgState* state = nullptr;
   double* partials = nullptr;
-  std::map<int, cudaGraphExec_t> graphs;  // iterations per graph -> instantiated graph
+  std::map<int, cudaGraphExec_t> graphs;  // 2 * iterations per graph + variant -> graph
+
+  // peer-memory exchange (comm.h).  comm_buf = [Mailbox | CommLocal | p_ext] is the one
+  // allocation exported through CUDA IPC; peer_base[g] is rank g's comm_buf mapped here.
+  bool p2p = false;
+  void* comm_buf = nullptr;
+  void* peer_base[MAX_RANKS] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  PeerComm cm = {};      // active description (world > 1 only when p2p)
+  PeerComm cm_off = {};  // disabled description (single GPU, NCCL mode)
 
   double iter_bytes() const;  // contract bytes per iteration: A + 88 n
   double k1_bytes() const;    // share of the matvec kernel: A + 16 n

@@ -9,23 +9,23 @@
 #define CGB200_ST_CONVERGED 2  /* r.r <= tol^2 * b.b (extension) */
 #define CGB200_ST_BREAKDOWN 3  /* p.Ap not a positive finite number */
 #define CGB200_ST_EXACT 4      /* r.r == 0 exactly: stopped where the reference would divide 0/0 */
+#define CGB200_ST_COMM 5       /* a peer-memory exchange between GPUs timed out */
 
 struct CgState {
   double rr;      // r.r of the current residual
-  double ps;      // p.(A p)
+  double ps;      // p.(A p)   (single-reduction variant: r.(A r))
   double alpha;   // rr / ps                      (cg.c:113)
   double beta;    // rr_new / rr                  (cg.c:129)
   double bb;      // b.b
   double tol;     // relative tolerance on ||r||/||b||; 0 = fixed count (reference behaviour)
   double thresh;  // tol^2 * bb
-  double local;   // multi-GPU: this rank's partial sum awaiting the cross-GPU sum
+  double local[2];  // NCCL mode: this rank's partial sums awaiting the cross-GPU sum
   int iter;       // x updates performed so far
   int max_iter;   // reference semantics: stop after the update at k == max_iter
   int done;
   int status;
+  int variant;    // 0 classic (the reference's recurrence), 1 single-reduction
+  int sr_first;   // single-reduction: the next fused reduction is the loop-entry one
   unsigned int ticket[4];  // grid-reduction tickets (one per fused kernel)
-  // single-reduction variant scalars
-  double gamma;   // r.r
-  double delta;   // r.(A r)
-  double aux[6];
+  double aux[4];
 };

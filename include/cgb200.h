@@ -22,10 +22,15 @@ extern "C" {
 #define CGB200_CONVERGED 2 /* r.r <= tol^2 * b.b */
 #define CGB200_BREAKDOWN 3 /* p.Ap not positive and finite: stopped, last finite x kept */
 #define CGB200_EXACT 4     /* r.r == 0: stopped where the reference would compute 0/0 = NaN */
+#define CGB200_COMM_TIMEOUT 5 /* multi-GPU: a peer-memory exchange timed out (the call returns -1) */
 
 /* ---- recurrence variants ------------------------------------------------------------------ */
 #define CGB200_CLASSIC 0          /* Hestenes-Stiefel, the reference's recurrence (default) */
-#define CGB200_SINGLE_REDUCTION 1 /* Chronopoulos-Gear: one fused reduction per iteration */
+/* Chronopoulos-Gear recurrence: w = A r is formed instead of A p, r.r and r.w come out of ONE
+ * fused reduction inside the matvec kernel, and the four vector updates are one pass.  Same x in
+ * exact arithmetic, two kernels and one (cross-GPU) reduction per iteration instead of three and
+ * two; costs one more matvec at loop entry.  Same iteration-count semantics as the classic loop. */
+#define CGB200_SINGLE_REDUCTION 1
 
 /* ---- operator-API residency modes --------------------------------------------------------- */
 #define CGB200_EAGER 0    /* every op uploads its inputs and downloads its output (default) */
@@ -102,7 +107,8 @@ int cgb200_system_matvec(cgb200_system *sys, const double *v_host, double *s_hos
 int cgb200_system_true_relres(cgb200_system *sys, double *relres);
 /* Average device time (ms, CUDA events on the launching stream) of `reps` back-to-back launches
  * of one kernel of the loop on this system's buffers.  which: 1 = matvec+dot (K1),
- * 2 = x/r update + r.r (K2), 3 = direction update (K3). */
+ * 2 = x/r update + r.r (K2), 3 = direction update (K3); single-reduction variant: 4 = the fused
+ * vector update, 5 = matvec with both dot products. */
 int cgb200_system_time_kernel(cgb200_system *sys, int which, int reps, double *ms);
 /* Contract bytes per iteration for this rank and the share of the matvec kernel. */
 int cgb200_system_bytes(cgb200_system *sys, double *iter_bytes, double *k1_bytes);
@@ -126,11 +132,24 @@ long long cgb200_system_nnz(cgb200_system *sys);
  * Needs no device. */
 int cgb200_plan_partition(int world, int rank, long long n_global, const long long *info4,
                           int dense, long long *out10);
+/* Peer-memory mode: which of its rows rank `rank` stores into which peer's gather vector, and
+ * whose completion flags it waits for (csrc/partition.h plan_push; host-only, needs no device).
+ * out[42]: {npush, 8 x {peer, begin, end, dst_index}, nwait, 8 x wait_src}; unused entries -1/0. */
+int cgb200_plan_push(int world, int rank, long long n_global, const long long *info4, int dense,
+                     long long *out42);
 int cgb200_dist_unique_id(void *id128);
 int cgb200_dist_init(int rank, int world, const void *id128);
 int cgb200_dist_finalize(void);
 int cgb200_dist_rank(void);
 int cgb200_dist_world(void);
+/* All ranks have finished the work queued so far (set-up / tear-down ordering). */
+int cgb200_dist_barrier(void);
+/* How the GPUs exchange data inside the loop: "single" (one rank), "p2p" (default: kernels store
+ * halo rows and partial sums straight into peer memory over NVLink, CUDA IPC mappings) or "nccl"
+ * (NCCL send/recv, all-gather and all-reduce between the kernels; CGB200_COMM=nccl, and the
+ * automatic fallback when IPC mapping is not possible -- see cgb200_system_comm_is_p2p). */
+const char *cgb200_dist_comm_mode(void);
+int cgb200_system_comm_is_p2p(cgb200_system *sys);
 
 #ifdef __cplusplus
 }

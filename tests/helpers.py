@@ -80,6 +80,11 @@ def oracle():
         C.c_int, c_int_p, c_int_p, c_double_p, c_double_p, C.c_int, C.c_double, C.c_int,
         c_double_p, c_double_p, c_int_p,
     ]
+    L.oracle_conj_grad_sr.restype = C.c_int
+    L.oracle_conj_grad_sr.argtypes = [
+        C.c_int, c_int_p, c_int_p, c_double_p, c_double_p, C.c_int, C.c_double,
+        c_double_p, c_double_p, c_int_p,
+    ]
     L.oracle_true_relres.restype = C.c_double
     L.oracle_true_relres.argtypes = [C.c_int, c_int_p, c_int_p, c_double_p, c_double_p, c_double_p]
     L.oracle_num_threads.restype = C.c_int
@@ -207,6 +212,19 @@ def oracle_cg(sysm, max_iter, tol=0.0, guard=0):
     it = oracle().oracle_conj_grad(
         sysm.n, iptr(sysm.row_ptr), iptr(sysm.cols), dptr(sysm.vals), dptr(sysm.b),
         max_iter, tol, guard, dptr(x), C.byref(rr), C.byref(st),
+    )
+    return x, it, rr.value, st.value
+
+
+def oracle_cg_sr(sysm, max_iter, tol=0.0):
+    """Same as oracle_cg for the single-reduction recurrence (not in the reference; restates the
+    product's optional variant so that it can be compared with something that rounds alike)."""
+    x = np.empty(sysm.n, dtype=np.float64)
+    rr = C.c_double(0.0)
+    st = C.c_int(0)
+    it = oracle().oracle_conj_grad_sr(
+        sysm.n, iptr(sysm.row_ptr), iptr(sysm.cols), dptr(sysm.vals), dptr(sysm.b),
+        max_iter, tol, dptr(x), C.byref(rr), C.byref(st),
     )
     return x, it, rr.value, st.value
 

@@ -50,10 +50,10 @@ def gpu_cg(pkg, L, sysm, max_iter):
     return x
 
 
-def gpu_solve(pkg, L, sysm, max_iter, tol):
+def gpu_solve(pkg, L, sysm, max_iter, tol, variant=0):
     A, b = _structs(pkg, sysm)
     xp = pkg.MvSparseP()
-    o = pkg.Opts(max_iter, tol, 0, 0, 0)
+    o = pkg.Opts(max_iter, tol, variant, 0, 0)
     r = pkg.Result()
     assert L.cgb200_solve(C.byref(A), C.byref(b), C.byref(xp), C.byref(o), C.byref(r)) == 0, pkg.last_error()
     x = _take(xp, sysm.n)
@@ -295,6 +295,49 @@ def test_tolerance_mode_matches_oracle(pkg, gpu_lib, mk):
     assert r.relres <= TOL_RES
     assert H.true_relres(s, x) <= TOL_RES * 1.05
     assert np.linalg.norm(x - xo) / np.linalg.norm(xo) <= TOL_X
+
+
+# ---------------------------------------------------------------------------------------------
+# single-reduction variant (extension; the reference has one recurrence): against its own CPU
+# restatement at equal K, and against the classic oracle (same x in exact arithmetic)
+# ---------------------------------------------------------------------------------------------
+
+
+@pytest.mark.parametrize("mk,M", LOOP_CASES)
+def test_single_reduction_fixed_count(pkg, gpu_lib, mk, M):
+    s = mk()
+    x, r = gpu_solve(pkg, gpu_lib, s, M, 0.0, variant=pkg.SINGLE_REDUCTION)
+    xs, it, _, _ = H.oracle_cg_sr(s, M)
+    assert r.iterations == it == M + 1 and r.status == pkg.MAXITER
+    assert np.linalg.norm(x - xs) / np.linalg.norm(xs) <= TOL_X, s.name
+    xo, _, _, _ = H.oracle_cg(s, M)
+    assert np.linalg.norm(x - xo) / np.linalg.norm(xo) <= TOL_X, s.name
+
+
+@pytest.mark.parametrize("mk", TOL_CASES)
+def test_single_reduction_tolerance(pkg, gpu_lib, mk):
+    s = mk()
+    x, r = gpu_solve(pkg, gpu_lib, s, 100000, TOL_RES, variant=pkg.SINGLE_REDUCTION)
+    xo, it, rr, st = H.oracle_cg(s, 100000, tol=TOL_RES, guard=1)
+    assert st == 1 and r.status == pkg.CONVERGED
+    assert abs(r.iterations - it) <= ITER_SLACK, (r.iterations, it)
+    assert H.true_relres(s, x) <= TOL_RES * 1.05
+    assert np.linalg.norm(x - xo) / np.linalg.norm(xo) <= TOL_X
+
+
+def test_single_reduction_known_answers_and_breakdown(pkg, gpu_lib):
+    s = H.tridiag4()
+    x, r = gpu_solve(pkg, gpu_lib, s, 1, 0.0, variant=pkg.SINGLE_REDUCTION)
+    assert np.allclose(x, [2.0, 3.0, 3.0, 2.0], rtol=0, atol=1e-14) and r.iterations == 2
+    # past exact convergence: stops (EXACT or BREAKDOWN on a residual of rounding noise), finite x
+    x, r = gpu_solve(pkg, gpu_lib, s, 10, 0.0, variant=pkg.SINGLE_REDUCTION)
+    assert np.all(np.isfinite(x)) and np.allclose(x, [2.0, 3.0, 3.0, 2.0], rtol=0, atol=1e-12)
+    assert r.status in (pkg.EXACT, pkg.BREAKDOWN, pkg.MAXITER)
+    # deterministic run to run
+    t = H.lap(128, 128)
+    x1, _ = gpu_solve(pkg, gpu_lib, t, 150, 0.0, variant=pkg.SINGLE_REDUCTION)
+    x2, _ = gpu_solve(pkg, gpu_lib, t, 150, 0.0, variant=pkg.SINGLE_REDUCTION)
+    assert np.array_equal(_bits(x1), _bits(x2))
 
 
 # ---------------------------------------------------------------------------------------------

@@ -1,10 +1,14 @@
-"""CPU, world_size 2 over gloo: the host-side logic of the multi-GPU layer.
+"""CPU, world_size 2 and 3 over gloo: the host-side logic of the multi-GPU layer.
 
 The row-block plan (csrc/partition.cpp, reached through the C ABI cgb200_plan_partition) decides
 halo widths, the local gather layout and who sends what.  Two real processes execute that plan with
 gloo send/recv standing in for NCCL and the oracle's CPU operators standing in for the kernels, and
 must reproduce the one-rank result: bit-exact for the matvec (row sums do not depend on the
-partition) and to reduction-order tolerance for a CG solve (dot products are summed per rank)."""
+partition) and to reduction-order tolerance for a CG solve (dot products are summed per rank).
+The peer-memory layout (cgb200_plan_push: which rows each rank stores at which index of which
+peer's gather vector) is executed the same way, one message per push item written at the planned
+index, and must fill the gather vector exactly like the send/recv scheme; the single-reduction
+recurrence runs on top of it against its CPU restatement."""
 import os
 import socket
 import sys
@@ -33,6 +37,24 @@ def _plan(pkg, world, rank, n, info, dense=0):
     return dict(zip(keys, [int(v) for v in out]))
 
 
+def _push_plan(pkg, world, rank, n, info, dense=0):
+    import ctypes as C
+
+    arr = (C.c_longlong * (4 * world))(*[int(v) for row in info for v in row])
+    out = (C.c_longlong * 42)()
+    assert pkg.lib().cgb200_plan_push(world, rank, n, arr, dense, out) == 0, pkg.last_error()
+    items = [dict(peer=int(out[1 + 4 * t]), begin=int(out[2 + 4 * t]), end=int(out[3 + 4 * t]),
+                  dst=int(out[4 + 4 * t])) for t in range(int(out[0]))]
+    waits = [int(out[34 + i]) for i in range(int(out[33]))]
+    return items, waits
+
+
+CUTS = {
+    2: {"lap2d": [24 * 7], "lap3d": [8 * 7 * 6], "banded": [170], "dense": [40]},
+    3: {"lap2d": [24 * 5, 24 * 11], "lap3d": [8 * 7 * 3, 8 * 7 * 7], "banded": [120, 290], "dense": [30, 61]},
+}
+
+
 def _worker(rank, world, port, case, q):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -51,9 +73,9 @@ def _worker(rank, world, port, case, q):
              "dense": lambda: HH.dense(96)}[case]()
         n = s.n
         # contiguous row blocks; uneven on purpose
-        cut = {"lap2d": 24 * 7, "lap3d": 8 * 7 * 6, "banded": 170, "dense": 40}[case]
-        row0 = [0, cut][rank]
-        nloc = [cut, n - cut][rank]
+        bounds = [0] + CUTS[world][case] + [n]
+        row0 = bounds[rank]
+        nloc = bounds[rank + 1] - bounds[rank]
         rp = s.row_ptr[row0:row0 + nloc + 1].astype(np.int64)
         lo_k, hi_k = int(rp[0]), int(rp[-1])
         cols_g = s.cols[lo_k:hi_k].copy()
@@ -65,16 +87,20 @@ def _worker(rank, world, port, case, q):
         info = [t.tolist() for t in allinfo]
         dense = 1 if case == "dense" else 0
         P = _plan(pkg, world, rank, n, info, dense)
-        other = _plan(pkg, world, 1 - rank, n, info, dense)
-        # both ranks must agree on the scheme and on matching message sizes
-        assert P["allgather"] == other["allgather"]
+        plans = [_plan(pkg, world, g_, n, info, dense) for g_ in range(world)]
+        # all ranks must agree on the scheme and on matching message sizes
+        assert all(pl["allgather"] == P["allgather"] for pl in plans)
         if not P["allgather"]:
             if rank == 0:
-                assert P["send_hi"] == other["recv_lo"] and P["recv_hi"] == other["send_lo"]
                 assert P["h_lo"] == 0 and P["send_lo"] == 0
             else:
-                assert P["send_lo"] == other["recv_hi"] and P["recv_lo"] == other["send_hi"]
+                lower = plans[rank - 1]
+                assert P["send_lo"] == lower["recv_hi"] and P["recv_lo"] == lower["send_hi"]
+            if rank == world - 1:
                 assert P["h_hi"] == 0 and P["send_hi"] == 0
+            else:
+                upper = plans[rank + 1]
+                assert P["send_hi"] == upper["recv_lo"] and P["recv_hi"] == upper["send_lo"]
             assert P["off"] % 16 == 0 and P["off"] >= P["h_lo"]
             assert P["ext_len"] == P["off"] + nloc + P["h_hi"]
         else:
@@ -114,10 +140,38 @@ def _worker(rank, world, port, case, q):
             if rank + 1 < world and P["recv_hi"]:
                 p_ext[P["off"] + nloc:P["off"] + nloc + P["recv_hi"]] = buf_hi.numpy()
 
-        def matvec(v_own):
+        # peer-memory layout: my push items, and (from the peers' plans) what lands where in mine
+        my_items, my_waits = _push_plan(pkg, world, rank, n, info, dense)
+        incoming = []
+        for g_ in range(world):
+            if g_ == rank:
+                continue
+            for it_ in _push_plan(pkg, world, g_, n, info, dense)[0]:
+                if it_["peer"] == rank:
+                    incoming.append((g_, it_))
+        assert sorted(my_waits) == sorted({g_ for g_, _ in incoming})
+
+        def exchange_push(p_ext):
+            own = p_ext[P["off"]:P["off"] + nloc]
+            reqs, bufs = [], []
+            for it_ in my_items:
+                reqs.append(dist.isend(torch.from_numpy(own[it_["begin"]:it_["end"]].copy()), it_["peer"]))
+            for g_, it_ in incoming:
+                buf = torch.zeros(it_["end"] - it_["begin"], dtype=torch.float64)
+                bufs.append((it_["dst"], buf))
+                reqs.append(dist.irecv(buf, g_))
+            for r_ in reqs:
+                r_.wait()
+            for dst, buf in bufs:
+                assert dst >= 0 and dst + len(buf) <= P["ext_len"]
+                # a push never lands on the rows this rank owns
+                assert dst + len(buf) <= P["off"] or dst >= P["off"] + nloc
+                p_ext[dst:dst + len(buf)] = buf.numpy()
+
+        def matvec(v_own, push=False):
             p_ext = np.zeros(P["ext_len"])
             p_ext[P["off"]:P["off"] + nloc] = v_own
-            exchange(p_ext)
+            (exchange_push if push else exchange)(p_ext)
             out = np.empty(nloc)
             O.oracle_spmv(nloc, HH.iptr(rp_l), HH.iptr(cols_l), HH.dptr(vals), HH.dptr(p_ext), HH.dptr(out))
             return out
@@ -133,6 +187,8 @@ def _worker(rank, world, port, case, q):
         O.oracle_spmv(n, HH.iptr(s.row_ptr), HH.iptr(s.cols), HH.dptr(s.vals), HH.dptr(v), HH.dptr(want))
         got = matvec(v[row0:row0 + nloc].copy())
         ok_mv = bool(np.array_equal(got.view(np.uint64), want[row0:row0 + nloc].view(np.uint64)))
+        got2 = matvec(v[row0:row0 + nloc].copy(), push=True)
+        ok_mv = ok_mv and bool(np.array_equal(got2.view(np.uint64), want[row0:row0 + nloc].view(np.uint64)))
 
         # 2) the loop of cg.c:104-135 on row blocks with global scalars
         b = s.b[row0:row0 + nloc].copy()
@@ -153,22 +209,54 @@ def _worker(rank, world, port, case, q):
             rr = rr_new
         xo, _, _, _ = HH.oracle_cg(s, M)
         diff = float(np.linalg.norm(x - xo[row0:row0 + nloc]) / np.linalg.norm(xo))
-        q.put((rank, ok_mv, diff, P))
+
+        # 3) the single-reduction recurrence (include/cgb200.h) over the peer-memory layout: one
+        #    fused pair of sums per iteration, against its CPU restatement
+        x = np.zeros(nloc)
+        g_v = b.copy()
+        d = np.zeros(nloc)
+        sv = np.zeros(nloc)
+        w = matvec(g_v, push=True)
+
+        def gsum2(a_, b_):
+            t = torch.tensor([a_, b_], dtype=torch.float64)
+            dist.all_reduce(t)
+            return float(t[0]), float(t[1])
+
+        rr, rw = gsum2(float(np.dot(g_v, g_v)), float(np.dot(g_v, w)))
+        alpha, beta = rr / rw, 0.0
+        for k in range(M + 1):
+            d = g_v + beta * d
+            sv = w + beta * sv
+            x = x + alpha * d
+            g_v = g_v - alpha * sv
+            w = matvec(g_v, push=True)
+            rr_new, rw = gsum2(float(np.dot(g_v, g_v)), float(np.dot(g_v, w)))
+            if k == M:
+                break
+            beta = rr_new / rr
+            alpha = rr_new / (rw - beta * rr_new / alpha)
+            rr = rr_new
+        xs, its, _, _ = HH.oracle_cg_sr(s, M)
+        assert its == M + 1
+        diff_sr = float(np.linalg.norm(x - xs[row0:row0 + nloc]) / np.linalg.norm(xs))
+        q.put((rank, ok_mv, max(diff, diff_sr), P))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("case", ["lap2d", "lap3d", "banded", "dense"])
-def test_two_rank_row_blocks_reproduce_one_rank(case):
+@pytest.mark.parametrize("world,case", [(2, "lap2d"), (2, "lap3d"), (2, "banded"), (2, "dense"),
+                                        (3, "lap3d"), (3, "banded"), (3, "dense")])
+def test_row_blocks_reproduce_one_rank(world, case):
     import torch.multiprocessing as mp
 
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, case, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, case, q)) for r in range(world)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=180) for _ in range(2)]
+    res = [q.get(timeout=180) for _ in range(world)]
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0

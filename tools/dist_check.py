@@ -23,12 +23,13 @@ L = pkg.lib()
 assert L.cgb200_init(lr) == 0, pkg.last_error()
 dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
 idbuf = (C.c_ubyte * 128)()
-if rank == 0:
+if rank == 0 and world > 1:
     assert L.cgb200_dist_unique_id(idbuf) == 0, pkg.last_error()
 t = torch.tensor(list(bytes(idbuf)), dtype=torch.uint8, device="cuda")
 dist.broadcast(t, 0)
 idbuf = (C.c_ubyte * 128).from_buffer_copy(bytes(t.cpu().tolist()))
 assert L.cgb200_dist_init(rank, world, idbuf) == 0, pkg.last_error()
+SR = pkg.SINGLE_REDUCTION
 
 
 def gather_x(d, n, counts):
@@ -68,7 +69,24 @@ r = d.solve(60)
 x = gather_x(d, s.n, [nx * ny * nzl] * world)
 xo, it, _, _ = H.oracle_cg(s, 60)
 rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+mode = "p2p" if L.cgb200_system_comm_is_p2p(d.h) else L.cgb200_dist_comm_mode().decode()
+if rank == 0:
+    print(f"comm {mode} (requested {os.environ.get('CGB200_COMM', 'p2p')}), world {world}", flush=True)
+if world > 1 and os.environ.get("CGB200_COMM", "p2p") == "p2p" and os.environ.get("CGB200_REQUIRE_P2P"):
+    assert mode == "p2p", "peer-memory mode was requested but the library fell back to NCCL"
 report("lap3d fixed-count", r.iterations == it and rel <= 1e-8, f"iters {r.iterations}/{it} rel {rel:.2e} world {r.world}")
+r = d.solve(60, variant=SR)
+x = gather_x(d, s.n, [nx * ny * nzl] * world)
+xs, its, _, _ = H.oracle_cg_sr(s, 60)
+rel = np.linalg.norm(x - xs) / np.linalg.norm(xs)
+report("lap3d fixed-count single-reduction", r.iterations == its and rel <= 1e-8, f"iters {r.iterations}/{its} rel {rel:.2e}")
+# back to back solves on the same system (mailbox epochs carry over), alternating variants
+for rep in range(3):
+    r = d.solve(17, variant=rep % 2)
+    x = gather_x(d, s.n, [nx * ny * nzl] * world)
+    xo17, it17, _, _ = H.oracle_cg(s, 17)
+    rel = np.linalg.norm(x - xo17) / np.linalg.norm(xo17)
+    report(f"lap3d repeat {rep}", r.iterations == it17 and rel <= 1e-8, f"rel {rel:.2e}")
 r = d.solve(100000, tol=1e-10)
 xo, it, _, st = H.oracle_cg(s, 100000, tol=1e-10, guard=1)
 x = gather_x(d, s.n, [nx * ny * nzl] * world)
@@ -76,6 +94,23 @@ tr = d.true_relres()
 rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
 report("lap3d tolerance", abs(r.iterations - it) <= 2 and tr <= 1.05e-10 and rel <= 1e-8,
        f"iters {r.iterations}/{it} true relres {tr:.2e} rel {rel:.2e}")
+r = d.solve(100000, tol=1e-10, variant=SR)
+x = gather_x(d, s.n, [nx * ny * nzl] * world)
+tr = d.true_relres()
+rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+report("lap3d tolerance single-reduction", abs(r.iterations - it) <= 2 and tr <= 1.05e-10 and rel <= 1e-8,
+       f"iters {r.iterations}/{it} true relres {tr:.2e} rel {rel:.2e}")
+# plain products through the exchange (operator-API path), bit-exact per row
+v = H.rhs(s.n, 77)
+want = np.empty(s.n)
+H.oracle().oracle_spmv(s.n, H.iptr(s.row_ptr), H.iptr(s.cols), H.dptr(s.vals), H.dptr(v), H.dptr(want))
+nl_ = nx * ny * nzl
+for rep in range(2):
+    got = d.matvec(v[rank * nl_:(rank + 1) * nl_])
+    okb = np.array_equal(got.view(np.uint64), want[rank * nl_:(rank + 1) * nl_].view(np.uint64))
+    tt = torch.tensor([1.0 if okb else 0.0], device="cuda")
+    dist.all_reduce(tt, op=dist.ReduceOp.MIN)
+    report(f"lap3d plain matvec bit-exact {rep}", tt.item() == 1.0, "")
 d.free()
 
 # 2) bigger slab so interior and boundary tiles both exist (tile = 512 rows)
@@ -88,6 +123,10 @@ x = gather_x(d, s.n, [nx * ny * nzl] * world)
 xo, it, _, _ = H.oracle_cg(s, 40)
 rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
 report("lap3d split-launch", r.iterations == it and rel <= 1e-8, f"rel {rel:.2e}")
+r = d.solve(40, variant=SR)
+x = gather_x(d, s.n, [nx * ny * nzl] * world)
+rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+report("lap3d split-launch single-reduction", r.iterations == it and rel <= 1e-8, f"rel {rel:.2e}")
 d.free()
 
 # 3) dense, all-gather mode
@@ -100,6 +139,10 @@ x = gather_x(d, n, [nl] * world)
 xo, it, _, _ = H.oracle_cg(s, 200, tol=1e-10, guard=1)
 rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
 report("dense all-gather", abs(r.iterations - it) <= 2 and rel <= 1e-8, f"iters {r.iterations}/{it} rel {rel:.2e}")
+r = d.solve(200, tol=1e-10, variant=SR)
+x = gather_x(d, n, [nl] * world)
+rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+report("dense all-gather single-reduction", abs(r.iterations - it) <= 2 and rel <= 1e-8, f"iters {r.iterations}/{it} rel {rel:.2e}")
 d.free()
 
 # 4) host CSR row blocks, uneven, banded (neighbour mode) and wide band (all-gather fallback)
@@ -110,11 +153,12 @@ for hb, name in ((7, "banded neighbour"), (900, "banded wide")):
     nl = cnt[rank]
     rp = s.row_ptr[row0:row0 + nl + 1]
     d = pkg.DeviceSystem.from_csr(s.n, row0, rp - rp[0], s.cols[rp[0]:rp[-1]], s.vals[rp[0]:rp[-1]], s.b[row0:row0 + nl])
-    r = d.solve(15)
-    x = gather_x(d, s.n, cnt)
-    xo, it, _, _ = H.oracle_cg(s, 15)
-    rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
-    report("from_csr " + name, r.iterations == it and rel <= 1e-8, f"rel {rel:.2e}")
+    for variant in (0, SR):
+        r = d.solve(15, variant=variant)
+        x = gather_x(d, s.n, cnt)
+        xo, it, _, _ = H.oracle_cg(s, 15)
+        rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+        report(f"from_csr {name} variant {variant}", r.iterations == it and rel <= 1e-8, f"rel {rel:.2e}")
     d.free()
 
 L.cgb200_dist_finalize()
