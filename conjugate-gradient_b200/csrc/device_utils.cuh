@@ -42,6 +42,21 @@ __device__ __forceinline__ double ld_keep(const double* ptr, uint64_t pol) {
   return v;
 }
 
+// Same, predicated inside the instruction (0.0 when !ok): no branch around the load, so a row's
+// gathers stay in one basic block and can all be in flight together.
+__device__ __forceinline__ double ld_keep_if(const double* ptr, uint64_t pol, bool ok) {
+  double v;
+  asm("{\n"
+      ".reg .pred p;\n"
+      "setp.ne.s32 p, %3, 0;\n"
+      "mov.f64 %0, 0d0000000000000000;\n"
+      "@p ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;\n"
+      "}\n"
+      : "=d"(v)
+      : "l"(ptr), "l"(pol), "r"((int)ok));
+  return v;
+}
+
 // Streamed-once operand, 128 bit: bypass L1 allocation, evict-first in L2.
 __device__ __forceinline__ double2 ld_stream2(const double* ptr, uint64_t pol) {
   double2 v;
@@ -122,6 +137,11 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
       "[%0], [%1], %2, [%3], %4;" ::"r"(smem_addr(dst_smem)),
       "l"(src_gmem), "r"(bytes), "r"(smem_addr(bar)), "l"(pol)
       : "memory");
+}
+
+// Asks L2 to fetch [src, src + bytes) (multiple of 16, 16-byte aligned); nothing is written.
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src_gmem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -228,7 +248,19 @@ __device__ __forceinline__ void st_relaxed_sys(double* p, double v) {
 // already have been running, so go to L2 (the coherence point for peer writes), never L1.
 __device__ __forceinline__ double ld_l2(const double* p) {
   double v;
-  asm volatile("ld.relaxed.gpu.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.gpu.global.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ double ld_l2_if(const double* p, bool ok) {
+  double v;
+  asm volatile("{\n"
+               ".reg .pred p;\n"
+               "setp.ne.s32 p, %2, 0;\n"
+               "mov.f64 %0, 0d0000000000000000;\n"
+               "@p ld.relaxed.gpu.global.f64 %0, [%1];\n"
+               "}\n"
+               : "=d"(v)
+               : "l"(p), "r"((int)ok));
   return v;
 }
 __device__ __forceinline__ unsigned long long global_ns() {

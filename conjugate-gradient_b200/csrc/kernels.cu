@@ -56,6 +56,12 @@ struct SpmvSmem {
   static constexpr size_t rp_bytes = (size_t)STAGES * RPN * 4;
   static constexpr size_t bar_bytes = (size_t)STAGES * 16;
   static constexpr size_t total = vals_bytes + cols_bytes + rp_bytes + bar_bytes + 16;
+  // CTAs per SM that shared memory and the thread count allow.  Told to the compiler through
+  // __launch_bounds__: ptxas otherwise budgets registers for the occupancy the block size alone
+  // would permit (3 CTAs of 544 threads -> 40 registers) and serialises the row's gathers to fit.
+  static constexpr int by_smem = (int)((227u * 1024u) / (total + 2048u));
+  static constexpr int by_threads = 2048 / (R + 32);
+  static constexpr int min_ctas = by_smem < by_threads ? (by_smem < 1 ? 1 : by_smem) : by_threads;
 };
 
 // Up to three runs of tiles, visited in this order.  With several GPUs run 0 holds the interior
@@ -70,39 +76,47 @@ __device__ __forceinline__ int vtile_to_tile(const TileRange& tr, int v) {
 
 // One row's share of a staged chunk: entries [k, k1) of the stage, ascending column order.
 // COHERENT = the gathered values may have been written by a peer GPU during this kernel.
+//
+// The gathers are the only long-latency operations of the consumer, so the body is kept free of
+// branches: the staged column indices and values are read unconditionally (reading a few entries
+// past the row stays inside the CTA's shared memory) and the gather is predicated inside the
+// instruction.  All (up to 8) gathers of a row are then issued back to back before the first
+// product is formed; with a branch around each load ptxas emitted load, multiply, add per entry,
+// i.e. one or two gathers in flight per thread.  The sum itself is still taken entry by entry in
+// ascending column order with unfused multiply and add (mv_ops.c:106-110,192-194).
 template <bool COHERENT>
 __device__ __forceinline__ double walk_row(const double* __restrict__ v_s,
                                            const int* __restrict__ c_s, int k, const int k1,
                                            const double* __restrict__ pg, const uint64_t pol,
                                            double acc) {
   while (k < k1) {
+    int c[8];
     double v[8], pv[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const bool ok = (k + j) < k1;
-      v[j] = 0.0;
-      pv[j] = 0.0;
-      if (ok) {
-        v[j] = v_s[k + j];
-        pv[j] = COHERENT ? ld_l2(pg + c_s[k + j]) : ld_keep(pg + c_s[k + j], pol);
-      }
-    }
+    for (int j = 0; j < 8; ++j) c[j] = c_s[k + j];
 #pragma unroll
     for (int j = 0; j < 8; ++j)
-      if ((k + j) < k1) acc = __dadd_rn(acc, __dmul_rn(v[j], pv[j]));
+      pv[j] = COHERENT ? ld_l2_if(pg + c[j], (k + j) < k1) : ld_keep_if(pg + c[j], pol, (k + j) < k1);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = v_s[k + j];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const double t = __dadd_rn(acc, __dmul_rn(v[j], pv[j]));
+      acc = (k + j) < k1 ? t : acc;
+    }
     k += 8;
   }
   return acc;
 }
 
 template <int R, int CAP, int STAGES>
-__global__ void __launch_bounds__(R + 32)
+__global__ void __launch_bounds__(R + 32, SpmvSmem<R, CAP, STAGES>::min_ctas)
 k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
               const int* __restrict__ rowptr, int nrows, const double* __restrict__ pg,
               const double* __restrict__ pown, double* __restrict__ s, const TileRange tr,
-              const int wait_from, double* __restrict__ partials,
-              unsigned int* __restrict__ ticket, CgState* S, const int mode, const int hint,
-              const __grid_constant__ PeerComm cm) {
+              const int wait_from, const long long lead, const long long plen,
+              double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
+              const int mode, const int hint, const __grid_constant__ PeerComm cm) {
   using SM = SpmvSmem<R, CAP, STAGES>;
   constexpr int THREADS = R + 32;
   constexpr int CWARPS = R / 32;
@@ -160,6 +174,14 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
           const int t2 = vtile_to_tile(tr, vt2);
           nlo = __ldg(rowptr + t2 * R);
           nhi = __ldg(rowptr + min(t2 * R + R, nrows));
+          if (lead >= 0) {
+            // banded matrix: the only gathered values of the next tile that nobody has touched yet
+            // are the R entries at its upper band edge; have L2 fetch them one tile ahead so the
+            // consumers' first touch is an L2 hit instead of a DRAM round trip per row
+            const long long i0 = ((long long)t2 * R + lead) & ~1ll;
+            const long long cnt = min((long long)R + 2, plen - i0) & ~1ll;
+            if (cnt > 0) bulk_prefetch_l2(pg + i0, (uint32_t)cnt * 8u);
+          }
         }
         const int nchunks = max(1, (hi - lo + CAP - 1) / CAP);
 #pragma unroll 1
@@ -369,6 +391,150 @@ k_gemv_rows(const double* __restrict__ A, long long ld, int nrows, int ncols,
     v[1] = 0.0;
   }
   if (last) finish_block<THREADS>(S, cm, fin, v[0], v[1]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1-dense, balanced form (the default whenever 256-bit loads are possible).
+//
+// k_gemv_rows deals whole row groups to CTAs, so the slowest CTA owns ceil(groups / grid) of them:
+// 3 % idle tail on one GPU (8192 groups over 444 CTAs), 30 % on an eighth of the matrix.  Here the
+// work is cut into units of RB rows x CW columns and CTA c owns the contiguous unit range
+// [U c / grid, U (c+1) / grid): every CTA streams the same number of bytes (+- one unit).  Row
+// groups that straddle two CTAs are finished by the last CTA of the grid: each CTA leaves at most
+// two records {group, RB partial row sums} (its first and its last group when incomplete), and the
+// CTA that draws the last ticket adds the records of a group in CTA order -- fixed order, so s and
+// p.s stay run-to-run reproducible -- before it closes the fused reduction.
+// ---------------------------------------------------------------------------------------------
+
+constexpr int GEMV_REC_OFFSET = 2 * PART_STRIDE;  // records live behind the reduction partials
+
+template <int THREADS, int RB>
+__global__ void __launch_bounds__(THREADS)
+k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
+             const double* __restrict__ pg, const double* __restrict__ pown,
+             double* __restrict__ s, double* __restrict__ partials,
+             unsigned int* __restrict__ ticket, CgState* S, const int mode, const int wait,
+             const __grid_constant__ PeerComm cm) {
+  constexpr int CW = THREADS * 4;  // columns per unit: one 256-bit load per thread
+  constexpr int REC = RB + 1;
+  const int fin = mode & MV_FIN_MASK;
+  if (fin != FIN_NONE && S->done) return;
+  __shared__ double sm_red[RB][THREADS / 32];
+  __shared__ double sm_rec[2][REC];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < 2) sm_rec[tid][0] = -1.0;
+  if (wait) {  // the peers' slices of the gather vector must have landed (all-gather mode)
+    if (tid == 0) wait_halo(cm, S);
+  }
+  __syncthreads();
+
+  const int cpg = (ncols + CW - 1) / CW;          // units per row group
+  const int ngroups = (nrows + RB - 1) / RB;
+  const long long U = (long long)ngroups * cpg;
+  long long u = U * blockIdx.x / gridDim.x;
+  const long long u1 = U * (blockIdx.x + 1) / gridDim.x;
+  double dot = 0.0, dot2 = 0.0;
+  int nrec = 0;
+
+#pragma unroll 1
+  while (u < u1) {
+    const int g = (int)(u / cpg), ka = (int)(u % cpg);
+    const int kb = (int)min((long long)cpg, ka + (u1 - u));
+    const int row0 = g * RB;
+    const double* rowp[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) rowp[r] = A + (long long)min(row0 + r, nrows - 1) * ld;
+    double acc[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) acc[r] = 0.0;
+    const int cend = min(kb * CW, ncols);
+#pragma unroll 2
+    for (int c = ka * CW + tid * 4; c < cend; c += CW) {
+      const double4_t pv = *reinterpret_cast<const double4_t*>(pg + c);
+      double4_t a[RB];
+#pragma unroll
+      for (int r = 0; r < RB; ++r) a[r] = ld_stream4(rowp[r] + c);
+#pragma unroll
+      for (int r = 0; r < RB; ++r) {
+        acc[r] = fma(a[r].x, pv.x, acc[r]);
+        acc[r] = fma(a[r].y, pv.y, acc[r]);
+        acc[r] = fma(a[r].z, pv.z, acc[r]);
+        acc[r] = fma(a[r].w, pv.w, acc[r]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < RB; ++r) acc[r] = warp_sum(acc[r]);
+    __syncthreads();
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < RB; ++r) sm_red[r][warp] = acc[r];
+    }
+    __syncthreads();
+    const bool whole = (ka == 0 && kb == cpg);
+    if (tid < RB) {
+      double t = 0.0;
+#pragma unroll
+      for (int w = 0; w < THREADS / 32; ++w) t += sm_red[tid][w];
+      if (whole) {
+        if (row0 + tid < nrows) {
+          s[row0 + tid] = t;
+          if (fin != FIN_NONE) {
+            const double gv = pown[row0 + tid];
+            dot += gv * t;
+            dot2 += gv * gv;
+          }
+        }
+      } else {
+        sm_rec[nrec][1 + tid] = t;
+        if (tid == 0) sm_rec[nrec][0] = (double)g;
+      }
+    }
+    if (!whole) ++nrec;  // at most the first and the last group of a CTA are incomplete
+    u += kb - ka;
+  }
+  __syncthreads();
+  double* recs = partials + GEMV_REC_OFFSET;
+  if (tid < 2 * REC) recs[(size_t)blockIdx.x * 2 * REC + tid] = (&sm_rec[0][0])[tid];
+
+  double v[2] = {dot, dot2};
+  if (!grid_reduce<THREADS, 2>(v, partials, ticket)) return;
+
+  // last CTA: finish the row groups shared between CTAs
+  const int nslots = 2 * (int)gridDim.x;
+  double fdot = 0.0, fdot2 = 0.0;
+  for (int i = tid; i < nslots; i += THREADS) {
+    const double gi = __ldcg(recs + (size_t)i * REC);
+    if (gi < 0.0) continue;
+    int j = i - 1;
+    while (j >= 0 && __ldcg(recs + (size_t)j * REC) < 0.0) --j;
+    if (j >= 0 && __ldcg(recs + (size_t)j * REC) == gi) continue;  // not the first record of its group
+    double t[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) t[r] = 0.0;
+    for (int k = i; k < nslots; ++k) {
+      const double gk = __ldcg(recs + (size_t)k * REC);
+      if (gk < 0.0) continue;
+      if (gk != gi) break;
+#pragma unroll
+      for (int r = 0; r < RB; ++r) t[r] += __ldcg(recs + (size_t)k * REC + 1 + r);
+    }
+    const int row0 = (int)gi * RB;
+#pragma unroll
+    for (int r = 0; r < RB; ++r)
+      if (row0 + r < nrows) {
+        s[row0 + r] = t[r];
+        if (fin != FIN_NONE) {
+          const double gv = pown[row0 + r];
+          fdot += gv * t[r];
+          fdot2 += gv * gv;
+        }
+      }
+  }
+  if (fin == FIN_NONE) return;
+  __shared__ double sm_fix[THREADS / 32];
+  fdot = block_sum<THREADS>(fdot, sm_fix);
+  fdot2 = block_sum<THREADS>(fdot2, sm_fix);
+  finish_block<THREADS>(S, cm, fin, v[0] + fdot, (mode & MV_DUAL) ? v[1] + fdot2 : 0.0);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -785,6 +951,20 @@ __global__ void k_analyze(const int* __restrict__ rowptr, const int* __restrict_
   }
 }
 
+// Largest (gather index of a row's last entry) - (local row) over all rows: the offset of the upper
+// band edge in the gather vector (columns are ascending within a row).
+__global__ void k_upper_band(const int* __restrict__ rowptr, const int* __restrict__ cols, int nrows,
+                             int* __restrict__ out) {
+  const int stride = gridDim.x * blockDim.x;
+  int mx = -0x7fffffff - 1;
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < nrows; r += stride) {
+    const int a = rowptr[r], b = rowptr[r + 1];
+    if (b > a) mx = max(mx, cols[b - 1] - r);
+  }
+  for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(out, mx);
+}
+
 __global__ void k_shift_cols(int* __restrict__ cols, long long nnz, int shift) {
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += stride)
@@ -814,6 +994,7 @@ static inline int vec_grid(long long n) {
 }
 
 int max_partials() { return PART_STRIDE; }
+int partials_doubles() { return 3 * PART_STRIDE; }  // two reduction values + GEMV records
 
 // SpMV tile configurations.  One is chosen per process (CGB200_SPMV_CFG, default 0); DESIGN.md
 // records the sweep that picked the default.
@@ -822,18 +1003,19 @@ struct SpmvCfg {
   size_t smem;
   const void* fn;
   void (*launch)(int grid, cudaStream_t st, const CsrDev& A, const double* pg, const double* pown,
-                 double* s, const TileRange& tr, int wait_from, double* partials,
-                 unsigned int* ticket, CgState* S, int mode, int hint, const PeerComm& cm);
+                 double* s, const TileRange& tr, int wait_from, long long lead, long long plen,
+                 double* partials, unsigned int* ticket, CgState* S, int mode, int hint,
+                 const PeerComm& cm);
 };
 
 template <int R, int CAP, int STAGES>
 static void spmv_launch_t(int grid, cudaStream_t st, const CsrDev& A, const double* pg,
                           const double* pown, double* s, const TileRange& tr, int wait_from,
-                          double* partials, unsigned int* ticket, CgState* S, int mode, int hint,
-                          const PeerComm& cm) {
+                          long long lead, long long plen, double* partials, unsigned int* ticket,
+                          CgState* S, int mode, int hint, const PeerComm& cm) {
   k_spmv_stream<R, CAP, STAGES><<<grid, R + 32, SpmvSmem<R, CAP, STAGES>::total, st>>>(
-      A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s, tr, wait_from, partials, ticket, S, mode,
-      hint, cm);
+      A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s, tr, wait_from, lead, plen, partials, ticket,
+      S, mode, hint, cm);
 }
 
 #define SPMV_CFG(R, CAP, ST)                                                        \
@@ -895,8 +1077,8 @@ cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, d
   const int nvt = (tr.e[0] - tr.b[0]) + (tr.e[1] - tr.b[1]) + (tr.e[2] - tr.b[2]);
   if (nvt <= 0) return cudaSuccess;
   const SpmvCfg& c = spmv_cfg();
-  c.launch(spmv_grid_for(nvt), st, A, pg, pown, s, tr, wait_from, partials, ticket, S, mode,
-           g_spmv_hint, cm);
+  c.launch(spmv_grid_for(nvt), st, A, pg, pown, s, tr, wait_from, A.lead, A.plen, partials, ticket,
+           S, mode, g_spmv_hint, cm);
   ++g_launches;
   return cudaGetLastError();
 }
@@ -924,14 +1106,45 @@ static cudaError_t launch_gemv_vec(const double* A, long long ld, int nrows, int
   return cudaGetLastError();
 }
 
+static cudaError_t launch_gemv_units(const double* A, long long ld, int nrows, int ncols,
+                                     const double* pg, const double* pown, double* s,
+                                     double* partials, unsigned int* ticket, CgState* S, int mode,
+                                     int wait, const PeerComm& cm, cudaStream_t st) {
+  static int bps = 0;
+  if (!bps) {
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_gemv_units<GV_T, GV_RB>, GV_T, 0);
+    if (bps < 1) bps = 1;
+  }
+  const long long units =
+      (long long)((nrows + GV_RB - 1) / GV_RB) * ((ncols + GV_T * 4 - 1) / (GV_T * 4));
+  long long grid = (long long)sm_count() * bps;
+  if (grid > units) grid = units;
+  const long long cap = PART_STRIDE / (2 * (GV_RB + 1));  // room for two records per CTA
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  k_gemv_units<GV_T, GV_RB><<<(int)grid, GV_T, 0, st>>>(A, ld, nrows, ncols, pg, pown, s, partials,
+                                                       ticket, S, mode, wait, cm);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
 cudaError_t launch_gemv(const double* A, long long ld, int nrows, int ncols, const double* pg,
                         const double* pown, double* s, double* partials, unsigned int* ticket,
                         CgState* S, int mode, int wait, const PeerComm& cm, cudaStream_t st) {
+  static int force_rows = -1;
+  if (force_rows < 0) {
+    const char* e = getenv("CGB200_GEMV_ROWS");  // 1 = whole row groups per CTA (comparison runs)
+    force_rows = (e && atoi(e) > 0) ? 1 : 0;
+  }
   const bool al32 = ((uintptr_t)A % 32 == 0) && ((uintptr_t)pg % 32 == 0);
   const bool al16 = ((uintptr_t)A % 16 == 0) && ((uintptr_t)pg % 16 == 0);
-  if (ld % 4 == 0 && ncols % 4 == 0 && al32)
+  if (ld % 4 == 0 && ncols % 4 == 0 && al32) {
+    if (!force_rows)
+      return launch_gemv_units(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, wait,
+                               cm, st);
     return launch_gemv_vec<4>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, wait,
                               cm, st);
+  }
   if (ld % 2 == 0 && ncols % 2 == 0 && al16)
     return launch_gemv_vec<2>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, wait,
                               cm, st);
@@ -1041,6 +1254,16 @@ cudaError_t launch_analyze(const int* rowptr, const int* cols, int nrows, long l
   cudaError_t e = cudaMemcpyAsync(out3, init, sizeof(init), cudaMemcpyHostToDevice, st);
   if (e != cudaSuccess) return e;
   k_analyze<<<sm_count() * 4, 256, 0, st>>>(rowptr, cols, nrows, nnz, ncols, out3);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_upper_band(const int* rowptr, const int* cols, int nrows, int* out1,
+                              cudaStream_t st) {
+  static const int init = -0x7fffffff - 1;
+  cudaError_t e = cudaMemcpyAsync(out1, &init, sizeof(int), cudaMemcpyHostToDevice, st);
+  if (e != cudaSuccess) return e;
+  k_upper_band<<<sm_count() * 4, 256, 0, st>>>(rowptr, cols, nrows, out1);
   ++g_launches;
   return cudaGetLastError();
 }

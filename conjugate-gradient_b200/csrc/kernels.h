@@ -17,6 +17,9 @@ struct CsrDev {
   int* rowptr = nullptr;
   int nrows = 0;
   long long nnz = 0;
+  // banded matrices: gather index of the upper band edge = local row + lead (-1: no prefetch);
+  // plen = length of the gather vector
+  long long lead = -1, plen = 0;
 };
 
 // `mode` of the matvec kernels: a finish kind (what the last CTA does with the fused dot
@@ -42,6 +45,7 @@ struct TileRange {
 
 int sm_count();
 int max_partials();
+int partials_doubles();
 int spmv_rows_per_tile();
 int spmv_grid_for(int ntiles);
 long long launch_count();
@@ -80,6 +84,8 @@ cudaError_t launch_gen_dense(int n, int row0, int nloc, unsigned long long seed,
                              cudaStream_t st);
 cudaError_t launch_analyze(const int* rowptr, const int* cols, int nrows, long long nnz, int ncols,
                            int* out3, cudaStream_t st);
+cudaError_t launch_upper_band(const int* rowptr, const int* cols, int nrows, int* out1,
+                              cudaStream_t st);
 cudaError_t launch_shift_cols(int* cols, long long nnz, int shift, cudaStream_t st);
 
 }  // namespace cgb

@@ -134,7 +134,7 @@ int ensure_init(int device) {
   c.device = device;
   CUDA_OK(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
   CUDA_OK(cudaStreamCreateWithFlags(&c.comm_stream, cudaStreamNonBlocking));
-  CUDA_OK(cudaMalloc(&c.partials, sizeof(double) * max_partials() * 2));
+  CUDA_OK(cudaMalloc(&c.partials, sizeof(double) * partials_doubles()));
   CUDA_OK(cudaMalloc(&c.d_state, sizeof(CgState)));
   CUDA_OK(cudaMemset(c.d_state, 0, sizeof(CgState)));
   CUDA_OK(cudaMallocHost(&c.h_state, sizeof(CgState) * 4));
@@ -457,7 +457,7 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
   CUDA_OK(cudaMemsetAsync(S->x, 0, (nl + 16) * sizeof(double), c.stream));
   CUDA_OK(cudaMalloc(&S->state, sizeof(CgState)));
   CUDA_OK(cudaMemsetAsync(S->state, 0, sizeof(CgState), c.stream));
-  CUDA_OK(cudaMalloc(&S->partials, sizeof(double) * max_partials() * 2));
+  CUDA_OK(cudaMalloc(&S->partials, sizeof(double) * partials_doubles()));
   S->p_own = S->p_ext + S->off;
   if (S->comm_buf && setup_peer_comm(S, parts)) return -1;
 
@@ -468,6 +468,22 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
         return -1;
       }
       CUDA_OK(launch_shift_cols(S->A.cols, S->A.nnz, (int)col_shift, c.stream));
+    }
+    // upper band edge in gather space (after the shift): the stream kernel prefetches it
+    S->A.plen = S->ext_len;
+    S->A.lead = -1;
+    // (opt-in, CGB200_SPMV_PREFETCH=1: once the consumers keep a whole row's gathers in flight the
+    // prefetch no longer pays on the 3D stencils -- profiles/r01_spmv_gather_batching.md)
+    const char* pf = getenv("CGB200_SPMV_PREFETCH");
+    if (S->nloc > 0 && S->A.nnz > 0 && pf && atoi(pf) > 0) {
+      int* d1 = (int*)c.d_scratch + 8;
+      CUDA_OK(launch_upper_band(S->A.rowptr, S->A.cols, S->nloc, d1, c.stream));
+      CUDA_OK(cudaMemcpyAsync((int*)c.h_scratch + 8, d1, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+      CUDA_OK(cudaStreamSynchronize(c.stream));
+      const long long lead = ((int*)c.h_scratch)[8];
+      // worth it only for a band that is wide enough to fall out of the tile's own footprint and
+      // narrow enough to be a band at all
+      if (lead > 4 * spmv_rows_per_tile() && lead < S->ext_len) S->A.lead = lead;
     }
     const int R = spmv_rows_per_tile();
     S->ntiles = (S->nloc + R - 1) / R;

@@ -214,9 +214,11 @@ def test_mv_mult_ragged_rows_bit_exact(pkg, gpu_lib):
     gpu_lib.cgb200_invalidate(C.byref(A))
 
 
-@pytest.mark.parametrize("n", [1, 2, 3, 7, 64, 513, 1024, 2050])
+@pytest.mark.parametrize("n", [1, 2, 3, 7, 64, 513, 1024, 2050, 2052, 4104])
 def test_mv_mult_dense_path(pkg, gpu_lib, n):
-    # full rows take the values-only row-block GEMV; tree summation => tolerance, not bits
+    # full rows take the values-only GEMV; tree summation => tolerance, not bits.  n % 4 == 0 takes
+    # the balanced unit-range kernel (2052 and 4104: row groups shared between CTAs, fixed up by the
+    # last CTA), the rest the whole-row-group kernel
     s = H.dense(n)
     A, _ = _structs(pkg, s)
     v = H.rhs(n, 97)
@@ -242,6 +244,7 @@ LOOP_CASES = [
     (lambda: H.banded(3000, 5), 12),
     (lambda: H.dense(512), 3),
     (lambda: H.dense(1000), 4),
+    (lambda: H.dense(2052), 3),
     (lambda: H.lap(7, 5), 0),
     (lambda: H.lap(301, 299), 200),
 ]
