@@ -165,14 +165,29 @@ class Runner:
         if self.J is None:
             r = self.d.solve(K - 1, variant=self.variant)
             return r.iterations
-        while done < K:
-            j = min(self.J, K - done)
+        # back-to-back fixed-count solves, queued a few ahead of the GPU (cgb200_system_solve_async):
+        # right-hand side generation and the solve are stream-ordered, results are collected behind
+        pending = []
+        queued = 0
+
+        def collect():
+            nonlocal done
+            j_, t_ = pending.pop(0)
+            r = self.d.solve_wait(t_)
+            done += r.iterations
+            if r.iterations != j_:
+                raise RuntimeError(f"solve stopped early: {r.iterations} of {j_} (status {r.status})")
+
+        while queued < K:
+            j = min(self.J, K - queued)
             self.seed += 1
             self.d.gen_rhs(self.seed)     # fresh right-hand side, generated on the device
-            r = self.d.solve(j - 1, variant=self.variant)
-            done += r.iterations
-            if r.iterations != j:
-                raise RuntimeError(f"solve stopped early: {r.iterations} of {j} (status {r.status})")
+            pending.append((j, self.d.solve_async(j - 1, variant=self.variant)))
+            queued += j
+            if len(pending) >= 4:
+                collect()
+        while pending:
+            collect()
         return done
 
 

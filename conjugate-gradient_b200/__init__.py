@@ -148,6 +148,8 @@ def lib():
     L.cgb200_system_gen_rhs.argtypes = [C.c_void_p, C.c_uint64]
     L.cgb200_system_get_x.argtypes = [C.c_void_p, c_double_p]
     L.cgb200_system_solve.argtypes = [C.c_void_p, C.POINTER(Opts), C.POINTER(Result)]
+    L.cgb200_system_solve_async.argtypes = [C.c_void_p, C.POINTER(Opts), C.POINTER(C.c_longlong)]
+    L.cgb200_solve_wait.argtypes = [C.c_longlong, C.POINTER(Result)]
     L.cgb200_system_matvec.argtypes = [C.c_void_p, c_double_p, c_double_p]
     L.cgb200_system_true_relres.argtypes = [C.c_void_p, c_double_p]
     L.cgb200_system_time_kernel.argtypes = [C.c_void_p, C.c_int, C.c_int, c_double_p]
@@ -229,6 +231,19 @@ class DeviceSystem:
         o = Opts(max_iter, tol, variant, check_every, 0)
         r = Result()
         _check(lib().cgb200_system_solve(self.h, C.byref(o), C.byref(r)), "cgb200_system_solve")
+        return r
+
+    def solve_async(self, max_iter, variant=CLASSIC, check_every=0):
+        """Queue a fixed-count solve; returns a ticket for solve_wait()."""
+        o = Opts(max_iter, 0.0, variant, check_every, 0)
+        t = C.c_longlong(-1)
+        _check(lib().cgb200_system_solve_async(self.h, C.byref(o), C.byref(t)), "cgb200_system_solve_async")
+        return t.value
+
+    @staticmethod
+    def solve_wait(ticket):
+        r = Result()
+        _check(lib().cgb200_solve_wait(ticket, C.byref(r)), "cgb200_solve_wait")
         return r
 
     def gen_rhs(self, seed):

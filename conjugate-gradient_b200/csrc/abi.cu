@@ -627,6 +627,18 @@ int cgb200_system_solve(cgb200_system* sys, const cgb200_opts* opts, cgb200_resu
   return rc;
 }
 
+int cgb200_system_solve_async(cgb200_system* sys, const cgb200_opts* opts, long long* ticket) {
+  return system_solve_async((System*)sys, to_opts(opts), ticket);
+}
+
+int cgb200_solve_wait(long long ticket, cgb200_result* res) {
+  SolveResult r;
+  memset(&r, 0, sizeof(r));
+  const int rc = system_solve_wait(ticket, &r);
+  fill_result(r, res);
+  return rc;
+}
+
 int cgb200_system_matvec(cgb200_system* sys, const double* v_host, double* s_host) {
   if (!sys || !v_host || !s_host) return -1;
   return system_matvec((System*)sys, v_host, s_host);

@@ -1027,6 +1027,132 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Asynchronous fixed-count solves: enqueue now, collect the result later.  A fixed-count solve
+// needs no decision from the host (the stop flag only matters for a tolerance), so the whole of
+// it -- scalars upload, loop entry, the graph launches, the read-back of the final scalars -- is
+// queued without a single synchronisation and the host is free to queue the next right-hand side
+// and the next solve behind it: back-to-back solves leave no idle gap on the GPU.
+// ---------------------------------------------------------------------------------------------
+
+constexpr int ASYNC_SLOTS = 8;
+struct AsyncSlot {
+  CgState* up = nullptr;    // pinned: scalars uploaded at the start of the solve
+  CgState* down = nullptr;  // pinned: scalars read back at its end
+  cudaEvent_t t0 = nullptr, t1 = nullptr, done = nullptr;
+  long long launches = 0;
+  System* sys = nullptr;
+  long long ticket = -1;
+};
+static AsyncSlot g_async[ASYNC_SLOTS];
+static long long g_async_next = 0;
+
+static int async_slot_init(AsyncSlot& a) {
+  if (a.up) return 0;
+  CUDA_OK(cudaMallocHost(&a.up, sizeof(CgState) * 2));
+  a.down = a.up + 1;
+  CUDA_OK(cudaEventCreate(&a.t0));
+  CUDA_OK(cudaEventCreate(&a.t1));
+  CUDA_OK(cudaEventCreateWithFlags(&a.done, cudaEventDisableTiming));
+  return 0;
+}
+
+int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out) {
+  Ctx& c = g_ctx;
+  if (!S || !ticket_out) {
+    set_error("system_solve_async: NULL argument");
+    return -1;
+  }
+  if (o.tol > 0.0) {
+    set_error("system_solve_async: only fixed-count solves (tol = 0) can be queued; a tolerance "
+              "needs the host to watch the stop flag -- use cgb200_system_solve");
+    return -1;
+  }
+  if (o.variant != 0 && o.variant != 1) {
+    set_error("system_solve_async: unknown variant");
+    return -1;
+  }
+  AsyncSlot& a = g_async[g_async_next % ASYNC_SLOTS];
+  if (a.ticket >= 0) {
+    set_error("system_solve_async: too many solves in flight; collect earlier tickets first");
+    return -1;
+  }
+  if (async_slot_init(a)) return -1;
+  CUDA_OK(cudaSetDevice(c.device));
+  const int variant = o.variant;
+  const bool nccl = S->world > 1 && !S->p2p;
+  const PeerComm& cm = comm_of(S);
+  const long long launches0 = launch_count();
+  const int max_iter = o.max_iter < 0 ? 0 : o.max_iter;
+  memset(a.up, 0, sizeof(CgState));
+  a.up->max_iter = max_iter;
+  a.up->variant = variant;
+  if (variant == 1 && ensure_w(S)) return -1;
+  const long long total_updates = (long long)max_iter + 1;
+  int batch = o.check_every > 0 ? o.check_every : 32;
+  if (batch > total_updates) batch = (int)total_updates;
+  cudaGraphExec_t exec = nullptr;
+  if (get_graph(S, batch, variant, &exec)) return -1;
+  const int kpi = kernels_per_iteration(S, variant);
+
+  CUDA_OK(cudaMemcpyAsync(S->state, a.up, sizeof(CgState), cudaMemcpyHostToDevice, c.stream));
+  CUDA_OK(launch_init(S->x, S->r, S->p_own, S->s, S->b, S->nloc, variant == 1 ? 1 : 0, S->partials,
+                      &S->state->ticket[2], S->state, nccl ? FIN_LOCAL : FIN_INIT, cm, c.stream));
+  if (nccl && enqueue_nccl_finish(S, 1, FIN_INIT)) return -1;
+  if (variant == 1) {
+    if (enqueue_matvec(S, S->w, nccl ? FIN_LOCAL : FIN_SR, true, true)) return -1;
+    if (nccl && enqueue_nccl_finish(S, 2, FIN_SR)) return -1;
+  }
+  CUDA_OK(cudaEventRecord(a.t0, c.stream));
+  for (long long enq = 0; enq < total_updates; enq += batch) {
+    CUDA_OK(cudaGraphLaunch(exec, c.stream));
+    add_launches((long long)kpi * batch);
+  }
+  CUDA_OK(cudaEventRecord(a.t1, c.stream));
+  CUDA_OK(cudaMemcpyAsync(a.down, S->state, sizeof(CgState), cudaMemcpyDeviceToHost, c.stream));
+  CUDA_OK(cudaEventRecord(a.done, c.stream));
+  a.launches = launch_count() - launches0;
+  a.sys = S;
+  a.ticket = g_async_next++;
+  *ticket_out = a.ticket;
+  return 0;
+}
+
+int system_solve_wait(long long ticket, SolveResult* res) {
+  if (ticket < 0) {
+    set_error("system_solve_wait: bad ticket");
+    return -1;
+  }
+  AsyncSlot& a = g_async[ticket % ASYNC_SLOTS];
+  if (a.ticket != ticket) {
+    set_error("system_solve_wait: unknown or already collected ticket");
+    return -1;
+  }
+  CUDA_OK(cudaEventSynchronize(a.done));
+  float ms = 0.f;
+  CUDA_OK(cudaEventElapsedTime(&ms, a.t0, a.t1));
+  const CgState& f = *a.down;
+  if (res) {
+    res->iterations = f.iter;
+    res->status = f.status;
+    res->rr = f.rr;
+    res->bb = f.bb;
+    res->relres = f.bb > 0.0 ? sqrt(f.rr / f.bb) : 0.0;
+    res->seconds = ms * 1e-3;
+    res->bytes_per_iter = a.sys->iter_bytes();
+    res->path = a.sys->dense ? 1 : 0;
+    res->world = a.sys->world;
+    res->kernel_launches = a.launches;
+  }
+  a.ticket = -1;
+  a.sys = nullptr;
+  if (f.status == CGB200_ST_COMM) {
+    set_error("system_solve_wait: a peer-memory exchange between GPUs timed out");
+    return -1;
+  }
+  return 0;
+}
+
 int system_set_rhs(System* S, const double* b_host) {
   Ctx& c = g_ctx;
   CUDA_OK(cudaMemcpyAsync(S->b, b_host, sizeof(double) * S->nloc, cudaMemcpyHostToDevice, c.stream));

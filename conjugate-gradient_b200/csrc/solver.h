@@ -112,6 +112,8 @@ System* system_from_csr(long long n_global, long long row0, int nrows, const int
                         const int* cols, const double* vals, const double* b);
 int classify_tiles(System* S);
 int system_solve(System* S, const SolveOpts& o, SolveResult* res);
+int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out);
+int system_solve_wait(long long ticket, SolveResult* res);
 int system_set_rhs(System* S, const double* b_host);
 int system_gen_rhs(System* S, unsigned long long seed);
 int system_get_x(System* S, double* x_host);

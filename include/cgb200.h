@@ -100,6 +100,14 @@ int cgb200_system_set_rhs(cgb200_system *sys, const double *b_host);   /* H2D, n
 int cgb200_system_gen_rhs(cgb200_system *sys, uint64_t bseed);         /* on the device */
 int cgb200_system_get_x(cgb200_system *sys, double *x_host);           /* D2H, nrows doubles */
 int cgb200_system_solve(cgb200_system *sys, const cgb200_opts *opts, cgb200_result *res);
+/* Queues a fixed-count solve (opts->tol must be 0: the reference's semantics) behind whatever is
+ * already queued on the library's stream and returns at once with a ticket; right-hand sides
+ * set with cgb200_system_gen_rhs are queued the same way, so many solves run back to back without
+ * the GPU waiting for the host.  At most 8 tickets may be outstanding.  cgb200_solve_wait blocks
+ * until that solve has finished and fills the result.  x stays on the device: read it with
+ * cgb200_system_get_x after the wait of the LAST queued solve on that system. */
+int cgb200_system_solve_async(cgb200_system *sys, const cgb200_opts *opts, long long *ticket);
+int cgb200_solve_wait(long long ticket, cgb200_result *res);
 /* s = A v for a host vector v[n_local] (single rank) -> s_host; exercises the loop's matvec
  * kernel alone (mode PLAIN). */
 int cgb200_system_matvec(cgb200_system *sys, const double *v_host, double *s_host);

@@ -343,6 +343,33 @@ def test_single_reduction_known_answers_and_breakdown(pkg, gpu_lib):
     assert np.array_equal(_bits(x1), _bits(x2))
 
 
+def test_queued_fixed_count_solves_match_synchronous_ones(pkg, gpu_lib):
+    # cgb200_system_solve_async: several right-hand sides queued back to back, collected later
+    for variant in (pkg.CLASSIC, pkg.SINGLE_REDUCTION):
+        d = pkg.DeviceSystem.lap(48, 40, 6)
+        want = []
+        for seed in (101, 102, 103):
+            d.gen_rhs(seed)
+            r = d.solve(25, variant=variant)
+            want.append((r.iterations, r.rr, d.x()))
+        tickets = []
+        xs = []
+        for seed in (101, 102, 103):
+            d.gen_rhs(seed)
+            tickets.append(d.solve_async(25, variant=variant))
+        for i, t in enumerate(tickets):
+            r = d.solve_wait(t)
+            assert r.iterations == want[i][0] == 26 and r.status == pkg.MAXITER
+            assert r.rr == want[i][1]          # same kernels, same order: same bits
+        assert np.array_equal(_bits(d.x()), _bits(want[2][2]))
+        # a tolerance cannot be queued, and a ticket is collected once
+        o = pkg.Opts(10, 1e-8, 0, 0, 0)
+        tk = C.c_longlong(-1)
+        assert gpu_lib.cgb200_system_solve_async(d.h, C.byref(o), C.byref(tk)) == -1
+        assert gpu_lib.cgb200_solve_wait(tickets[0], C.byref(pkg.Result())) == -1
+        d.free()
+
+
 # ---------------------------------------------------------------------------------------------
 # device-resident systems and generators
 # ---------------------------------------------------------------------------------------------

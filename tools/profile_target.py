@@ -1,5 +1,5 @@
 """Small fixed workload for ncu captures: a few CG iterations of one BASELINE config on 1 GPU.
-usage: profile_target.py {dense|lap2d|lap3d512|lap3d384} [iterations]"""
+usage: profile_target.py {dense|lap2d|lap3d512|lap3d384} [iterations] [classic|sr]"""
 import os
 import sys
 
@@ -18,6 +18,7 @@ d = {
     "lap3d512": lambda: pkg.DeviceSystem.lap(512, 512, 512),
     "lap3d384": lambda: pkg.DeviceSystem.lap(384, 384, 384),
 }[w]()
-r = d.solve(iters - 1, check_every=iters)
+variant = pkg.SINGLE_REDUCTION if (len(sys.argv) > 3 and sys.argv[3] == "sr") else pkg.CLASSIC
+r = d.solve(iters - 1, check_every=iters, variant=variant)
 print(w, "iterations", r.iterations, "status", r.status, "relres", r.relres, "ms/iter", r.seconds * 1e3 / max(r.iterations, 1))
 d.free()
