@@ -231,16 +231,24 @@ def timed_steps(pkg, runner, K, W, world, sampler=None):
     return {"ms": ms_max, "steps": done, "warmup": w_done, "launches": int(launches), "t0": t0, "t1": t1}
 
 
-def roofline_for(pkg, d, peak, peak_src, kernel_name, workload, world):
+def roofline_for(pkg, d, peak, peak_src, kernel_name, workload, world, variant=0):
     it_b, k1_b = d.bytes()
-    t1 = d.time_kernel(1, 30)
-    ach = k1_b / (t1 * 1e-3) / 1e9
+    if variant == 0 and d.one_kernel_iteration():
+        # dense path: the whole classic iteration is ONE launch (k_cg_dense_iter) -- its algorithmic
+        # bytes are the contract bytes of an iteration (A + 88 n)
+        kernel_name, alg, which = "k_cg_dense_iter", it_b, 6
+        what = "the one-kernel iteration (matvec, both reductions, both vector updates)"
+    else:
+        alg, which, what = k1_b, 1, "the matvec kernel"
+    t1 = d.time_kernel(which, 30)
+    ach = alg / (t1 * 1e-3) / 1e9
     return {
         "bound": "hbm", "kernel": kernel_name, "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
         "frac": round(ach / peak, 4), "traffic": traffic_from_profiles(kernel_name, workload, world),
-        "algorithmic_bytes_per_launch": k1_b, "avg_launch_ms": round(t1, 5),
+        "algorithmic_bytes_per_launch": alg, "avg_launch_ms": round(t1, 5),
         "peak_source": peak_src,
-        "how": "CUDA events on the library's solve stream around 30 back-to-back launches of the matvec kernel (this rank's block), after 3 warm-ups",
+        "how": "CUDA events on the library's solve stream around 30 back-to-back launches of "
+               + what + " (this rank's block), after 3 warm-ups",
     }
 
 
@@ -518,8 +526,8 @@ def main():
     clocks = sampler.summary(tm["t0"], tm["t1"]) if sampler else None
     it_b, k1_b = d.bytes()
     value = tm["steps"] / (tm["ms"] * 1e-3)
-    kname = "k_gemv_rows" if info["kind"] == "dense" else "k_spmv_stream"
-    roof = roofline_for(pkg, d, peak, peak_src, kname, args.workload, world)
+    kname = "k_gemv_units" if info["kind"] == "dense" else "k_spmv_stream"
+    roof = roofline_for(pkg, d, peak, peak_src, kname, args.workload, world, variant)
     iter_gbs = it_b / (tm["ms"] / tm["steps"] * 1e-3) / 1e9
     true_rr = d.true_relres() if info["kind"] != "dense" else None
     line = {
@@ -527,7 +535,8 @@ def main():
         "warmup": tm["warmup"], "ms_per_step": round(tm["ms"] / tm["steps"], 5), "higher_is_better": True,
         "scaling": info["scaling"], "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": dict(workload_config(args.workload, world), iterations_per_solve=runner.J,
-                       variant=args.variant, comm=comm),
+                       variant=args.variant, comm=comm,
+                       kernels_per_iteration=1 if roof["kernel"] == "k_cg_dense_iter" else (3 if variant == 0 else 2)),
         "roofline": roof,
         "iteration": {"contract_bytes_per_rank": it_b, "achieved_gbs_per_gpu": round(iter_gbs, 1),
                       "frac_of_peak": round(iter_gbs / peak, 4),

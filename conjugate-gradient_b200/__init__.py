@@ -167,6 +167,7 @@ def lib():
     L.cgb200_dist_init.argtypes = [C.c_int, C.c_int, C.c_void_p]
     L.cgb200_dist_comm_mode.restype = C.c_char_p
     L.cgb200_system_comm_is_p2p.argtypes = [C.c_void_p]
+    L.cgb200_system_one_kernel_iteration.argtypes = [C.c_void_p]
     _lib = L
     return L
 
@@ -284,6 +285,10 @@ class DeviceSystem:
         v = C.c_double(0.0)
         _check(lib().cgb200_system_time_kernel(self.h, which, reps, C.byref(v)), "cgb200_system_time_kernel")
         return v.value
+
+    def one_kernel_iteration(self):
+        """True when a classic iteration of this system is one cooperative launch (dense path)."""
+        return bool(lib().cgb200_system_one_kernel_iteration(self.h))
 
     def bytes(self):
         a, b = C.c_double(0.0), C.c_double(0.0)

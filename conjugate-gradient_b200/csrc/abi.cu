@@ -650,7 +650,7 @@ int cgb200_system_true_relres(cgb200_system* sys, double* relres) {
 }
 
 int cgb200_system_time_kernel(cgb200_system* sys, int which, int reps, double* ms) {
-  if (!sys || !ms || reps < 1 || which < 1 || which > 5) return -1;
+  if (!sys || !ms || reps < 1 || which < 1 || which > 6) return -1;
   return system_time_kernel((System*)sys, which, reps, ms);
 }
 
@@ -737,6 +737,12 @@ int cgb200_dist_rank(void) { return ctx().rank; }
 int cgb200_dist_world(void) { return ctx().world; }
 int cgb200_dist_barrier(void) { return dist_barrier(); }
 const char* cgb200_dist_comm_mode(void) { return comm_mode_name(); }
+void cgb200_set_one_kernel_iteration(int on) { set_dense_iter_enabled(on); }
+
+int cgb200_system_one_kernel_iteration(cgb200_system* sys) {
+  return sys && dense_one_kernel((System*)sys) ? 1 : 0;
+}
+
 int cgb200_system_comm_is_p2p(cgb200_system* sys) { return sys && ((System*)sys)->p2p ? 1 : 0; }
 
 }  // extern "C"

@@ -387,6 +387,64 @@ __device__ __forceinline__ void wait_halo(const PeerComm& cm, CgState* S) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// Grid barrier of the one-kernel iteration (co-resident grid, cooperative launch): an epoch in
+// device memory.  The CTA that closed a fused reduction releases; everyone else waits.
+// ---------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ int ld_volatile_int(const int* p) {
+  return *(const volatile int*)p;
+}
+__device__ __forceinline__ double ld_volatile_f64(const double* p) {
+  return *(const volatile double*)p;
+}
+
+// Every thread of the releasing CTA calls this after its last store of the phase.
+template <int THREADS>
+__device__ __forceinline__ void grid_release(unsigned long long* epoch, unsigned long long e) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    st_release_gpu(epoch, e);
+  }
+}
+
+constexpr unsigned long long GRID_TIMEOUT_NS = 12000000000ull;  // > PEER_TIMEOUT_NS
+
+// Every thread of every CTA calls this; false (block-uniform) if the grid never got there.
+__device__ __forceinline__ bool grid_wait(const unsigned long long* epoch, unsigned long long e,
+                                          CgState* S) {
+  __shared__ int sh_ok;
+  if (threadIdx.x == 0) {
+    int ok = 1;
+    unsigned long long t0 = 0;
+    for (unsigned int it = 0; ld_acquire_gpu(epoch) < e; ++it) {
+      if ((it & 1023u) == 1023u) {
+        const unsigned long long now = global_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > GRID_TIMEOUT_NS) {
+          ok = 0;
+          comm_failed(S);
+          break;
+        }
+      }
+    }
+    sh_ok = ok;
+  }
+  __syncthreads();
+  const bool ok = sh_ok != 0;
+  __syncthreads();  // sh_ok may be rewritten by the next barrier
+  return ok;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Scalar bookkeeping of the loop (reference cg.c:113,125-134), run by exactly one thread per
 // iteration: the last block of the fused kernel (after the in-kernel cross-GPU sum when several
 // GPUs take part), or a one-thread kernel after an NCCL sum.

@@ -16,6 +16,8 @@
 // products differ (by summation order).
 #include "kernels.h"
 
+#include <string.h>
+
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -408,24 +410,23 @@ k_gemv_rows(const double* __restrict__ A, long long ld, int nrows, int ncols,
 
 constexpr int GEMV_REC_OFFSET = 2 * PART_STRIDE;  // records live behind the reduction partials
 
+// The unit loop of one CTA: streams its unit range, writes the rows it owns whole, leaves its
+// (at most two) incomplete row groups as records behind the reduction partials, and returns its
+// share of the fused dot products.
 template <int THREADS, int RB>
-__global__ void __launch_bounds__(THREADS)
-k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
-             const double* __restrict__ pg, const double* __restrict__ pown,
-             double* __restrict__ s, double* __restrict__ partials,
-             unsigned int* __restrict__ ticket, CgState* S, const int mode, const int wait,
-             const __grid_constant__ PeerComm cm) {
+__device__ __forceinline__ void gemv_units_stream(const double* __restrict__ A, long long ld,
+                                                  int nrows, int ncols,
+                                                  const double* __restrict__ pg,
+                                                  const double* __restrict__ pown,
+                                                  double* __restrict__ s,
+                                                  double* __restrict__ partials, const bool dots,
+                                                  double& dot, double& dot2) {
   constexpr int CW = THREADS * 4;  // columns per unit: one 256-bit load per thread
   constexpr int REC = RB + 1;
-  const int fin = mode & MV_FIN_MASK;
-  if (fin != FIN_NONE && S->done) return;
   __shared__ double sm_red[RB][THREADS / 32];
   __shared__ double sm_rec[2][REC];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid < 2) sm_rec[tid][0] = -1.0;
-  if (wait) {  // the peers' slices of the gather vector must have landed (all-gather mode)
-    if (tid == 0) wait_halo(cm, S);
-  }
   __syncthreads();
 
   const int cpg = (ncols + CW - 1) / CW;          // units per row group
@@ -433,7 +434,6 @@ k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
   const long long U = (long long)ngroups * cpg;
   long long u = U * blockIdx.x / gridDim.x;
   const long long u1 = U * (blockIdx.x + 1) / gridDim.x;
-  double dot = 0.0, dot2 = 0.0;
   int nrec = 0;
 
 #pragma unroll 1
@@ -478,7 +478,7 @@ k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
       if (whole) {
         if (row0 + tid < nrows) {
           s[row0 + tid] = t;
-          if (fin != FIN_NONE) {
+          if (dots) {
             const double gv = pown[row0 + tid];
             dot += gv * t;
             dot2 += gv * gv;
@@ -495,13 +495,21 @@ k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
   __syncthreads();
   double* recs = partials + GEMV_REC_OFFSET;
   if (tid < 2 * REC) recs[(size_t)blockIdx.x * 2 * REC + tid] = (&sm_rec[0][0])[tid];
+}
 
-  double v[2] = {dot, dot2};
-  if (!grid_reduce<THREADS, 2>(v, partials, ticket)) return;
-
-  // last CTA: finish the row groups shared between CTAs
+// Last CTA of the grid: finish the row groups shared between CTAs (records of one group are added
+// in CTA order) and return their share of the dot products, summed over the block into thread 0.
+template <int THREADS, int RB>
+__device__ __forceinline__ void gemv_units_fixup(int nrows, const double* __restrict__ pown,
+                                                 double* __restrict__ s,
+                                                 const double* __restrict__ partials,
+                                                 const bool dots, double& fdot, double& fdot2) {
+  constexpr int REC = RB + 1;
+  const int tid = threadIdx.x;
+  const double* recs = partials + GEMV_REC_OFFSET;
   const int nslots = 2 * (int)gridDim.x;
-  double fdot = 0.0, fdot2 = 0.0;
+  fdot = 0.0;
+  fdot2 = 0.0;
   for (int i = tid; i < nslots; i += THREADS) {
     const double gi = __ldcg(recs + (size_t)i * REC);
     if (gi < 0.0) continue;
@@ -523,18 +531,122 @@ k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
     for (int r = 0; r < RB; ++r)
       if (row0 + r < nrows) {
         s[row0 + r] = t[r];
-        if (fin != FIN_NONE) {
+        if (dots) {
           const double gv = pown[row0 + r];
           fdot += gv * t[r];
           fdot2 += gv * gv;
         }
       }
   }
-  if (fin == FIN_NONE) return;
+  if (!dots) return;
   __shared__ double sm_fix[THREADS / 32];
   fdot = block_sum<THREADS>(fdot, sm_fix);
   fdot2 = block_sum<THREADS>(fdot2, sm_fix);
+}
+
+template <int THREADS, int RB>
+__global__ void __launch_bounds__(THREADS)
+k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
+             const double* __restrict__ pg, const double* __restrict__ pown,
+             double* __restrict__ s, double* __restrict__ partials,
+             unsigned int* __restrict__ ticket, CgState* S, const int mode, const int wait,
+             const __grid_constant__ PeerComm cm) {
+  const int fin = mode & MV_FIN_MASK;
+  if (fin != FIN_NONE && S->done) return;
+  if (wait) {  // the peers' slices of the gather vector must have landed (all-gather mode)
+    if (threadIdx.x == 0) wait_halo(cm, S);
+  }
+  double dot = 0.0, dot2 = 0.0;
+  gemv_units_stream<THREADS, RB>(A, ld, nrows, ncols, pg, pown, s, partials, fin != FIN_NONE, dot,
+                                 dot2);
+  double v[2] = {dot, dot2};
+  if (!grid_reduce<THREADS, 2>(v, partials, ticket)) return;
+  double fdot, fdot2;
+  gemv_units_fixup<THREADS, RB>(nrows, pown, s, partials, fin != FIN_NONE, fdot, fdot2);
+  if (fin == FIN_NONE) return;
   finish_block<THREADS>(S, cm, fin, v[0] + fdot, (mode & MV_DUAL) ? v[1] + fdot2 : 0.0);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Dense path, the whole iteration in ONE launch (classic recurrence, cg.c:111-132).
+//
+// On the dense path the vectors are n doubles against n^2 of matrix: K2 and K3 are pure latency
+// (5-9 us each plus two launch boundaries), which is 2 % of an iteration on one GPU and 25 % on
+// an eighth of the matrix.  The persistent GEMV grid is co-resident (cooperative launch), so the
+// iteration continues behind two grid barriers instead of two more launches:
+//   phase A  s = A p, p.s (unit-range GEMV as above)         -> last CTA: [cross-GPU sum] alpha
+//   barrier  (the CTA that drew the last ticket releases the grid)
+//   phase B  x += alpha p ; r -= alpha s ; r.r  (each CTA a slice) -> last CTA: [sum] beta, stop
+//   barrier
+//   phase C  p = r + beta p, pushed into the peers' gather vectors, flags raised
+// The barriers are epochs in CgState (grid_epoch): a CTA reads the epoch when it starts -- nobody
+// can have released yet, a release needs every CTA's ticket -- and waits for epoch + 1, + 2.
+// `timing` != 0 leaves the scalars alone (alpha = beta = 0 state of system_time_kernel).
+// ---------------------------------------------------------------------------------------------
+
+template <int THREADS, int RB>
+__global__ void __launch_bounds__(THREADS, 4)
+k_cg_dense_iter(const double* __restrict__ A, long long ld, int nrows, int ncols,
+                const double* pg, double* pown, double* __restrict__ x, double* __restrict__ r,
+                double* s, double* __restrict__ partials, CgState* S, const int wait,
+                const int timing, const __grid_constant__ PeerComm cm) {
+  if (S->done) return;
+  const int tid = threadIdx.x;
+  __shared__ unsigned long long sh_e0;
+  if (tid == 0) {
+    sh_e0 = ld_acquire_gpu(&S->grid_epoch);
+    if (wait) wait_halo(cm, S);  // the peers' slices of p have landed (all-gather by push)
+  }
+  // (the __syncthreads at the top of gemv_units_stream publishes sh_e0 and orders the wait)
+
+  // ---- phase A -------------------------------------------------------------------------------
+  double dot = 0.0, dot2 = 0.0;
+  gemv_units_stream<THREADS, RB>(A, ld, nrows, ncols, pg, pown, s, partials, true, dot, dot2);
+  const unsigned long long e0 = sh_e0;
+  {
+    double v[1] = {dot};
+    if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[0])) {
+      double fdot, fdot2;
+      gemv_units_fixup<THREADS, RB>(nrows, pown, s, partials, true, fdot, fdot2);
+      if (!timing) finish_block<THREADS>(S, cm, FIN_PS, v[0] + fdot, 0.0);
+      grid_release<THREADS>(&S->grid_epoch, e0 + 1);
+    }
+  }
+  if (!grid_wait(&S->grid_epoch, e0 + 1, S)) return;
+  if (ld_volatile_int(&S->done)) return;
+
+  // ---- phase B -------------------------------------------------------------------------------
+  const double alpha = ld_volatile_f64(&S->alpha);
+  const long long gstride = (long long)gridDim.x * THREADS;
+  double acc = 0.0;
+  for (long long i = (long long)blockIdx.x * THREADS + tid; i < nrows; i += gstride) {
+    const double pv = pown[i];
+    const double sv = __ldcg(s + i);  // written by other CTAs of this launch: read at L2
+    const double xn = __dadd_rn(x[i], __dmul_rn(alpha, pv));
+    const double rn = __dsub_rn(r[i], __dmul_rn(alpha, sv));
+    x[i] = xn;
+    r[i] = rn;
+    acc = fma(rn, rn, acc);
+  }
+  {
+    double v[1] = {acc};
+    if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[1])) {
+      if (!timing) finish_block<THREADS>(S, cm, FIN_RR, v[0], 0.0);
+      grid_release<THREADS>(&S->grid_epoch, e0 + 2);
+    }
+  }
+  if (!grid_wait(&S->grid_epoch, e0 + 2, S)) return;
+  if (ld_volatile_int(&S->done)) return;
+
+  // ---- phase C -------------------------------------------------------------------------------
+  const double beta = ld_volatile_f64(&S->beta);
+  const bool pushing = cm.npush > 0;
+  for (long long i = (long long)blockIdx.x * THREADS + tid; i < nrows; i += gstride) {
+    const double pn = __dadd_rn(r[i], __dmul_rn(beta, pown[i]));
+    pown[i] = pn;
+    if (pushing) push_elem(cm, i, pn);
+  }
+  push_finish(cm);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1150,6 +1262,54 @@ cudaError_t launch_gemv(const double* A, long long ld, int nrows, int ncols, con
                               cm, st);
   return launch_gemv_vec<1>(A, ld, nrows, ncols, pg, pown, s, partials, ticket, S, mode, wait, cm,
                             st);
+}
+
+// The one-kernel iteration needs the unit-range GEMV's alignment (256-bit loads) and a grid that is
+// co-resident by construction: cooperative launch, so an impossible grid is an error, never a hang.
+static int g_dense_fused = -1;
+void set_dense_iter_enabled(int on) { g_dense_fused = on ? 1 : 0; }
+bool dense_iter_enabled() {
+  if (g_dense_fused < 0) {
+    const char* e = getenv("CGB200_DENSE_FUSED");  // 0 = three kernels per iteration (comparison runs)
+    g_dense_fused = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  return g_dense_fused != 0;
+}
+bool dense_iter_supported(const double* A, long long ld, int ncols, const double* pg) {
+  if (!dense_iter_enabled()) return false;
+  return ld % 4 == 0 && ncols % 4 == 0 && ((uintptr_t)A % 32 == 0) && ((uintptr_t)pg % 32 == 0);
+}
+
+cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int ncols,
+                                 const double* pg, double* pown, double* x, double* r, double* s,
+                                 double* partials, CgState* S, int wait, int timing,
+                                 const PeerComm& cm, cudaStream_t st) {
+  static int bps = 0;
+  if (!bps) {
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_cg_dense_iter<GV_T, GV_RB>, GV_T, 0);
+    if (bps < 1) bps = 1;
+  }
+  const long long units =
+      (long long)((nrows + GV_RB - 1) / GV_RB) * ((ncols + GV_T * 4 - 1) / (GV_T * 4));
+  long long grid = (long long)sm_count() * bps;
+  if (grid > units) grid = units;
+  const long long cap = PART_STRIDE / (2 * (GV_RB + 1));  // room for two records per CTA
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(GV_T);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, k_cg_dense_iter<GV_T, GV_RB>, A, ld, nrows, ncols, pg,
+                                           pown, x, r, s, partials, S, wait, timing, cm);
+  ++g_launches;
+  return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 cudaError_t launch_update_xr(double* x, double* r, const double* p, const double* s, long long n,

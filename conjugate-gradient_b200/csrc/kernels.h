@@ -58,6 +58,14 @@ cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, d
 cudaError_t launch_gemv(const double* A, long long ld, int nrows, int ncols, const double* pg,
                         const double* pown, double* s, double* partials, unsigned int* ticket,
                         CgState* S, int mode, int wait, const PeerComm& cm, cudaStream_t st);
+// dense path: the whole classic iteration in one cooperative launch (kernels.cu: k_cg_dense_iter)
+void set_dense_iter_enabled(int on);
+bool dense_iter_enabled();
+bool dense_iter_supported(const double* A, long long ld, int ncols, const double* pg);
+cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int ncols,
+                                 const double* pg, double* pown, double* x, double* r, double* s,
+                                 double* partials, CgState* S, int wait, int timing,
+                                 const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_update_xr(double* x, double* r, const double* p, const double* s, long long n,
                              double* partials, unsigned int* ticket, CgState* S, int fin,
                              const PeerComm& cm, cudaStream_t st);

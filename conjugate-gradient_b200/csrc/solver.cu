@@ -852,6 +852,14 @@ static int ensure_w(System* S) {
   return 0;
 }
 
+// Dense row block on one GPU or with the peer-memory exchange: one cooperative launch per
+// classic iteration (kernels.cu: k_cg_dense_iter).  NCCL mode keeps the three-kernel form (its
+// sums happen between launches).
+bool dense_one_kernel(const System* S) {
+  return S->dense && S->nloc > 0 && (S->world == 1 || S->p2p) &&
+         dense_iter_supported(S->A.vals, S->n_global, (int)S->n_global, S->p_ext);
+}
+
 // Classic recurrence (the reference's, cg.c:110-135): K1, K2, K3.
 // Single-reduction recurrence: one fused vector update, then K1 with both dot products.
 static int enqueue_iteration(System* S, int variant) {
@@ -865,6 +873,12 @@ static int enqueue_iteration(System* S, int variant) {
     if (nccl && enqueue_nccl_finish(S, 2, FIN_SR)) return -1;
     return 0;
   }
+  if (dense_one_kernel(S)) {  // dense path: the whole iteration behind two grid barriers
+    CUDA_OK(launch_cg_dense_iter(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext,
+                                 S->p_own, S->x, S->r, S->s, S->partials, st,
+                                 (S->world > 1 && S->p2p) ? 1 : 0, 0, cm, c.stream));
+    return 0;
+  }
   if (enqueue_matvec(S, S->s, nccl ? FIN_LOCAL : FIN_PS, false, true)) return -1;
   if (nccl && enqueue_nccl_finish(S, 1, FIN_PS)) return -1;
   CUDA_OK(launch_update_xr(S->x, S->r, S->p_own, S->s, S->nloc, S->partials, &st->ticket[1], st,
@@ -876,6 +890,7 @@ static int enqueue_iteration(System* S, int variant) {
 
 // Kernel nodes per captured iteration (for the launch counter)
 static int kernels_per_iteration(const System* S, int variant) {
+  if (variant == 0 && dense_one_kernel(S)) return 1;
   int k = variant == 1 ? 2 : 3;
   if (S->world > 1 && !S->p2p) {
     k += variant == 1 ? 1 : 2;  // bookkeeping kernels
@@ -888,7 +903,7 @@ static int kernels_per_iteration(const System* S, int variant) {
 
 static int get_graph(System* S, int iters, int variant, cudaGraphExec_t* out) {
   Ctx& c = g_ctx;
-  const int key = 2 * iters + variant;
+  const int key = 4 * iters + 2 * (dense_one_kernel(S) ? 1 : 0) + variant;
   auto it = S->graphs.find(key);
   if (it != S->graphs.end()) {
     *out = it->second;
@@ -1283,7 +1298,7 @@ int system_time_kernel(System* S, int which, int reps, double* ms_out) {
   h->rr = 1.0;
   h->max_iter = 0x7fffffff;
   CUDA_OK(cudaMemcpyAsync(S->state, h, sizeof(CgState), cudaMemcpyHostToDevice, c.stream));
-  if (which >= 4 && ensure_w(S)) return -1;
+  if ((which == 4 || which == 5) && ensure_w(S)) return -1;
   auto one = [&]() -> int {
     if (which == 1) {  // local kernel only: no exchange, sums left in state->local
       if (enqueue_matvec(S, S->s, FIN_LOCAL, false, false)) return -1;
@@ -1292,6 +1307,14 @@ int system_time_kernel(System* S, int which, int reps, double* ms_out) {
                                &S->state->ticket[1], S->state, FIN_LOCAL, S->cm_off, c.stream));
     } else if (which == 3) {
       CUDA_OK(launch_update_p(S->p_own, S->r, S->nloc, S->state, S->cm_off, c.stream));
+    } else if (which == 6) {  // the one-kernel dense iteration, scalars left alone
+      if (!dense_one_kernel(S)) {
+        set_error("system_time_kernel: this system does not run the one-kernel iteration");
+        return -1;
+      }
+      CUDA_OK(launch_cg_dense_iter(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext,
+                                   S->p_own, S->x, S->r, S->s, S->partials, S->state, 0, 1,
+                                   S->cm_off, c.stream));
     } else if (which == 4) {
       CUDA_OK(launch_update_sr(S->x, S->p_own, S->r, S->s, S->w, S->nloc, S->state, S->cm_off,
                                c.stream));

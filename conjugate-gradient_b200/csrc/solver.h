@@ -76,7 +76,7 @@ struct System {
   double* w = nullptr;  // single-reduction variant only: w = A r (allocated on first use)
   CgState* state = nullptr;
   double* partials = nullptr;
-  std::map<int, cudaGraphExec_t> graphs;  // 2 * iterations per graph + variant -> graph
+  std::map<int, cudaGraphExec_t> graphs;  // 4 * iterations per graph + 2 * one-kernel + variant -> graph
 
   // peer-memory exchange (comm.h).  comm_buf = [Mailbox | CommLocal | p_ext] is the one
   // allocation exported through CUDA IPC; peer_base[g] is rank g's comm_buf mapped here.
@@ -111,6 +111,7 @@ System* system_dense(int n, int row0, int nrows, unsigned long long aseed, unsig
 System* system_from_csr(long long n_global, long long row0, int nrows, const int* row_ptr,
                         const int* cols, const double* vals, const double* b);
 int classify_tiles(System* S);
+bool dense_one_kernel(const System* S);  // classic iterations of S run as one cooperative launch
 int system_solve(System* S, const SolveOpts& o, SolveResult* res);
 int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out);
 int system_solve_wait(long long ticket, SolveResult* res);

@@ -27,5 +27,6 @@ struct CgState {
   int variant;    // 0 classic (the reference's recurrence), 1 single-reduction
   int sr_first;   // single-reduction: the next fused reduction is the loop-entry one
   unsigned int ticket[4];  // grid-reduction tickets (one per fused kernel)
-  double aux[4];
+  unsigned long long grid_epoch;  // grid barriers passed by the one-kernel iteration (dense path)
+  double aux[3];
 };

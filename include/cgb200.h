@@ -116,8 +116,15 @@ int cgb200_system_true_relres(cgb200_system *sys, double *relres);
 /* Average device time (ms, CUDA events on the launching stream) of `reps` back-to-back launches
  * of one kernel of the loop on this system's buffers.  which: 1 = matvec+dot (K1),
  * 2 = x/r update + r.r (K2), 3 = direction update (K3); single-reduction variant: 4 = the fused
- * vector update, 5 = matvec with both dot products. */
+ * vector update, 5 = matvec with both dot products; 6 = the one-kernel classic iteration of the
+ * dense path (only where cgb200_system_one_kernel_iteration() is 1). */
 int cgb200_system_time_kernel(cgb200_system *sys, int which, int reps, double *ms);
+/* 1 if a classic iteration of this system is ONE cooperative launch (dense row block, one GPU or
+ * peer-memory mode): matvec, both reductions and both vector updates behind two grid barriers. */
+int cgb200_system_one_kernel_iteration(cgb200_system *sys);
+/* Process-wide switch for the above (default on; CGB200_DENSE_FUSED=0 also turns it off): with 0 the
+ * dense path runs the same three kernels per iteration as the CSR path.  For comparison runs. */
+void cgb200_set_one_kernel_iteration(int on);
 /* Contract bytes per iteration for this rank and the share of the matvec kernel. */
 int cgb200_system_bytes(cgb200_system *sys, double *iter_bytes, double *k1_bytes);
 /* Copies the matrix block to host arrays (any may be NULL): vals[nnz], cols[nnz] (global column

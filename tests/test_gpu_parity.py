@@ -370,6 +370,67 @@ def test_queued_fixed_count_solves_match_synchronous_ones(pkg, gpu_lib):
         d.free()
 
 
+def _dev(pkg, s):
+    return pkg.DeviceSystem.from_csr(s.n, 0, s.row_ptr, s.cols, s.vals, s.b)
+
+
+@pytest.mark.parametrize("n", [256, 1000, 2052, 4096])
+def test_dense_one_kernel_iteration_matches_three_kernel_form(pkg, gpu_lib, n):
+    # dense path: matvec, both reductions and both vector updates in ONE cooperative launch
+    # (k_cg_dense_iter) against the K1/K2/K3 form of the same recurrence, and against the oracle
+    s = H.dense(n)
+    xo, it_o, _, _ = H.oracle_cg(s, 4)
+    got = {}
+    try:
+        for on in (1, 0):
+            gpu_lib.cgb200_set_one_kernel_iteration(on)
+            d = _dev(pkg, s)
+            assert d.one_kernel_iteration() == bool(on)
+            l0 = gpu_lib.cgb200_launch_count()
+            r = d.solve(4, check_every=5)
+            launches = gpu_lib.cgb200_launch_count() - l0
+            assert r.iterations == it_o == 5 and r.status == pkg.MAXITER
+            assert launches == 1 + (5 if on else 15), launches      # k_init + kernels of 5 iterations
+            rt = d.solve(500, tol=1e-10)
+            got[on] = (d.x(), r.rr, rt.iterations, rt.status, d.true_relres())
+            d.gen_rhs(3)
+            r1 = d.solve(4)
+            x1 = d.x()
+            d.gen_rhs(3)
+            r2 = d.solve(4)
+            assert r1.rr == r2.rr and np.array_equal(_bits(x1), _bits(d.x()))   # run-to-run bits
+            d.free()
+    finally:
+        gpu_lib.cgb200_set_one_kernel_iteration(1)
+    for on in (0, 1):
+        assert got[on][3] == pkg.CONVERGED and got[on][4] <= TOL_RES * 1.05
+    assert abs(got[1][2] - got[0][2]) <= 1
+    assert np.linalg.norm(got[1][0] - got[0][0]) <= 1e-12 * np.linalg.norm(got[0][0])
+    assert abs(got[1][1] - got[0][1]) <= 1e-10 * abs(got[0][1])
+    d = _dev(pkg, s)
+    d.solve(4)
+    assert np.linalg.norm(d.x() - xo) <= TOL_X * np.linalg.norm(xo)
+    d.free()
+
+
+def test_dense_one_kernel_iteration_breakdown_and_exact_stop(pkg, gpu_lib):
+    # the stop flag raised behind a grid barrier must stop every CTA of the launch: identity
+    # matrix converges exactly after one update (status EXACT, x = b), zero rhs stops at entry
+    n = 64
+    s = H.dense(n)
+    s.vals[:] = 0.0
+    s.vals[::n + 1] = 1.0
+    d = _dev(pkg, s)
+    assert d.one_kernel_iteration()
+    r = d.solve(10)
+    assert r.status == pkg.EXACT and r.iterations == 1
+    assert np.array_equal(d.x(), s.b)
+    d.set_rhs(np.zeros(n))
+    r = d.solve(10)
+    assert r.status == pkg.EXACT and r.iterations == 0 and not np.any(d.x())
+    d.free()
+
+
 # ---------------------------------------------------------------------------------------------
 # device-resident systems and generators
 # ---------------------------------------------------------------------------------------------
