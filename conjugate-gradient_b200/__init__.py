@@ -15,7 +15,8 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
-LIB_PATH = os.path.join(HERE, "libcgb200.so")
+# CGB200_LIBRARY: another build of the same library (A/B comparisons of kernel changes, tools/ab_build.sh)
+LIB_PATH = os.environ.get("CGB200_LIBRARY") or os.path.join(HERE, "libcgb200.so")
 CG_DRIVER = os.path.join(HERE, "cg")
 
 c_double_p = C.POINTER(C.c_double)

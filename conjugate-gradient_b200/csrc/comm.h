@@ -19,10 +19,12 @@ namespace cgb {
 
 constexpr int MAX_RANKS = 8;
 
+// One rank's contribution to one cross-GPU sum, in flagged words (the scheme NCCL calls LL): each
+// 64-bit word carries 32 bits of payload and the 32-bit number of the reduction it belongs to, and
+// an aligned 64-bit store is indivisible, so a word whose flag matches is a word whose payload has
+// arrived.  No fence on the sending side, no acquire on the receiving side: one NVLink crossing.
 struct RedSlot {
-  double v[2];
-  unsigned long long epoch;  // number of the reduction these values belong to
-  unsigned long long pad;
+  unsigned long long w[4];  // {v0.lo, e}, {v0.hi, e}, {v1.lo, e}, {v1.hi, e}
 };
 
 // Lives in the owner's device memory; written by peers (and by the owner itself for its own slot).

@@ -294,9 +294,18 @@ __device__ __forceinline__ void comm_failed(CgState* S) {
 // Sum of (t0, t1) over all ranks, formed inside the calling kernel.  Called by every thread of
 // ONE block per GPU (the last block of a fused reduction) with the local totals valid in thread
 // 0; thread g < world stores this rank's pair into rank g's mailbox and then collects rank g's
-// pair from the local mailbox; thread 0 adds the G pairs in rank order, so every rank obtains the
-// same bits and takes the same branches.  Slots are indexed by the reduction number modulo 4: a
+// pair from the local mailbox (flagged words, comm.h: RedSlot); thread 0 adds the G pairs in rank
+// order, so every rank obtains the same bits and takes the same branches.  Slots are indexed by the reduction number modulo 4: a
 // peer can be at most one reduction ahead (it needs this rank's next contribution to go further).
+__device__ __forceinline__ void st_ll2(unsigned long long* p, unsigned long long a,
+                                       unsigned long long b) {
+  asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void ld_ll2(const unsigned long long* p, unsigned long long& a,
+                                       unsigned long long& b) {
+  asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+
 template <int THREADS>
 __device__ __forceinline__ bool peer_allreduce(const PeerComm& cm, CgState* S, double& t0,
                                                double& t1) {
@@ -317,14 +326,32 @@ __device__ __forceinline__ bool peer_allreduce(const PeerComm& cm, CgState* S, d
   const int slot = (int)(e & 3ull);
   if ((int)threadIdx.x < cm.world) {
     const int g = threadIdx.x;
+    const unsigned long long flag = (e % 0xffffffffull + 1ull) << 32;  // never 0 (fresh memory)
+    const unsigned long long a = (unsigned long long)__double_as_longlong(sh[2 * MAX_RANKS]);
+    const unsigned long long b = (unsigned long long)__double_as_longlong(sh[2 * MAX_RANKS + 1]);
     RedSlot* dst = &cm.mbox[g]->red[slot][cm.rank];
-    st_relaxed_sys(&dst->v[0], sh[2 * MAX_RANKS]);
-    st_relaxed_sys(&dst->v[1], sh[2 * MAX_RANKS + 1]);
-    st_release_sys(&dst->epoch, e);  // orders the two value stores before the flag
+    st_ll2(&dst->w[0], flag | (a & 0xffffffffull), flag | (a >> 32));
+    st_ll2(&dst->w[2], flag | (b & 0xffffffffull), flag | (b >> 32));
     const RedSlot* src = &cm.mbox[cm.rank]->red[slot][g];
-    if (spin_until(&src->epoch, e, true)) {
-      sh[2 * g] = ld_relaxed_sys(&src->v[0]);
-      sh[2 * g + 1] = ld_relaxed_sys(&src->v[1]);
+    unsigned long long w0, w1, w2, w3, tstart = 0;
+    bool ok = false;
+    for (unsigned int it = 0;; ++it) {
+      ld_ll2(&src->w[0], w0, w1);
+      ld_ll2(&src->w[2], w2, w3);
+      const unsigned long long hi = 0xffffffff00000000ull;
+      if ((w0 & hi) == flag && (w1 & hi) == flag && (w2 & hi) == flag && (w3 & hi) == flag) {
+        ok = true;
+        break;
+      }
+      if ((it & 255u) == 255u) {
+        const unsigned long long now = global_ns();
+        if (tstart == 0) tstart = now;
+        else if (now - tstart > PEER_TIMEOUT_NS) break;
+      }
+    }
+    if (ok) {
+      sh[2 * g] = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
+      sh[2 * g + 1] = __longlong_as_double((long long)((w2 & 0xffffffffull) | (w3 << 32)));
     } else {
       sh_fail = 1;
     }

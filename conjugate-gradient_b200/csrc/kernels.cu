@@ -409,10 +409,119 @@ k_gemv_rows(const double* __restrict__ A, long long ld, int nrows, int ncols,
 // ---------------------------------------------------------------------------------------------
 
 constexpr int GEMV_REC_OFFSET = 2 * PART_STRIDE;  // records live behind the reduction partials
+constexpr int GEMV_CNT_OFFSET = 3 * PART_STRIDE;  // per-group arrival counters (unsigned, zero at rest)
+constexpr int GEMV_GDOT_OFFSET = 1024;            // dot-product shares of the shared groups: the
+                                                  // `extra` partials of grid_reduce, slot = owner CTA
+constexpr int GEMV_MAX_GRID = 819;                // PART_STRIDE / (2 * (RB + 1)) records, < 1024 slots
 
-// The unit loop of one CTA: streams its unit range, writes the rows it owns whole, leaves its
-// (at most two) incomplete row groups as records behind the reduction partials, and returns its
-// share of the fused dot products.
+// Unit u belongs to the CTA with the largest c such that U c / G <= u.
+__device__ __forceinline__ int gemv_cta_of(long long u, long long U, int G) {
+  return (int)(((u + 1) * G - 1) / U);
+}
+
+// Cold tail of gemv_units_stream, kept out of line so that its index arithmetic (64-bit divisions)
+// costs the streaming loop no registers.  Called by every thread of the CTA after the records
+// have been written; gid0/gid1 are the group numbers of this CTA's records (nrec of them).
+template <int THREADS, int RB>
+__device__ __noinline__ void gemv_units_shared_groups(int nrows, int ncols,
+                                                      const double* __restrict__ pown,
+                                                      double* __restrict__ s,
+                                                      double* __restrict__ partials,
+                                                      const bool dots, const int nrec,
+                                                      const double gid0, const double gid1) {
+  constexpr int CW = THREADS * 4;
+  constexpr int REC = RB + 1;
+  __shared__ int sm_fin[2][3];  // per record: finishing?, first CTA, last CTA of the group
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int G = (int)gridDim.x;
+  const int cpg = (ncols + CW - 1) / CW;
+  const int ngroups = (nrows + RB - 1) / RB;
+  const long long U = (long long)ngroups * cpg;
+  const long long ubeg = U * blockIdx.x / G;
+  const long long u1 = U * (blockIdx.x + 1) / G;
+  const double* recs = partials + GEMV_REC_OFFSET;
+  unsigned int* cnt = reinterpret_cast<unsigned int*>(partials + GEMV_CNT_OFFSET);
+  double* gd = partials + GEMV_GDOT_OFFSET;
+  if (tid == 0) {
+    // this CTA's own slot stays empty unless the group cut by its upper boundary starts in it
+    if ((int)blockIdx.x < G - 1) {
+      const long long gcut = u1 / cpg;
+      if (u1 % cpg == 0 || ubeg > gcut * cpg) {
+        gd[blockIdx.x] = 0.0;
+        gd[PART_STRIDE + blockIdx.x] = 0.0;
+      }
+    }
+    __threadfence();
+    for (int i = 0; i < 2; ++i) {
+      int fin = 0, kf = 0, kl = 0;
+      if (i < nrec) {
+        const long long g0 = (long long)(i == 0 ? gid0 : gid1) * cpg;
+        kf = gemv_cta_of(g0, U, G);
+        kl = gemv_cta_of(g0 + cpg - 1, U, G);
+        const unsigned int old = atomicAdd(&cnt[kf], 1u);
+        if (old == (unsigned int)(kl - kf)) {  // every contributor has arrived
+          cnt[kf] = 0u;
+          fin = 1;
+        }
+      }
+      sm_fin[i][0] = fin;
+      sm_fin[i][1] = kf;
+      sm_fin[i][2] = kl;
+    }
+    __threadfence();
+  }
+  __syncthreads();
+#pragma unroll 1
+  for (int i = 0; i < 2; ++i) {
+    if (!sm_fin[i][0]) continue;  // block-uniform
+    if (warp == 0) {
+      const int kf = sm_fin[i][1], kl = sm_fin[i][2];
+      const long long g = (long long)(i == 0 ? gid0 : gid1);
+      const int row = (int)g * RB + lane;
+      double t = 0.0;
+      if (lane < RB) {
+#pragma unroll 4
+        for (int k = kf; k <= kl; ++k) {
+          // CTA k's record of group g: its second record iff g is not its first group and its
+          // first group was incomplete too (it starts inside a group)
+          const long long bk = U * k / G;
+          const int slot = (bk / cpg != g && bk % cpg != 0) ? 1 : 0;
+          t += __ldcg(recs + ((size_t)k * 2 + slot) * REC + 1 + lane);
+        }
+        if (row < nrows) s[row] = t;
+      }
+      if (dots) {
+        double d1 = 0.0, d2 = 0.0;
+        if (lane < RB && row < nrows) {
+          const double gv = pown[row];
+          d1 = gv * t;
+          d2 = gv * gv;
+        }
+        double a1 = 0.0, a2 = 0.0;
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {  // row order
+          a1 += __shfl_sync(0xffffffffu, d1, r);
+          a2 += __shfl_sync(0xffffffffu, d2, r);
+        }
+        if (lane == 0) {
+          gd[kf] = a1;
+          gd[PART_STRIDE + kf] = a2;
+        }
+      }
+    }
+  }
+  // (the stores above are ordered before this CTA's ticket by the fence inside grid_reduce, which
+  // follows a block-wide barrier)
+}
+
+
+// The unit loop of one CTA: streams its unit range, writes the rows it owns whole, leaves its (at
+// most two) incomplete row groups as records behind the reduction partials, and returns its share
+// of the fused dot products.  A shared group is finished by whichever of its CTAs arrives last
+// (one arrival counter per group): it adds the group's records in CTA order -- fixed order, s stays
+// run-to-run reproducible -- writes the rows and leaves the group's share of the dot products in
+// the slot of the group's first CTA, which the closing reduction folds in in slot order.  So the
+// grid's last CTA has nothing left to finish and the fix-ups hide behind the stream of the others.
 template <int THREADS, int RB>
 __device__ __forceinline__ void gemv_units_stream(const double* __restrict__ A, long long ld,
                                                   int nrows, int ncols,
@@ -423,17 +532,20 @@ __device__ __forceinline__ void gemv_units_stream(const double* __restrict__ A, 
                                                   double& dot, double& dot2) {
   constexpr int CW = THREADS * 4;  // columns per unit: one 256-bit load per thread
   constexpr int REC = RB + 1;
+  static_assert(RB <= 32, "row group wider than a warp");
   __shared__ double sm_red[RB][THREADS / 32];
   __shared__ double sm_rec[2][REC];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid < 2) sm_rec[tid][0] = -1.0;
   __syncthreads();
 
+  const int G = (int)gridDim.x;
   const int cpg = (ncols + CW - 1) / CW;          // units per row group
   const int ngroups = (nrows + RB - 1) / RB;
   const long long U = (long long)ngroups * cpg;
-  long long u = U * blockIdx.x / gridDim.x;
-  const long long u1 = U * (blockIdx.x + 1) / gridDim.x;
+  const long long ubeg = U * blockIdx.x / G;
+  const long long u1 = U * (blockIdx.x + 1) / G;
+  long long u = ubeg;
   int nrec = 0;
 
 #pragma unroll 1
@@ -495,57 +607,14 @@ __device__ __forceinline__ void gemv_units_stream(const double* __restrict__ A, 
   __syncthreads();
   double* recs = partials + GEMV_REC_OFFSET;
   if (tid < 2 * REC) recs[(size_t)blockIdx.x * 2 * REC + tid] = (&sm_rec[0][0])[tid];
-}
 
-// Last CTA of the grid: finish the row groups shared between CTAs (records of one group are added
-// in CTA order) and return their share of the dot products, summed over the block into thread 0.
-template <int THREADS, int RB>
-__device__ __forceinline__ void gemv_units_fixup(int nrows, const double* __restrict__ pown,
-                                                 double* __restrict__ s,
-                                                 const double* __restrict__ partials,
-                                                 const bool dots, double& fdot, double& fdot2) {
-  constexpr int REC = RB + 1;
-  const int tid = threadIdx.x;
-  const double* recs = partials + GEMV_REC_OFFSET;
-  const int nslots = 2 * (int)gridDim.x;
-  fdot = 0.0;
-  fdot2 = 0.0;
-  for (int i = tid; i < nslots; i += THREADS) {
-    const double gi = __ldcg(recs + (size_t)i * REC);
-    if (gi < 0.0) continue;
-    int j = i - 1;
-    while (j >= 0 && __ldcg(recs + (size_t)j * REC) < 0.0) --j;
-    if (j >= 0 && __ldcg(recs + (size_t)j * REC) == gi) continue;  // not the first record of its group
-    double t[RB];
-#pragma unroll
-    for (int r = 0; r < RB; ++r) t[r] = 0.0;
-    for (int k = i; k < nslots; ++k) {
-      const double gk = __ldcg(recs + (size_t)k * REC);
-      if (gk < 0.0) continue;
-      if (gk != gi) break;
-#pragma unroll
-      for (int r = 0; r < RB; ++r) t[r] += __ldcg(recs + (size_t)k * REC + 1 + r);
-    }
-    const int row0 = (int)gi * RB;
-#pragma unroll
-    for (int r = 0; r < RB; ++r)
-      if (row0 + r < nrows) {
-        s[row0 + r] = t[r];
-        if (dots) {
-          const double gv = pown[row0 + r];
-          fdot += gv * t[r];
-          fdot2 += gv * gv;
-        }
-      }
-  }
-  if (!dots) return;
-  __shared__ double sm_fix[THREADS / 32];
-  fdot = block_sum<THREADS>(fdot, sm_fix);
-  fdot2 = block_sum<THREADS>(fdot2, sm_fix);
+  __syncthreads();  // the records are written (block-wide) before thread 0 fences and arrives
+  gemv_units_shared_groups<THREADS, RB>(nrows, ncols, pown, s, partials, dots, nrec,
+                                        sm_rec[0][0], sm_rec[1][0]);
 }
 
 template <int THREADS, int RB>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, 4)
 k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
              const double* __restrict__ pg, const double* __restrict__ pown,
              double* __restrict__ s, double* __restrict__ partials,
@@ -559,12 +628,12 @@ k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
   double dot = 0.0, dot2 = 0.0;
   gemv_units_stream<THREADS, RB>(A, ld, nrows, ncols, pg, pown, s, partials, fin != FIN_NONE, dot,
                                  dot2);
-  double v[2] = {dot, dot2};
-  if (!grid_reduce<THREADS, 2>(v, partials, ticket)) return;
-  double fdot, fdot2;
-  gemv_units_fixup<THREADS, RB>(nrows, pown, s, partials, fin != FIN_NONE, fdot, fdot2);
   if (fin == FIN_NONE) return;
-  finish_block<THREADS>(S, cm, fin, v[0] + fdot, (mode & MV_DUAL) ? v[1] + fdot2 : 0.0);
+  double v[2] = {dot, dot2};
+  if (!grid_reduce<THREADS, 2>(v, partials, ticket, partials + GEMV_GDOT_OFFSET,
+                               (int)gridDim.x - 1))
+    return;
+  finish_block<THREADS>(S, cm, fin, v[0], (mode & MV_DUAL) ? v[1] : 0.0);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -584,18 +653,27 @@ k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
 // `timing` != 0 leaves the scalars alone (alpha = beta = 0 state of system_time_kernel).
 // ---------------------------------------------------------------------------------------------
 
+// `trace` (normally null): cycle counts of the phases, accumulated by thread 0 of the CTA that
+// closes each phase, relative to that CTA's own start (tools/dense_trace.py).
 template <int THREADS, int RB>
 __global__ void __launch_bounds__(THREADS, 4)
 k_cg_dense_iter(const double* __restrict__ A, long long ld, int nrows, int ncols,
                 const double* pg, double* pown, double* __restrict__ x, double* __restrict__ r,
                 double* s, double* __restrict__ partials, CgState* S, const int wait,
-                const int timing, const __grid_constant__ PeerComm cm) {
+                const int timing, unsigned long long* __restrict__ trace,
+                const __grid_constant__ PeerComm cm) {
   if (S->done) return;
   const int tid = threadIdx.x;
-  __shared__ unsigned long long sh_e0;
+  __shared__ unsigned long long sh_e0, sh_t0;
+  long long c0 = 0;
   if (tid == 0) {
     sh_e0 = ld_acquire_gpu(&S->grid_epoch);
+    if (trace) {
+      c0 = clock64();
+      sh_t0 = global_ns();
+    }
     if (wait) wait_halo(cm, S);  // the peers' slices of p have landed (all-gather by push)
+    if (trace && blockIdx.x == 0) atomicAdd(trace + 0, (unsigned long long)(clock64() - c0));
   }
   // (the __syncthreads at the top of gemv_units_stream publishes sh_e0 and orders the wait)
 
@@ -603,12 +681,41 @@ k_cg_dense_iter(const double* __restrict__ A, long long ld, int nrows, int ncols
   double dot = 0.0, dot2 = 0.0;
   gemv_units_stream<THREADS, RB>(A, ld, nrows, ncols, pg, pown, s, partials, true, dot, dot2);
   const unsigned long long e0 = sh_e0;
+  if (trace && tid == 0) {  // spread of the CTAs' start and stream-end times (ns, global timer)
+    atomicMin(trace + 8, sh_t0);
+    atomicMax(trace + 9, sh_t0);
+    const unsigned long long t1 = global_ns();
+    atomicMin(trace + 10, t1);
+    atomicMax(trace + 11, t1);
+    atomicAdd(trace + 12, t1 - sh_t0);
+    trace[16 + blockIdx.x] += t1 - sh_t0;  // per-CTA sum of GEMV durations (this CTA is the only writer)
+    unsigned int smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    trace[16 + 1024 + blockIdx.x] = smid;
+  }
   {
     double v[1] = {dot};
-    if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[0])) {
-      double fdot, fdot2;
-      gemv_units_fixup<THREADS, RB>(nrows, pown, s, partials, true, fdot, fdot2);
-      if (!timing) finish_block<THREADS>(S, cm, FIN_PS, v[0] + fdot, 0.0);
+    if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[0], partials + GEMV_GDOT_OFFSET,
+                                (int)gridDim.x - 1)) {
+      if (trace && tid == 0) {
+        atomicAdd(trace + 1, (unsigned long long)(clock64() - c0));
+        // per-launch spreads (ns): CTA starts, ends of the CTAs' GEMV shares, first start -> first end
+        volatile unsigned long long* tv = trace;
+        const unsigned long long s0 = tv[8], s1 = tv[9], f0 = tv[10], f1 = tv[11];
+        tv[13] += s1 - s0;
+        tv[14] += f1 - f0;
+        tv[15] += f0 - s0;
+        tv[2] += f1 - s0;  // first start -> last end
+        tv[8] = ~0ull;
+        tv[10] = ~0ull;
+        tv[9] = 0ull;
+        tv[11] = 0ull;
+      }
+      if (!timing) finish_block<THREADS>(S, cm, FIN_PS, v[0], 0.0);
+      if (trace && tid == 0) {
+        atomicAdd(trace + 3, (unsigned long long)(clock64() - c0));
+        atomicAdd(trace + 7, 1ull);
+      }
       grid_release<THREADS>(&S->grid_epoch, e0 + 1);
     }
   }
@@ -631,7 +738,9 @@ k_cg_dense_iter(const double* __restrict__ A, long long ld, int nrows, int ncols
   {
     double v[1] = {acc};
     if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[1])) {
+      if (trace && tid == 0) atomicAdd(trace + 4, (unsigned long long)(clock64() - c0));
       if (!timing) finish_block<THREADS>(S, cm, FIN_RR, v[0], 0.0);
+      if (trace && tid == 0) atomicAdd(trace + 5, (unsigned long long)(clock64() - c0));
       grid_release<THREADS>(&S->grid_epoch, e0 + 2);
     }
   }
@@ -647,6 +756,7 @@ k_cg_dense_iter(const double* __restrict__ A, long long ld, int nrows, int ncols
     if (pushing) push_elem(cm, i, pn);
   }
   push_finish(cm);
+  if (trace && tid == 0 && blockIdx.x == 0) atomicAdd(trace + 6, (unsigned long long)(clock64() - c0));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1106,7 +1216,8 @@ static inline int vec_grid(long long n) {
 }
 
 int max_partials() { return PART_STRIDE; }
-int partials_doubles() { return 3 * PART_STRIDE; }  // two reduction values + GEMV records
+int partials_doubles() { return 3 * PART_STRIDE + 1024; }  // two reduction values, GEMV records, group counters
+size_t partials_zero_offset() { return (size_t)GEMV_CNT_OFFSET; }  // doubles from here on start as zero
 
 // SpMV tile configurations.  One is chosen per process (CGB200_SPMV_CFG, default 0); DESIGN.md
 // records the sweep that picked the default.
@@ -1226,12 +1337,14 @@ static cudaError_t launch_gemv_units(const double* A, long long ld, int nrows, i
   if (!bps) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_gemv_units<GV_T, GV_RB>, GV_T, 0);
     if (bps < 1) bps = 1;
+    const char* e = getenv("CGB200_GEMV_BPS");  // fewer CTAs per SM (experiments)
+    if (e && atoi(e) > 0 && atoi(e) < bps) bps = atoi(e);
   }
   const long long units =
       (long long)((nrows + GV_RB - 1) / GV_RB) * ((ncols + GV_T * 4 - 1) / (GV_T * 4));
   long long grid = (long long)sm_count() * bps;
   if (grid > units) grid = units;
-  const long long cap = PART_STRIDE / (2 * (GV_RB + 1));  // room for two records per CTA
+  const long long cap = GEMV_MAX_GRID;  // room for two records per CTA
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
   k_gemv_units<GV_T, GV_RB><<<(int)grid, GV_T, 0, st>>>(A, ld, nrows, ncols, pg, pown, s, partials,
@@ -1283,17 +1396,19 @@ bool dense_iter_supported(const double* A, long long ld, int ncols, const double
 cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int ncols,
                                  const double* pg, double* pown, double* x, double* r, double* s,
                                  double* partials, CgState* S, int wait, int timing,
-                                 const PeerComm& cm, cudaStream_t st) {
+                                 unsigned long long* trace, const PeerComm& cm, cudaStream_t st) {
   static int bps = 0;
   if (!bps) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_cg_dense_iter<GV_T, GV_RB>, GV_T, 0);
     if (bps < 1) bps = 1;
+    const char* e = getenv("CGB200_GEMV_BPS");  // fewer CTAs per SM (experiments)
+    if (e && atoi(e) > 0 && atoi(e) < bps) bps = atoi(e);
   }
   const long long units =
       (long long)((nrows + GV_RB - 1) / GV_RB) * ((ncols + GV_T * 4 - 1) / (GV_T * 4));
   long long grid = (long long)sm_count() * bps;
   if (grid > units) grid = units;
-  const long long cap = PART_STRIDE / (2 * (GV_RB + 1));  // room for two records per CTA
+  const long long cap = GEMV_MAX_GRID;  // room for two records per CTA
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
   cudaLaunchConfig_t cfg = {};
@@ -1307,7 +1422,7 @@ cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int n
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const cudaError_t e = cudaLaunchKernelEx(&cfg, k_cg_dense_iter<GV_T, GV_RB>, A, ld, nrows, ncols, pg,
-                                           pown, x, r, s, partials, S, wait, timing, cm);
+                                           pown, x, r, s, partials, S, wait, timing, trace, cm);
   ++g_launches;
   return e != cudaSuccess ? e : cudaGetLastError();
 }

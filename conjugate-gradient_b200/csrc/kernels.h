@@ -46,6 +46,7 @@ struct TileRange {
 int sm_count();
 int max_partials();
 int partials_doubles();
+size_t partials_zero_offset();  // the tail of a partials buffer (group counters) must start zeroed
 int spmv_rows_per_tile();
 int spmv_grid_for(int ntiles);
 long long launch_count();
@@ -65,7 +66,7 @@ bool dense_iter_supported(const double* A, long long ld, int ncols, const double
 cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int ncols,
                                  const double* pg, double* pown, double* x, double* r, double* s,
                                  double* partials, CgState* S, int wait, int timing,
-                                 const PeerComm& cm, cudaStream_t st);
+                                 unsigned long long* trace, const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_update_xr(double* x, double* r, const double* p, const double* s, long long n,
                              double* partials, unsigned int* ticket, CgState* S, int fin,
                              const PeerComm& cm, cudaStream_t st);

@@ -135,6 +135,7 @@ int ensure_init(int device) {
   CUDA_OK(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
   CUDA_OK(cudaStreamCreateWithFlags(&c.comm_stream, cudaStreamNonBlocking));
   CUDA_OK(cudaMalloc(&c.partials, sizeof(double) * partials_doubles()));
+  CUDA_OK(cudaMemset(c.partials, 0, sizeof(double) * partials_doubles()));
   CUDA_OK(cudaMalloc(&c.d_state, sizeof(CgState)));
   CUDA_OK(cudaMemset(c.d_state, 0, sizeof(CgState)));
   CUDA_OK(cudaMallocHost(&c.h_state, sizeof(CgState) * 4));
@@ -303,6 +304,7 @@ System::~System() {
     cudaFree(p_ext);
   cudaFree(state);
   cudaFree(partials);
+  cudaFree(trace);
 }
 
 // Allocates the matrix arrays with the padding the bulk copies may over-read (zero-filled).
@@ -414,6 +416,10 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
   std::vector<PartInfo> parts(c.world);
   for (int g = 0; g < c.world; ++g)
     parts[g] = PartInfo{all[4 * g + 0], all[4 * g + 1], all[4 * g + 2], all[4 * g + 3]};
+  // diagnostics (tools/gemv_rows_sweep.py): a lone row block [0, nloc) of a wider matrix, for timing
+  // its kernels on one GPU; such a system is not a solvable one
+  if (c.world == 1 && S->row0 == 0 && S->nloc < S->n_global && getenv("CGB200_TIMING_BLOCKS"))
+    parts[0].nloc = S->n_global;
   Plan plan;
   const char* perr = nullptr;
   if (plan_partition(c.world, c.rank, S->n_global, parts.data(), S->dense ? 1 : 0, &plan, &perr)) {
@@ -458,6 +464,7 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
   CUDA_OK(cudaMalloc(&S->state, sizeof(CgState)));
   CUDA_OK(cudaMemsetAsync(S->state, 0, sizeof(CgState), c.stream));
   CUDA_OK(cudaMalloc(&S->partials, sizeof(double) * partials_doubles()));
+  CUDA_OK(cudaMemsetAsync(S->partials, 0, sizeof(double) * partials_doubles(), c.stream));
   S->p_own = S->p_ext + S->off;
   if (S->comm_buf && setup_peer_comm(S, parts)) return -1;
 
@@ -876,7 +883,7 @@ static int enqueue_iteration(System* S, int variant) {
   if (dense_one_kernel(S)) {  // dense path: the whole iteration behind two grid barriers
     CUDA_OK(launch_cg_dense_iter(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext,
                                  S->p_own, S->x, S->r, S->s, S->partials, st,
-                                 (S->world > 1 && S->p2p) ? 1 : 0, 0, cm, c.stream));
+                                 (S->world > 1 && S->p2p) ? 1 : 0, 0, S->trace, cm, c.stream));
     return 0;
   }
   if (enqueue_matvec(S, S->s, nccl ? FIN_LOCAL : FIN_PS, false, true)) return -1;
@@ -1168,6 +1175,30 @@ int system_solve_wait(long long ticket, SolveResult* res) {
   return 0;
 }
 
+// Phase trace of the one-kernel iteration (tools/dense_trace.py): on = allocate + zero the
+// counters and rebuild the graphs with the trace pointer; read = copy the 8 counters out.
+constexpr int TRACE_WORDS = 16 + 2048;  // counters, per-CTA duration sums, per-CTA SM ids
+int system_trace(System* S, int on, unsigned long long* out) {
+  Ctx& c = g_ctx;
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  if (out && S->trace)
+    CUDA_OK(cudaMemcpy(out, S->trace, TRACE_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  if (on && !S->trace) CUDA_OK(cudaMalloc(&S->trace, TRACE_WORDS * sizeof(unsigned long long)));
+  if (on) {
+    std::vector<unsigned long long> z(TRACE_WORDS, 0ull);
+    z[8] = z[10] = ~0ull;  // minima
+    CUDA_OK(cudaMemcpy(S->trace, z.data(), TRACE_WORDS * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+  }
+  if (!on && S->trace) {
+    cudaFree(S->trace);
+    S->trace = nullptr;
+  }
+  for (auto& kv : S->graphs)
+    if (kv.second) cudaGraphExecDestroy(kv.second);
+  S->graphs.clear();
+  return 0;
+}
+
 int system_set_rhs(System* S, const double* b_host) {
   Ctx& c = g_ctx;
   CUDA_OK(cudaMemcpyAsync(S->b, b_host, sizeof(double) * S->nloc, cudaMemcpyHostToDevice, c.stream));
@@ -1314,7 +1345,7 @@ int system_time_kernel(System* S, int which, int reps, double* ms_out) {
       }
       CUDA_OK(launch_cg_dense_iter(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext,
                                    S->p_own, S->x, S->r, S->s, S->partials, S->state, 0, 1,
-                                   S->cm_off, c.stream));
+                                   nullptr, S->cm_off, c.stream));
     } else if (which == 4) {
       CUDA_OK(launch_update_sr(S->x, S->p_own, S->r, S->s, S->w, S->nloc, S->state, S->cm_off,
                                c.stream));

@@ -76,6 +76,7 @@ struct System {
   double* w = nullptr;  // single-reduction variant only: w = A r (allocated on first use)
   CgState* state = nullptr;
   double* partials = nullptr;
+  unsigned long long* trace = nullptr;  // phase trace of the one-kernel iteration (diagnostics)
   std::map<int, cudaGraphExec_t> graphs;  // 4 * iterations per graph + 2 * one-kernel + variant -> graph
 
   // peer-memory exchange (comm.h).  comm_buf = [Mailbox | CommLocal | p_ext] is the one
@@ -115,6 +116,7 @@ bool dense_one_kernel(const System* S);  // classic iterations of S run as one c
 int system_solve(System* S, const SolveOpts& o, SolveResult* res);
 int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out);
 int system_solve_wait(long long ticket, SolveResult* res);
+int system_trace(System* S, int on, unsigned long long* out16);
 int system_set_rhs(System* S, const double* b_host);
 int system_gen_rhs(System* S, unsigned long long seed);
 int system_get_x(System* S, double* x_host);

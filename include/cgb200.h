@@ -125,6 +125,18 @@ int cgb200_system_one_kernel_iteration(cgb200_system *sys);
 /* Process-wide switch for the above (default on; CGB200_DENSE_FUSED=0 also turns it off): with 0 the
  * dense path runs the same three kernels per iteration as the CSR path.  For comparison runs. */
 void cgb200_set_one_kernel_iteration(int on);
+/* Diagnostics of the one-kernel iteration: SM-cycle counts of its phases, summed over launches by
+ * the CTA that closes each phase, relative to that CTA's start.  out16 (may be NULL) receives the
+ * counters accumulated so far: [0] wait for the peers' slices of p, [1] GEMV done (last ticket),
+ * [2] (ns) first CTA start to last CTA's end of the GEMV, [3] alpha known (after the cross-GPU sum), [4] x/r update done,
+ * [5] beta known, [6] p updated and pushed, [7] launches traced; global-timer ns over all CTAs
+ * [12] sum of the CTAs' GEMV durations, and per-launch spreads summed over launches: [13] latest
+ * minus earliest CTA start, [14] latest minus earliest end of a CTA's GEMV share, [15] earliest
+ * start to earliest end ([8..11] are scratch); [16 + c] sum of CTA c's GEMV durations (ns),
+ * [16 + 1024 + c] the SM CTA c ran on.  out16 holds 16 + 2048 words.
+ * on != 0 (re)starts tracing, on == 0 stops it; either way the system's captured graphs are
+ * rebuilt. */
+int cgb200_system_trace(cgb200_system *sys, int on, unsigned long long *out16);
 /* Contract bytes per iteration for this rank and the share of the matvec kernel. */
 int cgb200_system_bytes(cgb200_system *sys, double *iter_bytes, double *k1_bytes);
 /* Copies the matrix block to host arrays (any may be NULL): vals[nnz], cols[nnz] (global column
