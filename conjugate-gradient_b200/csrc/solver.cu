@@ -1000,10 +1000,12 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
   }
 
   const long long total_updates = (long long)max_iter + 1;
-  int batch = o.check_every > 0 ? o.check_every : 32;
-  if (batch > total_updates) batch = (int)total_updates;
-  cudaGraphExec_t exec = nullptr;
-  if (get_graph(S, batch, variant, &exec)) return -1;
+  // Iterations per graph launch.  The stop flag is looked at one batch behind, so up to two
+  // batches of early-exit launches follow a tolerance stop: with a tolerance and no explicit
+  // check_every the batches start small and double (4, 8, 16, 32), which keeps that overrun short
+  // for systems that converge in a handful of iterations and costs nothing for long solves.
+  const int batch_max = o.check_every > 0 ? o.check_every : 32;
+  int batch = (o.check_every > 0 || !(o.tol > 0.0)) ? batch_max : 4;
   const int kpi = kernels_per_iteration(S, variant);
 
   CUDA_OK(cudaEventRecord(c.t0, c.stream));
@@ -1011,9 +1013,14 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
   int k = 0;
   bool stop = false;
   while (enq < total_updates && !stop) {
+    int nb = batch;
+    if (nb > total_updates) nb = (int)total_updates;
+    cudaGraphExec_t exec = nullptr;
+    if (get_graph(S, nb, variant, &exec)) return -1;
     CUDA_OK(cudaGraphLaunch(exec, c.stream));
-    add_launches((long long)kpi * batch);
-    enq += batch;
+    add_launches((long long)kpi * nb);
+    enq += nb;
+    if (batch < batch_max) batch = std::min(batch_max, batch * 2);
     CUDA_OK(cudaMemcpyAsync(&c.h_state[k & 1], S->state, sizeof(CgState), cudaMemcpyDeviceToHost,
                             c.stream));
     CUDA_OK(cudaEventRecord(c.poll_ev[k & 1], c.stream));

@@ -69,6 +69,8 @@ ALG = {  # algorithmic bytes per launch
 def alg_bytes(w, kernel):
     a = ALG[w]
     n, nnz = a["n"], a["nnz"]
+    if kernel.startswith("k_cg_dense"):  # the whole iteration: contract bytes A + 88 n
+        return 8.0 * nnz + 88.0 * n
     if kernel.startswith("k_gemv"):
         return 8.0 * nnz + 16.0 * n
     if kernel.startswith("k_spmv"):
