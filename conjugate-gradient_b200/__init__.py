@@ -169,6 +169,7 @@ def lib():
     L.cgb200_dist_comm_mode.restype = C.c_char_p
     L.cgb200_system_comm_is_p2p.argtypes = [C.c_void_p]
     L.cgb200_system_one_kernel_iteration.argtypes = [C.c_void_p]
+    L.cgb200_system_use_pattern_format.argtypes = [C.c_void_p, C.c_int]
     _lib = L
     return L
 
@@ -286,6 +287,13 @@ class DeviceSystem:
         v = C.c_double(0.0)
         _check(lib().cgb200_system_time_kernel(self.h, which, reps, C.byref(v)), "cgb200_system_time_kernel")
         return v.value
+
+    def use_pattern_format(self, on=True):
+        """Switch the matvec to the row-pattern dictionary format; True if it applies to this matrix."""
+        rc = lib().cgb200_system_use_pattern_format(self.h, 1 if on else 0)
+        if rc < 0:
+            raise CgError("cgb200_system_use_pattern_format failed: " + last_error())
+        return rc == 1
 
     def one_kernel_iteration(self):
         """True when a classic iteration of this system is one cooperative launch (dense path)."""

@@ -737,6 +737,10 @@ int cgb200_dist_rank(void) { return ctx().rank; }
 int cgb200_dist_world(void) { return ctx().world; }
 int cgb200_dist_barrier(void) { return dist_barrier(); }
 const char* cgb200_dist_comm_mode(void) { return comm_mode_name(); }
+int cgb200_system_use_pattern_format(cgb200_system* sys, int on) {
+  return system_use_pattern((System*)sys, on);
+}
+
 int cgb200_system_trace(cgb200_system* sys, int on, unsigned long long* out16) {
   if (!sys) return -1;
   return system_trace((System*)sys, on, out16);

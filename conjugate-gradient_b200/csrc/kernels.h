@@ -22,6 +22,17 @@ struct CsrDev {
   long long lead = -1, plen = 0;
 };
 
+// Row-pattern dictionary format (pattern.cu): one byte per row naming the row's pattern
+// {(column - row, value)}; the dictionary (ntypes x lpad entries, lpad a multiple of 8) is copied
+// into shared memory by the kernel.  Built only for matrices with at most 255 distinct rows.
+struct PatDev {
+  unsigned char* type = nullptr;  // nrows
+  int* len = nullptr;             // ntypes
+  int* rel = nullptr;             // ntypes * lpad, column (gather space) minus local row
+  double* val = nullptr;          // ntypes * lpad
+  int ntypes = 0, lpad = 0;
+};
+
 // `mode` of the matvec kernels: a finish kind (what the last CTA does with the fused dot
 // products) in the low bits plus flags.
 //   FIN_NONE   s = A p only (mv_mult of the operator API)
@@ -56,6 +67,12 @@ cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, d
                         const TileRange& tr, int wait_from, double* partials,
                         unsigned int* ticket, CgState* S, int mode, const PeerComm& cm,
                         cudaStream_t st);
+int pattern_grid_for(const PatDev& P, int ntiles);
+cudaError_t launch_spmv_pattern(const PatDev& P, int nrows, const double* pg, const double* pown,
+                                double* s, const TileRange& tr, int wait_from, double* partials,
+                                unsigned int* ticket, CgState* S, int mode, const PeerComm& cm,
+                                cudaStream_t st);
+void free_pattern(PatDev* P);
 cudaError_t launch_gemv(const double* A, long long ld, int nrows, int ncols, const double* pg,
                         const double* pown, double* s, double* partials, unsigned int* ticket,
                         CgState* S, int mode, int wait, const PeerComm& cm, cudaStream_t st);

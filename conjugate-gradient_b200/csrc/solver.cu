@@ -290,6 +290,7 @@ System::~System() {
       if (peer_base[g]) cudaIpcCloseMemHandle(peer_base[g]);
     dist_barrier();
   }
+  free_pattern(&pat);
   cudaFree(A.vals);
   cudaFree(A.cols);
   cudaFree(A.rowptr);
@@ -803,9 +804,16 @@ static int enqueue_matvec(System* S, double* out, int fin, bool dual, bool excha
     return 0;
   }
   const TileRange all_tiles = {{0, 0, 0}, {S->ntiles, 0, 0}};
+  // CSR stream kernel, or the pattern kernel when the system was switched to that format
+  auto spmv = [&](const TileRange& tr, int wait_from, double* partials, int md) -> cudaError_t {
+    if (S->pat_active)
+      return launch_spmv_pattern(S->pat, S->nloc, S->p_ext, S->p_own, out, tr, wait_from, partials,
+                                 &st->ticket[0], st, md, cm, c.stream);
+    return launch_spmv(S->A, S->p_ext, S->p_own, out, tr, wait_from, partials, &st->ticket[0], st,
+                       md, cm, c.stream);
+  };
   if (!multi) {
-    CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, out, all_tiles, NO_WAIT, S->partials,
-                        &st->ticket[0], st, mode, cm, c.stream));
+    CUDA_OK(spmv(all_tiles, NO_WAIT, S->partials, mode));
     return 0;
   }
   const bool has_interior = !S->allgather && S->tb_hi > S->tb_lo;
@@ -817,8 +825,7 @@ static int enqueue_matvec(System* S, double* out, int fin, bool dual, bool excha
       tr = TileRange{{S->tb_lo, 0, S->tb_hi}, {S->tb_hi, S->tb_lo, S->ntiles}};
       if (cm.nwait > 0) wait_from = S->tb_hi - S->tb_lo;
     }
-    CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, out, tr, wait_from, S->partials,
-                        &st->ticket[0], st, mode, cm, c.stream));
+    CUDA_OK(spmv(tr, wait_from, S->partials, mode));
     return 0;
   }
   // NCCL mode
@@ -826,21 +833,19 @@ static int enqueue_matvec(System* S, double* out, int fin, bool dual, bool excha
   if (enqueue_exchange_begin(S)) return -1;
   if (!split) {
     if (enqueue_exchange_end(S)) return -1;
-    CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, out, all_tiles, NO_WAIT, S->partials,
-                        &st->ticket[0], st, mode, cm, c.stream));
+    CUDA_OK(spmv(all_tiles, NO_WAIT, S->partials, mode));
     return 0;
   }
   // interior tiles while the halo is in flight, then the boundary tiles finish the reduction
   const TileRange interior = {{S->tb_lo, 0, 0}, {S->tb_hi, 0, 0}};
   const TileRange boundary = {{0, S->tb_hi, 0}, {S->tb_lo, S->ntiles, 0}};
-  const int g_int = spmv_grid_for(S->tb_hi - S->tb_lo);
+  const int g_int = S->pat_active ? pattern_grid_for(S->pat, S->tb_hi - S->tb_lo)
+                                  : spmv_grid_for(S->tb_hi - S->tb_lo);
   const int int_mode = (fin == FIN_NONE) ? mode : (mode | MV_PARTIAL);
-  CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, out, interior, NO_WAIT,
-                      S->partials + MV_EXTRA_OFFSET, &st->ticket[0], st, int_mode, cm, c.stream));
+  CUDA_OK(spmv(interior, NO_WAIT, S->partials + MV_EXTRA_OFFSET, int_mode));
   if (enqueue_exchange_end(S)) return -1;
   const int fin_mode = (fin == FIN_NONE) ? mode : (mode | (g_int << 8));
-  CUDA_OK(launch_spmv(S->A, S->p_ext, S->p_own, out, boundary, NO_WAIT, S->partials,
-                      &st->ticket[0], st, fin_mode, cm, c.stream));
+  CUDA_OK(spmv(boundary, NO_WAIT, S->partials, fin_mode));
   return 0;
 }
 
@@ -943,15 +948,48 @@ static int get_graph(System* S, int iters, int variant, cudaGraphExec_t* out) {
   return 0;
 }
 
-double System::iter_bytes() const {
+// Matrix bytes the matvec streams per launch: CSR 12 nnz + 4 (n + 1), dense values only 8 nnz,
+// pattern format one byte per row (the dictionary stays in shared memory).
+double System::matrix_bytes() const {
   const double n = (double)nloc;
-  const double a = dense ? 8.0 * (double)A.nnz : 12.0 * (double)A.nnz + 4.0 * (n + 1.0);
-  return a + 88.0 * n;
+  if (dense) return 8.0 * (double)A.nnz;
+  if (pat_active) return n;
+  return 12.0 * (double)A.nnz + 4.0 * (n + 1.0);
 }
-double System::k1_bytes() const {
-  const double n = (double)nloc;
-  const double a = dense ? 8.0 * (double)A.nnz : 12.0 * (double)A.nnz + 4.0 * (n + 1.0);
-  return a + 16.0 * n;
+double System::iter_bytes() const { return matrix_bytes() + 88.0 * (double)nloc; }
+double System::k1_bytes() const { return matrix_bytes() + 16.0 * (double)nloc; }
+
+// Switches the matvec of a CSR system between the stream kernel and the row-pattern kernel.
+int system_use_pattern(System* S, int on) {
+  Ctx& c = g_ctx;
+  if (!S) {
+    set_error("system_use_pattern: NULL system");
+    return -1;
+  }
+  CUDA_OK(cudaSetDevice(c.device));
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  int result = 0;
+  if (on && !S->dense && S->nloc > 0) {
+    if (!S->pat.type) {
+      std::string why;
+      const int rc = build_pattern(S->A, &S->pat, c.stream, &why);
+      if (rc < 0) return -1;
+      if (rc == 0) set_error("pattern format not applicable: " + why);
+    }
+    result = S->pat.type ? 1 : 0;
+  } else if (on) {
+    set_error("pattern format not applicable: dense or empty row block");
+  }
+  // every rank must take the same path only in the sense of correctness of its own rows: the
+  // exchange, the reductions and the tile classification do not depend on the format
+  const bool active = result == 1;
+  if (active != S->pat_active) {
+    S->pat_active = active;
+    for (auto& kv : S->graphs)
+      if (kv.second) cudaGraphExecDestroy(kv.second);
+    S->graphs.clear();
+  }
+  return result;
 }
 
 int system_solve(System* S, const SolveOpts& o, SolveResult* res) {

@@ -56,6 +56,8 @@ struct System {
   int nloc = 0;
   bool dense = false;  // values[] is a row-major nloc x n_global block, no index arrays
   CsrDev A;
+  PatDev pat;               // row-pattern dictionary form of A (pattern.cu), built on request
+  bool pat_active = false;  // the matvec runs k_spmv_pattern instead of the CSR stream kernel
 
   // gather space of the matvec: p_ext = [ lower halo | owned rows | upper halo ] (neighbour mode)
   // or the whole global vector (single rank, all-gather mode)
@@ -87,6 +89,7 @@ struct System {
   PeerComm cm = {};      // active description (world > 1 only when p2p)
   PeerComm cm_off = {};  // disabled description (single GPU, NCCL mode)
 
+  double matrix_bytes() const;  // bytes of A the matvec streams per launch in the current format
   double iter_bytes() const;  // contract bytes per iteration: A + 88 n
   double k1_bytes() const;    // share of the matvec kernel: A + 16 n
   ~System();
@@ -116,6 +119,9 @@ bool dense_one_kernel(const System* S);  // classic iterations of S run as one c
 int system_solve(System* S, const SolveOpts& o, SolveResult* res);
 int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out);
 int system_solve_wait(long long ticket, SolveResult* res);
+// 1 = S now runs the pattern matvec, 0 = not compressible (stays on CSR; reason in last_error), -1 = failure
+int system_use_pattern(System* S, int on);
+int build_pattern(const CsrDev& A, PatDev* out, cudaStream_t st, std::string* why);
 int system_trace(System* S, int on, unsigned long long* out16);
 int system_set_rhs(System* S, const double* b_host);
 int system_gen_rhs(System* S, unsigned long long seed);

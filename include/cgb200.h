@@ -125,6 +125,16 @@ int cgb200_system_one_kernel_iteration(cgb200_system *sys);
 /* Process-wide switch for the above (default on; CGB200_DENSE_FUSED=0 also turns it off): with 0 the
  * dense path runs the same three kernels per iteration as the CSR path.  For comparison runs. */
 void cgb200_set_one_kernel_iteration(int on);
+/* Row-pattern dictionary format (not in the reference, whose only layout is CSR,
+ * mv_ops.h:17-23).  A CSR row block with at most 255 distinct rows -- a row being the list of
+ * (column - row, value) pairs, as in constant-coefficient stencil and Toeplitz band matrices -- is
+ * re-encoded as one byte per row plus a dictionary, and the matvec of the loop streams that byte
+ * instead of 12 bytes per entry.  Row sums are formed from the same values in the same ascending
+ * column order with unfused multiply and add: s = A p is bit-identical to the CSR kernel's.
+ * on != 0: build (first time) and switch; returns 1 if the system now runs the pattern matvec,
+ * 0 if the matrix does not qualify (it stays on CSR; cgb200_last_error() says why), -1 on a CUDA
+ * failure.  on == 0 switches back to CSR.  With several ranks each rank decides for its own rows. */
+int cgb200_system_use_pattern_format(cgb200_system *sys, int on);
 /* Diagnostics of the one-kernel iteration: SM-cycle counts of its phases, summed over launches by
  * the CTA that closes each phase, relative to that CTA's start.  out16 (may be NULL) receives the
  * counters accumulated so far: [0] wait for the peers' slices of p, [1] GEMV done (last ticket),

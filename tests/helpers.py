@@ -191,6 +191,19 @@ def banded(n, half_bw, seed=3, bseed=7):
     return System(rp, ci, va, rhs(n, bseed), name=f"banded_{n}_{half_bw}")
 
 
+def toeplitz(n, coeffs, bseed=7):
+    """Symmetric Toeplitz band: A[i, i+k] = A[i+k, i] = coeffs[k] (coeffs[0] the diagonal), clipped at
+    the edges.  Few distinct rows once written as (column - row, value): a pattern-format case."""
+    h = len(coeffs) - 1
+    rp, ci, va = [0], [], []
+    for i in range(n):
+        for j in range(max(0, i - h), min(n, i + h + 1)):
+            ci.append(j)
+            va.append(coeffs[abs(j - i)])
+        rp.append(len(ci))
+    return System(rp, ci, va, rhs(n, bseed), name=f"toeplitz_{n}_{h}")
+
+
 def tridiag4():
     """The 4x4 known-answer system: tridiag(-1,2,-1), b = 1."""
     rp = [0, 2, 5, 8, 10]

@@ -432,6 +432,82 @@ def test_dense_one_kernel_iteration_breakdown_and_exact_stop(pkg, gpu_lib):
 
 
 # ---------------------------------------------------------------------------------------------
+# row-pattern dictionary format: same arithmetic, one byte per row
+# ---------------------------------------------------------------------------------------------
+
+PATTERN_SYSTEMS = [
+    lambda: H.tridiag4(),
+    lambda: H.lap(32, 32),
+    lambda: H.lap(100, 37),
+    lambda: H.lap(12, 12, 12),
+    lambda: H.lap(33, 17, 9),
+    lambda: H.lap(1, 1, 700),                                     # 1D chain
+    lambda: H.toeplitz(3000, [9.0, -1.0, -0.5, 0.25, -2.0]),
+    lambda: H.toeplitz(1500, [12.0] + [-0.5 + 0.03 * k for k in range(1, 14)]),   # 27 entries per row: 4 passes of 8
+    lambda: H.lap(256, 256),
+]
+
+
+@pytest.mark.parametrize("mk", PATTERN_SYSTEMS)
+def test_pattern_format_matvec_bit_exact_and_solves(pkg, gpu_lib, mk):
+    s = mk()
+    d = _dev(pkg, s)
+    v = H.rhs(s.n, 99)
+    want = np.empty(s.n)
+    H.oracle().oracle_spmv(s.n, H.iptr(s.row_ptr), H.iptr(s.cols), H.dptr(s.vals), H.dptr(v), H.dptr(want))
+    csr_mv = d.matvec(v)
+    M = 1 if s.n <= 4 else 12
+    r0 = d.solve(M)
+    x_csr = d.x()
+    assert d.use_pattern_format(True), pkg.last_error()
+    it_b, k1_b = d.bytes()
+    assert it_b == s.n + 88 * s.n and k1_b == s.n + 16 * s.n        # one byte per row
+    pat_mv = d.matvec(v)
+    assert np.array_equal(_bits(pat_mv), _bits(want)) and np.array_equal(_bits(csr_mv), _bits(want)), s.name
+    for variant in (pkg.CLASSIC, pkg.SINGLE_REDUCTION):
+        r1 = d.solve(M, variant=variant)
+        assert r1.iterations == r0.iterations and r1.status == r0.status
+        x_pat = d.x()
+        assert np.linalg.norm(x_pat - x_csr) <= 1e-11 * np.linalg.norm(x_csr), (s.name, variant)
+    xo, it_o, _, _ = H.oracle_cg(s, M)
+    d.solve(M)
+    assert np.linalg.norm(d.x() - xo) <= TOL_X * np.linalg.norm(xo)
+    # and back: the CSR kernel again, same bits as before the switch
+    assert d.use_pattern_format(False) is False
+    d.solve(M)
+    assert np.array_equal(_bits(d.x()), _bits(x_csr))
+    d.free()
+
+
+def test_pattern_format_refuses_matrices_without_few_patterns(pkg, gpu_lib):
+    s = H.banded(3000, 5)                # random values: every row is its own pattern
+    d = _dev(pkg, s)
+    assert d.use_pattern_format(True) is False
+    assert "pattern format not applicable" in pkg.last_error()
+    xo, _, _, _ = H.oracle_cg(s, 10)
+    d.solve(10)                           # still on CSR, still right
+    assert np.linalg.norm(d.x() - xo) <= TOL_X * np.linalg.norm(xo)
+    d.free()
+    d = pkg.DeviceSystem.dense(256)       # dense path has no index arrays to compress
+    assert d.use_pattern_format(True) is False
+    d.free()
+    s = H.toeplitz(400, [60.0] + [-0.7] * 40)   # 81 entries per row: longer than a dictionary entry
+    d = _dev(pkg, s)
+    assert d.use_pattern_format(True) is False
+    d.free()
+
+
+def test_pattern_format_device_generated_laplacian_converges(pkg, gpu_lib):
+    d = pkg.DeviceSystem.lap(96, 80, 48)
+    r_csr = d.solve(5000, tol=1e-10)
+    assert d.use_pattern_format(True)
+    r_pat = d.solve(5000, tol=1e-10)
+    assert r_pat.status == pkg.CONVERGED and abs(r_pat.iterations - r_csr.iterations) <= ITER_SLACK
+    assert d.true_relres() <= TOL_RES * 1.05
+    d.free()
+
+
+# ---------------------------------------------------------------------------------------------
 # device-resident systems and generators
 # ---------------------------------------------------------------------------------------------
 

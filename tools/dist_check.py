@@ -127,6 +127,23 @@ r = d.solve(40, variant=SR)
 x = gather_x(d, s.n, [nx * ny * nzl] * world)
 rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
 report("lap3d split-launch single-reduction", r.iterations == it and rel <= 1e-8, f"rel {rel:.2e}")
+# the same slab in the row-pattern dictionary format: interior + boundary tiles, halo waits
+if hasattr(L, "cgb200_system_use_pattern_format"):
+    okp = d.use_pattern_format(True)
+    for variant, nm in ((0, "classic"), (SR, "single-reduction")):
+        r = d.solve(40, variant=variant)
+        x = gather_x(d, s.n, [nx * ny * nzl] * world)
+        rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+        report(f"lap3d pattern format {nm}", okp and r.iterations == it and rel <= 1e-8, f"rel {rel:.2e}")
+    v = H.rhs(s.n, 78)
+    want = np.empty(s.n)
+    H.oracle().oracle_spmv(s.n, H.iptr(s.row_ptr), H.iptr(s.cols), H.dptr(s.vals), H.dptr(v), H.dptr(want))
+    nl_ = nx * ny * nzl
+    got = d.matvec(v[rank * nl_:(rank + 1) * nl_])
+    okb = np.array_equal(got.view(np.uint64), want[rank * nl_:(rank + 1) * nl_].view(np.uint64))
+    tt = torch.tensor([1.0 if okb else 0.0], device="cuda")
+    dist.all_reduce(tt, op=dist.ReduceOp.MIN)
+    report("lap3d pattern format plain matvec bit-exact", tt.item() == 1.0, "")
 d.free()
 
 # 3) dense, all-gather mode
