@@ -25,12 +25,24 @@ struct CsrDev {
 // Row-pattern dictionary format (pattern.cu): one byte per row naming the row's pattern
 // {(column - row, value)}; the dictionary (ntypes x lpad entries, lpad a multiple of 8) is copied
 // into shared memory by the kernel.  Built only for matrices with at most 255 distinct rows.
+constexpr int PAT_MAX_WIN = 4;
 struct PatDev {
   unsigned char* type = nullptr;  // nrows
   int* len = nullptr;             // ntypes
   int* rel = nullptr;             // ntypes * lpad, column (gather space) minus local row
   double* val = nullptr;          // ntypes * lpad
-  int ntypes = 0, lpad = 0;
+  int ntypes = 0, lpad = 0, maxlen = 0;
+  // staged form (k_spmv_pattern_tma): the column offsets of all patterns fall into at most
+  // PAT_MAX_WIN clusters; for a block of consecutive rows each cluster is one contiguous window of
+  // the gather vector, copied into shared memory by bulk async copies.  soff = position of an
+  // entry's operand inside the staged windows, relative to the row's position in the block.
+  bool staged = false;
+  int* soff = nullptr;            // ntypes * lpad
+  int nwin = 0;
+  int wlo[PAT_MAX_WIN] = {0, 0, 0, 0};    // lowest column offset of the window (even)
+  int wspan[PAT_MAX_WIN] = {0, 0, 0, 0};  // highest minus lowest offset
+  int wbase[PAT_MAX_WIN] = {0, 0, 0, 0};  // first element of the window inside a stage
+  int stage_elems = 0;            // doubles of gather vector per stage
 };
 
 // `mode` of the matvec kernels: a finish kind (what the last CTA does with the fused dot
@@ -67,11 +79,11 @@ cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, d
                         const TileRange& tr, int wait_from, double* partials,
                         unsigned int* ticket, CgState* S, int mode, const PeerComm& cm,
                         cudaStream_t st);
-int pattern_grid_for(const PatDev& P, int ntiles);
+int pattern_grid_for(const PatDev& P, const TileRange& tr);
 cudaError_t launch_spmv_pattern(const PatDev& P, int nrows, const double* pg, const double* pown,
-                                double* s, const TileRange& tr, int wait_from, double* partials,
-                                unsigned int* ticket, CgState* S, int mode, const PeerComm& cm,
-                                cudaStream_t st);
+                                double* s, const TileRange& tr, int wait_from, long long plen,
+                                double* partials, unsigned int* ticket, CgState* S, int mode,
+                                const PeerComm& cm, cudaStream_t st);
 void free_pattern(PatDev* P);
 cudaError_t launch_gemv(const double* A, long long ld, int nrows, int ncols, const double* pg,
                         const double* pown, double* s, double* partials, unsigned int* ticket,

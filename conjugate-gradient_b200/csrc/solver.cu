@@ -807,8 +807,8 @@ static int enqueue_matvec(System* S, double* out, int fin, bool dual, bool excha
   // CSR stream kernel, or the pattern kernel when the system was switched to that format
   auto spmv = [&](const TileRange& tr, int wait_from, double* partials, int md) -> cudaError_t {
     if (S->pat_active)
-      return launch_spmv_pattern(S->pat, S->nloc, S->p_ext, S->p_own, out, tr, wait_from, partials,
-                                 &st->ticket[0], st, md, cm, c.stream);
+      return launch_spmv_pattern(S->pat, S->nloc, S->p_ext, S->p_own, out, tr, wait_from,
+                                 S->ext_len, partials, &st->ticket[0], st, md, cm, c.stream);
     return launch_spmv(S->A, S->p_ext, S->p_own, out, tr, wait_from, partials, &st->ticket[0], st,
                        md, cm, c.stream);
   };
@@ -839,7 +839,7 @@ static int enqueue_matvec(System* S, double* out, int fin, bool dual, bool excha
   // interior tiles while the halo is in flight, then the boundary tiles finish the reduction
   const TileRange interior = {{S->tb_lo, 0, 0}, {S->tb_hi, 0, 0}};
   const TileRange boundary = {{0, S->tb_hi, 0}, {S->tb_lo, S->ntiles, 0}};
-  const int g_int = S->pat_active ? pattern_grid_for(S->pat, S->tb_hi - S->tb_lo)
+  const int g_int = S->pat_active ? pattern_grid_for(S->pat, interior)
                                   : spmv_grid_for(S->tb_hi - S->tb_lo);
   const int int_mode = (fin == FIN_NONE) ? mode : (mode | MV_PARTIAL);
   CUDA_OK(spmv(interior, NO_WAIT, S->partials + MV_EXTRA_OFFSET, int_mode));

@@ -19,3 +19,10 @@ for f in sys.argv[1:]:
             continue
         print(f"     {k}: {w['value']} it/s {w['ms_per_step']} ms frac {w.get('frac_of_peak')} K1 {w['roofline']['avg_launch_ms']} ms "
               f"({w['roofline']['frac']}) other {w.get('other_variant', {}).get('value')}")
+        pf = w.get("pattern_format")
+        if pf and "value" in pf:
+            print(f"        pattern format: {pf['value']} it/s {pf['ms_per_step']} ms x{pf['speedup_vs_csr']} vs CSR | "
+                  f"{pf['achieved_gbs_per_gpu']} GB/s of its own {pf['bytes_per_iteration'] / 1e9:.2f} GB/iter "
+                  f"({pf['frac_of_peak']}) | K1 {pf['matvec']['avg_launch_ms']} ms {pf['matvec']['achieved']} GB/s")
+        elif pf:
+            print("        pattern format:", pf)

@@ -1,5 +1,5 @@
 """Small fixed workload for ncu captures: a few CG iterations of one BASELINE config on 1 GPU.
-usage: profile_target.py {dense|lap2d|lap3d512|lap3d384} [iterations] [classic|sr]"""
+usage: profile_target.py {dense|lap2d|lap3d512|lap3d384} [iterations] [classic|sr] [pattern]"""
 import os
 import sys
 
@@ -19,6 +19,8 @@ d = {
     "lap3d384": lambda: pkg.DeviceSystem.lap(384, 384, 384),
 }[w]()
 variant = pkg.SINGLE_REDUCTION if (len(sys.argv) > 3 and sys.argv[3] == "sr") else pkg.CLASSIC
+if len(sys.argv) > 4 and sys.argv[4] == "pattern":
+    assert d.use_pattern_format(True), pkg.last_error()
 r = d.solve(iters - 1, check_every=iters, variant=variant)
 print(w, "iterations", r.iterations, "status", r.status, "relres", r.relres, "ms/iter", r.seconds * 1e3 / max(r.iterations, 1))
 d.free()
