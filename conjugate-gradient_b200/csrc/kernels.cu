@@ -423,7 +423,7 @@ __device__ __forceinline__ int gemv_cta_of(long long u, long long U, int G) {
 // costs the streaming loop no registers.  Called by every thread of the CTA after the records
 // have been written; gid0/gid1 are the group numbers of this CTA's records (nrec of them).
 template <int THREADS, int RB>
-__device__ __noinline__ void gemv_units_shared_groups(int nrows, int ncols,
+__device__ __noinline__ void gemv_units_shared_groups(int nrows, int ncols, const int ngroups,
                                                       const double* __restrict__ pown,
                                                       double* __restrict__ s,
                                                       double* __restrict__ partials,
@@ -435,7 +435,6 @@ __device__ __noinline__ void gemv_units_shared_groups(int nrows, int ncols,
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int G = (int)gridDim.x;
   const int cpg = (ncols + CW - 1) / CW;
-  const int ngroups = (nrows + RB - 1) / RB;
   const long long U = (long long)ngroups * cpg;
   const long long ubeg = U * blockIdx.x / G;
   const long long u1 = U * (blockIdx.x + 1) / G;
@@ -524,7 +523,7 @@ __device__ __noinline__ void gemv_units_shared_groups(int nrows, int ncols,
 // grid's last CTA has nothing left to finish and the fix-ups hide behind the stream of the others.
 template <int THREADS, int RB>
 __device__ __forceinline__ void gemv_units_stream(const double* __restrict__ A, long long ld,
-                                                  int nrows, int ncols,
+                                                  int nrows, int ncols, const int ngroups,
                                                   const double* __restrict__ pg,
                                                   const double* __restrict__ pown,
                                                   double* __restrict__ s,
@@ -541,7 +540,6 @@ __device__ __forceinline__ void gemv_units_stream(const double* __restrict__ A, 
 
   const int G = (int)gridDim.x;
   const int cpg = (ncols + CW - 1) / CW;          // units per row group
-  const int ngroups = (nrows + RB - 1) / RB;
   const long long U = (long long)ngroups * cpg;
   const long long ubeg = U * blockIdx.x / G;
   const long long u1 = U * (blockIdx.x + 1) / G;
@@ -609,7 +607,7 @@ __device__ __forceinline__ void gemv_units_stream(const double* __restrict__ A, 
   if (tid < 2 * REC) recs[(size_t)blockIdx.x * 2 * REC + tid] = (&sm_rec[0][0])[tid];
 
   __syncthreads();  // the records are written (block-wide) before thread 0 fences and arrives
-  gemv_units_shared_groups<THREADS, RB>(nrows, ncols, pown, s, partials, dots, nrec,
+  gemv_units_shared_groups<THREADS, RB>(nrows, ncols, ngroups, pown, s, partials, dots, nrec,
                                         sm_rec[0][0], sm_rec[1][0]);
 }
 
@@ -626,14 +624,110 @@ k_gemv_units(const double* __restrict__ A, long long ld, int nrows, int ncols,
     if (threadIdx.x == 0) wait_halo(cm, S);
   }
   double dot = 0.0, dot2 = 0.0;
-  gemv_units_stream<THREADS, RB>(A, ld, nrows, ncols, pg, pown, s, partials, fin != FIN_NONE, dot,
-                                 dot2);
+  gemv_units_stream<THREADS, RB>(A, ld, nrows, ncols, (nrows + RB - 1) / RB, pg, pown, s, partials,
+                                 fin != FIN_NONE, dot, dot2);
   if (fin == FIN_NONE) return;
   double v[2] = {dot, dot2};
   if (!grid_reduce<THREADS, 2>(v, partials, ticket, partials + GEMV_GDOT_OFFSET,
                                (int)gridDim.x - 1))
     return;
   finish_block<THREADS>(S, cm, fin, v[0], (mode & MV_DUAL) ? v[1] : 0.0);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Dynamic tail of the dense matvec (one-kernel iteration only).
+//
+// A static equal split leaves the fastest SMs idle at the end of the launch: per-CTA stream times
+// differ by +-1 % SYSTEMATICALLY (the same SMs are slow in every launch and every process,
+// profiles/r01c_dense_cta_times_n32768.json), 46 us between the first and the last CTA on the
+// 8.6 GB matrix.  So the last few per cent of the row groups are not dealt statically: they form
+// a pool of chunks (one row group x GEMV_PCH units of columns) that CTAs draw from an atomic
+// counter once their static share is done.  Who computes a chunk varies from run to run; what is
+// computed does not: every chunk leaves its RB partial row sums and its share of p.s in slots
+// that belong to the chunk, and both are later added in chunk order -- results stay run-to-run
+// bit-reproducible.  The pool rows' s is formed in phase B from the chunk records.
+//
+// pool buffer (doubles): [cpc x P x RB chunk records][P * cpc chunk dot shares][counter]
+// ---------------------------------------------------------------------------------------------
+
+constexpr int GEMV_PCH = 2;  // units of columns per pool chunk (64 KB of matrix)
+
+__host__ __device__ __forceinline__ int gemv_chunks_per_group(int ncols, int threads) {
+  const int cpg = (ncols + threads * 4 - 1) / (threads * 4);
+  return (cpg + GEMV_PCH - 1) / GEMV_PCH;
+}
+
+template <int THREADS, int RB>
+__device__ __forceinline__ void gemv_pool_phase(const double* __restrict__ A, long long ld,
+                                                int nrows, int ncols, const int ngs, const int P,
+                                                const double* __restrict__ pg,
+                                                const double* __restrict__ pown,
+                                                double* __restrict__ pool) {
+  constexpr int CW = THREADS * 4;
+  __shared__ double sm_pred[RB][THREADS / 32];
+  __shared__ unsigned int sm_next;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int cpc = gemv_chunks_per_group(ncols, THREADS);
+  const unsigned int nchunks = (unsigned int)P * cpc;
+  double* rec = pool;
+  double* cdot = pool + (size_t)cpc * P * RB;
+  unsigned int* ctr = reinterpret_cast<unsigned int*>(cdot + nchunks);
+  if (tid == 0) sm_next = atomicAdd(ctr, 1u);
+  __syncthreads();
+  unsigned int q = sm_next;
+#pragma unroll 1
+  while (q < nchunks) {
+    __syncthreads();  // everyone holds q: sm_next and sm_pred may be rewritten
+    unsigned int nxt = 0;
+    if (tid == 0) nxt = atomicAdd(ctr, 1u);  // the next draw travels while this chunk streams
+    const int j = (int)(q / cpc), k = (int)(q % cpc);
+    const int row0 = (ngs + j) * RB;
+    const double* rowp[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) rowp[r] = A + (long long)min(row0 + r, nrows - 1) * ld;
+    double gv = 0.0;
+    if (tid < RB && row0 + tid < nrows) gv = pown[row0 + tid];
+    double acc[RB];
+#pragma unroll
+    for (int r = 0; r < RB; ++r) acc[r] = 0.0;
+    const int cend = min((k + 1) * GEMV_PCH * CW, ncols);
+#pragma unroll 2
+    for (int c = k * GEMV_PCH * CW + tid * 4; c < cend; c += CW) {
+      const double4_t pv = *reinterpret_cast<const double4_t*>(pg + c);
+      double4_t a[RB];
+#pragma unroll
+      for (int r = 0; r < RB; ++r) a[r] = ld_stream4(rowp[r] + c);
+#pragma unroll
+      for (int r = 0; r < RB; ++r) {
+        acc[r] = fma(a[r].x, pv.x, acc[r]);
+        acc[r] = fma(a[r].y, pv.y, acc[r]);
+        acc[r] = fma(a[r].z, pv.z, acc[r]);
+        acc[r] = fma(a[r].w, pv.w, acc[r]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < RB; ++r) acc[r] = warp_sum(acc[r]);
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < RB; ++r) sm_pred[r][warp] = acc[r];
+    }
+    if (tid == 0) sm_next = nxt;
+    __syncthreads();
+    if (warp == 0) {
+      double t = 0.0;
+      if (lane < RB) {
+#pragma unroll
+        for (int w = 0; w < THREADS / 32; ++w) t += sm_pred[lane][w];
+        rec[((size_t)k * P + j) * RB + lane] = t;
+      }
+      const double d = (lane < RB && row0 + lane < nrows) ? gv * t : 0.0;
+      double a1 = 0.0;
+#pragma unroll
+      for (int r = 0; r < RB; ++r) a1 += __shfl_sync(0xffffffffu, d, r);  // row order
+      if (lane == 0) cdot[q] = a1;
+    }
+    q = sm_next;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -660,8 +754,8 @@ __global__ void __launch_bounds__(THREADS, 4)
 k_cg_dense_iter(const double* __restrict__ A, long long ld, int nrows, int ncols,
                 const double* pg, double* pown, double* __restrict__ x, double* __restrict__ r,
                 double* s, double* __restrict__ partials, CgState* S, const int wait,
-                const int timing, unsigned long long* __restrict__ trace,
-                const __grid_constant__ PeerComm cm) {
+                const int timing, unsigned long long* __restrict__ trace, const int pool_groups,
+                double* __restrict__ pool, const __grid_constant__ PeerComm cm) {
   if (S->done) return;
   const int tid = threadIdx.x;
   __shared__ unsigned long long sh_e0, sh_t0;
@@ -679,7 +773,9 @@ k_cg_dense_iter(const double* __restrict__ A, long long ld, int nrows, int ncols
 
   // ---- phase A -------------------------------------------------------------------------------
   double dot = 0.0, dot2 = 0.0;
-  gemv_units_stream<THREADS, RB>(A, ld, nrows, ncols, pg, pown, s, partials, true, dot, dot2);
+  const int ngs = (nrows + RB - 1) / RB - pool_groups;  // statically dealt row groups
+  gemv_units_stream<THREADS, RB>(A, ld, nrows, ncols, ngs, pg, pown, s, partials, true, dot, dot2);
+  if (pool_groups > 0) gemv_pool_phase<THREADS, RB>(A, ld, nrows, ncols, ngs, pool_groups, pg, pown, pool);
   const unsigned long long e0 = sh_e0;
   if (trace && tid == 0) {  // spread of the CTAs' start and stream-end times (ns, global timer)
     atomicMin(trace + 8, sh_t0);
@@ -711,6 +807,19 @@ k_cg_dense_iter(const double* __restrict__ A, long long ld, int nrows, int ncols
         tv[9] = 0ull;
         tv[11] = 0ull;
       }
+      if (pool_groups > 0) {  // the pool's shares of p.s, in chunk order
+        const int cpc = gemv_chunks_per_group(ncols, THREADS);
+        const int nchunks = pool_groups * cpc;
+        const double* cdot = pool + (size_t)cpc * pool_groups * RB;
+        double cd = 0.0;
+        for (int i = tid; i < nchunks; i += THREADS) cd += __ldcg(cdot + i);
+        __shared__ double sm_cd[THREADS / 32];
+        cd = block_sum<THREADS>(cd, sm_cd);
+        if (tid == 0) {
+          v[0] += cd;
+          *reinterpret_cast<unsigned int*>(pool + (size_t)cpc * pool_groups * RB + nchunks) = 0u;
+        }
+      }
       if (!timing) finish_block<THREADS>(S, cm, FIN_PS, v[0], 0.0);
       if (trace && tid == 0) {
         atomicAdd(trace + 3, (unsigned long long)(clock64() - c0));
@@ -725,10 +834,20 @@ k_cg_dense_iter(const double* __restrict__ A, long long ld, int nrows, int ncols
   // ---- phase B -------------------------------------------------------------------------------
   const double alpha = ld_volatile_f64(&S->alpha);
   const long long gstride = (long long)gridDim.x * THREADS;
+  const long long pool_row0 = pool_groups > 0 ? (long long)ngs * RB : (long long)nrows;
   double acc = 0.0;
   for (long long i = (long long)blockIdx.x * THREADS + tid; i < nrows; i += gstride) {
     const double pv = pown[i];
-    const double sv = __ldcg(s + i);  // written by other CTAs of this launch: read at L2
+    double sv;
+    if (i >= pool_row0) {  // a pool row: its chunks' partial sums, in chunk order
+      const int cpc = gemv_chunks_per_group(ncols, THREADS);
+      const size_t jr = (size_t)(i - pool_row0);  // == j * RB + r
+      sv = 0.0;
+      for (int k = 0; k < cpc; ++k) sv += __ldcg(pool + (size_t)k * pool_groups * RB + jr);
+      s[i] = sv;
+    } else {
+      sv = __ldcg(s + i);  // written by other CTAs of this launch: read at L2
+    }
     const double xn = __dadd_rn(x[i], __dmul_rn(alpha, pv));
     const double rn = __dsub_rn(r[i], __dmul_rn(alpha, sv));
     x[i] = xn;
@@ -1393,10 +1512,37 @@ bool dense_iter_supported(const double* A, long long ld, int ncols, const double
   return ld % 4 == 0 && ncols % 4 == 0 && ((uintptr_t)A % 32 == 0) && ((uintptr_t)pg % 32 == 0);
 }
 
+// Row groups left to the dynamic pool of the one-kernel iteration: about 3 % of the matrix plus
+// 40 MB (the end-of-launch spread has a fixed and a proportional part), at most a quarter, none
+// for small blocks.  CGB200_GEMV_POOL_PCT overrides the percentage (0 = static split only).
+int dense_pool_groups(int nrows, int ncols) {
+  static int pct = -2;
+  if (pct == -2) {
+    const char* e = getenv("CGB200_GEMV_POOL_PCT");
+    pct = e ? atoi(e) : -1;
+  }
+  const int ngroups = (nrows + GV_RB - 1) / GV_RB;
+  const double bytes = 8.0 * (double)nrows * (double)ncols;
+  if (bytes < 64e6 || ngroups < 4 * sm_count()) return 0;
+  double f = pct >= 0 ? pct / 100.0 : 0.03 + 40e6 / bytes;
+  if (f > 0.25) f = 0.25;
+  int P = (int)(f * ngroups);
+  if (P > 8192) P = 8192;
+  return P < 0 ? 0 : P;
+}
+
+size_t dense_pool_doubles(int nrows, int ncols) {
+  const int P = dense_pool_groups(nrows, ncols);
+  if (P <= 0) return 0;
+  const size_t cpc = (size_t)gemv_chunks_per_group(ncols, GV_T);
+  return cpc * P * GV_RB + cpc * P + 8;
+}
+
 cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int ncols,
                                  const double* pg, double* pown, double* x, double* r, double* s,
                                  double* partials, CgState* S, int wait, int timing,
-                                 unsigned long long* trace, const PeerComm& cm, cudaStream_t st) {
+                                 unsigned long long* trace, double* pool, const PeerComm& cm,
+                                 cudaStream_t st) {
   static int bps = 0;
   if (!bps) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_cg_dense_iter<GV_T, GV_RB>, GV_T, 0);
@@ -1404,8 +1550,9 @@ cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int n
     const char* e = getenv("CGB200_GEMV_BPS");  // fewer CTAs per SM (experiments)
     if (e && atoi(e) > 0 && atoi(e) < bps) bps = atoi(e);
   }
+  const int P = pool ? dense_pool_groups(nrows, ncols) : 0;
   const long long units =
-      (long long)((nrows + GV_RB - 1) / GV_RB) * ((ncols + GV_T * 4 - 1) / (GV_T * 4));
+      (long long)((nrows + GV_RB - 1) / GV_RB - P) * ((ncols + GV_T * 4 - 1) / (GV_T * 4));
   long long grid = (long long)sm_count() * bps;
   if (grid > units) grid = units;
   const long long cap = GEMV_MAX_GRID;  // room for two records per CTA
@@ -1422,7 +1569,8 @@ cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int n
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const cudaError_t e = cudaLaunchKernelEx(&cfg, k_cg_dense_iter<GV_T, GV_RB>, A, ld, nrows, ncols, pg,
-                                           pown, x, r, s, partials, S, wait, timing, trace, cm);
+                                           pown, x, r, s, partials, S, wait, timing, trace, P, pool,
+                                           cm);
   ++g_launches;
   return e != cudaSuccess ? e : cudaGetLastError();
 }

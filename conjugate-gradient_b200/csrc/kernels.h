@@ -95,7 +95,10 @@ bool dense_iter_supported(const double* A, long long ld, int ncols, const double
 cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int ncols,
                                  const double* pg, double* pown, double* x, double* r, double* s,
                                  double* partials, CgState* S, int wait, int timing,
-                                 unsigned long long* trace, const PeerComm& cm, cudaStream_t st);
+                                 unsigned long long* trace, double* pool, const PeerComm& cm,
+                                 cudaStream_t st);
+int dense_pool_groups(int nrows, int ncols);       // row groups dealt dynamically (0 = none)
+size_t dense_pool_doubles(int nrows, int ncols);   // size of the zero-initialised pool buffer
 cudaError_t launch_update_xr(double* x, double* r, const double* p, const double* s, long long n,
                              double* partials, unsigned int* ticket, CgState* S, int fin,
                              const PeerComm& cm, cudaStream_t st);

@@ -306,6 +306,7 @@ System::~System() {
   cudaFree(state);
   cudaFree(partials);
   cudaFree(trace);
+  cudaFree(gemv_pool);
 }
 
 // Allocates the matrix arrays with the padding the bulk copies may over-read (zero-filled).
@@ -467,6 +468,13 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
   CUDA_OK(cudaMalloc(&S->partials, sizeof(double) * partials_doubles()));
   CUDA_OK(cudaMemsetAsync(S->partials, 0, sizeof(double) * partials_doubles(), c.stream));
   S->p_own = S->p_ext + S->off;
+  if (S->dense) {  // chunk records of the dense matvec's dynamic tail (kernels.cu: gemv_pool_phase)
+    const size_t pd = dense_pool_doubles(S->nloc, (int)S->n_global);
+    if (pd > 0) {
+      CUDA_OK(cudaMalloc(&S->gemv_pool, pd * sizeof(double)));
+      CUDA_OK(cudaMemsetAsync(S->gemv_pool, 0, pd * sizeof(double), c.stream));
+    }
+  }
   if (S->comm_buf && setup_peer_comm(S, parts)) return -1;
 
   if (!S->dense) {
@@ -888,7 +896,8 @@ static int enqueue_iteration(System* S, int variant) {
   if (dense_one_kernel(S)) {  // dense path: the whole iteration behind two grid barriers
     CUDA_OK(launch_cg_dense_iter(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext,
                                  S->p_own, S->x, S->r, S->s, S->partials, st,
-                                 (S->world > 1 && S->p2p) ? 1 : 0, 0, S->trace, cm, c.stream));
+                                 (S->world > 1 && S->p2p) ? 1 : 0, 0, S->trace, S->gemv_pool, cm,
+                                 c.stream));
     return 0;
   }
   if (enqueue_matvec(S, S->s, nccl ? FIN_LOCAL : FIN_PS, false, true)) return -1;
@@ -1390,7 +1399,7 @@ int system_time_kernel(System* S, int which, int reps, double* ms_out) {
       }
       CUDA_OK(launch_cg_dense_iter(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext,
                                    S->p_own, S->x, S->r, S->s, S->partials, S->state, 0, 1,
-                                   nullptr, S->cm_off, c.stream));
+                                   nullptr, S->gemv_pool, S->cm_off, c.stream));
     } else if (which == 4) {
       CUDA_OK(launch_update_sr(S->x, S->p_own, S->r, S->s, S->w, S->nloc, S->state, S->cm_off,
                                c.stream));

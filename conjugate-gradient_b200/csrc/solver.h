@@ -78,6 +78,7 @@ struct System {
   double* w = nullptr;  // single-reduction variant only: w = A r (allocated on first use)
   CgState* state = nullptr;
   double* partials = nullptr;
+  double* gemv_pool = nullptr;          // dense path: chunk records of the matvec's dynamic tail
   unsigned long long* trace = nullptr;  // phase trace of the one-kernel iteration (diagnostics)
   std::map<int, cudaGraphExec_t> graphs;  // 4 * iterations per graph + 2 * one-kernel + variant -> graph
 
