@@ -33,7 +33,13 @@ namespace {
   } while (0)
 
 std::mutex g_tab_mu;
-int g_mode = CGB200_EAGER;
+// CGB200_MODE=resident starts the operator API in resident mode: the way to run an unmodified
+// caller of mv_ops.h (the reference's own cg.c loop) without a transfer per operator call
+static int initial_mode() {
+  const char* e = getenv("CGB200_MODE");
+  return (e && strcmp(e, "resident") == 0) ? CGB200_RESIDENT : CGB200_EAGER;
+}
+int g_mode = initial_mode();
 
 // ---- device mirrors of caller structs (keyed by struct address) -----------------------------
 
@@ -347,6 +353,37 @@ struct __mv_sparse* mv_deep_copy(struct __mv_sparse* orig) {
   if (!orig) return NULL;
   {
     std::lock_guard<std::mutex> lk(g_tab_mu);
+    // resident mode, vector whose current values live on the device (cg.c:117,120 copy x and r
+    // every iteration): copy device to device and leave the host array of the copy stale, like
+    // every other resident-mode output -- no transfer, no synchronisation
+    auto it = g_vecs.find(orig);
+    if (g_mode == CGB200_RESIDENT && !orig->col_indices && !orig->row_ptr && it != g_vecs.end() &&
+        it->second.dev_valid && !it->second.host_valid && it->second.n == orig->size) {
+      struct __mv_sparse* cp = new_mv_struct();
+      if (!cp) return NULL;
+      cp->size = orig->size;
+      cp->nnz = orig->nnz;
+      cp->values = (double*)calloc(orig->nnz > 0 ? (size_t)orig->nnz : 1, sizeof(double));
+      if (!cp->values) {
+        free(cp);
+        return NULL;
+      }
+      const double* src = it->second.d;  // (taken before g_vecs[cp] may rehash the table)
+      const int n = it->second.n;
+      VectorEntry& e = g_vecs[cp];
+      if (ensure_vec_capacity(e, n) ||
+          (n > 0 && cudaMemcpyAsync(e.d, src, sizeof(double) * n, cudaMemcpyDeviceToDevice,
+                                    ctx().stream) != cudaSuccess)) {
+        set_error("mv_deep_copy: device copy failed");
+        drop_mirror(cp);
+        free(cp->values);
+        free(cp);
+        return NULL;
+      }
+      e.dev_valid = true;
+      e.host_valid = false;
+      return cp;
+    }
     if (sync_to_host(orig)) return NULL;
   }
   struct __mv_sparse* cp = new_mv_struct();

@@ -71,6 +71,12 @@ long long cgb200_launch_count(void);
 int cgb200_device_available(void);
 
 /* ---- operator-API residency (struct address -> device mirror table) ------------------------ */
+/* CGB200_EAGER (default): every operator call uploads its inputs and downloads its output --
+ * correct for any caller.  CGB200_RESIDENT: outputs stay on the device (host arrays go stale)
+ * until cgb200_to_host / print_sparse / mat_get_row / mv_deep_copy of a matrix ask for them;
+ * mv_deep_copy of a device-resident vector copies device to device.  The environment variable
+ * CGB200_MODE=resident selects resident mode at start-up for callers that cannot be edited (the
+ * reference's own cg.c loop: tests/test_gpu_dropin.py). */
 int cgb200_set_mode(int mode);
 int cgb200_to_device(struct __mv_sparse *obj); /* upload now; the mirror becomes valid */
 int cgb200_to_host(struct __mv_sparse *obj);   /* bring values back if the device copy is newer */

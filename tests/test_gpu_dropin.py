@@ -82,3 +82,15 @@ def test_reference_cg_c_runs_unmodified_on_libcgb200(gpu_lib):
         pytest.skip("oracle/_ref/cg_on_b200 not built (needs the reference tree at build time)")
     out = subprocess.run([exe, INPUT, "30"], stdout=subprocess.PIPE, text=True, check=True).stdout
     _close(_filtered(out), open(WANT).read().splitlines())
+
+
+def test_reference_cg_c_unmodified_in_resident_mode(gpu_lib):
+    # CGB200_MODE=resident: the reference loop's vectors stay on the device between operator calls
+    # (mv_deep_copy copies device to device); only dot_product's return value and the final
+    # print_sparse come back to the host.  Same output as the eager run and the CPU build.
+    exe = os.path.join(H.ORACLE_DIR, "_ref", "cg_on_b200")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/cg_on_b200 not built (needs the reference tree at build time)")
+    env = dict(os.environ, CGB200_MODE="resident")
+    out = subprocess.run([exe, INPUT, "30"], stdout=subprocess.PIPE, text=True, check=True, env=env).stdout
+    _close(_filtered(out), open(WANT).read().splitlines())

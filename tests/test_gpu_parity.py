@@ -432,6 +432,53 @@ def test_dense_one_kernel_iteration_breakdown_and_exact_stop(pkg, gpu_lib):
 
 
 # ---------------------------------------------------------------------------------------------
+# resident mode of the operator API: the reference's loop, statement by statement
+# ---------------------------------------------------------------------------------------------
+
+
+@pytest.mark.parametrize("mk,M", [(lambda: H.lap(32, 32), 30), (lambda: H.lap(9, 7, 5), 10), (lambda: H.dense(257), 4)])
+def test_reference_loop_through_the_operators_in_resident_mode(pkg, gpu_lib, mk, M):
+    # cg.c:104-135 written against mv_ops.h, as a caller of the library would: in resident mode
+    # nothing but the dot products' return values crosses the bus until cgb200_to_host
+    L = gpu_lib
+    s = mk()
+    A, b = _structs(pkg, s)
+    xo, it, _, _ = H.oracle_cg(s, M)
+    assert L.cgb200_set_mode(pkg.RESIDENT) == 0
+    try:
+        x_new = L.new_mv_struct_with_size(s.n)
+        r = L.mv_deep_copy(C.byref(b))
+        p = L.mv_deep_copy(r)
+        sv, sres = pkg.MvSparseP(), pkg.MvSparseP()
+        k = 0
+        while True:
+            assert L.mv_mult(C.byref(A), p, C.byref(sv)) == 0, pkg.last_error()
+            alpha = L.dot_product(r, r) / L.dot_product(p, sv)
+            assert L.sv_mult(alpha, p, C.byref(sres)) == 0
+            x_old = L.mv_deep_copy(x_new)                         # device to device
+            assert L.vec_add(x_old, sres, C.byref(x_new)) == 0
+            r_prev = L.mv_deep_copy(r)
+            assert L.sv_mult(alpha, sv, C.byref(sres)) == 0
+            assert L.vec_sub(r, sres, C.byref(r)) == 0             # in place (cg.c:123)
+            if k == M:
+                break
+            beta = L.dot_product(r, r) / L.dot_product(r_prev, r_prev)
+            assert L.sv_mult(beta, p, C.byref(sres)) == 0
+            assert L.vec_add(r, sres, C.byref(p)) == 0
+            k += 1
+            for o in (x_old, r_prev):
+                L.cgb200_free_all(o)
+        stale = _take(x_new, s.n)
+        assert L.cgb200_to_host(x_new) == 0
+        x = _take(x_new, s.n)
+    finally:
+        assert L.cgb200_set_mode(pkg.EAGER) == 0
+        L.cgb200_invalidate(C.byref(A))
+    assert not np.any(stale)                  # the host array was never written before to_host
+    assert np.linalg.norm(x - xo) <= TOL_X * np.linalg.norm(xo)
+
+
+# ---------------------------------------------------------------------------------------------
 # row-pattern dictionary format: same arithmetic, one byte per row
 # ---------------------------------------------------------------------------------------------
 
