@@ -573,7 +573,7 @@ def main():
     # ---- the other BASELINE configs, same run ----
     if not args.no_extras:
         extras = {}
-        names = ["lap2d4096", "lap3d512"] if world == 1 else ["lap3d512", "lap3d384w"]
+        names = ["lap2d4096", "lap3d512", "lap3d384w"] if world == 1 else ["lap3d512", "lap3d384w"]
         for nm in names:
             if nm == args.workload:
                 continue
