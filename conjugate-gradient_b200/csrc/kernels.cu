@@ -894,6 +894,28 @@ __device__ __forceinline__ long long vec_pairs(long long n, const void* a, const
   return (m & 15) ? 0 : (n >> 1);
 }
 
+// number of 4-element groups the 256-bit path may cover: all of them when every pointer is 32-byte
+// aligned, none otherwise.  256-bit accesses move 3 % more bytes per second than 128-bit ones on
+// the mixed read/write vector kernels (tools/exp/vec_bench.cu: 6740 vs 6567 GB/s on 512^3).
+__device__ __forceinline__ long long vec_quads(long long n, const void* a, const void* b,
+                                               const void* c, const void* d) {
+  const uintptr_t m = (uintptr_t)a | (uintptr_t)b | (uintptr_t)c | (uintptr_t)d;
+  return (m & 31) ? 0 : (n >> 2);
+}
+__device__ __forceinline__ double4_t ld4(const double* p) {
+  double4_t v;
+  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w)
+               : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st4(double* p, const double4_t v) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v.x), "d"(v.y), "d"(v.z),
+               "d"(v.w)
+               : "memory");
+}
+constexpr int VU4 = 2;  // unroll of the 256-bit loops (same bytes in flight as VU x 128 bit)
+
 __device__ __forceinline__ double2 ld2(const double* p) {
   return *reinterpret_cast<const double2*>(p);
 }
@@ -907,10 +929,44 @@ k_update_xr(double* __restrict__ x, double* __restrict__ r, const double* __rest
             const __grid_constant__ PeerComm cm) {
   if (S->done) return;
   const double alpha = S->alpha;
-  const long long n2 = vec_pairs(n, x, r, p, s);
+  const long long n4 = vec_quads(n, x, r, p, s);
+  const long long n2 = n4 > 0 ? 2 * n4 : vec_pairs(n, x, r, p, s);
   const long long stride = (long long)gridDim.x * VT;
   double acc = 0.0;
-  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * VU) {
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n4; i += stride * VU4) {
+    double4_t xv[VU4], rv[VU4], pv[VU4], sv[VU4];
+#pragma unroll
+    for (int u = 0; u < VU4; ++u) {
+      const long long j = i + u * stride;
+      if (j < n4) {
+        xv[u] = ld4(x + 4 * j);
+        pv[u] = ld4(p + 4 * j);
+        rv[u] = ld4(r + 4 * j);
+        sv[u] = ld4(s + 4 * j);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VU4; ++u) {
+      const long long j = i + u * stride;
+      if (j < n4) {
+        xv[u].x = __dadd_rn(xv[u].x, __dmul_rn(alpha, pv[u].x));
+        xv[u].y = __dadd_rn(xv[u].y, __dmul_rn(alpha, pv[u].y));
+        xv[u].z = __dadd_rn(xv[u].z, __dmul_rn(alpha, pv[u].z));
+        xv[u].w = __dadd_rn(xv[u].w, __dmul_rn(alpha, pv[u].w));
+        rv[u].x = __dsub_rn(rv[u].x, __dmul_rn(alpha, sv[u].x));
+        rv[u].y = __dsub_rn(rv[u].y, __dmul_rn(alpha, sv[u].y));
+        rv[u].z = __dsub_rn(rv[u].z, __dmul_rn(alpha, sv[u].z));
+        rv[u].w = __dsub_rn(rv[u].w, __dmul_rn(alpha, sv[u].w));
+        st4(x + 4 * j, xv[u]);
+        st4(r + 4 * j, rv[u]);
+        acc = fma(rv[u].x, rv[u].x, acc);
+        acc = fma(rv[u].y, rv[u].y, acc);
+        acc = fma(rv[u].z, rv[u].z, acc);
+        acc = fma(rv[u].w, rv[u].w, acc);
+      }
+    }
+  }
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; n4 == 0 && i < n2; i += stride * VU) {
     double2 xv[VU], rv[VU], pv[VU], sv[VU];
 #pragma unroll
     for (int u = 0; u < VU; ++u) {
@@ -956,9 +1012,38 @@ k_update_p(double* __restrict__ p, const double* __restrict__ r, long long n, co
   if (S->done) return;
   const double beta = S->beta;
   const bool pushing = cm.npush > 0;
-  const long long n2 = vec_pairs(n, p, r, nullptr, nullptr);
+  const long long n4 = vec_quads(n, p, r, nullptr, nullptr);
+  const long long n2 = n4 > 0 ? 2 * n4 : vec_pairs(n, p, r, nullptr, nullptr);
   const long long stride = (long long)gridDim.x * VT;
-  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * VU) {
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n4; i += stride * VU4) {
+    double4_t rv[VU4], pv[VU4];
+#pragma unroll
+    for (int u = 0; u < VU4; ++u) {
+      const long long j = i + u * stride;
+      if (j < n4) {
+        rv[u] = ld4(r + 4 * j);
+        pv[u] = ld4(p + 4 * j);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VU4; ++u) {
+      const long long j = i + u * stride;
+      if (j < n4) {
+        pv[u].x = __dadd_rn(rv[u].x, __dmul_rn(beta, pv[u].x));
+        pv[u].y = __dadd_rn(rv[u].y, __dmul_rn(beta, pv[u].y));
+        pv[u].z = __dadd_rn(rv[u].z, __dmul_rn(beta, pv[u].z));
+        pv[u].w = __dadd_rn(rv[u].w, __dmul_rn(beta, pv[u].w));
+        st4(p + 4 * j, pv[u]);
+        if (pushing) {
+          push_elem(cm, 4 * j, pv[u].x);
+          push_elem(cm, 4 * j + 1, pv[u].y);
+          push_elem(cm, 4 * j + 2, pv[u].z);
+          push_elem(cm, 4 * j + 3, pv[u].w);
+        }
+      }
+    }
+  }
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; n4 == 0 && i < n2; i += stride * VU) {
     double2 rv[VU], pv[VU];
 #pragma unroll
     for (int u = 0; u < VU; ++u) {
