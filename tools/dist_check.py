@@ -162,6 +162,36 @@ rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
 report("dense all-gather single-reduction", abs(r.iterations - it) <= 2 and rel <= 1e-8, f"iters {r.iterations}/{it} rel {rel:.2e}")
 d.free()
 
+# 3b) a dense system big enough for the matvec's dynamic tail (>= 64 MB per rank), in uneven row
+#     blocks that are not multiples of the row-group height and only 16-byte aligned
+n = 6144 + 1024 * world
+s = H.dense(n)
+cnt = blocks(n)
+if world > 1:
+    cnt[0] += 2
+    cnt[-1] -= 2
+row0 = sum(cnt[:rank])
+d = pkg.DeviceSystem.dense(n, row0, cnt[rank])
+xo, it, _, _ = H.oracle_cg(s, 4)
+for variant, nm in ((0, "classic (one-kernel iteration)"), (SR, "single-reduction")):
+    r = d.solve(4, variant=variant)
+    x = gather_x(d, n, cnt)
+    rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
+    report(f"dense uneven blocks, dynamic tail, {nm}", r.iterations == it and rel <= 1e-8,
+           f"iters {r.iterations}/{it} rel {rel:.2e} one-kernel {d.one_kernel_iteration()}")
+x1 = None
+for rep in range(2):   # the dynamic tail must not cost reproducibility
+    d.gen_rhs(5)
+    d.solve(4)
+    xr = d.x()
+    if x1 is None:
+        x1 = xr
+same = np.array_equal(x1.view(np.uint64), xr.view(np.uint64))
+tt = torch.tensor([1.0 if same else 0.0], device="cuda")
+dist.all_reduce(tt, op=dist.ReduceOp.MIN)
+report("dense dynamic tail run-to-run bits", tt.item() == 1.0, "")
+d.free()
+
 # 4) host CSR row blocks, uneven, banded (neighbour mode) and wide band (all-gather fallback)
 for hb, name in ((7, "banded neighbour"), (900, "banded wide")):
     s = H.banded(3001, hb)
