@@ -558,6 +558,14 @@ int classify_tiles(System* S) {
   return 0;
 }
 
+// CGB200_FORMAT=pattern: every CSR system tries the row-pattern dictionary format when it is
+// created (for callers that cannot be edited; cgb200_system_use_pattern_format is the API).
+static int maybe_auto_pattern(System* S) {
+  const char* f = getenv("CGB200_FORMAT");
+  if (!f || strcmp(f, "pattern") != 0 || S->dense || S->nloc <= 0) return 0;
+  return system_use_pattern(S, 1) < 0 ? -1 : 0;
+}
+
 System* system_lap(int nx, int ny, int nz, int z0, int nzl, unsigned long long bseed) {
   if (ensure_init(-1)) return nullptr;
   Ctx& c = g_ctx;
@@ -613,6 +621,7 @@ System* system_lap(int nx, int ny, int nz, int z0, int nzl, unsigned long long b
     delete S;
     return nullptr;
   }
+  if (maybe_auto_pattern(S)) { delete S; return nullptr; }
   return S;
 }
 
@@ -730,6 +739,7 @@ System* system_from_csr(long long n_global, long long row0, int nrows, const int
           cudaSuccess)
     return fail("b H2D");
   if (cudaStreamSynchronize(c.stream) != cudaSuccess) return fail("sync");
+  if (maybe_auto_pattern(S)) { delete S; return nullptr; }
   return S;
 }
 

@@ -19,6 +19,9 @@
  *     --gen dense:N | lap2d:N | lap3d:N    generate the system on the device instead of reading it
  *     --gpus G           row-block partition over G GPUs (one process per GPU, NCCL)
  *     --json             one machine-readable line: iterations, relres, seconds, it/s, GB/s
+ *     --variant classic|sr   the reference's recurrence (default) or the single-reduction one
+ *     --pattern          store stencil-like matrices as one byte per row (row-pattern dictionary
+ *                        format; same arithmetic, fewer bytes) when the matrix qualifies
  */
 #include <errno.h>
 #include <stdint.h>
@@ -121,13 +124,15 @@ typedef struct {
   const char *gen;
   int gpus;
   int json;
+  int variant;
+  int pattern;
 } options;
 
 static void usage(const char *p) {
   fprintf(stderr,
           "Usage: %s <input-data> <max-iterations> [suppress-output]\n"
           "       %s --gen dense:N|lap2d:N|lap3d:N <max-iterations> [--gpus G]\n"
-          "       options: --tol T  --check-every M  --json\n", p, p);
+          "       options: --tol T  --check-every M  --json  --variant classic|sr  --pattern\n", p, p);
 }
 
 static int parse(int argc, char **argv, options *o) {
@@ -142,6 +147,13 @@ static int parse(int argc, char **argv, options *o) {
     else if (!strcmp(a, "--gen") && i + 1 < argc) o->gen = argv[++i];
     else if (!strcmp(a, "--gpus") && i + 1 < argc) o->gpus = atoi(argv[++i]);
     else if (!strcmp(a, "--json")) o->json = 1;
+    else if (!strcmp(a, "--pattern")) o->pattern = 1;
+    else if (!strcmp(a, "--variant") && i + 1 < argc) {
+      const char *v = argv[++i];
+      if (!strcmp(v, "sr") || !strcmp(v, "single-reduction")) o->variant = CGB200_SINGLE_REDUCTION;
+      else if (!strcmp(v, "classic")) o->variant = CGB200_CLASSIC;
+      else { fprintf(stderr, "unknown variant %s\n", v); return -1; }
+    }
     else if (a[0] == '-' && a[1] == '-') { fprintf(stderr, "unknown option %s\n", a); return -1; }
     else {
       if (o->gen && npos == 0) npos = 1; /* no input file with --gen */
@@ -152,6 +164,7 @@ static int parse(int argc, char **argv, options *o) {
     }
   }
   if ((!o->input && !o->gen) || o->max_iter < 0 || o->gpus < 1) return -1;
+  if (o->pattern) setenv("CGB200_FORMAT", "pattern", 1); /* read by the library when a system is created */
   return 0;
 }
 
@@ -200,7 +213,7 @@ static int run_rank(const options *o, int rank, int world, const unsigned char *
     sys = cgb200_system_from_csr(A.size, r0, nl, A.row_ptr + r0, A.col_indices, A.values, b.values + r0);
   }
   if (!sys) { fprintf(stderr, "cg[%d]: %s\n", rank, cgb200_last_error()); return 1; }
-  cgb200_opts opts = {o->max_iter, o->tol, CGB200_CLASSIC, o->check_every, 0};
+  cgb200_opts opts = {o->max_iter, o->tol, o->variant, o->check_every, 0};
   cgb200_result res;
   struct timespec t0, t1;
   clock_gettime(CLOCK_MONOTONIC, &t0);
@@ -274,7 +287,7 @@ int main(int argc, char **argv) {
   struct timespec t0, t1;
   clock_gettime(CLOCK_MONOTONIC, &t0);
   if (o.tol > 0.0 || o.json || o.check_every > 0) {
-    cgb200_opts opts = {o.max_iter, o.tol, CGB200_CLASSIC, o.check_every, 0};
+    cgb200_opts opts = {o.max_iter, o.tol, o.variant, o.check_every, 0};
     rc = cgb200_solve(mat_A, vec_b, &vec_x, &opts, &res);
   } else {
     rc = conj_grad(o.max_iter, mat_A, vec_b, &vec_x);

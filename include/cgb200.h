@@ -139,7 +139,9 @@ void cgb200_set_one_kernel_iteration(int on);
  * column order with unfused multiply and add: s = A p is bit-identical to the CSR kernel's.
  * on != 0: build (first time) and switch; returns 1 if the system now runs the pattern matvec,
  * 0 if the matrix does not qualify (it stays on CSR; cgb200_last_error() says why), -1 on a CUDA
- * failure.  on == 0 switches back to CSR.  With several ranks each rank decides for its own rows. */
+ * failure.  on == 0 switches back to CSR.  With several ranks each rank decides for its own rows.
+ * The environment variable CGB200_FORMAT=pattern makes every CSR system try the format when it is
+ * created (callers that cannot be edited; `cg --pattern`). */
 int cgb200_system_use_pattern_format(cgb200_system *sys, int on);
 /* Diagnostics of the one-kernel iteration: SM-cycle counts of its phases, summed over launches by
  * the CTA that closes each phase, relative to that CTA's start.  out16 (may be NULL) receives the

@@ -94,3 +94,16 @@ def test_reference_cg_c_unmodified_in_resident_mode(gpu_lib):
     env = dict(os.environ, CGB200_MODE="resident")
     out = subprocess.run([exe, INPUT, "30"], stdout=subprocess.PIPE, text=True, check=True, env=env).stdout
     _close(_filtered(out), open(WANT).read().splitlines())
+
+
+def test_cg_driver_pattern_format_and_variant_flags(pkg, gpu_lib):
+    # --pattern: the config-1 stand-in is a 5-point stencil, so the matvec runs in the row-pattern
+    # dictionary format; same printed solution.  --variant sr: the single-reduction recurrence.
+    out = subprocess.run([pkg.CG_DRIVER, INPUT, "30", "--pattern"], stdout=subprocess.PIPE, text=True, check=True).stdout
+    _close(_filtered(out), open(WANT).read().splitlines())
+    out = subprocess.run([pkg.CG_DRIVER, "--gen", "lap3d:48", "2000", "y", "--tol", "1e-10", "--json", "--pattern",
+                          "--variant", "sr"], stdout=subprocess.PIPE, text=True, check=True).stdout
+    j = json.loads(out.splitlines()[-1])
+    assert j["status"] == pkg.CONVERGED and j["relres"] <= 1e-10
+    r = subprocess.run([pkg.CG_DRIVER, INPUT, "30", "--variant", "nope"], stderr=subprocess.PIPE, text=True)
+    assert r.returncode != 0
