@@ -73,6 +73,8 @@ def alg_bytes(w, kernel):
         return 8.0 * nnz + 88.0 * n
     if kernel.startswith("k_gemv"):
         return 8.0 * nnz + 16.0 * n
+    if kernel.startswith("k_spmv_pattern"):  # one byte per row instead of the CSR arrays
+        return 1.0 * n + 16.0 * n
     if kernel.startswith("k_spmv"):
         return 12.0 * nnz + 4.0 * (n + 1) + 16.0 * n
     return {"k_update_xr": 48.0 * n, "k_update_p": 24.0 * n, "k_update_sr": 72.0 * n}.get(kernel)
@@ -84,9 +86,14 @@ md = ["# ncu `--set full --clock-control none` captures, round " + tag + " (one 
       "`alg` = algorithmic bytes per launch (DESIGN.md section 4). Times under ncu are not bench values.", "",
       "| workload | variant | kernel | grid x block | regs | dyn smem KB | time us | DRAM read GB | DRAM write GB | traffic GB | alg GB | traffic/alg | GB/s | DRAM % of peak | L2 hit % | L1 hit % | warps active % |",
       "|---|---|---|---|---|---|---|---|---|---|---|---|---|---|---|---|---|"]
-for path in sorted(glob.glob(os.path.join(SRC, "prof_*_raw.csv"))):
-    m = re.match(r"prof_(\w+?)_(classic|sr)_raw\.csv", os.path.basename(path))
-    w, v = m.group(1), m.group(2)
+ONE = {"one_pat512_raw.csv": ("lap3d512", "pattern")}  # single-kernel captures (tools/ncu_one.sh)
+paths = sorted(glob.glob(os.path.join(SRC, "prof_*_raw.csv"))) + [os.path.join(SRC, k) for k in ONE if os.path.exists(os.path.join(SRC, k))]
+for path in paths:
+    if os.path.basename(path) in ONE:
+        w, v = ONE[os.path.basename(path)]
+    else:
+        m = re.match(r"prof_(\w+?)_(classic|sr)_raw\.csv", os.path.basename(path))
+        w, v = m.group(1), m.group(2)
     rows = read_raw(path)
     keep = os.path.join(DST, f"{tag}_ncu_{w}_{v}.csv")
     with open(keep, "w", newline="") as f:
@@ -104,7 +111,7 @@ for path in sorted(glob.glob(os.path.join(SRC, "prof_*_raw.csv"))):
         md.append(f"| {w} | {v} | {kname} | {int(avg('grid'))} x {int(avg('block'))} | {int(avg('regs'))} | {avg('dyn_smem') / 1e3:.1f} | {t:.1f} | "
                   f"{rd / 1e9:.4f} | {wrt / 1e9:.4f} | {(rd + wrt) / 1e9:.4f} | {alg / 1e9 if alg else 0:.4f} | {(rd + wrt) / alg if alg else 0:.3f} | "
                   f"{(rd + wrt) / t / 1e3:.0f} | {avg('dram_pct'):.1f} | {avg('l2_hit_pct'):.1f} | {avg('l1_hit_pct'):.1f} | {avg('warps_active_pct'):.1f} |")
-        if v == "classic" or kname == "k_update_sr":
+        if v == "classic" or kname == "k_update_sr" or kname.startswith("k_spmv_pattern"):
             traffic["_by_workload"].setdefault(w, {})[kname] = round(rd + wrt)
 with open(os.path.join(DST, f"{tag}_ncu_summary.md"), "w") as f:
     f.write("\n".join(md) + "\n")
