@@ -415,8 +415,28 @@ def cpu_reference_run(workload, budget_s, want_steps, host_arrays=None):
     m = min(m, 5)   # fixed-count CG on this matrix is past convergence after ~6 iterations
     tm, _ = run(m - 1)
     val = m / tm
+    # beside it, for context: the same loop as a tuned CPU program would run it -- O(nnz) CSR matvec,
+    # fused passes, OpenMP over all host cores (oracle_cg_iterations_mt; timing only, its reduction
+    # order is not the reference's).  Reported, never used as the baseline of a ratio.
+    port = None
+    try:
+        O = H.oracle()
+        O.oracle_cg_iterations_mt.restype = C.c_double
+        O.oracle_cg_iterations_mt.argtypes = [C.c_int, H.c_int_p, H.c_int_p, H.c_double_p, H.c_double_p, C.c_int,
+                                              H.c_double_p]
+        xs = np.empty(n)
+        O.oracle_cg_iterations_mt(n, H.iptr(rp), H.iptr(ci), H.dptr(va), H.dptr(b), 1, H.dptr(xs))  # warm-up
+        tp = time.perf_counter()
+        O.oracle_cg_iterations_mt(n, H.iptr(rp), H.iptr(ci), H.dptr(va), H.dptr(b), 5, H.dptr(xs))
+        tp = time.perf_counter() - tp
+        port = {"value": round(5 / tp, 3), "unit": UNIT, "cores": int(O.oracle_num_threads()), "kind": "port",
+                "sample": "5 iterations of the O(nnz) CSR restatement with fused passes, OpenMP over all host "
+                          "threads (oracle/cg_oracle.c: oracle_cg_iterations_mt, -O2), same system",
+                "seconds": round(tp, 3)}
+    except Exception as e:  # noqa: BLE001
+        port = {"error": repr(e)}
     cb = {
-        "value": round(val, 5), "unit": UNIT, "cores": 1, "kind": kind,
+        "value": round(val, 5), "unit": UNIT, "cores": 1, "kind": kind, "tuned_port_all_cores": port,
         "sample": f"{m} iteration(s) (max_iter={m - 1}) of {'the unmodified reference conj_grad (oracle/_ref, gcc -g as its Makefile)' if have_ref else 'the oracle port (oracle/cg_oracle.c, -O2)'} on the full dense n=32768 CSR system, after a 1-iteration warm-up ({t1:.1f} s)",
         "seconds": round(tm, 2),
     }
