@@ -68,12 +68,14 @@ struct SpmvSmem {
 
 // Up to three runs of tiles, visited in this order.  With several GPUs run 0 holds the interior
 // tiles (columns inside the owned block) and runs 1-2 the boundary tiles that gather halo values.
-__device__ __forceinline__ int vtile_to_tile(const TileRange& tr, int v) {
+__device__ __forceinline__ int vtile_to_tile(const TileRange& tr, int v, const bool rev = false) {
   const int n0 = tr.e[0] - tr.b[0];
-  if (v < n0) return tr.b[0] + v;
+  if (v < n0) return rev ? tr.e[0] - 1 - v : tr.b[0] + v;
   v -= n0;
   const int n1 = tr.e[1] - tr.b[1];
-  return v < n1 ? tr.b[1] + v : tr.b[2] + (v - n1);
+  if (v < n1) return rev ? tr.e[1] - 1 - v : tr.b[1] + v;
+  v -= n1;
+  return rev ? tr.e[2] - 1 - v : tr.b[2] + v;
 }
 
 // One row's share of a staged chunk: entries [k, k1) of the stage, ascending column order.
@@ -123,6 +125,7 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
   constexpr int THREADS = R + 32;
   constexpr int CWARPS = R / 32;
   const int fin = mode & MV_FIN_MASK;
+  const bool rev = (mode & MV_REV) != 0;
   if (fin != FIN_NONE && S->done) return;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -157,7 +160,7 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
       int vt = blockIdx.x;
       int nlo = 0, nhi = 0;
       if (vt < nvt) {
-        const int t = vtile_to_tile(tr, vt);
+        const int t = vtile_to_tile(tr, vt, rev);
         nlo = __ldg(rowptr + t * R);
         nhi = __ldg(rowptr + min(t * R + R, nrows));
       }
@@ -169,11 +172,11 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
           wait_halo(cm, S);
           waited = true;
         }
-        const int t = vtile_to_tile(tr, vt);
+        const int t = vtile_to_tile(tr, vt, rev);
         const int lo = nlo & ~3, hi = (nhi + 3) & ~3;
         const int vt2 = vt + gridDim.x;
         if (vt2 < nvt) {
-          const int t2 = vtile_to_tile(tr, vt2);
+          const int t2 = vtile_to_tile(tr, vt2, rev);
           nlo = __ldg(rowptr + t2 * R);
           nhi = __ldg(rowptr + min(t2 * R + R, nrows));
           if (lead >= 0) {
@@ -213,7 +216,7 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
     int item = 0;
 #pragma unroll 1
     for (int vt = blockIdx.x; vt < nvt; vt += gridDim.x) {
-      const int t = vtile_to_tile(tr, vt);
+      const int t = vtile_to_tile(tr, vt, rev);
       const int row = t * R + tid;
       const int rows_valid = min(R, nrows - t * R);
       const bool boundary = vt >= wait_from;
@@ -925,7 +928,7 @@ __device__ __forceinline__ void st2(double* p, double2 v) { *reinterpret_cast<do
 __global__ void __launch_bounds__(VT)
 k_update_xr(double* __restrict__ x, double* __restrict__ r, const double* __restrict__ p,
             const double* __restrict__ s, long long n, double* __restrict__ partials,
-            unsigned int* __restrict__ ticket, CgState* S, const int fin,
+            unsigned int* __restrict__ ticket, CgState* S, const int fin, const int rev,
             const __grid_constant__ PeerComm cm) {
   if (S->done) return;
   const double alpha = S->alpha;
@@ -937,8 +940,9 @@ k_update_xr(double* __restrict__ x, double* __restrict__ r, const double* __rest
     double4_t xv[VU4], rv[VU4], pv[VU4], sv[VU4];
 #pragma unroll
     for (int u = 0; u < VU4; ++u) {
-      const long long j = i + u * stride;
-      if (j < n4) {
+      const long long jj = i + u * stride;
+      const long long j = rev ? n4 - 1 - jj : jj;
+      if (jj < n4) {
         xv[u] = ld4(x + 4 * j);
         pv[u] = ld4(p + 4 * j);
         rv[u] = ld4(r + 4 * j);
@@ -947,8 +951,9 @@ k_update_xr(double* __restrict__ x, double* __restrict__ r, const double* __rest
     }
 #pragma unroll
     for (int u = 0; u < VU4; ++u) {
-      const long long j = i + u * stride;
-      if (j < n4) {
+      const long long jj = i + u * stride;
+      const long long j = rev ? n4 - 1 - jj : jj;
+      if (jj < n4) {
         xv[u].x = __dadd_rn(xv[u].x, __dmul_rn(alpha, pv[u].x));
         xv[u].y = __dadd_rn(xv[u].y, __dmul_rn(alpha, pv[u].y));
         xv[u].z = __dadd_rn(xv[u].z, __dmul_rn(alpha, pv[u].z));
@@ -1008,7 +1013,7 @@ k_update_xr(double* __restrict__ x, double* __restrict__ r, const double* __rest
 // (cg.c:131-132)
 __global__ void __launch_bounds__(VT)
 k_update_p(double* __restrict__ p, const double* __restrict__ r, long long n, const CgState* S,
-           const __grid_constant__ PeerComm cm) {
+           const int rev, const __grid_constant__ PeerComm cm) {
   if (S->done) return;
   const double beta = S->beta;
   const bool pushing = cm.npush > 0;
@@ -1019,16 +1024,18 @@ k_update_p(double* __restrict__ p, const double* __restrict__ r, long long n, co
     double4_t rv[VU4], pv[VU4];
 #pragma unroll
     for (int u = 0; u < VU4; ++u) {
-      const long long j = i + u * stride;
-      if (j < n4) {
+      const long long jj = i + u * stride;
+      const long long j = rev ? n4 - 1 - jj : jj;
+      if (jj < n4) {
         rv[u] = ld4(r + 4 * j);
         pv[u] = ld4(p + 4 * j);
       }
     }
 #pragma unroll
     for (int u = 0; u < VU4; ++u) {
-      const long long j = i + u * stride;
-      if (j < n4) {
+      const long long jj = i + u * stride;
+      const long long j = rev ? n4 - 1 - jj : jj;
+      if (jj < n4) {
         pv[u].x = __dadd_rn(rv[u].x, __dmul_rn(beta, pv[u].x));
         pv[u].y = __dadd_rn(rv[u].y, __dmul_rn(beta, pv[u].y));
         pv[u].z = __dadd_rn(rv[u].z, __dmul_rn(beta, pv[u].z));
@@ -1081,7 +1088,7 @@ k_update_p(double* __restrict__ p, const double* __restrict__ r, long long n, co
 __global__ void __launch_bounds__(VT)
 k_update_sr(double* __restrict__ x, double* __restrict__ g, double* __restrict__ d,
             double* __restrict__ s, const double* __restrict__ w, long long n, const CgState* S,
-            const __grid_constant__ PeerComm cm) {
+            const int rev, const __grid_constant__ PeerComm cm) {
   if (S->done) return;
   const double alpha = S->alpha, beta = S->beta;
   const bool pushing = cm.npush > 0;
@@ -1093,8 +1100,9 @@ k_update_sr(double* __restrict__ x, double* __restrict__ g, double* __restrict__
     double2 xv[U], gv[U], dv[U], sv[U], wv[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const long long j = i + u * stride;
-      if (j < n2) {
+      const long long jj = i + u * stride;
+      const long long j = rev ? n2 - 1 - jj : jj;
+      if (jj < n2) {
         gv[u] = ld2(g + 2 * j);
         dv[u] = ld2(d + 2 * j);
         wv[u] = ld2(w + 2 * j);
@@ -1104,8 +1112,9 @@ k_update_sr(double* __restrict__ x, double* __restrict__ g, double* __restrict__
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const long long j = i + u * stride;
-      if (j < n2) {
+      const long long jj = i + u * stride;
+      const long long j = rev ? n2 - 1 - jj : jj;
+      if (jj < n2) {
         dv[u].x = __dadd_rn(gv[u].x, __dmul_rn(beta, dv[u].x));
         dv[u].y = __dadd_rn(gv[u].y, __dmul_rn(beta, dv[u].y));
         sv[u].x = __dadd_rn(wv[u].x, __dmul_rn(beta, sv[u].x));
@@ -1661,23 +1670,24 @@ cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int n
 }
 
 cudaError_t launch_update_xr(double* x, double* r, const double* p, const double* s, long long n,
-                             double* partials, unsigned int* ticket, CgState* S, int fin,
+                             double* partials, unsigned int* ticket, CgState* S, int fin, int rev,
                              const PeerComm& cm, cudaStream_t st) {
-  k_update_xr<<<vec_grid(n), VT, 0, st>>>(x, r, p, s, n, partials, ticket, S, fin, cm);
+  k_update_xr<<<vec_grid(n), VT, 0, st>>>(x, r, p, s, n, partials, ticket, S, fin, rev, cm);
   ++g_launches;
   return cudaGetLastError();
 }
 
-cudaError_t launch_update_p(double* p, const double* r, long long n, const CgState* S,
+cudaError_t launch_update_p(double* p, const double* r, long long n, const CgState* S, int rev,
                             const PeerComm& cm, cudaStream_t st) {
-  k_update_p<<<vec_grid(n), VT, 0, st>>>(p, r, n, S, cm);
+  k_update_p<<<vec_grid(n), VT, 0, st>>>(p, r, n, S, rev, cm);
   ++g_launches;
   return cudaGetLastError();
 }
 
 cudaError_t launch_update_sr(double* x, double* g, double* d, double* s, const double* w,
-                             long long n, const CgState* S, const PeerComm& cm, cudaStream_t st) {
-  k_update_sr<<<vec_grid(n), VT, 0, st>>>(x, g, d, s, w, n, S, cm);
+                             long long n, const CgState* S, int rev, const PeerComm& cm,
+                             cudaStream_t st) {
+  k_update_sr<<<vec_grid(n), VT, 0, st>>>(x, g, d, s, w, n, S, rev, cm);
   ++g_launches;
   return cudaGetLastError();
 }

@@ -56,6 +56,7 @@ enum : int { FIN_NONE = 0, FIN_INIT = 1, FIN_PS = 2, FIN_RR = 3, FIN_SR = 4, FIN
 constexpr int MV_FIN_MASK = 0x0f;
 constexpr int MV_PARTIAL = 0x10;  // publish per-CTA partials only (first half of a split launch)
 constexpr int MV_DUAL = 0x20;     // also reduce the square of the gathered vector's owned block
+constexpr int MV_REV = 0x40;      // visit each run of tiles from its last tile to its first (sweep direction)
 // a finishing launch adds `extra` partials left at partials[MV_EXTRA_OFFSET ..] by a preceding
 // MV_PARTIAL launch: mode |= extra << 8
 constexpr int MV_EXTRA_OFFSET = 4096;
@@ -99,13 +100,15 @@ cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int n
                                  cudaStream_t st);
 int dense_pool_groups(int nrows, int ncols);       // row groups dealt dynamically (0 = none)
 size_t dense_pool_doubles(int nrows, int ncols);   // size of the zero-initialised pool buffer
+// rev != 0: the vector kernels sweep from the last element to the first (see solver.cu: sweep_dir)
 cudaError_t launch_update_xr(double* x, double* r, const double* p, const double* s, long long n,
-                             double* partials, unsigned int* ticket, CgState* S, int fin,
+                             double* partials, unsigned int* ticket, CgState* S, int fin, int rev,
                              const PeerComm& cm, cudaStream_t st);
-cudaError_t launch_update_p(double* p, const double* r, long long n, const CgState* S,
+cudaError_t launch_update_p(double* p, const double* r, long long n, const CgState* S, int rev,
                             const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_update_sr(double* x, double* g, double* d, double* s, const double* w,
-                             long long n, const CgState* S, const PeerComm& cm, cudaStream_t st);
+                             long long n, const CgState* S, int rev, const PeerComm& cm,
+                             cudaStream_t st);
 cudaError_t launch_init(double* x, double* r, double* p, double* s, const double* b, long long n,
                         int sr, double* partials, unsigned int* ticket, CgState* S, int fin,
                         const PeerComm& cm, cudaStream_t st);

@@ -337,12 +337,14 @@ __device__ __forceinline__ double pattern_row(const double* __restrict__ val_s,
   return acc;
 }
 
-__device__ __forceinline__ int pat_vtile_to_tile(const TileRange& tr, int v) {
+__device__ __forceinline__ int pat_vtile_to_tile(const TileRange& tr, int v, const bool rev) {
   const int n0 = tr.e[0] - tr.b[0];
-  if (v < n0) return tr.b[0] + v;
+  if (v < n0) return rev ? tr.e[0] - 1 - v : tr.b[0] + v;
   v -= n0;
   const int n1 = tr.e[1] - tr.b[1];
-  return v < n1 ? tr.b[1] + v : tr.b[2] + (v - n1);
+  if (v < n1) return rev ? tr.e[1] - 1 - v : tr.b[1] + v;
+  v -= n1;
+  return rev ? tr.e[2] - 1 - v : tr.b[2] + v;
 }
 
 // Two rows of at most 8 entries each, all 16 gathers issued before the first product is formed.
@@ -393,6 +395,7 @@ k_spmv_pattern(const unsigned char* __restrict__ type, const int* __restrict__ l
                unsigned int* __restrict__ ticket, CgState* S, const int mode, const int hint,
                const __grid_constant__ PeerComm cm) {
   const int fin = mode & MV_FIN_MASK;
+  const bool rev = (mode & MV_REV) != 0;
   if (fin != FIN_NONE && S->done) return;
   extern __shared__ __align__(16) unsigned char pat_smem[];
   double* val_s = reinterpret_cast<double*>(pat_smem);
@@ -423,7 +426,7 @@ k_spmv_pattern(const unsigned char* __restrict__ type, const int* __restrict__ l
     int row[PAT_B], ty[PAT_B];
 #pragma unroll
     for (int j = 0; j < PAT_B; ++j) {
-      row[j] = j < nb ? pat_vtile_to_tile(tr, v0 + j) * R + tid : nrows;
+      row[j] = j < nb ? pat_vtile_to_tile(tr, v0 + j, rev) * R + tid : nrows;
       ty[j] = row[j] < nrows ? (int)type[row[j]] : -1;
     }
     if (lpad == 8) {
@@ -524,16 +527,22 @@ struct PatWin {
 };
 
 // Blocks never straddle two runs of the tile range, so a block's rows are consecutive.
-__device__ __forceinline__ bool pt_decode(const TileRange& tr, int g, int& tile0, int& nb,
-                                          int& vfirst) {
+__device__ __forceinline__ bool pt_decode(const TileRange& tr, int g, const bool rev, int& tile0,
+                                          int& nb, int& vfirst) {
   int pre = 0;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
     const int lenk = tr.e[k] - tr.b[k];
     const int nblk = (lenk + PT_PB - 1) / PT_PB;
     if (g < nblk) {
-      tile0 = tr.b[k] + g * PT_PB;
-      nb = min(PT_PB, tr.e[k] - tile0);
+      if (rev) {  // the run's blocks from its end: block g ends PT_PB * g tiles before the run's end
+        const int hi = tr.e[k] - g * PT_PB;
+        tile0 = max(tr.b[k], hi - PT_PB);
+        nb = hi - tile0;
+      } else {
+        tile0 = tr.b[k] + g * PT_PB;
+        nb = min(PT_PB, tr.e[k] - tile0);
+      }
       vfirst = pre + g * PT_PB;
       return true;
     }
@@ -565,6 +574,7 @@ k_spmv_pattern_tma(const unsigned char* __restrict__ type, const int* __restrict
   constexpr int CWARPS = R / 32;
   constexpr int TYB = PT_PB * R;  // pattern bytes per stage
   const int fin = mode & MV_FIN_MASK;
+  const bool rev = (mode & MV_REV) != 0;
   if (fin != FIN_NONE && S->done) return;
 
   extern __shared__ __align__(128) unsigned char pt_smem[];
@@ -603,7 +613,7 @@ k_spmv_pattern_tma(const unsigned char* __restrict__ type, const int* __restrict
       int item = 0;
       int tile0 = 0, nb = 0, vfirst = 0;
 #pragma unroll 1
-      for (int g = blockIdx.x; pt_decode(tr, g, tile0, nb, vfirst); g += gridDim.x, ++item) {
+      for (int g = blockIdx.x; pt_decode(tr, g, rev, tile0, nb, vfirst); g += gridDim.x, ++item) {
         if (vfirst + nb - 1 >= wait_from && !waited) {
           // first block with boundary tiles: the peers' rows of the gather vector must have landed,
           // and the bulk copies (async proxy) must be ordered behind that acquire
@@ -646,7 +656,7 @@ k_spmv_pattern_tma(const unsigned char* __restrict__ type, const int* __restrict
     int item = 0;
     int tile0 = 0, nb = 0, vfirst = 0;
 #pragma unroll 1
-    for (int g = blockIdx.x; pt_decode(tr, g, tile0, nb, vfirst); g += gridDim.x, ++item) {
+    for (int g = blockIdx.x; pt_decode(tr, g, rev, tile0, nb, vfirst); g += gridDim.x, ++item) {
       const int stage = item % stages;
       mbar_wait(&full[stage], (uint32_t)(item / stages) & 1u);
       const double* pw = p_area + (size_t)stage * win.stage_elems;
