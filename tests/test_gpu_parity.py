@@ -214,6 +214,81 @@ def test_mv_mult_ragged_rows_bit_exact(pkg, gpu_lib):
     gpu_lib.cgb200_invalidate(C.byref(A))
 
 
+def _random_spd(rng, n, avg, symmetric=True):
+    """Random sparse symmetric strictly diagonally dominant matrix (SPD), sorted unique columns per
+    row, irreducible through a chain i -- i+1 (so the reference's row scan cannot bleed)."""
+    nnz_off = max(1, int(avg * n / 2))
+    i = rng.integers(0, n, nnz_off)
+    j = rng.integers(0, n, nnz_off)
+    keep = i != j
+    i, j = i[keep], j[keep]
+    chain = np.arange(n - 1)
+    i = np.concatenate([i, chain])
+    j = np.concatenate([j, chain + 1])
+    if n >= 7000:  # two hub rows longer than one pipeline stage of the stream kernel (3584 entries)
+        for hub in (3, n // 2):
+            nb = rng.choice(n, size=4200, replace=False)
+            nb = nb[nb != hub]
+            i = np.concatenate([i, np.full(len(nb), hub)])
+            j = np.concatenate([j, nb])
+    lo, hi = np.minimum(i, j), np.maximum(i, j)     # one value per unordered pair, then mirror
+    key = lo.astype(np.int64) * n + hi
+    _, first = np.unique(key, return_index=True)
+    lo, hi = lo[first], hi[first]
+    v = rng.uniform(-1.0, 1.0, len(lo))
+    rows = np.concatenate([lo, hi])
+    cols = np.concatenate([hi, lo])
+    vals = np.concatenate([v, v])
+    absrow = np.zeros(n)
+    np.add.at(absrow, rows, np.abs(vals))
+    rows = np.concatenate([rows, np.arange(n)])
+    cols = np.concatenate([cols, np.arange(n)])
+    vals = np.concatenate([vals, absrow + 1.0])
+    order = np.argsort(rows.astype(np.int64) * n + cols, kind="stable")
+    rows, cols, vals = rows[order], cols[order], vals[order]
+    rp = np.zeros(n + 1, dtype=np.int64)
+    np.add.at(rp, rows + 1, 1)
+    rp = np.cumsum(rp)
+    return H.System(rp, cols, vals, H.rhs(n, int(rng.integers(1, 1 << 30))), f"random_spd_{n}_{avg}")
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_sparse_spd_systems_matvec_bits_and_fixed_count_solve(pkg, gpu_lib, seed):
+    # randomised structure: sizes off every tile / vector-width boundary, row lengths from 1 to
+    # hundreds (rows longer than a pipeline stage included at the larger densities)
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.choice([1, 2, 5, 31, 511, 513, 1000, 2049, 4097, 7777, 20011]))
+    avg = float(rng.choice([1.5, 4.0, 9.0, 30.0])) if n > 8 else 1.5
+    s = _random_spd(rng, n, avg)
+    A, _ = _structs(pkg, s)
+    v = H.rhs(n, 55 + seed)
+    out = pkg.MvSparseP()
+    assert gpu_lib.mv_mult(C.byref(A), C.byref(_vec(pkg, v)), C.byref(out)) == 0, pkg.last_error()
+    want = np.empty(n)
+    H.oracle().oracle_spmv(n, H.iptr(s.row_ptr), H.iptr(s.cols), H.dptr(s.vals), H.dptr(v), H.dptr(want))
+    full = s.nnz == n * n                      # tiny cases can come out dense: tree-summed path
+    if full:
+        assert np.allclose(_take(out, n), want, rtol=1e-13, atol=0)
+    else:
+        assert np.array_equal(_bits(_take(out, n)), _bits(want)), s.name
+    gpu_lib.cgb200_invalidate(C.byref(A))
+    M = int(rng.integers(0, 9))
+    xo, it, _, st = H.oracle_cg(s, M, guard=1)
+    for variant, orc in ((0, (xo, it)), (1, None)):
+        x, r = gpu_solve(pkg, gpu_lib, s, M, 0.0, variant)
+        if variant == 1:
+            xs, its, _, _ = H.oracle_cg_sr(s, M)
+            orc = (xs, its)
+        if r.status in (pkg.EXACT, pkg.BREAKDOWN):
+            continue                            # converged to round-off before M (tiny systems)
+        assert r.iterations == orc[1], (s.name, variant)
+        # the single-reduction recurrence amplifies rounding differences on badly scaled systems (the
+        # hub rows): its two CPU forms already differ by `drift`, so allow the device that much
+        drift = np.linalg.norm(orc[0] - xo) / np.linalg.norm(xo) if variant == 1 else 0.0
+        err = np.linalg.norm(x - orc[0]) / np.linalg.norm(orc[0])
+        assert err <= max(TOL_X, 20 * drift), (s.name, variant, err, drift)
+
+
 @pytest.mark.parametrize("n", [1, 2, 3, 7, 64, 513, 1024, 2050, 2052, 4104])
 def test_mv_mult_dense_path(pkg, gpu_lib, n):
     # full rows take the values-only GEMV; tree summation => tolerance, not bits.  n % 4 == 0 takes
