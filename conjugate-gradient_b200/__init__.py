@@ -46,7 +46,7 @@ class Opts(C.Structure):
         ("tol", C.c_double),
         ("variant", C.c_int),
         ("check_every", C.c_int),
-        ("reserved", C.c_int),
+        ("flags", C.c_int),
     ]
 
 
@@ -70,6 +70,7 @@ class Result(C.Structure):
 RUNNING, MAXITER, CONVERGED, BREAKDOWN, EXACT, COMM_TIMEOUT = 0, 1, 2, 3, 4, 5
 CLASSIC, SINGLE_REDUCTION = 0, 1
 EAGER, RESIDENT = 0, 1
+OPT_JACOBI, OPT_X0 = 1, 2
 
 # every symbol include/mv_ops.h and include/cgb200.h declare (checked by tests/test_abi_symbols.py)
 MV_OPS_SYMBOLS = [
@@ -148,6 +149,7 @@ def lib():
     L.cgb200_system_set_rhs.argtypes = [C.c_void_p, c_double_p]
     L.cgb200_system_gen_rhs.argtypes = [C.c_void_p, C.c_uint64]
     L.cgb200_system_get_x.argtypes = [C.c_void_p, c_double_p]
+    L.cgb200_system_set_x.argtypes = [C.c_void_p, c_double_p]
     L.cgb200_system_solve.argtypes = [C.c_void_p, C.POINTER(Opts), C.POINTER(Result)]
     L.cgb200_system_solve_async.argtypes = [C.c_void_p, C.POINTER(Opts), C.POINTER(C.c_longlong)]
     L.cgb200_solve_wait.argtypes = [C.c_longlong, C.POINTER(Result)]
@@ -230,8 +232,15 @@ class DeviceSystem:
     def nnz(self):
         return lib().cgb200_system_nnz(self.h)
 
-    def solve(self, max_iter, tol=0.0, variant=CLASSIC, check_every=0):
-        o = Opts(max_iter, tol, variant, check_every, 0)
+    def solve(self, max_iter, tol=0.0, variant=CLASSIC, check_every=0, jacobi=False, x0=None):
+        """x0: None = start from zero (the reference, cg.c:104); True = start from the x the system
+        holds (a previous solve's); an array = upload it first.  jacobi: diagonal preconditioner."""
+        flags = OPT_JACOBI if jacobi else 0
+        if x0 is not None:
+            flags |= OPT_X0
+            if x0 is not True:
+                self.set_x(x0)
+        o = Opts(max_iter, tol, variant, check_every, flags)
         r = Result()
         _check(lib().cgb200_system_solve(self.h, C.byref(o), C.byref(r)), "cgb200_system_solve")
         return r
@@ -258,6 +267,13 @@ class DeviceSystem:
         b = np.ascontiguousarray(b, dtype=np.float64)
         assert len(b) == self.rows
         _check(lib().cgb200_system_set_rhs(self.h, b.ctypes.data_as(c_double_p)), "cgb200_system_set_rhs")
+
+    def set_x(self, x0):
+        import numpy as np
+
+        x0 = np.ascontiguousarray(x0, dtype=np.float64)
+        assert len(x0) == self.rows
+        _check(lib().cgb200_system_set_x(self.h, x0.ctypes.data_as(c_double_p)), "cgb200_system_set_x")
 
     def x(self):
         import numpy as np

@@ -299,6 +299,14 @@ int solve_host(struct __mv_sparse* A, struct __mv_sparse* b, struct __mv_sparse*
   if (sync_to_host(b)) return -1;
   const int n = b->size;
   if (n > 0) CU_OK(cudaMemcpyAsync(sys->b, b->values, sizeof(double) * n, cudaMemcpyHostToDevice, c.stream));
+  if (o.flags & CGB200_OPT_X0) {  // extension: *x holds the initial guess (the reference starts at 0)
+    if (!*x || (*x)->size != n || !(*x)->values) {
+      set_error("CGB200_OPT_X0: *x must be a vector of A's size holding the initial guess");
+      return -1;
+    }
+    if (sync_to_host(*x)) return -1;
+    if (n > 0) CU_OK(cudaMemcpyAsync(sys->x, (*x)->values, sizeof(double) * n, cudaMemcpyHostToDevice, c.stream));
+  }
   if (system_solve(sys, o, res)) return -1;
   // the reference hands back a freshly allocated vector (cg.c:104,138)
   struct __mv_sparse* xv = (struct __mv_sparse*)calloc(1, sizeof(struct __mv_sparse));
@@ -608,6 +616,7 @@ static SolveOpts to_opts(const cgb200_opts* o) {
     s.tol = o->tol;
     s.variant = o->variant;
     s.check_every = o->check_every;
+    s.flags = o->flags;
   }
   return s;
 }
@@ -649,6 +658,11 @@ int cgb200_system_set_rhs(cgb200_system* sys, const double* b_host) {
 int cgb200_system_gen_rhs(cgb200_system* sys, uint64_t bseed) {
   if (!sys) return -1;
   return system_gen_rhs((System*)sys, bseed);
+}
+
+int cgb200_system_set_x(cgb200_system* sys, const double* x_host) {
+  if (!sys || !x_host) return -1;
+  return system_set_x((System*)sys, x_host);
 }
 
 int cgb200_system_get_x(cgb200_system* sys, double* x_host) {

@@ -572,11 +572,60 @@ __device__ __forceinline__ void finish_sr(CgState* S, double rw, double rr) {
   S->rr = rr;
 }
 
+// General loop entry (extensions: initial guess x0, Jacobi preconditioner M = diag(A)).  With a
+// preconditioner the recurrence runs on r.z (z = M^-1 r), which takes the place of r.r in S->rr, and
+// the stop test keeps looking at the true r.r, carried in S->aux[0].
+//   FIN_BB     b.b known: threshold and a clean state (nothing decided yet)
+//   FIN_INIT2  r0 = b - A x0 formed: r0.z0 and r0.r0
+//   FIN_RZ     after the x/r update: r.z and r.r
+__device__ __forceinline__ void finish_bb(CgState* S, double bb) {
+  S->bb = bb;
+  S->thresh = S->tol * S->tol * bb;
+  S->iter = 0;
+  S->alpha = 0.0;
+  S->beta = 0.0;
+  S->ps = 0.0;
+  S->done = 0;
+  S->status = CGB200_ST_RUNNING;
+  S->sr_first = 1;
+}
+
+__device__ __forceinline__ void finish_init2(CgState* S, double rz, double rr) {
+  S->rr = rz;
+  S->aux[0] = rr;
+  if (rr == 0.0) {  // x0 solves the system exactly
+    S->done = 1;
+    S->status = CGB200_ST_EXACT;
+  } else if (S->thresh > 0.0 && rr <= S->thresh) {
+    S->done = 1;
+    S->status = CGB200_ST_CONVERGED;
+  }
+}
+
+__device__ __forceinline__ void finish_rz(CgState* S, double rz_new, double rr_new) {
+  const int k = S->iter;
+  S->iter = k + 1;
+  if (S->thresh > 0.0 && rr_new <= S->thresh) {
+    S->done = 1;
+    S->status = CGB200_ST_CONVERGED;
+  } else if (k >= S->max_iter) {
+    S->done = 1;
+    S->status = CGB200_ST_MAXITER;
+  } else {
+    S->beta = rz_new / S->rr;
+  }
+  S->rr = rz_new;
+  S->aux[0] = rr_new;
+}
+
 __device__ __forceinline__ void apply_finish(CgState* S, int fin, double t0, double t1) {
   if (fin == FIN_INIT) finish_init(S, t0);
   else if (fin == FIN_PS) finish_ps(S, t0);
   else if (fin == FIN_RR) finish_rr(S, t0);
   else if (fin == FIN_SR) finish_sr(S, t0, t1);
+  else if (fin == FIN_BB) finish_bb(S, t0);
+  else if (fin == FIN_INIT2) finish_init2(S, t0, t1);
+  else if (fin == FIN_RZ) finish_rz(S, t0, t1);
 }
 
 // Block-wide epilogue of a fused reduction, run by the last block only (totals in thread 0).

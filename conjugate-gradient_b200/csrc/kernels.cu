@@ -1173,6 +1173,186 @@ k_init(double* __restrict__ x, double* __restrict__ r, double* __restrict__ p,
   if (grid_reduce<VT, 1>(v, partials, ticket)) finish_block<VT>(S, cm, fin, v[0], 0.0);
 }
 
+// ---------------------------------------------------------------------------------------------
+// General loop entry and the Jacobi-preconditioned vector kernels.  Extensions:
+// the reference always starts from x = 0 (cg.c:104) and has no preconditioner.  Same unfused
+// roundings as the reference's operators; z = dinv .* r is never stored.
+// ---------------------------------------------------------------------------------------------
+
+// b.b (threshold of the stop test); x = 0 unless the caller supplied an initial guess
+__global__ void __launch_bounds__(VT)
+k_init_bb(double* __restrict__ x, const double* __restrict__ b, long long n, const int zero_x,
+          double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
+          const int fin, const __grid_constant__ PeerComm cm) {
+  const long long stride = (long long)gridDim.x * VT;
+  double acc = 0.0;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n; i += stride) {
+    const double v = b[i];
+    if (zero_x) x[i] = 0.0;
+    acc = fma(v, v, acc);
+  }
+  double v[1] = {acc};
+  if (grid_reduce<VT, 1>(v, partials, ticket)) finish_block<VT>(S, cm, fin, v[0], 0.0);
+}
+
+// r = b - s (s = A x0; s == nullptr: r = b), p = z = dinv .* r (dinv == nullptr: z = r), p pushed
+// to the peers, partial r.z and r.r
+__global__ void __launch_bounds__(VT)
+k_init_r(double* __restrict__ r, double* __restrict__ p, const double* __restrict__ b,
+         const double* __restrict__ s, const double* __restrict__ dinv, long long n,
+         double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
+         const int fin, const __grid_constant__ PeerComm cm) {
+  const long long stride = (long long)gridDim.x * VT;
+  const bool pushing = cm.npush > 0;
+  double arz = 0.0, arr = 0.0;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n; i += stride) {
+    const double rv = s ? __dsub_rn(b[i], s[i]) : b[i];
+    const double zv = dinv ? __dmul_rn(dinv[i], rv) : rv;
+    r[i] = rv;
+    p[i] = zv;
+    if (pushing) push_elem(cm, i, zv);
+    arz = fma(rv, zv, arz);
+    arr = fma(rv, rv, arr);
+  }
+  push_finish(cm);
+  double v[2] = {arz, arr};
+  if (grid_reduce<VT, 2>(v, partials, ticket)) finish_block<VT>(S, cm, fin, v[0], v[1]);
+}
+
+// K2 with the preconditioner: x += alpha p ; r -= alpha s ; partial r.(dinv .* r) and r.r
+__global__ void __launch_bounds__(VT)
+k_update_xr_pc(double* __restrict__ x, double* __restrict__ r, const double* __restrict__ p,
+               const double* __restrict__ s, const double* __restrict__ dinv, long long n,
+               double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
+               const int fin, const __grid_constant__ PeerComm cm) {
+  if (S->done) return;
+  const double alpha = S->alpha;
+  const uintptr_t al = (uintptr_t)x | (uintptr_t)r | (uintptr_t)p | (uintptr_t)s | (uintptr_t)dinv;
+  const long long n2 = (al & 15) ? 0 : (n >> 1);
+  const long long stride = (long long)gridDim.x * VT;
+  constexpr int U = 2;
+  double arz = 0.0, arr = 0.0;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * U) {
+    double2 xv[U], rv[U], pv[U], sv[U], dv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        xv[u] = ld2(x + 2 * j);
+        pv[u] = ld2(p + 2 * j);
+        rv[u] = ld2(r + 2 * j);
+        sv[u] = ld2(s + 2 * j);
+        dv[u] = ld2(dinv + 2 * j);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        xv[u].x = __dadd_rn(xv[u].x, __dmul_rn(alpha, pv[u].x));
+        xv[u].y = __dadd_rn(xv[u].y, __dmul_rn(alpha, pv[u].y));
+        rv[u].x = __dsub_rn(rv[u].x, __dmul_rn(alpha, sv[u].x));
+        rv[u].y = __dsub_rn(rv[u].y, __dmul_rn(alpha, sv[u].y));
+        st2(x + 2 * j, xv[u]);
+        st2(r + 2 * j, rv[u]);
+        arz = fma(rv[u].x, __dmul_rn(dv[u].x, rv[u].x), arz);
+        arz = fma(rv[u].y, __dmul_rn(dv[u].y, rv[u].y), arz);
+        arr = fma(rv[u].x, rv[u].x, arr);
+        arr = fma(rv[u].y, rv[u].y, arr);
+      }
+    }
+  }
+  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride) {
+    const double xn = __dadd_rn(x[j], __dmul_rn(alpha, p[j]));
+    const double rn = __dsub_rn(r[j], __dmul_rn(alpha, s[j]));
+    x[j] = xn;
+    r[j] = rn;
+    arz = fma(rn, __dmul_rn(dinv[j], rn), arz);
+    arr = fma(rn, rn, arr);
+  }
+  double v[2] = {arz, arr};
+  if (grid_reduce<VT, 2>(v, partials, ticket)) finish_block<VT>(S, cm, fin, v[0], v[1]);
+}
+
+// K3 with the preconditioner: p = dinv .* r + beta p, pushed to the peers
+__global__ void __launch_bounds__(VT)
+k_update_p_pc(double* __restrict__ p, const double* __restrict__ r, const double* __restrict__ dinv,
+              long long n, const CgState* S, const __grid_constant__ PeerComm cm) {
+  if (S->done) return;
+  const double beta = S->beta;
+  const bool pushing = cm.npush > 0;
+  const long long n2 = vec_pairs(n, p, r, dinv, nullptr);
+  const long long stride = (long long)gridDim.x * VT;
+  for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * VU) {
+    double2 rv[VU], pv[VU], dv[VU];
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        rv[u] = ld2(r + 2 * j);
+        pv[u] = ld2(p + 2 * j);
+        dv[u] = ld2(dinv + 2 * j);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VU; ++u) {
+      const long long j = i + u * stride;
+      if (j < n2) {
+        pv[u].x = __dadd_rn(__dmul_rn(dv[u].x, rv[u].x), __dmul_rn(beta, pv[u].x));
+        pv[u].y = __dadd_rn(__dmul_rn(dv[u].y, rv[u].y), __dmul_rn(beta, pv[u].y));
+        st2(p + 2 * j, pv[u]);
+        if (pushing) {
+          push_elem(cm, 2 * j, pv[u].x);
+          push_elem(cm, 2 * j + 1, pv[u].y);
+        }
+      }
+    }
+  }
+  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride) {
+    const double pn = __dadd_rn(__dmul_rn(dinv[j], r[j]), __dmul_rn(beta, p[j]));
+    p[j] = pn;
+    if (pushing) push_elem(cm, j, pn);
+  }
+  push_finish(cm);
+}
+
+// dinv[i] = 1 / A_ii for the owned rows.  CSR: the entry whose gather index is diag_off + i
+// (columns ascend within a row: binary search).  bad counts rows without a positive finite diagonal.
+__global__ void k_diag_inv_csr(const int* __restrict__ rowptr, const int* __restrict__ cols,
+                               const double* __restrict__ vals, int nrows, long long diag_off,
+                               double* __restrict__ dinv, int* __restrict__ bad) {
+  const int stride = gridDim.x * blockDim.x;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nrows; i += stride) {
+    int lo = rowptr[i], hi = rowptr[i + 1];
+    const long long want = diag_off + i;
+    double d = 0.0;
+    while (lo < hi) {
+      const int mid = lo + ((hi - lo) >> 1);
+      const long long c = cols[mid];
+      if (c == want) {
+        d = vals[mid];
+        break;
+      }
+      if (c < want) lo = mid + 1;
+      else hi = mid;
+    }
+    const bool okd = d > 0.0 && !isinf(d);
+    dinv[i] = okd ? 1.0 / d : 0.0;
+    if (!okd) atomicAdd(bad, 1);
+  }
+}
+
+__global__ void k_diag_inv_dense(const double* __restrict__ vals, long long ld, int nrows,
+                                 long long row0, double* __restrict__ dinv, int* __restrict__ bad) {
+  const int stride = gridDim.x * blockDim.x;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nrows; i += stride) {
+    const double d = vals[(size_t)i * ld + row0 + i];
+    const bool okd = d > 0.0 && !isinf(d);
+    dinv[i] = okd ? 1.0 / d : 0.0;
+    if (!okd) atomicAdd(bad, 1);
+  }
+}
+
 // Stand-alone push of the owned block's boundary rows (operator-API matvecs, residual checks):
 // the loop itself never launches this, its vector kernels push as they write.
 __global__ void __launch_bounds__(VT)
@@ -1189,7 +1369,7 @@ k_push(const double* __restrict__ p, const __grid_constant__ PeerComm cm) {
 
 // One-thread bookkeeping kernel used after an NCCL sum of S->local (NCCL mode only).
 __global__ void k_finish(CgState* S, int which) {
-  if (which != FIN_INIT && S->done) return;
+  if (which != FIN_INIT && which != FIN_BB && S->done) return;
   apply_finish(S, which, S->local[0], S->local[1]);
 }
 
@@ -1712,6 +1892,49 @@ cudaError_t launch_push(const double* p, const PeerComm& cm, cudaStream_t st) {
 
 cudaError_t launch_finish(CgState* S, int which, cudaStream_t st) {
   k_finish<<<1, 1, 0, st>>>(S, which);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_init_bb(double* x, const double* b, long long n, int zero_x, double* partials,
+                           unsigned int* ticket, CgState* S, int fin, const PeerComm& cm,
+                           cudaStream_t st) {
+  k_init_bb<<<vec_grid(n), VT, 0, st>>>(x, b, n, zero_x, partials, ticket, S, fin, cm);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_init_r(double* r, double* p, const double* b, const double* s,
+                          const double* dinv, long long n, double* partials, unsigned int* ticket,
+                          CgState* S, int fin, const PeerComm& cm, cudaStream_t st) {
+  k_init_r<<<vec_grid(n), VT, 0, st>>>(r, p, b, s, dinv, n, partials, ticket, S, fin, cm);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_update_xr_pc(double* x, double* r, const double* p, const double* s,
+                                const double* dinv, long long n, double* partials,
+                                unsigned int* ticket, CgState* S, int fin, const PeerComm& cm,
+                                cudaStream_t st) {
+  k_update_xr_pc<<<vec_grid(n), VT, 0, st>>>(x, r, p, s, dinv, n, partials, ticket, S, fin, cm);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_update_p_pc(double* p, const double* r, const double* dinv, long long n,
+                               const CgState* S, const PeerComm& cm, cudaStream_t st) {
+  k_update_p_pc<<<vec_grid(n), VT, 0, st>>>(p, r, dinv, n, S, cm);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_diag_inv(const CsrDev& A, bool dense, long long ld, long long diag_off,
+                            double* dinv, int* bad, cudaStream_t st) {
+  if (dense)
+    k_diag_inv_dense<<<sm_count() * 4, 256, 0, st>>>(A.vals, ld, A.nrows, diag_off, dinv, bad);
+  else
+    k_diag_inv_csr<<<sm_count() * 4, 256, 0, st>>>(A.rowptr, A.cols, A.vals, A.nrows, diag_off,
+                                                   dinv, bad);
   ++g_launches;
   return cudaGetLastError();
 }

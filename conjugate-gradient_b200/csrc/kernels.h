@@ -51,8 +51,12 @@ struct PatDev {
 //   FIN_PS     + p.s   -> alpha = rr / ps                      (classic recurrence, cg.c:113)
 //   FIN_SR     + r.w and r.r (MV_DUAL) -> alpha, beta          (single-reduction variant)
 //   FIN_LOCAL  + the sums are left in S->local for the caller (NCCL mode, kernel timing)
-// FIN_INIT / FIN_RR are the finish kinds of the vector kernels.
-enum : int { FIN_NONE = 0, FIN_INIT = 1, FIN_PS = 2, FIN_RR = 3, FIN_SR = 4, FIN_LOCAL = 5 };
+// FIN_INIT / FIN_RR are the finish kinds of the vector kernels; FIN_BB / FIN_INIT2 / FIN_RZ those
+// of the general loop entry (initial guess, Jacobi preconditioner: extensions, not in cg.c).
+enum : int {
+  FIN_NONE = 0, FIN_INIT = 1, FIN_PS = 2, FIN_RR = 3, FIN_SR = 4, FIN_LOCAL = 5,
+  FIN_BB = 6, FIN_INIT2 = 7, FIN_RZ = 8
+};
 constexpr int MV_FIN_MASK = 0x0f;
 constexpr int MV_PARTIAL = 0x10;  // publish per-CTA partials only (first half of a split launch)
 constexpr int MV_DUAL = 0x20;     // also reduce the square of the gathered vector's owned block
@@ -112,6 +116,23 @@ cudaError_t launch_update_sr(double* x, double* g, double* d, double* s, const d
 cudaError_t launch_init(double* x, double* r, double* p, double* s, const double* b, long long n,
                         int sr, double* partials, unsigned int* ticket, CgState* S, int fin,
                         const PeerComm& cm, cudaStream_t st);
+// general loop entry (initial guess) and the Jacobi-preconditioned vector kernels (extensions)
+cudaError_t launch_init_bb(double* x, const double* b, long long n, int zero_x, double* partials,
+                           unsigned int* ticket, CgState* S, int fin, const PeerComm& cm,
+                           cudaStream_t st);
+cudaError_t launch_init_r(double* r, double* p, const double* b, const double* s,
+                          const double* dinv, long long n, double* partials, unsigned int* ticket,
+                          CgState* S, int fin, const PeerComm& cm, cudaStream_t st);
+cudaError_t launch_update_xr_pc(double* x, double* r, const double* p, const double* s,
+                                const double* dinv, long long n, double* partials,
+                                unsigned int* ticket, CgState* S, int fin, const PeerComm& cm,
+                                cudaStream_t st);
+cudaError_t launch_update_p_pc(double* p, const double* r, const double* dinv, long long n,
+                               const CgState* S, const PeerComm& cm, cudaStream_t st);
+// dinv = 1 / diag of the owned rows; diag_off = gather index (CSR) or global column (dense) of
+// row 0's diagonal; *bad = rows without a positive finite diagonal
+cudaError_t launch_diag_inv(const CsrDev& A, bool dense, long long ld, long long diag_off,
+                            double* dinv, int* bad, cudaStream_t st);
 cudaError_t launch_push(const double* p, const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_finish(CgState* S, int which, cudaStream_t st);
 cudaError_t launch_dot(const double* a, const double* b, long long n, double* partials,

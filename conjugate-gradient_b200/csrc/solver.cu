@@ -299,6 +299,7 @@ System::~System() {
   cudaFree(r);
   cudaFree(s);
   cudaFree(w);
+  cudaFree(dinv);
   if (comm_buf)
     cudaFree(comm_buf);  // p_ext lives inside it
   else
@@ -887,7 +888,7 @@ static int ensure_w(System* S) {
 // classic iteration (kernels.cu: k_cg_dense_iter).  NCCL mode keeps the three-kernel form (its
 // sums happen between launches).
 bool dense_one_kernel(const System* S) {
-  return S->dense && S->nloc > 0 && (S->world == 1 || S->p2p) &&
+  return S->dense && S->nloc > 0 && !S->pc_loop && (S->world == 1 || S->p2p) &&
          dense_iter_supported(S->A.vals, S->n_global, (int)S->n_global, S->p_ext);
 }
 
@@ -918,6 +919,15 @@ static int enqueue_iteration(System* S, int variant, int it = 0) {
     CUDA_OK(launch_update_sr(S->x, S->p_own, S->r, S->s, S->w, S->nloc, st, 0, cm, c.stream));
     if (enqueue_matvec(S, S->w, nccl ? FIN_LOCAL : FIN_SR, true, true, sw)) return -1;
     if (nccl && enqueue_nccl_finish(S, 2, FIN_SR)) return -1;
+    return 0;
+  }
+  if (S->pc_loop) {  // Jacobi-preconditioned recurrence (extension): K1 unchanged, K2/K3 carry dinv
+    if (enqueue_matvec(S, S->s, nccl ? FIN_LOCAL : FIN_PS, false, true, false)) return -1;
+    if (nccl && enqueue_nccl_finish(S, 1, FIN_PS)) return -1;
+    CUDA_OK(launch_update_xr_pc(S->x, S->r, S->p_own, S->s, S->dinv, S->nloc, S->partials,
+                                &st->ticket[1], st, nccl ? FIN_LOCAL : FIN_RZ, cm, c.stream));
+    if (nccl && enqueue_nccl_finish(S, 2, FIN_RZ)) return -1;
+    CUDA_OK(launch_update_p_pc(S->p_own, S->r, S->dinv, S->nloc, st, cm, c.stream));
     return 0;
   }
   if (dense_one_kernel(S)) {  // dense path: the whole iteration behind two grid barriers
@@ -953,7 +963,7 @@ static int kernels_per_iteration(const System* S, int variant) {
 
 static int get_graph(System* S, int iters, int variant, cudaGraphExec_t* out) {
   Ctx& c = g_ctx;
-  const int key = 4 * iters + 2 * (dense_one_kernel(S) ? 1 : 0) + variant;
+  const int key = 8 * iters + 4 * (S->pc_loop ? 1 : 0) + 2 * (dense_one_kernel(S) ? 1 : 0) + variant;
   auto it = S->graphs.find(key);
   if (it != S->graphs.end()) {
     *out = it->second;
@@ -1030,6 +1040,48 @@ int system_use_pattern(System* S, int on) {
   return result;
 }
 
+// 1 / diag(A) of the owned rows, built once per system.  A row without a positive finite diagonal
+// entry makes the Jacobi preconditioner meaningless: refused, on every rank alike.
+static int ensure_dinv(System* S) {
+  Ctx& c = g_ctx;
+  if (S->dinv) return 0;
+  double* d = nullptr;
+  CUDA_OK(cudaMalloc(&d, ((size_t)S->nloc + 16) * sizeof(double)));
+  int* bad = (int*)c.d_scratch;
+  CUDA_OK(cudaMemsetAsync(bad, 0, sizeof(int), c.stream));
+  if (S->nloc > 0)
+    CUDA_OK(launch_diag_inv(S->A, S->dense, S->n_global, S->dense ? S->row0 : S->off, d, bad,
+                            c.stream));
+  CUDA_OK(cudaMemcpyAsync(c.h_scratch, bad, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  long long nbad = *(const int*)c.h_scratch;
+  if (S->world > 1) {
+    std::vector<long long> all;
+    if (allgather_i64(&nbad, 1, all)) {
+      cudaFree(d);
+      return -1;
+    }
+    nbad = 0;
+    for (long long v : all) nbad += v;
+  }
+  if (nbad > 0) {
+    cudaFree(d);
+    set_error("Jacobi preconditioner: " + std::to_string(nbad) +
+              " row(s) without a positive finite diagonal entry");
+    return -1;
+  }
+  S->dinv = d;
+  return 0;
+}
+
+// Marks the system as running the preconditioned loop for the duration of one solve (the graph
+// cache and the one-kernel dense iteration look at it).
+struct PcScope {
+  System* S;
+  PcScope(System* s, bool on) : S(s) { S->pc_loop = on; }
+  ~PcScope() { S->pc_loop = false; }
+};
+
 int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
   Ctx& c = g_ctx;
   if (!S) {
@@ -1040,7 +1092,14 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
     set_error("system_solve: variant must be CGB200_CLASSIC or CGB200_SINGLE_REDUCTION");
     return -1;
   }
+  const bool jacobi = (o.flags & 1) != 0, warm = (o.flags & 2) != 0;
+  if ((jacobi || warm) && o.variant != 0) {
+    set_error("system_solve: CGB200_OPT_JACOBI / CGB200_OPT_X0 need the classic recurrence");
+    return -1;
+  }
   CUDA_OK(cudaSetDevice(c.device));
+  if (jacobi && ensure_dinv(S)) return -1;
+  PcScope pc_scope(S, jacobi);
   const int variant = o.variant;
   const bool multi = S->world > 1;
   const bool nccl = multi && !S->p2p;
@@ -1066,10 +1125,28 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
   }
   if (variant == 1 && ensure_w(S)) return -1;
 
+  if (jacobi || warm) {
+    // general loop entry (extension): r = b - A x0, p = z = dinv .* r.  The sum of b.b sits between
+    // the product A x0 and the push of p, so no rank overwrites halo slots a peer still reads.
+    if (warm) {
+      CUDA_OK(cudaMemcpyAsync(S->p_own, S->x, sizeof(double) * S->nloc, cudaMemcpyDeviceToDevice,
+                              c.stream));
+      if (multi && S->p2p) CUDA_OK(launch_push(S->p_own, S->cm, c.stream));
+      if (enqueue_matvec(S, S->s, FIN_NONE, false, true)) return -1;
+    }
+    CUDA_OK(launch_init_bb(S->x, S->b, S->nloc, warm ? 0 : 1, S->partials, &S->state->ticket[2],
+                           S->state, nccl ? FIN_LOCAL : FIN_BB, cm, c.stream));
+    if (nccl && enqueue_nccl_finish(S, 1, FIN_BB)) return -1;
+    CUDA_OK(launch_init_r(S->r, S->p_own, S->b, warm ? S->s : nullptr, jacobi ? S->dinv : nullptr,
+                          S->nloc, S->partials, &S->state->ticket[1], S->state,
+                          nccl ? FIN_LOCAL : FIN_INIT2, cm, c.stream));
+    if (nccl && enqueue_nccl_finish(S, 2, FIN_INIT2)) return -1;
+  } else {
   // loop entry: x = 0, r = p = b, rr = bb = b.b                         (cg.c:104-108)
   CUDA_OK(launch_init(S->x, S->r, S->p_own, S->s, S->b, S->nloc, variant == 1 ? 1 : 0, S->partials,
                       &S->state->ticket[2], S->state, nccl ? FIN_LOCAL : FIN_INIT, cm, c.stream));
   if (nccl && enqueue_nccl_finish(S, 1, FIN_INIT)) return -1;
+  }
   if (variant == 1) {  // w = A r, alpha_0 = r.r / r.w
     if (enqueue_matvec(S, S->w, nccl ? FIN_LOCAL : FIN_SR, true, true)) return -1;
     if (nccl && enqueue_nccl_finish(S, 2, FIN_SR)) return -1;
@@ -1116,11 +1193,11 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
   if (res) {
     res->iterations = f.iter;
     res->status = f.status;
-    res->rr = f.rr;
+    res->rr = jacobi ? f.aux[0] : f.rr;  // with a preconditioner S->rr carries r.z
     res->bb = f.bb;
-    res->relres = f.bb > 0.0 ? sqrt(f.rr / f.bb) : 0.0;
+    res->relres = f.bb > 0.0 ? sqrt(res->rr / f.bb) : 0.0;
     res->seconds = ms * 1e-3;
-    res->bytes_per_iter = S->iter_bytes();
+    res->bytes_per_iter = S->iter_bytes() + (jacobi ? 16.0 * (double)S->nloc : 0.0);
     res->path = S->dense ? 1 : 0;
     res->world = S->world;
     res->kernel_launches = launch_count() - launches0;
@@ -1175,6 +1252,11 @@ int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out) {
   }
   if (o.variant != 0 && o.variant != 1) {
     set_error("system_solve_async: unknown variant");
+    return -1;
+  }
+  if (o.flags != 0) {
+    set_error("system_solve_async: CGB200_OPT_JACOBI / CGB200_OPT_X0 are not available for queued "
+              "solves -- use cgb200_system_solve");
     return -1;
   }
   AsyncSlot& a = g_async[g_async_next % ASYNC_SLOTS];
@@ -1292,6 +1374,13 @@ int system_set_rhs(System* S, const double* b_host) {
 int system_gen_rhs(System* S, unsigned long long seed) {
   Ctx& c = g_ctx;
   CUDA_OK(launch_gen_rhs(S->b, S->row0, S->nloc, seed, c.stream));
+  return 0;
+}
+
+int system_set_x(System* S, const double* x_host) {
+  Ctx& c = g_ctx;
+  CUDA_OK(cudaMemcpyAsync(S->x, x_host, sizeof(double) * S->nloc, cudaMemcpyHostToDevice, c.stream));
+  CUDA_OK(cudaStreamSynchronize(c.stream));
   return 0;
 }
 

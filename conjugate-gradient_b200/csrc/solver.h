@@ -76,6 +76,8 @@ struct System {
 
   double *b = nullptr, *x = nullptr, *r = nullptr, *s = nullptr;
   double* w = nullptr;  // single-reduction variant only: w = A r (allocated on first use)
+  double* dinv = nullptr;  // 1 / diag(A) of the owned rows (Jacobi preconditioner; built on first use)
+  bool pc_loop = false;    // the solve in progress runs the preconditioned vector kernels
   CgState* state = nullptr;
   double* partials = nullptr;
   double* gemv_pool = nullptr;          // dense path: chunk records of the matvec's dynamic tail
@@ -101,6 +103,7 @@ struct SolveOpts {
   double tol = 0.0;
   int variant = 0;
   int check_every = 0;
+  int flags = 0;  // CGB200_OPT_JACOBI (1) | CGB200_OPT_X0 (2)
 };
 
 struct SolveResult {
@@ -127,6 +130,7 @@ int system_trace(System* S, int on, unsigned long long* out16);
 int system_set_rhs(System* S, const double* b_host);
 int system_gen_rhs(System* S, unsigned long long seed);
 int system_get_x(System* S, double* x_host);
+int system_set_x(System* S, const double* x_host);  // initial guess for a CGB200_OPT_X0 solve
 int system_matvec(System* S, const double* v_host, double* s_host);
 int system_matvec_dev(System* S, const double* v_dev, double* s_host_or_null);
 int system_true_relres(System* S, double* relres);

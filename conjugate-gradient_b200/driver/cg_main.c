@@ -22,6 +22,7 @@
  *     --variant classic|sr   the reference's recurrence (default) or the single-reduction one
  *     --pattern          store stencil-like matrices as one byte per row (row-pattern dictionary
  *                        format; same arithmetic, fewer bytes) when the matrix qualifies
+ *     --jacobi           diagonal (Jacobi) preconditioner (classic recurrence only)
  */
 #include <errno.h>
 #include <stdint.h>
@@ -126,13 +127,14 @@ typedef struct {
   int json;
   int variant;
   int pattern;
+  int jacobi;
 } options;
 
 static void usage(const char *p) {
   fprintf(stderr,
           "Usage: %s <input-data> <max-iterations> [suppress-output]\n"
           "       %s --gen dense:N|lap2d:N|lap3d:N <max-iterations> [--gpus G]\n"
-          "       options: --tol T  --check-every M  --json  --variant classic|sr  --pattern\n", p, p);
+          "       options: --tol T  --check-every M  --json  --variant classic|sr  --pattern  --jacobi\n", p, p);
 }
 
 static int parse(int argc, char **argv, options *o) {
@@ -148,6 +150,7 @@ static int parse(int argc, char **argv, options *o) {
     else if (!strcmp(a, "--gpus") && i + 1 < argc) o->gpus = atoi(argv[++i]);
     else if (!strcmp(a, "--json")) o->json = 1;
     else if (!strcmp(a, "--pattern")) o->pattern = 1;
+    else if (!strcmp(a, "--jacobi")) o->jacobi = 1;
     else if (!strcmp(a, "--variant") && i + 1 < argc) {
       const char *v = argv[++i];
       if (!strcmp(v, "sr") || !strcmp(v, "single-reduction")) o->variant = CGB200_SINGLE_REDUCTION;
@@ -213,7 +216,7 @@ static int run_rank(const options *o, int rank, int world, const unsigned char *
     sys = cgb200_system_from_csr(A.size, r0, nl, A.row_ptr + r0, A.col_indices, A.values, b.values + r0);
   }
   if (!sys) { fprintf(stderr, "cg[%d]: %s\n", rank, cgb200_last_error()); return 1; }
-  cgb200_opts opts = {o->max_iter, o->tol, o->variant, o->check_every, 0};
+  cgb200_opts opts = {o->max_iter, o->tol, o->variant, o->check_every, o->jacobi ? CGB200_OPT_JACOBI : 0};
   cgb200_result res;
   struct timespec t0, t1;
   clock_gettime(CLOCK_MONOTONIC, &t0);
@@ -286,8 +289,8 @@ int main(int argc, char **argv) {
   memset(&res, 0, sizeof(res));
   struct timespec t0, t1;
   clock_gettime(CLOCK_MONOTONIC, &t0);
-  if (o.tol > 0.0 || o.json || o.check_every > 0) {
-    cgb200_opts opts = {o.max_iter, o.tol, o.variant, o.check_every, 0};
+  if (o.tol > 0.0 || o.json || o.check_every > 0 || o.jacobi || o.variant != CGB200_CLASSIC) {
+    cgb200_opts opts = {o.max_iter, o.tol, o.variant, o.check_every, o.jacobi ? CGB200_OPT_JACOBI : 0};
     rc = cgb200_solve(mat_A, vec_b, &vec_x, &opts, &res);
   } else {
     rc = conj_grad(o.max_iter, mat_A, vec_b, &vec_x);

@@ -32,6 +32,20 @@ extern "C" {
  * two; costs one more matvec at loop entry.  Same iteration-count semantics as the classic loop. */
 #define CGB200_SINGLE_REDUCTION 1
 
+/* ---- solve options beyond the reference (cgb200_opts.flags; classic recurrence only) ---------
+ * The reference always starts from x = 0 (cg.c:104-108) and has no preconditioner; both options
+ * are additive and leave the default path untouched.
+ * CGB200_OPT_JACOBI  diagonal (Jacobi) preconditioner M = diag(A): z = M^-1 r is formed inside the
+ *                    two vector kernels (never stored), alpha = r.z / p.Ap, beta = r.z / (r.z)_prev,
+ *                    p = z + beta p; the stop test still looks at the true r.r.  Costs 16 n more
+ *                    bytes per iteration.  Refused (-1) when a row has no positive finite diagonal.
+ * CGB200_OPT_X0      start from an initial guess: r0 = b - A x0 (one more matvec at loop entry).
+ *                    cgb200_solve: *x on entry is the guess (not modified, not freed; *x is replaced
+ *                    by a freshly allocated vector as in conj_grad).  cgb200_system_solve: the guess
+ *                    is the x the system holds -- the previous solve's, or cgb200_system_set_x. */
+#define CGB200_OPT_JACOBI 1
+#define CGB200_OPT_X0 2
+
 /* ---- operator-API residency modes --------------------------------------------------------- */
 #define CGB200_EAGER 0    /* every op uploads its inputs and downloads its output (default) */
 #define CGB200_RESIDENT 1 /* outputs stay on the device until cgb200_to_host()/print/get_row */
@@ -41,7 +55,7 @@ typedef struct cgb200_opts {
   double tol;      /* stop when ||r||/||b|| <= tol; 0 = fixed count (reference behaviour) */
   int variant;     /* CGB200_CLASSIC | CGB200_SINGLE_REDUCTION */
   int check_every; /* iterations per graph launch / host poll of the stop flag; 0 = default */
-  int reserved;
+  int flags;       /* 0 (the reference's loop) or CGB200_OPT_JACOBI | CGB200_OPT_X0 */
 } cgb200_opts;
 
 typedef struct cgb200_result {
@@ -105,6 +119,7 @@ void cgb200_system_free(cgb200_system *sys);
 int cgb200_system_set_rhs(cgb200_system *sys, const double *b_host);   /* H2D, nrows doubles */
 int cgb200_system_gen_rhs(cgb200_system *sys, uint64_t bseed);         /* on the device */
 int cgb200_system_get_x(cgb200_system *sys, double *x_host);           /* D2H, nrows doubles */
+int cgb200_system_set_x(cgb200_system *sys, const double *x_host);     /* H2D: guess for CGB200_OPT_X0 */
 int cgb200_system_solve(cgb200_system *sys, const cgb200_opts *opts, cgb200_result *res);
 /* Queues a fixed-count solve (opts->tol must be 0: the reference's semantics) behind whatever is
  * already queued on the library's stream and returns at once with a ticket; right-hand sides

@@ -85,6 +85,12 @@ def oracle():
         C.c_int, c_int_p, c_int_p, c_double_p, c_double_p, C.c_int, C.c_double,
         c_double_p, c_double_p, c_int_p,
     ]
+    L.oracle_pcg.restype = C.c_int
+    L.oracle_pcg.argtypes = [
+        C.c_int, c_int_p, c_int_p, c_double_p, c_double_p, c_double_p, c_double_p, C.c_int, C.c_double,
+        c_double_p, c_double_p, c_int_p,
+    ]
+    L.oracle_diag_inv.argtypes = [C.c_int, c_int_p, c_int_p, c_double_p, c_double_p]
     L.oracle_true_relres.restype = C.c_double
     L.oracle_true_relres.argtypes = [C.c_int, c_int_p, c_int_p, c_double_p, c_double_p, c_double_p]
     L.oracle_num_threads.restype = C.c_int
@@ -226,6 +232,26 @@ def oracle_cg(sysm, max_iter, tol=0.0, guard=0):
         sysm.n, iptr(sysm.row_ptr), iptr(sysm.cols), dptr(sysm.vals), dptr(sysm.b),
         max_iter, tol, guard, dptr(x), C.byref(rr), C.byref(st),
     )
+    return x, it, rr.value, st.value
+
+
+def diag_inv(sysm):
+    d = np.empty(sysm.n, dtype=np.float64)
+    oracle().oracle_diag_inv(sysm.n, iptr(sysm.row_ptr), iptr(sysm.cols), dptr(sysm.vals), dptr(d))
+    return d
+
+
+def oracle_pcg(sysm, max_iter, tol=0.0, x0=None, jacobi=False):
+    """Returns (x, updates, rr, status) from the preconditioned / warm-started restatement."""
+    x = np.empty(sysm.n, dtype=np.float64)
+    rr = C.c_double(0.0)
+    st = C.c_int(0)
+    dinv = diag_inv(sysm) if jacobi else None
+    x0c = np.ascontiguousarray(x0, dtype=np.float64) if x0 is not None else None
+    it = oracle().oracle_pcg(
+        sysm.n, iptr(sysm.row_ptr), iptr(sysm.cols), dptr(sysm.vals), dptr(sysm.b),
+        dptr(x0c) if x0c is not None else None, dptr(dinv) if dinv is not None else None,
+        max_iter, tol, dptr(x), C.byref(rr), C.byref(st))
     return x, it, rr.value, st.value
 
 

@@ -100,6 +100,19 @@ tr = d.true_relres()
 rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
 report("lap3d tolerance single-reduction", abs(r.iterations - it) <= 2 and tr <= 1.05e-10 and rel <= 1e-8,
        f"iters {r.iterations}/{it} true relres {tr:.2e} rel {rel:.2e}")
+# solve options beyond the reference: initial guess + Jacobi preconditioner through the exchange
+if hasattr(L, "cgb200_system_set_x"):
+    nl_ = nx * ny * nzl
+    x0 = np.random.default_rng(3).standard_normal(s.n)
+    for jac, warm in ((True, False), (False, True), (True, True)):
+        xo_, it_, _, _ = H.oracle_pcg(s, 25, x0=x0 if warm else None, jacobi=jac)
+        r = d.solve(25, jacobi=jac, x0=x0[rank * nl_:(rank + 1) * nl_] if warm else None)
+        x = gather_x(d, s.n, [nl_] * world)
+        rel = np.linalg.norm(x - xo_) / np.linalg.norm(xo_)
+        report(f"lap3d options jacobi={int(jac)} x0={int(warm)}", r.iterations == it_ and rel <= 1e-8, f"rel {rel:.2e}")
+    r = d.solve(100000, tol=1e-10, jacobi=True, x0=True)
+    tr = d.true_relres()
+    report("lap3d options tolerance restart", r.status == pkg.CONVERGED and tr <= 1.05e-10, f"iters {r.iterations} true relres {tr:.2e}")
 # plain products through the exchange (operator-API path), bit-exact per row
 v = H.rhs(s.n, 77)
 want = np.empty(s.n)
@@ -179,6 +192,13 @@ for variant, nm in ((0, "classic (one-kernel iteration)"), (SR, "single-reductio
     rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
     report(f"dense uneven blocks, dynamic tail, {nm}", r.iterations == it and rel <= 1e-8,
            f"iters {r.iterations}/{it} rel {rel:.2e} one-kernel {d.one_kernel_iteration()}")
+if hasattr(L, "cgb200_system_set_x"):
+    x0 = np.random.default_rng(4).standard_normal(n)
+    xo_, it_, _, _ = H.oracle_pcg(s, 4, x0=x0, jacobi=True)
+    r = d.solve(4, jacobi=True, x0=x0[row0:row0 + cnt[rank]])
+    x = gather_x(d, n, cnt)
+    rel = np.linalg.norm(x - xo_) / np.linalg.norm(xo_)
+    report("dense uneven blocks, jacobi + x0", r.iterations == it_ and rel <= 1e-8, f"rel {rel:.2e}")
 x1 = None
 for rep in range(2):   # the dynamic tail must not cost reproducibility
     d.gen_rhs(5)
@@ -206,6 +226,13 @@ for hb, name in ((7, "banded neighbour"), (900, "banded wide")):
         xo, it, _, _ = H.oracle_cg(s, 15)
         rel = np.linalg.norm(x - xo) / np.linalg.norm(xo)
         report(f"from_csr {name} variant {variant}", r.iterations == it and rel <= 1e-8, f"rel {rel:.2e}")
+    if hasattr(L, "cgb200_system_set_x"):
+        x0 = np.random.default_rng(5).standard_normal(s.n)
+        xo_, it_, _, _ = H.oracle_pcg(s, 15, x0=x0, jacobi=True)
+        r = d.solve(15, jacobi=True, x0=x0[row0:row0 + nl])
+        x = gather_x(d, s.n, cnt)
+        rel = np.linalg.norm(x - xo_) / np.linalg.norm(xo_)
+        report(f"from_csr {name} jacobi + x0", r.iterations == it_ and rel <= 1e-8, f"rel {rel:.2e}")
     d.free()
 
 L.cgb200_dist_finalize()
