@@ -231,6 +231,31 @@ def timed_steps(pkg, runner, K, W, world, sampler=None):
     return {"ms": ms_max, "steps": done, "warmup": w_done, "launches": int(launches), "t0": t0, "t1": t1}
 
 
+def time_to_solution(pkg, d, info, world, variant=0, tol=1e-10, fixed=None, cap=60000):
+    """One solve from x0 = 0 to ||r||/||b|| <= tol (north_star's stop test; the reference itself has
+    none) -- or `fixed` iterations (BASELINE configs[4]) -- timed on the device (CUDA
+    events around the loop, max over ranks), with the residual recomputed from scratch afterwards."""
+    d.gen_rhs(7)
+    dist_sync(world)
+    if fixed:
+        r = d.solve(fixed - 1, variant=variant)
+    else:
+        r = d.solve(cap, tol=tol, variant=variant)
+    dist_sync(world)
+    sec = max_over_ranks(r.seconds, world)
+    out = {"iterations": int(r.iterations), "seconds": round(sec, 5),
+           "status": "converged" if r.status == pkg.CONVERGED else ("max_iter" if fixed else f"status {r.status}"),
+           "relres_recursive": float(r.relres),
+           "timing": "CUDA events around the device loop (cgb200_result.seconds), max over ranks; x0 = 0"}
+    out["stop"] = f"fixed {fixed} iterations" if fixed else f"||r||/||b|| <= {tol:g}"
+    try:
+        out["relres_true"] = float(d.true_relres())
+    except Exception as e:  # noqa: BLE001
+        out["relres_true"] = None
+        out["relres_true_error"] = repr(e)
+    return out
+
+
 def roofline_for(pkg, d, peak, peak_src, kernel_name, workload, world, variant=0):
     it_b, k1_b = d.bytes()
     if variant == 0 and d.one_kernel_iteration():
@@ -565,6 +590,11 @@ def main():
         "clocks": clocks,
     }
     J = runner.J
+    try:
+        line["time_to_solution"] = time_to_solution(pkg, d, info, world, variant,
+                                                    fixed=500 if args.workload == "lap3d384w" else None)
+    except Exception as e:  # noqa: BLE001
+        line["time_to_solution"] = {"error": repr(e)}
     # the other recurrence on the same system, same K (explains, does not replace, the headline)
     try:
         other = Runner(pkg, d, info, 1 - variant)
@@ -609,6 +639,11 @@ def main():
                       "achieved_gbs_per_gpu": round(gbs, 1), "frac_of_peak": round(gbs / peak, 4),
                       "config": workload_config(nm, world)}
                 ex["roofline"] = roofline_for(pkg, dx, peak, peak_src, "k_spmv_stream", nm, world)
+                try:
+                    ex["time_to_solution"] = time_to_solution(pkg, dx, ix, world, variant,
+                                                              fixed=500 if nm == "lap3d384w" else None)
+                except Exception as e:  # noqa: BLE001
+                    ex["time_to_solution"] = {"error": repr(e)}
                 ry = Runner(pkg, dx, ix, 1 - variant)
                 ty = timed_steps(pkg, ry, k, 5, world)
                 ex["other_variant"] = {"variant": "classic" if variant else "single-reduction",
