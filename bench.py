@@ -282,6 +282,59 @@ def roofline_for(pkg, d, peak, peak_src, kernel_name, workload, world, variant=0
 # -------------------------------------------------------------------------------------------------
 
 
+def operator_api_loop(pkg, A, b, bnp, bs, J):
+    """The reference's own loop (cg.c:104-135) kept by the caller and run operator by operator
+    against libcgb200.so in resident mode -- what a user gets who relinks mv_ops but keeps their
+    cg.c.  12 operator launches, 4 scalar read-backs (dot_product returns by value) and 2 deep
+    copies per iteration, as the reference issues them; b in and x out every solve."""
+    L = pkg.lib()
+    assert L.cgb200_set_mode(pkg.RESIDENT) == 0
+    iters = 0
+    try:
+        t = time.perf_counter()
+        for bi in bs:
+            bnp[:] = bi
+            L.cgb200_invalidate(C.byref(b))
+            x_new = L.new_mv_struct_with_size(b.size)
+            r = L.mv_deep_copy(C.byref(b))
+            p = L.mv_deep_copy(r)
+            sv, sres = pkg.MvSparseP(), pkg.MvSparseP()
+            k = 0
+            while True:
+                assert L.mv_mult(C.byref(A), p, C.byref(sv)) == 0, pkg.last_error()
+                alpha = L.dot_product(r, r) / L.dot_product(p, sv)
+                L.sv_mult(alpha, p, C.byref(sres))
+                x_old = L.mv_deep_copy(x_new)
+                L.vec_add(x_old, sres, C.byref(x_new))
+                r_prev = L.mv_deep_copy(r)
+                L.sv_mult(alpha, sv, C.byref(sres))
+                L.vec_sub(r, sres, C.byref(r))
+                iters += 1
+                if k == J - 1:
+                    L.cgb200_free_all(x_old)
+                    L.cgb200_free_all(r_prev)
+                    break
+                beta = L.dot_product(r, r) / L.dot_product(r_prev, r_prev)
+                L.sv_mult(beta, p, C.byref(sres))
+                L.vec_add(r, sres, C.byref(p))
+                k += 1
+                L.cgb200_free_all(x_old)       # the reference leaks these two per iteration
+                L.cgb200_free_all(r_prev)
+            assert L.cgb200_to_host(x_new) == 0, pkg.last_error()
+            chk = float(x_new.contents.values[0])
+            for o in (x_new, r, p, sv, sres):
+                L.cgb200_free_all(o)
+        sec = time.perf_counter() - t
+    finally:
+        L.cgb200_set_mode(pkg.EAGER)
+    assert chk == chk
+    return {"value": round(iters / sec, 2), "unit": UNIT, "solves": len(bs), "iterations_per_solve": J,
+            "mode": "CGB200_RESIDENT",
+            "note": "the reference's loop statement by statement through mv_mult / dot_product / sv_mult / vec_add / "
+                    "vec_sub / mv_deep_copy (12 launches, 4 scalar read-backs per iteration); wall clock, b in and x out "
+                    "every solve"}
+
+
 def e2e_host_structs(pkg, d, info, J, solves=8):
     """N = 1: cgb200_solve(A, b, &x) on struct __mv_sparse host arrays (pinned), every solve copying
     its right-hand side host->device and its solution device->host.  A is uploaded by the first
@@ -325,6 +378,10 @@ def e2e_host_structs(pkg, d, info, J, solves=8):
         it, _ = one()
         iters += it
     warm_s = time.perf_counter() - t
+    try:
+        ops = operator_api_loop(pkg, A, b, bnp, bs, int(round(iters / solves)))
+    except Exception as e:  # noqa: BLE001
+        ops = {"error": repr(e)}
     L.cgb200_invalidate(C.byref(A))
     a_bytes = 8 * nnz if info["kind"] == "dense" else 12 * nnz + 4 * (n + 1)
     per_solve_iters = iters / solves
@@ -338,6 +395,7 @@ def e2e_host_structs(pkg, d, info, J, solves=8):
         "cold_first_call": {"value": round(it_cold / cold_s, 3), "unit": UNIT, "seconds": round(cold_s, 3),
                             "h2d_bytes": a_bytes + 8 * n, "note": "includes uploading A"},
         "note": "A stays device-resident between calls while its struct is unchanged (fingerprinted); every solve copies b in and x out",
+        "operator_api": ops,
     }
 
 

@@ -132,6 +132,10 @@ def lib():
     L.cgb200_last_error.restype = C.c_char_p
     L.cgb200_launch_count.restype = C.c_longlong
     L.cgb200_device_available.restype = C.c_int
+    L.cgb200_guard_check.restype = C.c_longlong
+    L.cgb200_guard_check.argtypes = []
+    L.cgb200_guard_selftest.restype = C.c_int
+    L.cgb200_guard_selftest.argtypes = []
     L.cgb200_set_mode.argtypes = [C.c_int]
     for name in ("cgb200_to_device", "cgb200_to_host", "cgb200_invalidate"):
         getattr(L, name).argtypes = [MvSparseP]

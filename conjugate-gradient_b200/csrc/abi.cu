@@ -12,10 +12,12 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <map>
 #include <mutex>
 #include <unordered_map>
 #include <vector>
 
+#include "devmem.h"
 #include "../../include/cgb200.h"
 #include "solver.h"
 
@@ -69,18 +71,22 @@ size_t g_scratch_cap[3] = {0, 0, 0};
 
 int scratch(int slot, size_t n, double** out) {
   if (g_scratch_cap[slot] < n + 2) {
-    if (g_scratch[slot]) cudaFree(g_scratch[slot]);
+    if (g_scratch[slot]) dev_free(g_scratch[slot]);
     g_scratch[slot] = nullptr;
     g_scratch_cap[slot] = 0;
-    CU_OK(cudaMalloc(&g_scratch[slot], (n + 2) * sizeof(double)));
+    CU_OK(DEV_ALLOC(&g_scratch[slot], (n + 2) * sizeof(double)));
     g_scratch_cap[slot] = n + 2;
   }
   *out = g_scratch[slot];
   return 0;
 }
 
-// Sampled fingerprint of a matrix's host arrays: catches a caller that rebuilt or edited the
-// matrix behind an unchanged struct address (not a proof; cgb200_invalidate() is the contract).
+// Sampled fingerprint of a matrix's host arrays: catches a caller that rebuilt the matrix behind an
+// unchanged struct address (not a proof; cgb200_invalidate() is the contract).  It runs on every
+// mv_mult / solve, and on a multi-gigabyte matrix every sample is a cache and TLB miss: 64 + 32
+// samples cost ~15 us where the first version's 2048 + 1024 cost ~0.5 ms per operator call --
+// more than a third of a dense n = 32768 matvec -- without seeing more of a 10^9-entry array in
+// any way that matters (either figure is a vanishing fraction).
 uint64_t mix(uint64_t h, uint64_t v) {
   h ^= v + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
   return h;
@@ -88,7 +94,7 @@ uint64_t mix(uint64_t h, uint64_t v) {
 uint64_t fingerprint(const struct __mv_sparse* A) {
   uint64_t h = 1469598103934665603ull;
   const long long nnz = A->nnz, n = A->size;
-  const long long step_v = nnz > 2048 ? nnz / 2048 : 1;
+  const long long step_v = nnz > 64 ? nnz / 64 : 1;
   for (long long k = 0; k < nnz; k += step_v) {
     uint64_t bits;
     memcpy(&bits, &A->values[k], 8);
@@ -100,7 +106,7 @@ uint64_t fingerprint(const struct __mv_sparse* A) {
     memcpy(&bits, &A->values[nnz - 1], 8);
     h = mix(h, bits);
   }
-  const long long step_r = n > 1024 ? n / 1024 : 1;
+  const long long step_r = n > 32 ? n / 32 : 1;
   for (long long i = 0; i <= n; i += step_r) h = mix(h, (uint64_t)(uint32_t)A->row_ptr[i]);
   h = mix(h, (uint64_t)(uint32_t)A->row_ptr[n]);
   return h;
@@ -142,6 +148,35 @@ System* matrix_system(struct __mv_sparse* A) {
   return sys;
 }
 
+// Device vectors released by free_mv_struct / cgb200_free_all / a resize are kept for the next
+// operator output of the same capacity: a caller written like the reference's loop creates and
+// drops two vectors per iteration (cg.c:117,120), and a cudaMalloc + cudaFree pair per vector
+// (the free synchronises the device) would cost more than the operators themselves on small
+// systems.  Bounded: at most 16 buffers / 4 GiB; flushed on allocation failure and at shutdown.
+std::multimap<int, double*> g_vec_pool;  // capacity (doubles) -> buffer
+size_t g_vec_pool_bytes = 0;
+constexpr size_t VEC_POOL_MAX_BYTES = 4ull << 30;
+constexpr size_t VEC_POOL_MAX_COUNT = 16;
+
+void vec_pool_flush() {
+  for (auto& kv : g_vec_pool) dev_free(kv.second);
+  g_vec_pool.clear();
+  g_vec_pool_bytes = 0;
+}
+
+void vec_release(double* d, int cap) {
+  if (!d) return;
+  const size_t bytes = ((size_t)cap + 2) * sizeof(double);
+  // guard mode frees at once: the guards are checked at the free, and a reused buffer would hold
+  // stale values instead of the poison that exposes uninitialised reads
+  if (dev_guard_enabled() || g_vec_pool.size() >= VEC_POOL_MAX_COUNT || g_vec_pool_bytes + bytes > VEC_POOL_MAX_BYTES) {
+    dev_free(d);
+    return;
+  }
+  g_vec_pool.emplace(cap, d);
+  g_vec_pool_bytes += bytes;
+}
+
 void drop_mirror(const void* obj) {
   auto im = g_mats.find(obj);
   if (im != g_mats.end()) {
@@ -150,17 +185,30 @@ void drop_mirror(const void* obj) {
   }
   auto iv = g_vecs.find(obj);
   if (iv != g_vecs.end()) {
-    cudaFree(iv->second.d);
+    vec_release(iv->second.d, iv->second.cap);
     g_vecs.erase(iv);
   }
 }
 
 int ensure_vec_capacity(VectorEntry& e, int n) {
   if (e.cap < n || !e.d) {
-    if (e.d) cudaFree(e.d);
+    if (e.d) vec_release(e.d, e.cap);
     e.d = nullptr;
     e.cap = 0;
-    CU_OK(cudaMalloc(&e.d, ((size_t)n + 2) * sizeof(double)));
+    auto it = g_vec_pool.find(n);  // exact capacity only: a pooled buffer never grows a footprint
+    if (it != g_vec_pool.end()) {
+      e.d = it->second;
+      g_vec_pool_bytes -= ((size_t)n + 2) * sizeof(double);
+      g_vec_pool.erase(it);
+    } else {
+      cudaError_t err = DEV_ALLOC(&e.d, ((size_t)n + 2) * sizeof(double));
+      if (err != cudaSuccess && !g_vec_pool.empty()) {
+        cudaGetLastError();
+        vec_pool_flush();
+        err = DEV_ALLOC(&e.d, ((size_t)n + 2) * sizeof(double));
+      }
+      CU_OK(err);
+    }
     e.cap = n;
   }
   e.n = n;
@@ -516,10 +564,11 @@ void cgb200_shutdown(void) {
   std::lock_guard<std::mutex> lk(g_tab_mu);
   for (auto& kv : g_mats) delete kv.second.sys;
   g_mats.clear();
-  for (auto& kv : g_vecs) cudaFree(kv.second.d);
+  for (auto& kv : g_vecs) dev_free(kv.second.d);
+  vec_pool_flush();
   g_vecs.clear();
   for (int i = 0; i < 3; ++i) {
-    if (g_scratch[i]) cudaFree(g_scratch[i]);
+    if (g_scratch[i]) dev_free(g_scratch[i]);
     g_scratch[i] = nullptr;
     g_scratch_cap[i] = 0;
   }
@@ -528,6 +577,11 @@ void cgb200_shutdown(void) {
 
 const char* cgb200_last_error(void) { return last_error(); }
 long long cgb200_launch_count(void) { return launch_count(); }
+long long cgb200_guard_check(void) { return dev_guard_check(); }
+int cgb200_guard_selftest(void) {
+  if (ensure_init(-1)) return -1;
+  return dev_guard_selftest();
+}
 
 int cgb200_device_available(void) {
   int n = 0;

@@ -25,6 +25,7 @@
 #include <string>
 #include <vector>
 
+#include "devmem.h"
 #include "device_utils.cuh"
 #include "kernels.h"
 #include "solver.h"
@@ -135,11 +136,11 @@ __global__ void k_pat_assign(const int* __restrict__ rowptr, const int* __restri
 }
 
 void free_pattern(PatDev* P) {
-  cudaFree(P->type);
-  cudaFree(P->len);
-  cudaFree(P->rel);
-  cudaFree(P->val);
-  cudaFree(P->soff);
+  dev_free(P->type);
+  dev_free(P->len);
+  dev_free(P->rel);
+  dev_free(P->val);
+  dev_free(P->soff);
   *P = PatDev();
 }
 
@@ -173,8 +174,8 @@ int build_pattern(const CsrDev& A, PatDev* out, cudaStream_t st, std::string* wh
     *why = "no CSR arrays";
     return 0;
   }
-  PAT_OK(cudaMalloc(&d_table, sizeof(PatSlot) * PAT_TABLE));
-  PAT_OK(cudaMalloc(&d_flags, 2 * sizeof(int)));
+  PAT_OK(DEV_ALLOC(&d_table, sizeof(PatSlot) * PAT_TABLE));
+  PAT_OK(DEV_ALLOC(&d_flags, 2 * sizeof(int)));
   PAT_OK(cudaMemsetAsync(d_table, 0, sizeof(PatSlot) * PAT_TABLE, st));
   PAT_OK(cudaMemsetAsync(d_flags, 0, 2 * sizeof(int), st));
   k_pat_collect<<<grid, 256, 0, st>>>(A.rowptr, A.cols, A.vals, nrows, d_table, d_flags);
@@ -229,11 +230,11 @@ int build_pattern(const CsrDev& A, PatDev* out, cudaStream_t st, std::string* wh
   }
   P.ntypes = (int)used.size();
   P.lpad = lpad;
-  PAT_OK(cudaMalloc(&P.type, (size_t)nrows + 64));
-  PAT_OK(cudaMalloc(&P.len, sizeof(int) * std::max(1, P.ntypes)));
-  PAT_OK(cudaMalloc(&P.rel, sizeof(int) * std::max<size_t>(1, rel.size())));
-  PAT_OK(cudaMalloc(&P.val, sizeof(double) * std::max<size_t>(1, val.size())));
-  PAT_OK(cudaMalloc(&d_slot_id, PAT_TABLE));
+  PAT_OK(DEV_ALLOC(&P.type, (size_t)nrows + 64));
+  PAT_OK(DEV_ALLOC(&P.len, sizeof(int) * std::max(1, P.ntypes)));
+  PAT_OK(DEV_ALLOC(&P.rel, sizeof(int) * std::max<size_t>(1, rel.size())));
+  PAT_OK(DEV_ALLOC(&P.val, sizeof(double) * std::max<size_t>(1, val.size())));
+  PAT_OK(DEV_ALLOC(&d_slot_id, PAT_TABLE));
   {
     // staged form: cluster the column offsets of all patterns into windows
     std::vector<int> offs;
@@ -272,7 +273,7 @@ int build_pattern(const CsrDev& A, PatDev* out, cudaStream_t st, std::string* wh
           while (w + 1 < nwin && d >= lo[w + 1]) ++w;
           soff[(size_t)t * lpad + j] = P.wbase[w] + d - lo[w];
         }
-      PAT_OK(cudaMalloc(&P.soff, sizeof(int) * soff.size()));
+      PAT_OK(DEV_ALLOC(&P.soff, sizeof(int) * soff.size()));
       PAT_OK(cudaMemcpy(P.soff, soff.data(), sizeof(int) * soff.size(), cudaMemcpyHostToDevice));
       P.nwin = nwin;
       P.stage_elems = (int)elems;
@@ -298,9 +299,9 @@ int build_pattern(const CsrDev& A, PatDev* out, cudaStream_t st, std::string* wh
   P = PatDev();
   rc = 1;
 done:
-  cudaFree(d_table);
-  cudaFree(d_flags);
-  cudaFree(d_slot_id);
+  dev_free(d_table);
+  dev_free(d_flags);
+  dev_free(d_slot_id);
   free_pattern(&P);
   return rc;
 }

@@ -9,6 +9,7 @@
 // by a one-thread bookkeeping kernel, and the search direction is exchanged before K1:
 // neighbour halo send/recv overlapped with the interior tiles of K1 (stencil-like matrices) or
 // an all-gather (dense / wide coupling).
+#include "devmem.h"
 #include "solver.h"
 
 #include <dlfcn.h>
@@ -134,12 +135,12 @@ int ensure_init(int device) {
   c.device = device;
   CUDA_OK(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
   CUDA_OK(cudaStreamCreateWithFlags(&c.comm_stream, cudaStreamNonBlocking));
-  CUDA_OK(cudaMalloc(&c.partials, sizeof(double) * partials_doubles()));
+  CUDA_OK(DEV_ALLOC(&c.partials, sizeof(double) * partials_doubles()));
   CUDA_OK(cudaMemset(c.partials, 0, sizeof(double) * partials_doubles()));
-  CUDA_OK(cudaMalloc(&c.d_state, sizeof(CgState)));
+  CUDA_OK(DEV_ALLOC(&c.d_state, sizeof(CgState)));
   CUDA_OK(cudaMemset(c.d_state, 0, sizeof(CgState)));
   CUDA_OK(cudaMallocHost(&c.h_state, sizeof(CgState) * 4));
-  CUDA_OK(cudaMalloc(&c.d_scratch, 64));
+  CUDA_OK(DEV_ALLOC(&c.d_scratch, 64));
   CUDA_OK(cudaMallocHost(&c.h_scratch, 64));
   for (int i = 0; i < 2; ++i) CUDA_OK(cudaEventCreateWithFlags(&c.poll_ev[i], cudaEventDisableTiming));
   CUDA_OK(cudaEventCreate(&c.t0));
@@ -162,10 +163,10 @@ void shutdown() {
     g_nccl.CommDestroy((ncclComm_t)c.comm);
     c.comm = nullptr;
   }
-  cudaFree(c.partials);
-  cudaFree(c.d_state);
+  dev_free(c.partials);
+  dev_free(c.d_state);
   cudaFreeHost(c.h_state);
-  cudaFree(c.d_scratch);
+  dev_free(c.d_scratch);
   cudaFreeHost(c.h_scratch);
   cudaStreamDestroy(c.stream);
   cudaStreamDestroy(c.comm_stream);
@@ -227,7 +228,7 @@ static int allgather_i64(const long long* mine, int count, std::vector<long long
     return 0;
   }
   long long* d = nullptr;
-  CUDA_OK(cudaMalloc(&d, sizeof(long long) * count * c.world));
+  CUDA_OK(DEV_ALLOC(&d, sizeof(long long) * count * c.world));
   CUDA_OK(cudaMemcpyAsync(d + (size_t)c.rank * count, mine, sizeof(long long) * count,
                           cudaMemcpyHostToDevice, c.stream));
   NCCL_OK(g_nccl.AllGather(d + (size_t)c.rank * count, d, (size_t)count, ncclInt64,
@@ -235,7 +236,7 @@ static int allgather_i64(const long long* mine, int count, std::vector<long long
   CUDA_OK(cudaMemcpyAsync(all.data(), d, sizeof(long long) * count * c.world,
                           cudaMemcpyDeviceToHost, c.stream));
   CUDA_OK(cudaStreamSynchronize(c.stream));
-  cudaFree(d);
+  dev_free(d);
   return 0;
 }
 
@@ -248,13 +249,13 @@ static int allgather_bytes(const void* mine, int bytes, std::vector<unsigned cha
     return 0;
   }
   unsigned char* d = nullptr;
-  CUDA_OK(cudaMalloc(&d, (size_t)bytes * c.world));
+  CUDA_OK(DEV_ALLOC(&d, (size_t)bytes * c.world));
   CUDA_OK(cudaMemcpyAsync(d + (size_t)c.rank * bytes, mine, bytes, cudaMemcpyHostToDevice, c.stream));
   NCCL_OK(g_nccl.AllGather(d + (size_t)c.rank * bytes, d, (size_t)bytes, ncclInt8,
                            (ncclComm_t)c.comm, c.stream));
   CUDA_OK(cudaMemcpyAsync(all.data(), d, (size_t)bytes * c.world, cudaMemcpyDeviceToHost, c.stream));
   CUDA_OK(cudaStreamSynchronize(c.stream));
-  cudaFree(d);
+  dev_free(d);
   return 0;
 }
 
@@ -291,23 +292,25 @@ System::~System() {
     dist_barrier();
   }
   free_pattern(&pat);
-  cudaFree(A.vals);
-  cudaFree(A.cols);
-  cudaFree(A.rowptr);
-  cudaFree(b);
-  cudaFree(x);
-  cudaFree(r);
-  cudaFree(s);
-  cudaFree(w);
-  cudaFree(dinv);
-  if (comm_buf)
+  dev_free(A.vals);
+  dev_free(A.cols);
+  dev_free(A.rowptr);
+  dev_free(b);
+  dev_free(x);
+  dev_free(r);
+  dev_free(s);
+  dev_free(w);
+  dev_free(dinv);
+  if (comm_buf) {
+    dev_guard_unwatch((char*)comm_buf + COMM_PEXT_OFFSET + ((size_t)ext_len + 16) * sizeof(double));
     cudaFree(comm_buf);  // p_ext lives inside it
-  else
-    cudaFree(p_ext);
-  cudaFree(state);
-  cudaFree(partials);
-  cudaFree(trace);
-  cudaFree(gemv_pool);
+  } else {
+    dev_free(p_ext);
+  }
+  dev_free(state);
+  dev_free(partials);
+  dev_free(trace);
+  dev_free(gemv_pool);
 }
 
 // Allocates the matrix arrays with the padding the bulk copies may over-read (zero-filled).
@@ -315,13 +318,13 @@ static int alloc_matrix(System* S, long long nnz, bool with_index) {
   S->A.nnz = nnz;
   S->A.nrows = S->nloc;
   const size_t vpad = (size_t)nnz + 64;
-  CUDA_OK(cudaMalloc(&S->A.vals, vpad * sizeof(double)));
+  CUDA_OK(DEV_ALLOC(&S->A.vals, vpad * sizeof(double)));
   CUDA_OK(cudaMemsetAsync(S->A.vals + nnz, 0, 64 * sizeof(double), g_ctx.stream));
   if (with_index) {
-    CUDA_OK(cudaMalloc(&S->A.cols, vpad * sizeof(int)));
+    CUDA_OK(DEV_ALLOC(&S->A.cols, vpad * sizeof(int)));
     CUDA_OK(cudaMemsetAsync(S->A.cols + nnz, 0, 64 * sizeof(int), g_ctx.stream));
     const size_t rpad = (size_t)S->nloc + 1 + 1024 + 64;
-    CUDA_OK(cudaMalloc(&S->A.rowptr, rpad * sizeof(int)));
+    CUDA_OK(DEV_ALLOC(&S->A.rowptr, rpad * sizeof(int)));
     CUDA_OK(cudaMemsetAsync(S->A.rowptr, 0, rpad * sizeof(int), g_ctx.stream));
   }
   return 0;
@@ -445,10 +448,10 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
   const long long col_shift = plan.col_shift;  // global column -> index in p_ext
 
   const size_t nl = (size_t)S->nloc;
-  CUDA_OK(cudaMalloc(&S->b, (nl + 16) * sizeof(double)));
-  CUDA_OK(cudaMalloc(&S->x, (nl + 16) * sizeof(double)));
-  CUDA_OK(cudaMalloc(&S->r, (nl + 16) * sizeof(double)));
-  CUDA_OK(cudaMalloc(&S->s, (nl + 16) * sizeof(double)));
+  CUDA_OK(DEV_ALLOC(&S->b, (nl + 16) * sizeof(double)));
+  CUDA_OK(DEV_ALLOC(&S->x, (nl + 16) * sizeof(double)));
+  CUDA_OK(DEV_ALLOC(&S->r, (nl + 16) * sizeof(double)));
+  CUDA_OK(DEV_ALLOC(&S->s, (nl + 16) * sizeof(double)));
   S->cm_off.world = 1;
   S->cm = S->cm_off;
   if (c.world > 1 && c.comm_mode == 1 && c.world <= MAX_RANKS) {
@@ -456,23 +459,28 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
     // never a sub-allocation of a block shared with other buffers
     size_t bytes = COMM_PEXT_OFFSET + ((size_t)S->ext_len + 16) * sizeof(double);
     bytes = (bytes + (2u << 20) - 1) / (2u << 20) * (2u << 20);
+    const size_t used = COMM_PEXT_OFFSET + ((size_t)S->ext_len + 16) * sizeof(double);
+    if (dev_guard_enabled() && bytes - used < 4096) bytes += 2u << 20;  // room for a guard band
     CUDA_OK(cudaMalloc(&S->comm_buf, bytes));
     CUDA_OK(cudaMemsetAsync(S->comm_buf, 0, bytes, c.stream));
     S->p_ext = (double*)((char*)S->comm_buf + COMM_PEXT_OFFSET);
+    // guard mode: the peers store into p_ext; the slack behind it must stay untouched
+    CUDA_OK(cudaStreamSynchronize(c.stream));
+    CUDA_OK(dev_guard_watch((char*)S->comm_buf + used, bytes - used, used, __FILE__, __LINE__));
   } else {
-    CUDA_OK(cudaMalloc(&S->p_ext, ((size_t)S->ext_len + 16) * sizeof(double)));
+    CUDA_OK(DEV_ALLOC(&S->p_ext, ((size_t)S->ext_len + 16) * sizeof(double)));
     CUDA_OK(cudaMemsetAsync(S->p_ext, 0, ((size_t)S->ext_len + 16) * sizeof(double), c.stream));
   }
   CUDA_OK(cudaMemsetAsync(S->x, 0, (nl + 16) * sizeof(double), c.stream));
-  CUDA_OK(cudaMalloc(&S->state, sizeof(CgState)));
+  CUDA_OK(DEV_ALLOC(&S->state, sizeof(CgState)));
   CUDA_OK(cudaMemsetAsync(S->state, 0, sizeof(CgState), c.stream));
-  CUDA_OK(cudaMalloc(&S->partials, sizeof(double) * partials_doubles()));
+  CUDA_OK(DEV_ALLOC(&S->partials, sizeof(double) * partials_doubles()));
   CUDA_OK(cudaMemsetAsync(S->partials, 0, sizeof(double) * partials_doubles(), c.stream));
   S->p_own = S->p_ext + S->off;
   if (S->dense) {  // chunk records of the dense matvec's dynamic tail (kernels.cu: gemv_pool_phase)
     const size_t pd = dense_pool_doubles(S->nloc, (int)S->n_global);
     if (pd > 0) {
-      CUDA_OK(cudaMalloc(&S->gemv_pool, pd * sizeof(double)));
+      CUDA_OK(DEV_ALLOC(&S->gemv_pool, pd * sizeof(double)));
       CUDA_OK(cudaMemsetAsync(S->gemv_pool, 0, pd * sizeof(double), c.stream));
     }
   }
@@ -535,7 +543,7 @@ __global__ void k_tile_span(const int* __restrict__ rowptr, const int* __restric
 int classify_tiles(System* S) {
   Ctx& c = g_ctx;
   unsigned char* d_flag = nullptr;
-  CUDA_OK(cudaMalloc(&d_flag, S->ntiles));
+  CUDA_OK(DEV_ALLOC(&d_flag, S->ntiles));
   const int R = spmv_rows_per_tile();
   k_tile_span<<<(S->ntiles + 127) / 128, 128, 0, c.stream>>>(
       S->A.rowptr, S->A.cols, S->nloc, R, S->ntiles, (int)S->off, (int)(S->off + S->nloc), d_flag);
@@ -543,7 +551,7 @@ int classify_tiles(System* S) {
   std::vector<unsigned char> flag(S->ntiles);
   CUDA_OK(cudaMemcpyAsync(flag.data(), d_flag, S->ntiles, cudaMemcpyDeviceToHost, c.stream));
   CUDA_OK(cudaStreamSynchronize(c.stream));
-  cudaFree(d_flag);
+  dev_free(d_flag);
   int lo = 0, hi = S->ntiles;
   while (lo < S->ntiles && flag[lo]) ++lo;
   while (hi > lo && flag[hi - 1]) --hi;
@@ -879,7 +887,7 @@ static int enqueue_nccl_finish(System* S, int count, int which) {
 
 static int ensure_w(System* S) {
   if (S->w) return 0;
-  CUDA_OK(cudaMalloc(&S->w, ((size_t)S->nloc + 16) * sizeof(double)));
+  CUDA_OK(DEV_ALLOC(&S->w, ((size_t)S->nloc + 16) * sizeof(double)));
   CUDA_OK(cudaMemsetAsync(S->w, 0, ((size_t)S->nloc + 16) * sizeof(double), g_ctx.stream));
   return 0;
 }
@@ -1046,7 +1054,7 @@ static int ensure_dinv(System* S) {
   Ctx& c = g_ctx;
   if (S->dinv) return 0;
   double* d = nullptr;
-  CUDA_OK(cudaMalloc(&d, ((size_t)S->nloc + 16) * sizeof(double)));
+  CUDA_OK(DEV_ALLOC(&d, ((size_t)S->nloc + 16) * sizeof(double)));
   int* bad = (int*)c.d_scratch;
   CUDA_OK(cudaMemsetAsync(bad, 0, sizeof(int), c.stream));
   if (S->nloc > 0)
@@ -1058,14 +1066,14 @@ static int ensure_dinv(System* S) {
   if (S->world > 1) {
     std::vector<long long> all;
     if (allgather_i64(&nbad, 1, all)) {
-      cudaFree(d);
+      dev_free(d);
       return -1;
     }
     nbad = 0;
     for (long long v : all) nbad += v;
   }
   if (nbad > 0) {
-    cudaFree(d);
+    dev_free(d);
     set_error("Jacobi preconditioner: " + std::to_string(nbad) +
               " row(s) without a positive finite diagonal entry");
     return -1;
@@ -1348,14 +1356,14 @@ int system_trace(System* S, int on, unsigned long long* out) {
   CUDA_OK(cudaStreamSynchronize(c.stream));
   if (out && S->trace)
     CUDA_OK(cudaMemcpy(out, S->trace, TRACE_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-  if (on && !S->trace) CUDA_OK(cudaMalloc(&S->trace, TRACE_WORDS * sizeof(unsigned long long)));
+  if (on && !S->trace) CUDA_OK(DEV_ALLOC(&S->trace, TRACE_WORDS * sizeof(unsigned long long)));
   if (on) {
     std::vector<unsigned long long> z(TRACE_WORDS, 0ull);
     z[8] = z[10] = ~0ull;  // minima
     CUDA_OK(cudaMemcpy(S->trace, z.data(), TRACE_WORDS * sizeof(unsigned long long), cudaMemcpyHostToDevice));
   }
   if (!on && S->trace) {
-    cudaFree(S->trace);
+    dev_free(S->trace);
     S->trace = nullptr;
   }
   for (auto& kv : S->graphs)

@@ -83,6 +83,16 @@ const char *cgb200_last_error(void);
 long long cgb200_launch_count(void);
 /* 1 when a CUDA device is usable, 0 otherwise (never touches the oracle or any CPU path). */
 int cgb200_device_available(void);
+/* Guard mode (debug aid; environment variable CGB200_GUARD=1, read at the first allocation): every
+ * device buffer of the library sits between two 4 KiB guard bands and is filled, guards and
+ * payload, with 0xFF -- an out-of-bounds store damages a guard, an out-of-bounds or
+ * uninitialised load yields NaN / -1 and breaks parity.  Returns -1 when guard mode is off, else
+ * the number of buffers whose guards were found damaged so far (freed ones included;
+ * cgb200_last_error() and stderr name the allocation site).  Synchronises the device. */
+long long cgb200_guard_check(void);
+/* Positive control: stores one byte just outside a scratch buffer on either side and reports
+ * whether the guards caught both (1), missed one (0); -1 when guard mode is off. */
+int cgb200_guard_selftest(void);
 
 /* ---- operator-API residency (struct address -> device mirror table) ------------------------ */
 /* CGB200_EAGER (default): every operator call uploads its inputs and downloads its output --

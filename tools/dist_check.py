@@ -235,6 +235,15 @@ for hb, name in ((7, "banded neighbour"), (900, "banded wide")):
         report(f"from_csr {name} jacobi + x0", r.iterations == it_ and rel <= 1e-8, f"rel {rel:.2e}")
     d.free()
 
+# 5) run under CGB200_GUARD=1: no kernel stored outside a device buffer on any rank (csrc/devmem.h)
+if hasattr(L, "cgb200_guard_check"):
+    L.cgb200_guard_check.restype = C.c_longlong
+    bad = int(L.cgb200_guard_check())
+    if bad >= 0:
+        tg = torch.tensor([float(bad)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tg, op=dist.ReduceOp.SUM)
+        report("guard bands intact on every rank", tg.item() == 0.0, f"{int(tg.item())} damaged")
+
 L.cgb200_dist_finalize()
 dist.barrier()
 dist.destroy_process_group()
