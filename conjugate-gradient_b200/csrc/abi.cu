@@ -35,6 +35,9 @@ namespace {
   } while (0)
 
 std::mutex g_tab_mu;
+// doubles behind every device vector of the operator API: the matvec kernels may over-read their
+// gather vector by up to a vector load (solver.cu pads the systems' own vectors the same way)
+constexpr size_t VEC_PAD = 16;
 // CGB200_MODE=resident starts the operator API in resident mode: the way to run an unmodified
 // caller of mv_ops.h (the reference's own cg.c loop) without a transfer per operator call
 static int initial_mode() {
@@ -60,6 +63,13 @@ struct VectorEntry {
   int n = 0;
   bool dev_valid = false;   // device copy holds the current values
   bool host_valid = false;  // host array holds the current values
+  // resident mode: v.v of the current device values, once a dot_product(v, v) has computed it.
+  // The reference's loop asks for r.r twice per residual (cg.c:129 then cg.c:113) and once more
+  // for the copy it keeps (r_prev, cg.c:120,129): the kernel is deterministic, so handing back the
+  // stored value is bit-identical to recomputing it and saves two launches and two host
+  // synchronisations per iteration.  Cleared by every write; carried over by mv_deep_copy.
+  bool sd_valid = false;
+  double sd = 0.0;
 };
 
 std::unordered_map<const void*, MatrixEntry> g_mats;
@@ -70,12 +80,12 @@ double* g_scratch[3] = {nullptr, nullptr, nullptr};
 size_t g_scratch_cap[3] = {0, 0, 0};
 
 int scratch(int slot, size_t n, double** out) {
-  if (g_scratch_cap[slot] < n + 2) {
+  if (g_scratch_cap[slot] < n + VEC_PAD) {
     if (g_scratch[slot]) dev_free(g_scratch[slot]);
     g_scratch[slot] = nullptr;
     g_scratch_cap[slot] = 0;
-    CU_OK(DEV_ALLOC(&g_scratch[slot], (n + 2) * sizeof(double)));
-    g_scratch_cap[slot] = n + 2;
+    CU_OK(DEV_ALLOC(&g_scratch[slot], (n + VEC_PAD) * sizeof(double)));
+    g_scratch_cap[slot] = n + VEC_PAD;
   }
   *out = g_scratch[slot];
   return 0;
@@ -166,7 +176,7 @@ void vec_pool_flush() {
 
 void vec_release(double* d, int cap) {
   if (!d) return;
-  const size_t bytes = ((size_t)cap + 2) * sizeof(double);
+  const size_t bytes = ((size_t)cap + VEC_PAD) * sizeof(double);
   // guard mode frees at once: the guards are checked at the free, and a reused buffer would hold
   // stale values instead of the poison that exposes uninitialised reads
   if (dev_guard_enabled() || g_vec_pool.size() >= VEC_POOL_MAX_COUNT || g_vec_pool_bytes + bytes > VEC_POOL_MAX_BYTES) {
@@ -198,14 +208,14 @@ int ensure_vec_capacity(VectorEntry& e, int n) {
     auto it = g_vec_pool.find(n);  // exact capacity only: a pooled buffer never grows a footprint
     if (it != g_vec_pool.end()) {
       e.d = it->second;
-      g_vec_pool_bytes -= ((size_t)n + 2) * sizeof(double);
+      g_vec_pool_bytes -= ((size_t)n + VEC_PAD) * sizeof(double);
       g_vec_pool.erase(it);
     } else {
-      cudaError_t err = DEV_ALLOC(&e.d, ((size_t)n + 2) * sizeof(double));
+      cudaError_t err = DEV_ALLOC(&e.d, ((size_t)n + VEC_PAD) * sizeof(double));
       if (err != cudaSuccess && !g_vec_pool.empty()) {
         cudaGetLastError();
         vec_pool_flush();
-        err = DEV_ALLOC(&e.d, ((size_t)n + 2) * sizeof(double));
+        err = DEV_ALLOC(&e.d, ((size_t)n + VEC_PAD) * sizeof(double));
       }
       CU_OK(err);
     }
@@ -230,6 +240,7 @@ int dev_input(struct __mv_sparse* v, int slot, const double** out) {
       CU_OK(cudaMemcpyAsync(e.d, v->values, sizeof(double) * n, cudaMemcpyHostToDevice, c.stream));
     e.dev_valid = true;
     e.host_valid = true;
+    e.sd_valid = false;
     *out = e.d;
     return 0;
   }
@@ -284,6 +295,7 @@ int finish_output(struct __mv_sparse* o, double* d) {
     VectorEntry& e = g_vecs[o];
     e.dev_valid = true;
     e.host_valid = false;
+    e.sd_valid = false;
     return 0;
   }
   if (o->size > 0)
@@ -426,6 +438,8 @@ struct __mv_sparse* mv_deep_copy(struct __mv_sparse* orig) {
       }
       const double* src = it->second.d;  // (taken before g_vecs[cp] may rehash the table)
       const int n = it->second.n;
+      const bool sd_valid = it->second.sd_valid;
+      const double sd = it->second.sd;
       VectorEntry& e = g_vecs[cp];
       if (ensure_vec_capacity(e, n) ||
           (n > 0 && cudaMemcpyAsync(e.d, src, sizeof(double) * n, cudaMemcpyDeviceToDevice,
@@ -438,6 +452,8 @@ struct __mv_sparse* mv_deep_copy(struct __mv_sparse* orig) {
       }
       e.dev_valid = true;
       e.host_valid = false;
+      e.sd_valid = sd_valid;
+      e.sd = sd;
       return cp;
     }
     if (sync_to_host(orig)) return NULL;
@@ -495,6 +511,11 @@ double dot_product(struct __mv_sparse* vec_a, struct __mv_sparse* vec_b) {
   Ctx& c = ctx();
   const double *da = nullptr, *db = nullptr;
   if (dev_input(vec_a, 0, &da)) return -1.0;
+  const bool self = vec_b == vec_a && g_mode == CGB200_RESIDENT;
+  if (self) {
+    const VectorEntry& e = g_vecs[vec_a];
+    if (e.sd_valid) return e.sd;
+  }
   if (vec_b == vec_a)
     db = da;
   else if (dev_input(vec_b, 1, &db))
@@ -508,7 +529,13 @@ double dot_product(struct __mv_sparse* vec_a, struct __mv_sparse* vec_b) {
     set_error(std::string("dot_product: ") + cudaGetErrorString(cudaGetLastError()));
     return -1.0;
   }
-  return *(double*)c.h_scratch;
+  const double v = *(double*)c.h_scratch;
+  if (self) {
+    VectorEntry& e = g_vecs[vec_a];
+    e.sd = v;
+    e.sd_valid = true;
+  }
+  return v;
 }
 
 int sv_mult(double s, struct __mv_sparse* vec_a, struct __mv_sparse** out) {
@@ -537,10 +564,9 @@ int mv_mult(struct __mv_sparse* mat_A, struct __mv_sparse* vec_b, struct __mv_sp
   if (g_mode == CGB200_EAGER) CU_OK(cudaStreamSynchronize(c.stream));
   if (prepare_out(out, n, vec_b->nnz)) return -1;
   if (n == 0) return 0;
-  if (system_matvec_dev(sys, db, nullptr)) return -1;
   double* dout = nullptr;
   if (dev_output(*out, 2, &dout)) return -1;
-  CU_OK(cudaMemcpyAsync(dout, sys->s, sizeof(double) * n, cudaMemcpyDeviceToDevice, c.stream));
+  if (system_matvec_into(sys, db, dout)) return -1;
   return finish_output(*out, dout);
 }
 
@@ -602,6 +628,7 @@ int cgb200_set_mode(int mode) {
       struct __mv_sparse* o = (struct __mv_sparse*)kv.first;
       if (kv.second.dev_valid && !kv.second.host_valid) sync_to_host(o);
       kv.second.dev_valid = false;
+      kv.second.sd_valid = false;
     }
   }
   g_mode = mode;
@@ -621,6 +648,7 @@ int cgb200_to_device(struct __mv_sparse* obj) {
   CU_OK(cudaStreamSynchronize(ctx().stream));
   e.dev_valid = true;
   e.host_valid = true;
+  e.sd_valid = false;
   return 0;
 }
 

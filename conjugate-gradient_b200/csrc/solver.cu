@@ -1417,6 +1417,28 @@ int system_matvec_dev(System* S, const double* v_dev, double* s_host_or_null) {
   return 0;
 }
 
+// Single rank: s = A v straight from a caller's device vector into a caller's device buffer --
+// no staging copies and no host synchronisation (the operator API's resident mode, abi.cu).
+// Both buffers hold at least nloc + 16 doubles (the padding the kernels may over-read) and are
+// distinct.  Anything else takes the staged path above and copies the result out.
+int system_matvec_into(System* S, const double* v_dev, double* out_dev) {
+  Ctx& c = g_ctx;
+  if (S->world != 1 || S->off != 0 || v_dev == out_dev) {
+    if (system_matvec_dev(S, v_dev, nullptr)) return -1;
+    CUDA_OK(cudaMemcpyAsync(out_dev, S->s, sizeof(double) * S->nloc, cudaMemcpyDeviceToDevice,
+                            c.stream));
+    return 0;
+  }
+  double* const ext = S->p_ext;
+  double* const own = S->p_own;
+  S->p_ext = const_cast<double*>(v_dev);  // read-only in a plain product
+  S->p_own = S->p_ext;
+  const int rc = enqueue_matvec(S, out_dev, FIN_NONE, false, false);
+  S->p_ext = ext;
+  S->p_own = own;
+  return rc;
+}
+
 int system_matvec(System* S, const double* v_host, double* s_host) {
   Ctx& c = g_ctx;
   CUDA_OK(cudaMemcpyAsync(S->p_own, v_host, sizeof(double) * S->nloc, cudaMemcpyHostToDevice,

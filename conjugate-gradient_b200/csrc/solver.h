@@ -133,6 +133,7 @@ int system_get_x(System* S, double* x_host);
 int system_set_x(System* S, const double* x_host);  // initial guess for a CGB200_OPT_X0 solve
 int system_matvec(System* S, const double* v_host, double* s_host);
 int system_matvec_dev(System* S, const double* v_dev, double* s_host_or_null);
+int system_matvec_into(System* S, const double* v_dev, double* out_dev);
 int system_true_relres(System* S, double* relres);
 int system_time_kernel(System* S, int which, int reps, double* ms_out);
 int system_download(System* S, double* vals, int* cols, int* row_ptr);

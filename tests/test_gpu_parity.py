@@ -553,6 +553,83 @@ def test_reference_loop_through_the_operators_in_resident_mode(pkg, gpu_lib, mk,
     assert np.linalg.norm(x - xo) <= TOL_X * np.linalg.norm(xo)
 
 
+@pytest.mark.gpu
+def test_resident_mode_stored_self_dot_follows_every_write(pkg, gpu_lib):
+    # resident mode answers a repeated dot_product(v, v) from the value stored with v (the
+    # reference's loop asks for r.r twice per residual): every write must drop it, a deep copy
+    # carries it, and the answer is bit-identical to the kernel's in eager mode
+    L = gpu_lib
+    n = 5000
+    a = H.rhs(n, 11)
+    c = H.rhs(n, 12)
+    va, vc = _vec(pkg, a), _vec(pkg, c)
+    eager = L.dot_product(C.byref(va), C.byref(va))
+    s = a + c
+    vs = _vec(pkg, s)
+    eager_sum = L.dot_product(C.byref(vs), C.byref(vs))
+    assert L.cgb200_set_mode(pkg.RESIDENT) == 0
+    try:
+        r = L.mv_deep_copy(C.byref(va))
+        d1 = L.dot_product(r, r)
+        d2 = L.dot_product(r, r)                                   # stored value
+        cp = L.mv_deep_copy(r)
+        d3 = L.dot_product(cp, cp)                                 # carried by the copy
+        assert L.vec_add(r, C.byref(vc), C.byref(r)) == 0           # in-place write
+        d4 = L.dot_product(r, r)
+        d5 = L.dot_product(cp, cp)                                 # the copy did not change
+        assert L.sv_mult(2.0, r, C.byref(cp)) == 0                  # cp overwritten
+        d6 = L.dot_product(cp, cp)
+        for o in (r, cp):
+            L.cgb200_free_all(o)
+    finally:
+        assert L.cgb200_set_mode(pkg.EAGER) == 0
+        for v in (va, vc, vs):
+            L.cgb200_invalidate(C.byref(v))
+    assert _bits(np.array([d1, d2, d3, d5])).tolist() == [_bits(np.array([eager]))[0]] * 4
+    assert _bits(np.array([d4]))[0] == _bits(np.array([eager_sum]))[0]
+    assert d6 == 4.0 * eager_sum                                    # scaling by 2 is exact
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["eager", "resident"])
+@pytest.mark.parametrize("mk", [lambda: H.lap(40, 23), lambda: H.dense(130), lambda: H.lap(9, 8, 7)])
+def test_mv_mult_writes_straight_into_the_output_vector(pkg, gpu_lib, mk, mode):
+    # the operator's matvec gathers from the caller's device vector and stores into the output's
+    # device buffer (no staging); an existing output is reused, and an output that IS the input
+    # (not something the reference supports, mv_ops.c:178-181 zeroes it first) must not corrupt
+    L = gpu_lib
+    s = mk()
+    A, _ = _structs(pkg, s)
+    v = H.rhs(s.n, 5)
+    want = np.empty(s.n)
+    H.oracle().oracle_spmv(s.n, H.iptr(s.row_ptr), H.iptr(s.cols), H.dptr(s.vals), H.dptr(v), H.dptr(want))
+    vhost = v.copy()                                              # must outlive the struct that points at it
+    vv = _vec(pkg, vhost)
+    assert L.cgb200_set_mode(pkg.RESIDENT if mode == "resident" else pkg.EAGER) == 0
+    try:
+        out = pkg.MvSparseP()
+        assert L.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0, pkg.last_error()
+        assert L.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0      # existing output reused
+        assert L.cgb200_to_host(out) == 0
+        got = _take(out, s.n)
+        w = L.mv_deep_copy(C.byref(vv))
+        assert L.mv_mult(C.byref(A), w, C.byref(w)) == 0                  # output aliases the input
+        assert L.cgb200_to_host(w) == 0
+        alias = _take(w, s.n)
+        for o in (out, w):
+            L.cgb200_free_all(o)
+    finally:
+        assert L.cgb200_set_mode(pkg.EAGER) == 0
+        L.cgb200_invalidate(C.byref(A))
+        L.cgb200_invalidate(C.byref(vv))
+    if s.nnz == s.n * s.n:     # dense path: row sums are tree-ordered, not the reference's sequence
+        scale = 4 * s.n * np.finfo(float).eps * (np.abs(s.vals).reshape(s.n, s.n) @ np.abs(v))
+        assert np.all(np.abs(got - want) <= scale) and np.array_equal(_bits(alias), _bits(got))
+    else:
+        assert np.array_equal(_bits(got), _bits(want))
+        assert np.array_equal(_bits(alias), _bits(want))
+
+
 # ---------------------------------------------------------------------------------------------
 # row-pattern dictionary format: same arithmetic, one byte per row
 # ---------------------------------------------------------------------------------------------
