@@ -70,6 +70,15 @@ struct VectorEntry {
   // synchronisations per iteration.  Cleared by every write; carried over by mv_deep_copy.
   bool sd_valid = false;
   double sd = 0.0;
+  // resident mode: a deferred sv_mult.  The mirror's values are lazy_s * (the values of lazy_src's
+  // mirror) and have not been computed: the reference's loop reads each scaled vector exactly once,
+  // in the vec_add / vec_sub that follows (cg.c:115-118, 122-123, 131-132), and that operator then
+  // forms a +/- fl(s*b) itself in one pass -- same two roundings, one pass over memory less.  Any
+  // other reader computes the values first (materialize), and so does anything about to change
+  // or release the source (before_write), so a deferred vector never observes a changed source.
+  bool lazy = false;
+  double lazy_s = 0.0;
+  const void* lazy_src = nullptr;
 };
 
 std::unordered_map<const void*, MatrixEntry> g_mats;
@@ -158,6 +167,49 @@ System* matrix_system(struct __mv_sparse* A) {
   return sys;
 }
 
+std::vector<const void*> g_lazy;  // structs whose mirror is a deferred scale (a handful at most)
+
+void lazy_forget(const void* obj) {
+  for (size_t i = 0; i < g_lazy.size(); ++i)
+    if (g_lazy[i] == obj) {
+      g_lazy[i] = g_lazy.back();
+      g_lazy.pop_back();
+      return;
+    }
+}
+
+// Computes the values of a deferred scale into its own buffer.
+int materialize(const void* obj) {
+  auto it = g_vecs.find(obj);
+  if (it == g_vecs.end() || !it->second.lazy) return 0;
+  VectorEntry& e = it->second;
+  auto is = g_vecs.find(e.lazy_src);
+  if (is == g_vecs.end() || !is->second.d || !e.d) {
+    set_error("internal: deferred scale lost its source");
+    return -1;
+  }
+  if (e.n > 0) CU_OK(launch_ewise(0, e.lazy_s, is->second.d, nullptr, e.d, e.n, ctx().stream));
+  e.lazy = false;
+  e.lazy_src = nullptr;
+  lazy_forget(obj);
+  return 0;
+}
+
+// obj's device values are about to change or go away: whoever defers a scale of them computes now.
+int before_write(const void* obj) {
+  if (g_lazy.empty()) return 0;
+  for (size_t i = 0; i < g_lazy.size();) {
+    const void* l = g_lazy[i];
+    auto it = g_vecs.find(l);
+    if (l != obj && it != g_vecs.end() && it->second.lazy && it->second.lazy_src == obj) {
+      if (materialize(l)) return -1;  // removes l from g_lazy: look at slot i again
+      continue;
+    }
+    ++i;
+  }
+  return 0;
+}
+
 // Device vectors released by free_mv_struct / cgb200_free_all / a resize are kept for the next
 // operator output of the same capacity: a caller written like the reference's loop creates and
 // drops two vectors per iteration (cg.c:117,120), and a cudaMalloc + cudaFree pair per vector
@@ -192,6 +244,10 @@ void drop_mirror(const void* obj) {
   if (im != g_mats.end()) {
     delete im->second.sys;
     g_mats.erase(im);
+  }
+  if (!g_lazy.empty()) {
+    before_write(obj);  // a deferred scale of these values is computed before they go
+    lazy_forget(obj);
   }
   auto iv = g_vecs.find(obj);
   if (iv != g_vecs.end()) {
@@ -232,8 +288,14 @@ int dev_input(struct __mv_sparse* v, int slot, const double** out) {
   if (g_mode == CGB200_RESIDENT) {
     VectorEntry& e = g_vecs[v];
     if (e.dev_valid && e.n == n) {
+      if (e.lazy && materialize(v)) return -1;
       *out = e.d;
       return 0;
+    }
+    if (before_write(v)) return -1;
+    if (e.lazy) {
+      e.lazy = false;
+      lazy_forget(v);
     }
     if (ensure_vec_capacity(e, n)) return -1;
     if (n > 0)
@@ -276,7 +338,13 @@ int prepare_out(struct __mv_sparse** out, int size, int nnz) {
 int dev_output(struct __mv_sparse* o, int slot, double** out) {
   const int n = o->size;
   if (g_mode == CGB200_RESIDENT) {
+    if (before_write(o)) return -1;
     VectorEntry& e = g_vecs[o];
+    if (e.lazy) {  // overwritten before anybody read it: the scale is never computed
+      e.lazy = false;
+      e.lazy_src = nullptr;
+      lazy_forget(o);
+    }
     if (e.cap < n || !e.d) {
       // growing must keep nothing: the op overwrites all n elements
       if (ensure_vec_capacity(e, n)) return -1;
@@ -308,6 +376,7 @@ int sync_to_host(struct __mv_sparse* o) {
   auto it = g_vecs.find(o);
   if (it == g_vecs.end()) return 0;
   VectorEntry& e = it->second;
+  if (e.lazy && materialize(o)) return -1;
   if (e.dev_valid && !e.host_valid && e.n == o->size && o->values) {
     Ctx& c = ctx();
     if (e.n > 0)
@@ -318,6 +387,68 @@ int sync_to_host(struct __mv_sparse* o) {
   return 0;
 }
 
+// Resident mode's two shortcuts (VectorEntry::lazy).  Returns 0 when the call has been dealt with,
+// -1 on failure, 1 when the general path should run.
+//   sv_mult(s, a, &out), out distinct from a: nothing is launched; out's mirror becomes "s * a".
+//   vec_add / vec_sub whose second operand is such a deferred scale: one pass forms
+//   a +/- fl(s * src); when the output is the scale's source (p = r + beta p through
+//   sres = beta p, cg.c:131-132) the same pass also stores the scaled vector.
+int ewise_resident(int op, double sca, struct __mv_sparse* a, struct __mv_sparse* b,
+                   struct __mv_sparse** out) {
+  Ctx& c = ctx();
+  const int n = a->size, nnz = a->nnz;
+  if (op == 0) {
+    if (*out == a || n <= 0) return 1;
+    const double* da = nullptr;
+    if (dev_input(a, 0, &da)) return -1;  // a on the device, computed if it was deferred itself
+    if (prepare_out(out, n, nnz)) return -1;
+    double* dout = nullptr;
+    if (dev_output(*out, 2, &dout)) return -1;  // buffer for a later materialize; drops old state
+    VectorEntry& e = g_vecs[*out];
+    e.dev_valid = true;
+    e.host_valid = false;
+    e.sd_valid = false;
+    e.lazy = true;
+    e.lazy_s = sca;
+    e.lazy_src = a;
+    g_lazy.push_back(*out);
+    return 0;
+  }
+  auto ib = g_vecs.find(b);
+  if (ib == g_vecs.end() || !ib->second.lazy || !ib->second.dev_valid || ib->second.n != n || b == a)
+    return 1;
+  const void* src = ib->second.lazy_src;
+  const double s = ib->second.lazy_s;
+  auto is = g_vecs.find(src);
+  if (is == g_vecs.end() || !is->second.d) return 1;
+  const double* da = nullptr;
+  if (dev_input(a, 0, &da)) return -1;
+  ib = g_vecs.find(b);  // (dev_input may have rehashed the table or touched what b defers)
+  if (ib == g_vecs.end() || !ib->second.lazy || ib->second.lazy_src != src) return 1;
+  if (src == (const void*)*out) {
+    // the output is the scale's source (p = r + beta p through sres = beta p, cg.c:131-132): one
+    // pass stores the scaled vector where b's values belong and the sum over the source
+    VectorEntry& eb = ib->second;
+    double* db = eb.d;
+    eb.lazy = false;  // its values exist once the kernel below has run
+    eb.lazy_src = nullptr;
+    lazy_forget(b);
+    if (prepare_out(out, n, nnz)) return -1;
+    double* dout = nullptr;
+    if (dev_output(*out, 2, &dout)) return -1;  // computes whoever else defers a scale of *out
+    if (*out == a) da = dout;
+    CU_OK(launch_ewise(op == 1 ? 5 : 6, s, da, dout, dout, n, c.stream, db));
+    return finish_output(*out, dout);
+  }
+  if (prepare_out(out, n, nnz)) return -1;
+  double* dout = nullptr;
+  if (dev_output(*out, 2, &dout)) return -1;  // (*out == b: b stops being deferred, it is overwritten)
+  if (*out == a) da = dout;
+  const double* dsrc = g_vecs.find(src)->second.d;
+  CU_OK(launch_ewise(op == 1 ? 3 : 4, s, da, dsrc, dout, n, c.stream));
+  return finish_output(*out, dout);
+}
+
 int ewise(int op, double sca, struct __mv_sparse* a, struct __mv_sparse* b, struct __mv_sparse** out) {
   if (!a || (op != 0 && !b) || !out) return -1;
   if (op != 0 && a->size != b->size) return -1;
@@ -325,6 +456,10 @@ int ewise(int op, double sca, struct __mv_sparse* a, struct __mv_sparse* b, stru
   std::lock_guard<std::mutex> lk(g_tab_mu);
   Ctx& c = ctx();
   const int n = a->size, nnz = a->nnz;
+  if (g_mode == CGB200_RESIDENT) {
+    const int rc = ewise_resident(op, sca, a, b, out);
+    if (rc <= 0) return rc;  // done (0) or failed (-1); 1 = take the general path below
+  }
   // inputs first: *out may alias an input whose host array prepare_out() is about to realloc
   const double *da = nullptr, *db = nullptr;
   if (dev_input(a, 0, &da)) return -1;
@@ -425,6 +560,7 @@ struct __mv_sparse* mv_deep_copy(struct __mv_sparse* orig) {
     // every iteration): copy device to device and leave the host array of the copy stale, like
     // every other resident-mode output -- no transfer, no synchronisation
     auto it = g_vecs.find(orig);
+    if (it != g_vecs.end() && it->second.lazy && materialize(orig)) return NULL;
     if (g_mode == CGB200_RESIDENT && !orig->col_indices && !orig->row_ptr && it != g_vecs.end() &&
         it->second.dev_valid && !it->second.host_valid && it->second.n == orig->size) {
       struct __mv_sparse* cp = new_mv_struct();
@@ -593,6 +729,7 @@ void cgb200_shutdown(void) {
   for (auto& kv : g_vecs) dev_free(kv.second.d);
   vec_pool_flush();
   g_vecs.clear();
+  g_lazy.clear();
   for (int i = 0; i < 3; ++i) {
     if (g_scratch[i]) dev_free(g_scratch[i]);
     g_scratch[i] = nullptr;
@@ -640,7 +777,12 @@ int cgb200_to_device(struct __mv_sparse* obj) {
   if (ensure_init(-1)) return -1;
   std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!is_vector(obj)) return matrix_system(obj) ? 0 : -1;
+  if (before_write(obj)) return -1;
   VectorEntry& e = g_vecs[obj];
+  if (e.lazy) {
+    e.lazy = false;
+    lazy_forget(obj);
+  }
   if (ensure_vec_capacity(e, obj->size)) return -1;
   if (obj->size > 0)
     CU_OK(cudaMemcpyAsync(e.d, obj->values, sizeof(double) * obj->size, cudaMemcpyHostToDevice,

@@ -1407,12 +1407,15 @@ k_dot(const double* __restrict__ a, const double* __restrict__ b, long long n,
   if (grid_sum<VT>(acc, partials, ticket, total)) *out = total;
 }
 
-// op: 0 = scale (out = sca*a; mv_ops.c:134-158), 1 = add (203-230), 2 = sub (232-259).
+// op: 0 = scale (out = sca*a; mv_ops.c:134-158), 1 = add (203-230), 2 = sub (232-259);
+// 3 / 4 = a +/- fl(sca*b): a scale whose only reader is the add/sub that follows it (the operator
+// API's resident mode defers the scale, abi.cu) -- the same two roundings in one pass;
+// 5 / 6 = the same with fl(sca*b) stored to out2 too (the add/sub overwrites the scale's source).
 // out may alias a or b (element-wise, each element read before it is written).
 template <int OP>
 __global__ void __launch_bounds__(VT)
-k_ewise(double sca, const double* a, const double* b, double* out, long long n) {
-  const long long n2 = vec_pairs(n, a, OP != 0 ? b : nullptr, out, nullptr);
+k_ewise(double sca, const double* a, const double* b, double* out, long long n, double* out2) {
+  const long long n2 = vec_pairs(n, a, OP != 0 ? b : nullptr, out, OP >= 5 ? out2 : nullptr);
   const long long stride = (long long)gridDim.x * VT;
   for (long long i = (long long)blockIdx.x * VT + threadIdx.x; i < n2; i += stride * VU) {
     double2 av[VU], bv[VU];
@@ -1435,16 +1438,41 @@ k_ewise(double sca, const double* a, const double* b, double* out, long long n) 
         } else if (OP == 1) {
           o.x = __dadd_rn(av[u].x, bv[u].x);
           o.y = __dadd_rn(av[u].y, bv[u].y);
-        } else {
+        } else if (OP == 2) {
           o.x = __dsub_rn(av[u].x, bv[u].x);
           o.y = __dsub_rn(av[u].y, bv[u].y);
+        } else if (OP == 3) {  // a + fl(sca * b): sv_mult then vec_add, same two roundings
+          o.x = __dadd_rn(av[u].x, __dmul_rn(sca, bv[u].x));
+          o.y = __dadd_rn(av[u].y, __dmul_rn(sca, bv[u].y));
+        } else if (OP == 4) {  // a - fl(sca * b)
+          o.x = __dsub_rn(av[u].x, __dmul_rn(sca, bv[u].x));
+          o.y = __dsub_rn(av[u].y, __dmul_rn(sca, bv[u].y));
+        } else {               // 5 / 6: as 3 / 4, and the scaled vector is stored as well (out2)
+          double2 t;
+          t.x = __dmul_rn(sca, bv[u].x);
+          t.y = __dmul_rn(sca, bv[u].y);
+          st2(out2 + 2 * j, t);
+          o.x = OP == 5 ? __dadd_rn(av[u].x, t.x) : __dsub_rn(av[u].x, t.x);
+          o.y = OP == 5 ? __dadd_rn(av[u].y, t.y) : __dsub_rn(av[u].y, t.y);
         }
         st2(out + 2 * j, o);
       }
     }
   }
-  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride)
-    out[j] = OP == 0 ? __dmul_rn(sca, a[j]) : OP == 1 ? __dadd_rn(a[j], b[j]) : __dsub_rn(a[j], b[j]);
+  for (long long j = 2 * n2 + (long long)blockIdx.x * VT + threadIdx.x; j < n; j += stride) {
+    if (OP >= 5) {
+      const double t = __dmul_rn(sca, b[j]);
+      const double av = a[j];
+      out2[j] = t;
+      out[j] = OP == 5 ? __dadd_rn(av, t) : __dsub_rn(av, t);
+    } else {
+      out[j] = OP == 0   ? __dmul_rn(sca, a[j])
+               : OP == 1 ? __dadd_rn(a[j], b[j])
+               : OP == 2 ? __dsub_rn(a[j], b[j])
+               : OP == 3 ? __dadd_rn(a[j], __dmul_rn(sca, b[j]))
+                         : __dsub_rn(a[j], __dmul_rn(sca, b[j]));
+    }
+  }
 }
 
 // r = b - s and partial sums of r.r and b.b (independent true-residual check)
@@ -1947,14 +1975,22 @@ cudaError_t launch_dot(const double* a, const double* b, long long n, double* pa
 }
 
 cudaError_t launch_ewise(int op, double sca, const double* a, const double* b, double* out,
-                         long long n, cudaStream_t st) {
+                         long long n, cudaStream_t st, double* out2) {
   const int g = vec_grid(n);
   if (op == 0)
-    k_ewise<0><<<g, VT, 0, st>>>(sca, a, b, out, n);
+    k_ewise<0><<<g, VT, 0, st>>>(sca, a, b, out, n, nullptr);
   else if (op == 1)
-    k_ewise<1><<<g, VT, 0, st>>>(sca, a, b, out, n);
+    k_ewise<1><<<g, VT, 0, st>>>(sca, a, b, out, n, nullptr);
+  else if (op == 2)
+    k_ewise<2><<<g, VT, 0, st>>>(sca, a, b, out, n, nullptr);
+  else if (op == 3)
+    k_ewise<3><<<g, VT, 0, st>>>(sca, a, b, out, n, nullptr);
+  else if (op == 4)
+    k_ewise<4><<<g, VT, 0, st>>>(sca, a, b, out, n, nullptr);
+  else if (op == 5)
+    k_ewise<5><<<g, VT, 0, st>>>(sca, a, b, out, n, out2);
   else
-    k_ewise<2><<<g, VT, 0, st>>>(sca, a, b, out, n);
+    k_ewise<6><<<g, VT, 0, st>>>(sca, a, b, out, n, out2);
   ++g_launches;
   return cudaGetLastError();
 }

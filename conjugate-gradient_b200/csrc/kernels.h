@@ -138,7 +138,7 @@ cudaError_t launch_finish(CgState* S, int which, cudaStream_t st);
 cudaError_t launch_dot(const double* a, const double* b, long long n, double* partials,
                        unsigned int* ticket, double* out, cudaStream_t st);
 cudaError_t launch_ewise(int op, double sca, const double* a, const double* b, double* out,
-                         long long n, cudaStream_t st);
+                         long long n, cudaStream_t st, double* out2 = nullptr);
 cudaError_t launch_resid_norms(const double* b, const double* s, long long n, double* partials,
                                unsigned int* ticket, double* out2, cudaStream_t st);
 cudaError_t launch_gen_rhs(double* b, long long row0, long long n, unsigned long long seed,

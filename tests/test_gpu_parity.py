@@ -591,6 +591,80 @@ def test_resident_mode_stored_self_dot_follows_every_write(pkg, gpu_lib):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 7, 4096, 50001])
+def test_resident_mode_deferred_scale_is_invisible(pkg, gpu_lib, n):
+    # resident mode defers sv_mult and lets the vec_add / vec_sub that reads the result form
+    # a +/- fl(s*b) in one pass; every other reader, and every write to the source, must see exactly
+    # what the eager operators produce (numpy: the same unfused roundings)
+    L = gpu_lib
+    a, c = H.rhs(n, 21), H.rhs(n, 22)
+    va, vc = _vec(pkg, a), _vec(pkg, c)
+    s1, s2 = 0.3721, -1.9
+
+    def host(ptr):
+        assert L.cgb200_to_host(ptr) == 0
+        return _take(ptr, n)
+
+    got = {}
+    assert L.cgb200_set_mode(pkg.RESIDENT) == 0
+    try:
+        ra, rc = L.mv_deep_copy(C.byref(va)), L.mv_deep_copy(C.byref(vc))
+        t, u, w = pkg.MvSparseP(), pkg.MvSparseP(), pkg.MvSparseP()
+        assert L.sv_mult(s1, ra, C.byref(t)) == 0                   # deferred
+        assert L.vec_add(rc, t, C.byref(u)) == 0                    # consumed in one pass
+        got["add"] = host(u)
+        got["t_after_use"] = host(t)                                # ... and still readable
+        assert L.sv_mult(s1, ra, C.byref(t)) == 0
+        assert L.vec_sub(rc, t, C.byref(t)) == 0                    # output is the deferred vector
+        got["sub_into_t"] = host(t)
+        assert L.sv_mult(s1, ra, C.byref(t)) == 0
+        assert L.vec_add(ra, rc, C.byref(ra)) == 0                  # the source changes first
+        got["t_before_src_write"] = host(t)
+        got["ra_sum"] = host(ra)
+        assert L.sv_mult(s2, ra, C.byref(t)) == 0
+        assert L.vec_add(rc, t, C.byref(ra)) == 0                   # the output is the source
+        got["out_is_src"] = host(ra)
+        got["t_after_out_is_src"] = host(t)                         # stored by the same pass
+        assert L.sv_mult(s1, rc, C.byref(t)) == 0
+        assert L.sv_mult(s2, rc, C.byref(t)) == 0                   # overwritten unread
+        assert L.sv_mult(s1, t, C.byref(w)) == 0                    # deferred on a deferred vector
+        assert L.sv_mult(s1, rc, C.byref(t)) == 0                   # its source is rewritten first
+        got["chain"] = host(w)
+        d = L.dot_product(t, t)                                     # another reader
+        cp = L.mv_deep_copy(t)
+        got["copy"] = host(cp)
+        assert L.sv_mult(s2, rc, C.byref(t)) == 0
+        L.cgb200_free_all(rc)                                       # the source goes away
+        got["src_freed"] = host(t)
+        assert L.sv_mult(s1, ra, C.byref(t)) == 0
+        assert L.vec_sub(ra, t, C.byref(ra)) == 0                   # in place on the first operand
+        got["in_place"] = host(ra)
+        assert L.sv_mult(s1, ra, C.byref(t)) == 0                   # left deferred at the mode switch
+    finally:
+        assert L.cgb200_set_mode(pkg.EAGER) == 0
+    got["left_deferred"] = _take(t, n)
+    for o in (ra, t, u, w, cp):
+        L.cgb200_free_all(o)
+    for v in (va, vc):
+        L.cgb200_invalidate(C.byref(v))
+    sa = s1 * a
+    want = {"add": c + sa, "t_after_use": sa, "sub_into_t": c - sa, "t_before_src_write": sa, "ra_sum": a + c}
+    ra1 = a + c
+    want["out_is_src"] = c + s2 * ra1
+    ra2 = want["out_is_src"]
+    want["t_after_out_is_src"] = s2 * ra1
+    want["chain"] = s1 * (s2 * c)
+    want["copy"] = s1 * c
+    want["src_freed"] = s2 * c
+    want["in_place"] = ra2 - s1 * ra2
+    want["left_deferred"] = s1 * want["in_place"]
+    for k, v in want.items():
+        assert np.array_equal(_bits(got[k]), _bits(v)), k
+    ref = _vec(pkg, want["copy"])                                   # eager dot of the same values
+    assert _bits(np.array([d]))[0] == _bits(np.array([L.dot_product(C.byref(ref), C.byref(ref))]))[0]
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("mode", ["eager", "resident"])
 @pytest.mark.parametrize("mk", [lambda: H.lap(40, 23), lambda: H.dense(130), lambda: H.lap(9, 8, 7)])
 def test_mv_mult_writes_straight_into_the_output_vector(pkg, gpu_lib, mk, mode):
