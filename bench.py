@@ -585,6 +585,7 @@ def main():
     ap.add_argument("--no-extras", action="store_true", help="skip the other BASELINE configs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-tts", action="store_true", help="skip the time-to-solution solves (profiling runs)")
     ap.add_argument("--cpu-leg", action="store_true", help="internal: print the cpu_baseline object only")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -658,8 +659,9 @@ def main():
     }
     J = runner.J
     try:
-        line["time_to_solution"] = time_to_solution(pkg, d, info, world, variant,
-                                                    fixed=500 if args.workload == "lap3d384w" else None)
+        if not args.no_tts:
+            line["time_to_solution"] = time_to_solution(pkg, d, info, world, variant,
+                                                        fixed=500 if args.workload == "lap3d384w" else None)
     except Exception as e:  # noqa: BLE001
         line["time_to_solution"] = {"error": repr(e)}
     # the other recurrence on the same system, same K (explains, does not replace, the headline)
@@ -707,8 +709,9 @@ def main():
                       "config": workload_config(nm, world)}
                 ex["roofline"] = roofline_for(pkg, dx, peak, peak_src, "k_spmv_stream", nm, world)
                 try:
-                    ex["time_to_solution"] = time_to_solution(pkg, dx, ix, world, variant,
-                                                              fixed=500 if nm == "lap3d384w" else None)
+                    if not args.no_tts:
+                        ex["time_to_solution"] = time_to_solution(pkg, dx, ix, world, variant,
+                                                                  fixed=500 if nm == "lap3d384w" else None)
                 except Exception as e:  # noqa: BLE001
                     ex["time_to_solution"] = {"error": repr(e)}
                 ry = Runner(pkg, dx, ix, 1 - variant)

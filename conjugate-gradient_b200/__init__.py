@@ -132,6 +132,8 @@ def lib():
     L.cgb200_last_error.restype = C.c_char_p
     L.cgb200_launch_count.restype = C.c_longlong
     L.cgb200_device_available.restype = C.c_int
+    L.cgb200_read_system.argtypes = [C.c_char_p, MvSparseP, MvSparseP]
+    L.cgb200_write_system.argtypes = [C.c_char_p, MvSparseP, MvSparseP, C.c_int]
     L.cgb200_guard_check.restype = C.c_longlong
     L.cgb200_guard_check.argtypes = []
     L.cgb200_guard_selftest.restype = C.c_int

@@ -9,7 +9,7 @@
  * the reference prints ("CG took approx N seconds", then print_sparse(x)).  Differences, all
  * deliberate: a file that cannot be opened or parsed is an error (the reference ignores the
  * reader's return code and iterates on empty structs, cg.c:65); a missing final newline and tokens
- * of any length are accepted (the reference never terminates / overruns its 64-byte token buffer);
+ * of any length are accepted, and the file is parsed by several threads (cgb200_read_system) (the reference never terminates / overruns its 64-byte token buffer);
  * `suppress-output` starting with 'y' really suppresses the vector (the reference parses it and
  * then ignores it, cg.c:56-57,78).
  *
@@ -23,6 +23,9 @@
  *     --pattern          store stencil-like matrices as one byte per row (row-pattern dictionary
  *                        format; same arithmetic, fewer bytes) when the matrix qualifies
  *     --jacobi           diagonal (Jacobi) preconditioner (classic recurrence only)
+ *     --dump FILE        write the system in the reference's text format before solving (a --gen
+ *                        system becomes an input file the unmodified reference can read);
+ *     --dump-binary FILE the same as the binary sidecar cgb200_read_system also accepts
  */
 #include <errno.h>
 #include <stdint.h>
@@ -35,83 +38,14 @@
 
 #include "cgb200.h"
 
-/* ---- growable arrays ---------------------------------------------------------------------- */
-typedef struct { int *v; size_t n, cap; } ivec;
-typedef struct { double *v; size_t n, cap; } dvec;
-
-static int ipush(ivec *a, int x) {
-  if (a->n == a->cap) {
-    size_t nc = a->cap ? a->cap * 2 : 1u << 16;
-    int *nv = (int *)realloc(a->v, nc * sizeof(int));
-    if (!nv) return -1;
-    a->v = nv; a->cap = nc;
-  }
-  a->v[a->n++] = x;
-  return 0;
-}
-static int dpush(dvec *a, double x) {
-  if (a->n == a->cap) {
-    size_t nc = a->cap ? a->cap * 2 : 1u << 16;
-    double *nv = (double *)realloc(a->v, nc * sizeof(double));
-    if (!nv) return -1;
-    a->v = nv; a->cap = nc;
-  }
-  a->v[a->n++] = x;
-  return 0;
-}
-
-/* Reads the 4-line text format into A and b.  0 on success, -1 with a message on stderr. */
+/* Reads the 4-line text format (or the binary sidecar) into A and b through the library's reader
+ * (csrc/sysio.cpp, the replacement of the reference's read_input_file, cg.c:146-218).
+ * 0 on success, -1 with a message on stderr. */
 static int read_system(const char *path, struct __mv_sparse *A, struct __mv_sparse *b) {
-  FILE *fp = fopen(path, "r");
-  if (!fp) {
-    fprintf(stderr, "Error: Failed to open input file (%s): %s\n", path, strerror(errno));
+  if (cgb200_read_system(path, A, b) != 0) {
+    fprintf(stderr, "Error: %s\n", cgb200_last_error());
     return -1;
   }
-  ivec cols = {0}, rp = {0};
-  dvec vals = {0}, rhs = {0};
-  char tok[512];
-  size_t tl = 0;
-  int line = 0, c, bad = 0;
-  for (;;) {
-    c = fgetc(fp);
-    if (c == ',' || c == '\n' || c == EOF) {
-      if (tl > 0 || c == ',') {
-        char *end = NULL;
-        tok[tl] = 0;
-        switch (line) {
-          case 0: bad |= ipush(&cols, (int)strtol(tok, &end, 10)); break;
-          case 1: bad |= ipush(&rp, (int)strtol(tok, &end, 10)); break;
-          case 2: bad |= dpush(&vals, strtod(tok, &end)); break;
-          case 3: bad |= dpush(&rhs, strtod(tok, &end)); break;
-          default: break;
-        }
-        if (end == tok) bad = 1; /* empty or non-numeric token */
-      }
-      tl = 0;
-      if (c == '\n') ++line;
-      if (c == EOF || line == 4) break;
-    } else if (c != '\r' && c != ' ' && c != '\t') {
-      if (tl + 1 >= sizeof(tok)) { bad = 1; break; }
-      tok[tl++] = (char)c;
-    }
-  }
-  fclose(fp);
-  if (bad || rp.n < 1 || cols.n != vals.n || rhs.n != rp.n - 1 || (size_t)rp.v[rp.n - 1] != vals.n) {
-    fprintf(stderr, "Error: malformed input (%s): %zu column indices, %zu row pointers, %zu values, %zu rhs entries\n",
-            path, cols.n, rp.n, vals.n, rhs.n);
-    free(cols.v); free(rp.v); free(vals.v); free(rhs.v);
-    return -1;
-  }
-  A->size = (int)rp.n - 1; /* cg.c:204 */
-  A->nnz = (int)vals.n;
-  A->values = vals.v;
-  A->col_indices = cols.v;
-  A->row_ptr = rp.v;
-  b->size = (int)rhs.n;
-  b->nnz = (int)rhs.n;
-  b->values = rhs.v;
-  b->col_indices = NULL;
-  b->row_ptr = NULL;
   return 0;
 }
 
@@ -123,6 +57,8 @@ typedef struct {
   double tol;
   int check_every;
   const char *gen;
+  const char *dump;   /* write the system (text format, or binary sidecar) before solving */
+  int dump_binary;
   int gpus;
   int json;
   int variant;
@@ -134,7 +70,8 @@ static void usage(const char *p) {
   fprintf(stderr,
           "Usage: %s <input-data> <max-iterations> [suppress-output]\n"
           "       %s --gen dense:N|lap2d:N|lap3d:N <max-iterations> [--gpus G]\n"
-          "       options: --tol T  --check-every M  --json  --variant classic|sr  --pattern  --jacobi\n", p, p);
+          "       options: --tol T  --check-every M  --json  --variant classic|sr  --pattern  --jacobi\n"
+          "                --dump FILE | --dump-binary FILE   (write the system before solving)\n", p, p);
 }
 
 static int parse(int argc, char **argv, options *o) {
@@ -147,6 +84,8 @@ static int parse(int argc, char **argv, options *o) {
     if (!strcmp(a, "--tol") && i + 1 < argc) o->tol = strtod(argv[++i], NULL);
     else if (!strcmp(a, "--check-every") && i + 1 < argc) o->check_every = atoi(argv[++i]);
     else if (!strcmp(a, "--gen") && i + 1 < argc) o->gen = argv[++i];
+    else if (!strcmp(a, "--dump") && i + 1 < argc) o->dump = argv[++i];
+    else if (!strcmp(a, "--dump-binary") && i + 1 < argc) { o->dump = argv[++i]; o->dump_binary = 1; }
     else if (!strcmp(a, "--gpus") && i + 1 < argc) o->gpus = atoi(argv[++i]);
     else if (!strcmp(a, "--json")) o->json = 1;
     else if (!strcmp(a, "--pattern")) o->pattern = 1;
@@ -216,6 +155,28 @@ static int run_rank(const options *o, int rank, int world, const unsigned char *
     sys = cgb200_system_from_csr(A.size, r0, nl, A.row_ptr + r0, A.col_indices, A.values, b.values + r0);
   }
   if (!sys) { fprintf(stderr, "cg[%d]: %s\n", rank, cgb200_last_error()); return 1; }
+  if (o->dump) {
+    if (world > 1) { fprintf(stderr, "--dump is single-GPU\n"); return 1; }
+    if (o->gen) { /* bring the generated block back as the reference's host structs */
+      const long long n = cgb200_system_rows(sys), nnz = cgb200_system_nnz(sys);
+      A.size = (int)n; A.nnz = (int)nnz;
+      A.values = malloc(sizeof(double) * (nnz > 0 ? nnz : 1));
+      A.col_indices = malloc(sizeof(int) * (nnz > 0 ? nnz : 1));
+      A.row_ptr = malloc(sizeof(int) * (n + 1));
+      b.size = b.nnz = (int)n;
+      b.values = malloc(sizeof(double) * (n > 0 ? n : 1));
+      if (!A.values || !A.col_indices || !A.row_ptr || !b.values ||
+          cgb200_system_download(sys, A.values, A.col_indices, A.row_ptr) != 0 ||
+          cgb200_system_get_b(sys, b.values) != 0) {
+        fprintf(stderr, "cg: --dump: %s\n", cgb200_last_error());
+        return 1;
+      }
+    }
+    if (cgb200_write_system(o->dump, &A, &b, o->dump_binary) != 0) {
+      fprintf(stderr, "cg: --dump: %s\n", cgb200_last_error());
+      return 1;
+    }
+  }
   cgb200_opts opts = {o->max_iter, o->tol, o->variant, o->check_every, o->jacobi ? CGB200_OPT_JACOBI : 0};
   cgb200_result res;
   struct timespec t0, t1;
@@ -282,6 +243,10 @@ int main(int argc, char **argv) {
   struct __mv_sparse *vec_b = new_mv_struct();
   struct __mv_sparse *vec_x = NULL;
   if (read_system(o.input, mat_A, vec_b) != 0) return 1;
+  if (o.dump && cgb200_write_system(o.dump, mat_A, vec_b, o.dump_binary) != 0) {
+    fprintf(stderr, "cg: --dump: %s\n", cgb200_last_error());
+    return 1;
+  }
 
   time_t start = time(NULL);
   int rc;

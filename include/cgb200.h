@@ -193,6 +193,24 @@ int cgb200_timer_stop(double *ms);
 long long cgb200_system_rows(cgb200_system *sys);
 long long cgb200_system_nnz(cgb200_system *sys);
 
+/* ---- systems on disk (host only) ------------------------------------------ */
+/* Replaces read_input_file (reference cg.c:146-218): fills caller-created A and b (new_mv_struct)
+ * from the reference's 4-line comma-separated text format -- line 0 column indices, 1 row
+ * pointers, 2 matrix values, 3 right-hand side; n = row pointers - 1 (cg.c:204) -- or from the
+ * binary sidecar cgb200_write_system(..., 1) produces (recognised by its magic).  The file is
+ * mapped and parsed by several threads (CGB200_IO_THREADS, default: all cores up to 32) into
+ * malloc'ed arrays of the exact size, which the caller owns like the reference's.  Every value has
+ * the bits the reference's strtol/strtod give it.  Unlike the reference (whose return code main
+ * ignores, cg.c:65, and whose reader spins forever on a file without a final newline): 0 / -1 with
+ * cgb200_last_error(); a missing final newline, CR LF and blanks around tokens are accepted; an
+ * empty or non-numeric token, a missing line or inconsistent counts are errors.  Needs no GPU. */
+int cgb200_read_system(const char *path, struct __mv_sparse *A, struct __mv_sparse *b);
+/* Writes A (CSR) and b in the text format above (binary == 0: integers in decimal, reals as the
+ * shortest decimal that reads back to the same bits, so the reference's reader reproduces the
+ * arrays exactly) or as the binary sidecar (binary != 0).  0 / -1. */
+int cgb200_write_system(const char *path, const struct __mv_sparse *A, const struct __mv_sparse *b,
+                        int binary);
+
 /* ---- multi-GPU: one process per GPU, NCCL over NVLink -------------------------------------- */
 /* Rank 0 obtains a 128-byte NCCL unique id and ships it to the other ranks by any means
  * (torch.distributed broadcast in bench.py, a pipe in the cg driver). */

@@ -16,7 +16,7 @@ for spec in "${SPECS[@]}"; do
   ncu -i gpurun_out/prof_${w}_${v}.ncu-rep --page raw --csv > gpurun_out/prof_${w}_${v}_raw.csv 2>/dev/null
   rm -f gpurun_out/prof_${w}_${v}.ncu-rep
 done
-python bench.py --steps 20 --warmup 3 --no-cpu > gpurun_out/bench_for_launchlist.json 2> gpurun_out/bench_for_launchlist.err || echo "plain bench failed"
+python bench.py --steps 20 --warmup 3 --no-cpu --no-tts > gpurun_out/bench_for_launchlist.json 2> gpurun_out/bench_for_launchlist.err || echo "plain bench failed"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv \
-    --log-file gpurun_out/launches_bench.csv python bench.py --steps 20 --warmup 3 --no-cpu > gpurun_out/bench_under_ncu.log 2>&1
+    --log-file gpurun_out/launches_bench.csv python bench.py --steps 20 --warmup 3 --no-cpu --no-tts > gpurun_out/bench_under_ncu.log 2>&1
 echo done

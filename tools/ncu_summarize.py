@@ -135,7 +135,7 @@ if os.path.exists(lp):
         a[1] += t
     tot = sum(a[1] for a in agg.values())
     with open(os.path.join(DST, f"{tag}_launches_bench_summary.md"), "w") as f:
-        f.write(f"# Launch list of `python bench.py --steps 20 --warmup 3 --no-cpu` under `ncu --metrics gpu__time_duration.sum --clock-control none` ({tag})\n\n"
+        f.write(f"# Launch list of `python bench.py --steps 20 --warmup 3 --no-cpu --no-tts` under `ncu --metrics gpu__time_duration.sum --clock-control none` ({tag})\n\n"
                 "Per-launch times are cold-cache and serialised; the kernel's SHARE is what must agree with the bench.\n"
                 "The run covers the headline workload (dense 32768), the end-to-end leg and the other two BASELINE workloads, set-up kernels included.\n\n"
                 "| kernel | launches | total ms | share |\n|---|---|---|---|\n")
