@@ -288,6 +288,191 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
 }
 
 // ---------------------------------------------------------------------------------------------
+// K1-sparse for long rows: a group of G lanes per row (CSR blocks whose mean row length is tens
+// to hundreds of entries -- banded and finite-element matrices, the course matrix of the
+// reference with ~345 entries per row, cg.c:231-232,260).
+//
+// The stream kernel above gives a row to one thread, which is right for stencil rows (all of a
+// row's gathers in flight at once) and wrong for long ones: a 512-row tile of 345-entry rows is
+// 50 pipeline stages, each thread takes ~7 entries per stage, and the launch is bound by the
+// stage hand-over latency (0.35 ms per product on n = 52269, ten times the HBM time).  Here the G
+// lanes of a group load G consecutive entries of their row at a time (values, column indices and
+// the gathered operands of UNR such steps are in flight together), each forms its product, and
+// the products are then added in ascending column order by a chain of G shuffles and adds that
+// every lane of the group executes alike: s[i] has the bits of the reference's left-to-right sum
+// (mv_ops.c:106-110,192-194), as in the stream kernel.  A warp serves 32/G rows, so the chain's
+// instructions are shared by that many rows.  CTAs own contiguous row ranges; one value per row
+// is stored by the group's first lane, which also carries the fused p.s (and p.p) partial sums.
+// Single GPU only (no halo wait): multi-rank systems keep the stream kernel.
+// ---------------------------------------------------------------------------------------------
+
+template <int THREADS, int G, int UNR>
+__global__ void __launch_bounds__(THREADS)
+k_spmv_rowgroup(const double* __restrict__ vals, const int* __restrict__ cols,
+                const int* __restrict__ rowptr, const int nrows, const double* __restrict__ pg,
+                const double* __restrict__ pown, double* __restrict__ s,
+                double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
+                const int mode, const __grid_constant__ PeerComm cm) {
+  constexpr int GROUPS = THREADS / G;  // rows in flight per CTA
+  const int fin = mode & MV_FIN_MASK;
+  const bool rev = (mode & MV_REV) != 0;
+  if (fin != FIN_NONE && S->done) return;
+  const uint64_t pol_keep = policy_evict_last();
+  const int gl = threadIdx.x & (G - 1);  // lane within the group
+  const int grp = threadIdx.x / G;
+  const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << ((threadIdx.x & 31) & ~(G - 1)));
+  const int cta = rev ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
+  const int r0 = (int)((long long)nrows * cta / gridDim.x);
+  const int r1 = (int)((long long)nrows * (cta + 1) / gridDim.x);
+  double dot = 0.0, dot2 = 0.0;
+#pragma unroll 1
+  for (int row = r0 + grp; row < r1; row += GROUPS) {
+    const int rs = __ldg(rowptr + row), re = __ldg(rowptr + row + 1);
+    double acc = 0.0;
+#pragma unroll 1
+    for (int k0 = rs; k0 < re; k0 += G * UNR) {
+      double t[UNR];
+      int c[UNR];
+      double v[UNR];
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const int k = k0 + u * G + gl;
+        const bool ok = k < re;
+        c[u] = ok ? __ldcs(cols + k) : 0;
+        v[u] = ok ? __ldcs(vals + k) : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) t[u] = ld_keep_if(pg + c[u], pol_keep, k0 + u * G + gl < re);
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) t[u] = __dmul_rn(v[u], t[u]);
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const int kb = k0 + u * G;
+#pragma unroll
+        for (int j = 0; j < G; ++j) {
+          const double tj = __shfl_sync(gmask, t[u], j, G);
+          const double a2 = __dadd_rn(acc, tj);
+          acc = (kb + j < re) ? a2 : acc;
+        }
+      }
+    }
+    if (gl == 0) {
+      s[row] = acc;
+      if (fin != FIN_NONE) {
+        const double g = pown[row];
+        dot += g * acc;
+        if (mode & MV_DUAL) dot2 += g * g;
+      }
+    }
+  }
+  if (fin == FIN_NONE) return;
+  double v2[2] = {dot, dot2};
+  bool last;
+  if (mode & MV_DUAL) {
+    last = grid_reduce<THREADS, 2>(v2, partials, ticket);
+  } else {
+    double v1[1] = {dot};
+    last = grid_reduce<THREADS, 1>(v1, partials, ticket);
+    v2[0] = v1[0];
+    v2[1] = 0.0;
+  }
+  if (last) finish_block<THREADS>(S, cm, fin, v2[0], v2[1]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1-sparse for long rows, second form: a warp per block of 32 rows, transposed through shared
+// memory.  The shuffle chain of k_spmv_rowgroup is bound by the shuffle unit (two 32-bit shuffles
+// per entry and group).  Here the warp loads 32 consecutive entries of one row per instruction
+// (256 B of values, 128 B of indices: fully coalesced), for each of its 32 rows in turn, UNR rows'
+// loads and gathers in flight together, and leaves the PRODUCTS in a 32 x 33 tile of shared
+// memory; then lane i adds row i's 32 products in ascending column order straight out of the
+// tile (conflict-free 64-bit reads), all 32 chains running side by side.  Same bits as the
+// reference's left-to-right row sum; about a quarter of an instruction per entry.
+// ---------------------------------------------------------------------------------------------
+
+template <int THREADS, int UNR>
+__global__ void __launch_bounds__(THREADS)
+k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
+                const int* __restrict__ rowptr, const int nrows, const double* __restrict__ pg,
+                const double* __restrict__ pown, double* __restrict__ s,
+                double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
+                const int mode, const __grid_constant__ PeerComm cm) {
+  constexpr int WARPS = THREADS / 32;
+  constexpr int LD = 33;  // tile row stride in doubles: lane i reads bank pair 2i + 2j (mod 32)
+  __shared__ double tile[WARPS][32 * LD];
+  const int fin = mode & MV_FIN_MASK;
+  const bool rev = (mode & MV_REV) != 0;
+  if (fin != FIN_NONE && S->done) return;
+  const uint64_t pol_keep = policy_evict_last();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double* const tw = tile[warp];
+  const int nblk = (nrows + 31) >> 5;
+  const int cta = rev ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
+  const int b0 = (int)((long long)nblk * cta / gridDim.x);
+  const int b1 = (int)((long long)nblk * (cta + 1) / gridDim.x);
+  double dot = 0.0, dot2 = 0.0;
+#pragma unroll 1
+  for (int blk = b0 + warp; blk < b1; blk += WARPS) {
+    const int row = blk * 32 + lane;
+    const bool rv = row < nrows;
+    const int rs = rv ? __ldg(rowptr + row) : 0;
+    const int re = rv ? __ldg(rowptr + row + 1) : 0;
+    const int maxlen = __reduce_max_sync(0xffffffffu, re - rs);
+    double acc = 0.0;
+#pragma unroll 1
+    for (int off = 0; off < maxlen; off += 32) {
+#pragma unroll 1
+      for (int i0 = 0; i0 < 32; i0 += UNR) {
+        int c[UNR];
+        double v[UNR];
+        bool ok[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+          const int k = __shfl_sync(0xffffffffu, rs, i0 + u) + off + lane;
+          ok[u] = k < __shfl_sync(0xffffffffu, re, i0 + u);
+          c[u] = ok[u] ? __ldcs(cols + k) : 0;
+          v[u] = ok[u] ? __ldcs(vals + k) : 0.0;
+        }
+        double t[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) t[u] = ld_keep_if(pg + c[u], pol_keep, ok[u]);
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) tw[(i0 + u) * LD + lane] = __dmul_rn(v[u], t[u]);
+      }
+      __syncwarp();
+      const int left = re - rs - off;  // entries of this lane's row that are in the tile
+      const double* mine = tw + lane * LD;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const double a2 = __dadd_rn(acc, mine[j]);
+        acc = j < left ? a2 : acc;
+      }
+      __syncwarp();
+    }
+    if (rv) {
+      s[row] = acc;
+      if (fin != FIN_NONE) {
+        const double g = pown[row];
+        dot += g * acc;
+        if (mode & MV_DUAL) dot2 += g * g;
+      }
+    }
+  }
+  if (fin == FIN_NONE) return;
+  double v2[2] = {dot, dot2};
+  bool last;
+  if (mode & MV_DUAL) {
+    last = grid_reduce<THREADS, 2>(v2, partials, ticket);
+  } else {
+    double v1[1] = {dot};
+    last = grid_reduce<THREADS, 1>(v1, partials, ticket);
+    v2[0] = v1[0];
+    v2[1] = 0.0;
+  }
+  if (last) finish_block<THREADS>(S, cm, fin, v2[0], v2[1]);
+}
+
+// ---------------------------------------------------------------------------------------------
 // K1-dense: row-block GEMV over values[] only, fused with p.s
 //
 // When every CSR row is full (nnz == n*n, row_ptr[i] == i*n) values[] is a row-major dense
@@ -1725,6 +1910,101 @@ cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, d
            S, mode, g_spmv_hint, cm);
   ++g_launches;
   return cudaGetLastError();
+}
+
+// Mean row length from which a single-GPU CSR block takes a long-row kernel instead of the stream
+// kernel (CGB200_SPMV_ROWGROUP_MIN; 0 = never).  Measured on B200 (tests/rowgroup_sweep.py,
+// profiles/r01f_longrow_sweep.log), matvec time stream / group(G=2) / rowblock(16):
+//   33 entries per row, n = 1e6:    0.076 / 0.125 / 0.120 ms     (stream at 0.84 of the HBM peak)
+//   65 entries per row, n = 4e5:    0.081 / 0.097 / 0.100 ms
+//   345 entries per row, n = 52269: 0.333 / 0.061 / 0.070 ms     (group at 0.55 of the HBM peak)
+// The stream kernel's per-stage hand-over dominates once a 512-row tile needs tens of stages.
+int spmv_rowgroup_min() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("CGB200_SPMV_ROWGROUP_MIN");
+    v = e ? atoi(e) : 128;
+    if (v < 0) v = 0;
+  }
+  return v;
+}
+
+template <int G, int UNR>
+static cudaError_t launch_spmv_rowgroup_cfg(const CsrDev& A, const double* pg, const double* pown,
+                                            double* s, double* partials, unsigned int* ticket,
+                                            CgState* S, int mode, const PeerComm& cm,
+                                            cudaStream_t st) {
+  constexpr int T = 256;
+  static int bps = 0;
+  if (!bps) {
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowgroup<T, G, UNR>, T, 0);
+    if (bps < 1) bps = 1;
+  }
+  const int rows_per_pass = T / G;
+  int grid = sm_count() * bps;
+  const int need = (A.nrows + rows_per_pass - 1) / rows_per_pass;
+  if (grid > need) grid = need;
+  if (grid > MAX_GRID) grid = MAX_GRID;
+  k_spmv_rowgroup<T, G, UNR><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s,
+                                                 partials, ticket, S, mode, cm);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+template <int T, int UNR>
+static cudaError_t launch_spmv_rowblock_cfg(const CsrDev& A, const double* pg, const double* pown,
+                                            double* s, double* partials, unsigned int* ticket,
+                                            CgState* S, int mode, const PeerComm& cm,
+                                            cudaStream_t st) {
+  static int bps = 0;
+  if (!bps) {
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowblock<T, UNR>, T, 0);
+    if (bps < 1) bps = 1;
+  }
+  const int nblk = (A.nrows + 31) / 32;
+  int grid = sm_count() * bps;
+  const int need = (nblk + T / 32 - 1) / (T / 32);
+  if (grid > need) grid = need;
+  if (grid > MAX_GRID) grid = MAX_GRID;
+  k_spmv_rowblock<T, UNR><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s,
+                                              partials, ticket, S, mode, cm);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_spmv_rowgroup(const CsrDev& A, const double* pg, const double* pown, double* s,
+                                 double* partials, unsigned int* ticket, CgState* S, int mode,
+                                 const PeerComm& cm, cudaStream_t st) {
+  if (A.nrows <= 0) return cudaSuccess;
+  // CGB200_SPMV_LONGROW=group (default): the shuffle-chain kernel; block8 / block16 / block32: the
+  // shared-memory transposition with that many rows' loads in flight per warp (kept selectable:
+  // fewer instructions per entry, but one slab at a time per warp leaves its loads unhidden at the
+  // occupancy its tile allows -- a software-pipelined version is the next step for this kernel)
+  static int form = -1;
+  if (form < 0) {
+    const char* e = getenv("CGB200_SPMV_LONGROW");
+    form = !e ? 0 : !strcmp(e, "group") ? 0 : !strcmp(e, "block8") ? 8 : !strcmp(e, "block32") ? 32
+           : !strcmp(e, "block16x2") ? 162 : !strcmp(e, "block16") ? 16 : 0;
+  }
+  if (form == 8) return launch_spmv_rowblock_cfg<128, 8>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+  if (form == 16) return launch_spmv_rowblock_cfg<128, 16>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+  if (form == 32) return launch_spmv_rowblock_cfg<128, 32>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+  if (form == 162) return launch_spmv_rowblock_cfg<64, 16>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+  // lanes per row (CGB200_SPMV_ROWGROUP_G): fewer lanes share the addition chain between more
+  // rows of a warp, more lanes make the loads of a row wider
+  static int g = 0;
+  if (!g) {
+    const char* e = getenv("CGB200_SPMV_ROWGROUP_G");
+    g = e ? atoi(e) : 2;
+    if (g != 2 && g != 4 && g != 8 && g != 16 && g != 32) g = 2;
+  }
+  switch (g) {
+    case 8: return launch_spmv_rowgroup_cfg<8, 4>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+    case 4: return launch_spmv_rowgroup_cfg<4, 8>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+    case 16: return launch_spmv_rowgroup_cfg<16, 2>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+    case 32: return launch_spmv_rowgroup_cfg<32, 1>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+    default: return launch_spmv_rowgroup_cfg<2, 8>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+  }
 }
 
 constexpr int GV_T = 256;

@@ -133,6 +133,12 @@ cudaError_t launch_update_p_pc(double* p, const double* r, const double* dinv, l
 // row 0's diagonal; *bad = rows without a positive finite diagonal
 cudaError_t launch_diag_inv(const CsrDev& A, bool dense, long long ld, long long diag_off,
                             double* dinv, int* bad, cudaStream_t st);
+// CSR matvec with a group of lanes per row, for blocks of long rows on one GPU (bit-identical to
+// launch_spmv); spmv_rowgroup_min() is the mean row length from which solver.cu chooses it.
+cudaError_t launch_spmv_rowgroup(const CsrDev& A, const double* pg, const double* pown, double* s,
+                                 double* partials, unsigned int* ticket, CgState* S, int mode,
+                                 const PeerComm& cm, cudaStream_t st);
+int spmv_rowgroup_min();
 cudaError_t launch_push(const double* p, const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_finish(CgState* S, int which, cudaStream_t st);
 cudaError_t launch_dot(const double* a, const double* b, long long n, double* partials,

@@ -841,6 +841,14 @@ static int enqueue_matvec(System* S, double* out, int fin, bool dual, bool excha
                        md, cm, c.stream);
   };
   if (!multi) {
+    // long rows on one GPU: a group of lanes per row instead of a thread per row (kernels.cu)
+    const int rg = spmv_rowgroup_min();
+    if (S->world == 1 && !S->pat_active && rg > 0 && S->A.nrows > 0 &&
+        S->A.nnz >= (long long)rg * S->A.nrows) {
+      CUDA_OK(launch_spmv_rowgroup(S->A, S->p_ext, S->p_own, out, S->partials, &st->ticket[0], st,
+                                   mode, cm, c.stream));
+      return 0;
+    }
     CUDA_OK(spmv(all_tiles, NO_WAIT, S->partials, mode));
     return 0;
   }

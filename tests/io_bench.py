@@ -4,7 +4,7 @@ course-sized system the reference's reader is pre-sized for (cg.c:231-232,260: a
 non-zeros, n = 52269): a banded SPD matrix, n = 52269, 345 entries per row.  Host only -- runs
 wherever oracle/_ref exists (this container); no GPU.
 
-    python tools/io_bench.py [n half_bandwidth] > profiles/<round>_io_bench.json
+    python tests/io_bench.py [n half_bandwidth] > profiles/<round>_io_bench.json
 
 Checker use of oracle/: the reference reader is the baseline being timed, and its arrays are
 compared bit for bit with the new reader's.

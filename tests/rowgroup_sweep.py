@@ -1,0 +1,43 @@
+"""Matvec kernel time on long-row CSR systems for the long-row kernels (CGB200_SPMV_LONGROW: the
+shuffle-chain k_spmv_rowgroup, the shared-memory k_spmv_rowblock with 8/16/32 rows in flight) and
+for the stream kernel (CGB200_SPMV_ROWGROUP_MIN=0).  One process per
+setting (the setting is read once).  GPU box:   python tests/rowgroup_sweep.py > gpurun_out/rowgroup_sweep.log
+Uses tests/helpers.py (oracle generators) to build the systems: test infrastructure."""
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+SYSTEMS = {"course n=52269 345/row": (52269, 172), "banded n=400000 65/row": (400000, 32),
+           "banded n=1000000 33/row": (1000000, 16)}
+
+if len(sys.argv) > 1 and sys.argv[1] == "one":
+    import __graft_entry__ as g
+    import helpers as H
+
+    pkg = g.load_package()
+    assert pkg.lib().cgb200_init(-1) == 0
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6550.0
+    out = {}
+    for name, (n, hb) in SYSTEMS.items():
+        s = H.banded(n, hb)
+        d = pkg.DeviceSystem.from_csr(s.n, 0, s.row_ptr, s.cols, s.vals, s.b)
+        _, k1 = d.bytes()
+        ms = d.time_kernel(1, 50)
+        r = d.solve(49)
+        out[name] = {"k1_ms": round(ms, 5), "k1_gbs": round(k1 / ms / 1e6, 1), "frac": round(k1 / ms / 1e6 / peak, 3),
+                     "iter_ms": round(r.seconds / r.iterations * 1e3, 5)}
+        d.free()
+    print(json.dumps(out))
+else:
+    cfgs = [("stream", {"CGB200_SPMV_ROWGROUP_MIN": "0"}),
+            ("group G=2", {"CGB200_SPMV_LONGROW": "group", "CGB200_SPMV_ROWGROUP_G": "2"})]
+    cfgs += [(f, {"CGB200_SPMV_LONGROW": f}) for f in ("block8", "block16", "block32", "block16x2")]
+    for label, env in cfgs:
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "one"], env=dict(os.environ, **env),
+                           stdout=subprocess.PIPE, text=True)
+        print(label, r.stdout.strip().splitlines()[-1] if r.stdout.strip() else "failed", flush=True)

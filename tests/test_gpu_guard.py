@@ -53,3 +53,22 @@ def test_gpu_suites_pass_with_guard_bands_and_poisoned_buffers(gpu_lib):
     tail = out.stdout[-3000:]
     assert out.returncode == 0, tail
     assert " passed" in tail and "failed" not in tail, tail
+
+
+@pytest.mark.gpu
+def test_stream_kernel_keeps_its_long_row_coverage(gpu_lib):
+    # single-GPU blocks with a mean row length >= 128 take the group-per-row kernel; multi-rank
+    # systems still run such rows through the stream kernel's chunked-row path, so the same
+    # bit-exactness tests are repeated with the selection switched off -- and once more with the
+    # shared-memory form of the long-row kernel, which is selectable but not the default
+    for extra in ({"CGB200_SPMV_ROWGROUP_MIN": "0"}, {"CGB200_SPMV_LONGROW": "block16", "CGB200_SPMV_ROWGROUP_MIN": "16"}):
+        _long_row_tests(extra)
+
+
+def _long_row_tests(extra):
+    e = dict(os.environ, **extra)
+    out = subprocess.run([sys.executable, "-m", "pytest", "tests/test_gpu_parity.py", "-q", "-x", "-m", "gpu",
+                          "-p", "no:cacheprovider", "-k", "csr_bit_exact or ragged or random_sparse or long_row"],
+                         cwd=ROOT, env=e, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    tail = out.stdout[-3000:]
+    assert out.returncode == 0 and " passed" in tail, tail

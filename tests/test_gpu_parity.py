@@ -214,6 +214,54 @@ def test_mv_mult_ragged_rows_bit_exact(pkg, gpu_lib):
     gpu_lib.cgb200_invalidate(C.byref(A))
 
 
+def test_mv_mult_long_ragged_rows_take_the_group_per_row_kernel_bit_exact(pkg, gpu_lib):
+    # mean row length >= 128 on one GPU: k_spmv_rowgroup (a group of lanes per row, products added in
+    # ascending column order by a shuffle chain).  Empty rows, lengths around the group size and the
+    # unrolled step, and rows of thousands of entries, all mixed
+    rng = np.random.default_rng(15)
+    n = 6000
+    rp, ci = [0], []
+    for i in range(n):
+        k = int(rng.choice([0, 1, 7, 8, 9, 31, 32, 33, 64, 345, 2500], p=[0.05, 0.05, 0.05, 0.05, 0.05, 0.05, 0.1, 0.1, 0.1, 0.3, 0.1]))
+        c = np.sort(rng.choice(n, size=min(k, n), replace=False))
+        ci.extend(c.tolist())
+        rp.append(len(ci))
+    assert len(ci) >= 128 * n                                       # the selection threshold (kernels.cu)
+    va = rng.standard_normal(len(ci))
+    s = H.System(rp, ci, va, np.zeros(n), "long_ragged")
+    A, _ = _structs(pkg, s)
+    want = np.empty(n)
+    for seed in (97, 98):
+        v = H.rhs(n, seed)
+        vv = _vec(pkg, v)
+        out = pkg.MvSparseP()
+        assert gpu_lib.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0, pkg.last_error()
+        H.oracle().oracle_spmv(n, H.iptr(s.row_ptr), H.iptr(s.cols), H.dptr(s.vals), H.dptr(v), H.dptr(want))
+        assert np.array_equal(_bits(_take(out, n)), _bits(want))
+    gpu_lib.cgb200_invalidate(C.byref(A))
+
+
+@pytest.mark.parametrize("variant", ["classic", "sr"])
+def test_long_row_system_solves_match_oracle(pkg, gpu_lib, variant):
+    # a scaled-down course matrix (banded, 201 entries per row): fused p.s of the group-per-row kernel
+    s = H.banded(4000, 100)
+    d = _dev(pkg, s)
+    if variant == "classic":
+        xo, it, _, _ = H.oracle_cg(s, 12)
+        r = d.solve(12)
+    else:
+        xo, it, _, _ = H.oracle_cg_sr(s, 12)
+        r = d.solve(12, variant=pkg.SINGLE_REDUCTION)
+    x = d.x()
+    assert r.iterations == it
+    assert np.linalg.norm(x - xo) <= TOL_X * np.linalg.norm(xo)
+    v = H.rhs(s.n, 3)
+    want = np.empty(s.n)
+    H.oracle().oracle_spmv(s.n, H.iptr(s.row_ptr), H.iptr(s.cols), H.dptr(s.vals), H.dptr(v), H.dptr(want))
+    assert np.array_equal(_bits(d.matvec(v)), _bits(want))
+    d.free()
+
+
 def _random_spd(rng, n, avg, symmetric=True):
     """Random sparse symmetric strictly diagonally dominant matrix (SPD), sorted unique columns per
     row, irreducible through a chain i -- i+1 (so the reference's row scan cannot bleed)."""
