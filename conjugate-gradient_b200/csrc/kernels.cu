@@ -381,16 +381,18 @@ k_spmv_rowgroup(const double* __restrict__ vals, const int* __restrict__ cols,
 
 // ---------------------------------------------------------------------------------------------
 // K1-sparse for long rows, second form: a warp per block of 32 rows, transposed through shared
-// memory.  The shuffle chain of k_spmv_rowgroup is bound by the shuffle unit (two 32-bit shuffles
-// per entry and group).  Here the warp loads 32 consecutive entries of one row per instruction
-// (256 B of values, 128 B of indices: fully coalesced), for each of its 32 rows in turn, UNR rows'
-// loads and gathers in flight together, and leaves the PRODUCTS in a 32 x 33 tile of shared
-// memory; then lane i adds row i's 32 products in ascending column order straight out of the
-// tile (conflict-free 64-bit reads), all 32 chains running side by side.  Same bits as the
-// reference's left-to-right row sum; about a quarter of an instruction per entry.
+// memory.  The shuffle chain of k_spmv_rowgroup is bound by the shuffle unit for wide groups and
+// by the number of memory lines a load instruction touches for narrow ones.  Here the warp loads
+// 32 consecutive entries of ONE row per instruction (256 B of values, 128 B of indices: fully
+// coalesced), for each of its 32 rows in turn, and leaves the PRODUCTS in a 32 x 33 tile of
+// shared memory; then lane i adds row i's 32 products in ascending column order straight out of
+// the tile (conflict-free 64-bit reads), all 32 chains side by side.  Same bits as the
+// reference's left-to-right row sum; about a quarter of an instruction per entry.  The indices
+// and values of the NEXT 32-column slab are fetched into registers before the chain of the
+// current one runs, so the DRAM latency of a slab hides behind the additions of the previous one.
 // ---------------------------------------------------------------------------------------------
 
-template <int THREADS, int UNR>
+template <int THREADS>
 __global__ void __launch_bounds__(THREADS)
 k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
                 const int* __restrict__ rowptr, const int nrows, const double* __restrict__ pg,
@@ -419,27 +421,39 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
     const int re = rv ? __ldg(rowptr + row + 1) : 0;
     const int maxlen = __reduce_max_sync(0xffffffffu, re - rs);
     double acc = 0.0;
+    int c[32];
+    double v[32];
+    unsigned ok = 0u;  // bit i: this lane holds an entry of row i in the slab in registers
+    // slab 0 into registers
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const int k = __shfl_sync(0xffffffffu, rs, i) + lane;
+      const bool o = k < __shfl_sync(0xffffffffu, re, i);
+      ok |= (o ? 1u : 0u) << i;
+      c[i] = o ? __ldcs(cols + k) : 0;
+      v[i] = o ? __ldcs(vals + k) : 0.0;
+    }
 #pragma unroll 1
     for (int off = 0; off < maxlen; off += 32) {
-#pragma unroll 1
-      for (int i0 = 0; i0 < 32; i0 += UNR) {
-        int c[UNR];
-        double v[UNR];
-        bool ok[UNR];
+      // products of the slab in registers -> tile
+      double t[32];
 #pragma unroll
-        for (int u = 0; u < UNR; ++u) {
-          const int k = __shfl_sync(0xffffffffu, rs, i0 + u) + off + lane;
-          ok[u] = k < __shfl_sync(0xffffffffu, re, i0 + u);
-          c[u] = ok[u] ? __ldcs(cols + k) : 0;
-          v[u] = ok[u] ? __ldcs(vals + k) : 0.0;
-        }
-        double t[UNR];
+      for (int i = 0; i < 32; ++i) t[i] = ld_keep_if(pg + c[i], pol_keep, (ok >> i) & 1u);
 #pragma unroll
-        for (int u = 0; u < UNR; ++u) t[u] = ld_keep_if(pg + c[u], pol_keep, ok[u]);
-#pragma unroll
-        for (int u = 0; u < UNR; ++u) tw[(i0 + u) * LD + lane] = __dmul_rn(v[u], t[u]);
-      }
+      for (int i = 0; i < 32; ++i) tw[i * LD + lane] = __dmul_rn(v[i], t[i]);
       __syncwarp();
+      // next slab's indices and values on their way while this slab is added up
+      ok = 0u;
+      if (off + 32 < maxlen) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int k = __shfl_sync(0xffffffffu, rs, i) + off + 32 + lane;
+          const bool o = k < __shfl_sync(0xffffffffu, re, i);
+          ok |= (o ? 1u : 0u) << i;
+          c[i] = o ? __ldcs(cols + k) : 0;
+          v[i] = o ? __ldcs(vals + k) : 0.0;
+        }
+      }
       const int left = re - rs - off;  // entries of this lane's row that are in the tile
       const double* mine = tw + lane * LD;
 #pragma unroll
@@ -1914,10 +1928,10 @@ cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, d
 
 // Mean row length from which a single-GPU CSR block takes a long-row kernel instead of the stream
 // kernel (CGB200_SPMV_ROWGROUP_MIN; 0 = never).  Measured on B200 (tests/rowgroup_sweep.py,
-// profiles/r01f_longrow_sweep.log), matvec time stream / group(G=2) / rowblock(16):
+// profiles/r01f_longrow_sweep.log), matvec time stream / group(G=2) / rowblock:
 //   33 entries per row, n = 1e6:    0.076 / 0.125 / 0.120 ms     (stream at 0.84 of the HBM peak)
 //   65 entries per row, n = 4e5:    0.081 / 0.097 / 0.100 ms
-//   345 entries per row, n = 52269: 0.333 / 0.061 / 0.070 ms     (group at 0.55 of the HBM peak)
+//   345 entries per row, n = 52269: 0.333 / 0.061 / 0.065 ms     (group at 0.55 of the HBM peak)
 // The stream kernel's per-stage hand-over dominates once a 512-row tile needs tens of stages.
 int spmv_rowgroup_min() {
   static int v = -1;
@@ -1929,12 +1943,11 @@ int spmv_rowgroup_min() {
   return v;
 }
 
-template <int G, int UNR>
+template <int T, int G, int UNR>
 static cudaError_t launch_spmv_rowgroup_cfg(const CsrDev& A, const double* pg, const double* pown,
                                             double* s, double* partials, unsigned int* ticket,
                                             CgState* S, int mode, const PeerComm& cm,
                                             cudaStream_t st) {
-  constexpr int T = 256;
   static int bps = 0;
   if (!bps) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowgroup<T, G, UNR>, T, 0);
@@ -1951,14 +1964,14 @@ static cudaError_t launch_spmv_rowgroup_cfg(const CsrDev& A, const double* pg, c
   return cudaGetLastError();
 }
 
-template <int T, int UNR>
+template <int T>
 static cudaError_t launch_spmv_rowblock_cfg(const CsrDev& A, const double* pg, const double* pown,
                                             double* s, double* partials, unsigned int* ticket,
                                             CgState* S, int mode, const PeerComm& cm,
                                             cudaStream_t st) {
   static int bps = 0;
   if (!bps) {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowblock<T, UNR>, T, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowblock<T>, T, 0);
     if (bps < 1) bps = 1;
   }
   const int nblk = (A.nrows + 31) / 32;
@@ -1966,8 +1979,8 @@ static cudaError_t launch_spmv_rowblock_cfg(const CsrDev& A, const double* pg, c
   const int need = (nblk + T / 32 - 1) / (T / 32);
   if (grid > need) grid = need;
   if (grid > MAX_GRID) grid = MAX_GRID;
-  k_spmv_rowblock<T, UNR><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s,
-                                              partials, ticket, S, mode, cm);
+  k_spmv_rowblock<T><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s, partials,
+                                         ticket, S, mode, cm);
   ++g_launches;
   return cudaGetLastError();
 }
@@ -1976,35 +1989,43 @@ cudaError_t launch_spmv_rowgroup(const CsrDev& A, const double* pg, const double
                                  double* partials, unsigned int* ticket, CgState* S, int mode,
                                  const PeerComm& cm, cudaStream_t st) {
   if (A.nrows <= 0) return cudaSuccess;
-  // CGB200_SPMV_LONGROW=group (default): the shuffle-chain kernel; block8 / block16 / block32: the
-  // shared-memory transposition with that many rows' loads in flight per warp (kept selectable:
-  // fewer instructions per entry, but one slab at a time per warp leaves its loads unhidden at the
-  // occupancy its tile allows -- a software-pipelined version is the next step for this kernel)
+  // CGB200_SPMV_LONGROW: group = the shuffle-chain kernel, block / block64 = the shared-memory
+  // transposition with 4 / 2 warps per CTA
   static int form = -1;
   if (form < 0) {
     const char* e = getenv("CGB200_SPMV_LONGROW");
-    form = !e ? 0 : !strcmp(e, "group") ? 0 : !strcmp(e, "block8") ? 8 : !strcmp(e, "block32") ? 32
-           : !strcmp(e, "block16x2") ? 162 : !strcmp(e, "block16") ? 16 : 0;
+    form = !e ? 0 : !strcmp(e, "group") ? 0 : !strcmp(e, "block64") ? 64 : !strncmp(e, "block", 5) ? 128 : 0;
   }
-  if (form == 8) return launch_spmv_rowblock_cfg<128, 8>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
-  if (form == 16) return launch_spmv_rowblock_cfg<128, 16>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
-  if (form == 32) return launch_spmv_rowblock_cfg<128, 32>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
-  if (form == 162) return launch_spmv_rowblock_cfg<64, 16>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
-  // lanes per row (CGB200_SPMV_ROWGROUP_G): fewer lanes share the addition chain between more
-  // rows of a warp, more lanes make the loads of a row wider
-  static int g = 0;
-  if (!g) {
+  if (form == 128) return launch_spmv_rowblock_cfg<128>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+  if (form == 64) return launch_spmv_rowblock_cfg<64>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+  // lanes per row, entries per lane in flight, threads per CTA (CGB200_SPMV_ROWGROUP_G = "G,UNR,T"):
+  // fewer lanes share the addition chain between more rows of a warp, more lanes make the loads
+  // of a row wider and give a small matrix more threads
+  static int cfg = -1;
+  if (cfg < 0) {
+    int g = 2, u = 8, t = 256;
     const char* e = getenv("CGB200_SPMV_ROWGROUP_G");
-    g = e ? atoi(e) : 2;
-    if (g != 2 && g != 4 && g != 8 && g != 16 && g != 32) g = 2;
+    if (e) sscanf(e, "%d,%d,%d", &g, &u, &t);
+    cfg = g * 10000 + u * 1000 + t;
   }
-  switch (g) {
-    case 8: return launch_spmv_rowgroup_cfg<8, 4>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
-    case 4: return launch_spmv_rowgroup_cfg<4, 8>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
-    case 16: return launch_spmv_rowgroup_cfg<16, 2>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
-    case 32: return launch_spmv_rowgroup_cfg<32, 1>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
-    default: return launch_spmv_rowgroup_cfg<2, 8>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+#define RG_CASE(G, U, T)   \
+  case G * 10000 + U * 1000 + T: \
+    return launch_spmv_rowgroup_cfg<T, G, U>(A, pg, pown, s, partials, ticket, S, mode, cm, st)
+  switch (cfg) {
+    RG_CASE(2, 16, 128);
+    RG_CASE(2, 16, 256);
+    RG_CASE(2, 8, 128);
+    RG_CASE(4, 8, 128);
+    RG_CASE(4, 8, 256);
+    RG_CASE(4, 16, 128);
+    RG_CASE(8, 4, 256);
+    RG_CASE(8, 8, 128);
+    RG_CASE(16, 2, 256);
+    RG_CASE(32, 1, 256);
+    default: break;
   }
+#undef RG_CASE
+  return launch_spmv_rowgroup_cfg<256, 2, 8>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
 }
 
 constexpr int GV_T = 256;

@@ -1,5 +1,5 @@
 """Matvec kernel time on long-row CSR systems for the long-row kernels (CGB200_SPMV_LONGROW: the
-shuffle-chain k_spmv_rowgroup, the shared-memory k_spmv_rowblock with 8/16/32 rows in flight) and
+shuffle-chain k_spmv_rowgroup, the shared-memory k_spmv_rowblock with 4 or 2 warps per CTA) and
 for the stream kernel (CGB200_SPMV_ROWGROUP_MIN=0).  One process per
 setting (the setting is read once).  GPU box:   python tests/rowgroup_sweep.py > gpurun_out/rowgroup_sweep.log
 Uses tests/helpers.py (oracle generators) to build the systems: test infrastructure."""
@@ -23,7 +23,10 @@ if len(sys.argv) > 1 and sys.argv[1] == "one":
     assert pkg.lib().cgb200_init(-1) == 0
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6550.0
     out = {}
+    only = sys.argv[2] if len(sys.argv) > 2 else ""   # e.g. "course": one system (ncu captures)
     for name, (n, hb) in SYSTEMS.items():
+        if only and not name.startswith(only):
+            continue
         s = H.banded(n, hb)
         d = pkg.DeviceSystem.from_csr(s.n, 0, s.row_ptr, s.cols, s.vals, s.b)
         _, k1 = d.bytes()
@@ -34,10 +37,11 @@ if len(sys.argv) > 1 and sys.argv[1] == "one":
         d.free()
     print(json.dumps(out))
 else:
-    cfgs = [("stream", {"CGB200_SPMV_ROWGROUP_MIN": "0"}),
-            ("group G=2", {"CGB200_SPMV_LONGROW": "group", "CGB200_SPMV_ROWGROUP_G": "2"})]
-    cfgs += [(f, {"CGB200_SPMV_LONGROW": f}) for f in ("block8", "block16", "block32", "block16x2")]
+    only = sys.argv[1] if len(sys.argv) > 1 else ""
+    cfgs = [(f"group {c}", {"CGB200_SPMV_LONGROW": "group", "CGB200_SPMV_ROWGROUP_G": c, "CGB200_SPMV_ROWGROUP_MIN": "16"})
+            for c in ("2,8,256", "2,16,256", "2,16,128", "2,8,128", "4,8,128", "4,8,256", "4,16,128", "8,8,128")]
+    cfgs += [("block", {"CGB200_SPMV_LONGROW": "block", "CGB200_SPMV_ROWGROUP_MIN": "16"}), ("stream", {"CGB200_SPMV_ROWGROUP_MIN": "0"})]
     for label, env in cfgs:
-        r = subprocess.run([sys.executable, os.path.abspath(__file__), "one"], env=dict(os.environ, **env),
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "one", only], env=dict(os.environ, **env),
                            stdout=subprocess.PIPE, text=True)
         print(label, r.stdout.strip().splitlines()[-1] if r.stdout.strip() else "failed", flush=True)

@@ -61,7 +61,7 @@ def test_stream_kernel_keeps_its_long_row_coverage(gpu_lib):
     # systems still run such rows through the stream kernel's chunked-row path, so the same
     # bit-exactness tests are repeated with the selection switched off -- and once more with the
     # shared-memory form of the long-row kernel, which is selectable but not the default
-    for extra in ({"CGB200_SPMV_ROWGROUP_MIN": "0"}, {"CGB200_SPMV_LONGROW": "block16", "CGB200_SPMV_ROWGROUP_MIN": "16"}):
+    for extra in ({"CGB200_SPMV_ROWGROUP_MIN": "0"}, {"CGB200_SPMV_LONGROW": "block", "CGB200_SPMV_ROWGROUP_MIN": "16"}):
         _long_row_tests(extra)
 
 
