@@ -392,41 +392,44 @@ k_spmv_rowgroup(const double* __restrict__ vals, const int* __restrict__ cols,
 // current one runs, so the DRAM latency of a slab hides behind the additions of the previous one.
 // ---------------------------------------------------------------------------------------------
 
-template <int THREADS>
+template <int THREADS, int ROWS>
 __global__ void __launch_bounds__(THREADS)
 k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
                 const int* __restrict__ rowptr, const int nrows, const double* __restrict__ pg,
                 const double* __restrict__ pown, double* __restrict__ s,
                 double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
                 const int mode, const __grid_constant__ PeerComm cm) {
+  // ROWS rows per warp and work unit (lane i < ROWS owns row i of the unit): fewer rows mean
+  // fewer registers for the prefetched slab, hence more warps per SM, and finer units -- both
+  // matter while a unit's time is set by latencies rather than by its bytes
   constexpr int WARPS = THREADS / 32;
   constexpr int LD = 33;  // tile row stride in doubles: lane i reads bank pair 2i + 2j (mod 32)
-  __shared__ double tile[WARPS][32 * LD];
+  __shared__ double tile[WARPS][ROWS * LD];
   const int fin = mode & MV_FIN_MASK;
   const bool rev = (mode & MV_REV) != 0;
   if (fin != FIN_NONE && S->done) return;
   const uint64_t pol_keep = policy_evict_last();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double* const tw = tile[warp];
-  const int nblk = (nrows + 31) >> 5;
+  const int nblk = (nrows + ROWS - 1) / ROWS;
   const int cta = rev ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
   const int b0 = (int)((long long)nblk * cta / gridDim.x);
   const int b1 = (int)((long long)nblk * (cta + 1) / gridDim.x);
   double dot = 0.0, dot2 = 0.0;
 #pragma unroll 1
   for (int blk = b0 + warp; blk < b1; blk += WARPS) {
-    const int row = blk * 32 + lane;
-    const bool rv = row < nrows;
+    const int row = blk * ROWS + lane;
+    const bool rv = lane < ROWS && row < nrows;
     const int rs = rv ? __ldg(rowptr + row) : 0;
     const int re = rv ? __ldg(rowptr + row + 1) : 0;
     const int maxlen = __reduce_max_sync(0xffffffffu, re - rs);
     double acc = 0.0;
-    int c[32];
-    double v[32];
+    int c[ROWS];
+    double v[ROWS];
     unsigned ok = 0u;  // bit i: this lane holds an entry of row i in the slab in registers
     // slab 0 into registers
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
+    for (int i = 0; i < ROWS; ++i) {
       const int k = __shfl_sync(0xffffffffu, rs, i) + lane;
       const bool o = k < __shfl_sync(0xffffffffu, re, i);
       ok |= (o ? 1u : 0u) << i;
@@ -436,17 +439,17 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
 #pragma unroll 1
     for (int off = 0; off < maxlen; off += 32) {
       // products of the slab in registers -> tile
-      double t[32];
+      double t[ROWS];
 #pragma unroll
-      for (int i = 0; i < 32; ++i) t[i] = ld_keep_if(pg + c[i], pol_keep, (ok >> i) & 1u);
+      for (int i = 0; i < ROWS; ++i) t[i] = ld_keep_if(pg + c[i], pol_keep, (ok >> i) & 1u);
 #pragma unroll
-      for (int i = 0; i < 32; ++i) tw[i * LD + lane] = __dmul_rn(v[i], t[i]);
+      for (int i = 0; i < ROWS; ++i) tw[i * LD + lane] = __dmul_rn(v[i], t[i]);
       __syncwarp();
       // next slab's indices and values on their way while this slab is added up
       ok = 0u;
       if (off + 32 < maxlen) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
+        for (int i = 0; i < ROWS; ++i) {
           const int k = __shfl_sync(0xffffffffu, rs, i) + off + 32 + lane;
           const bool o = k < __shfl_sync(0xffffffffu, re, i);
           ok |= (o ? 1u : 0u) << i;
@@ -454,12 +457,14 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
           v[i] = o ? __ldcs(vals + k) : 0.0;
         }
       }
-      const int left = re - rs - off;  // entries of this lane's row that are in the tile
-      const double* mine = tw + lane * LD;
+      if (lane < ROWS) {
+        const int left = re - rs - off;  // entries of this lane's row that are in the tile
+        const double* mine = tw + lane * LD;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const double a2 = __dadd_rn(acc, mine[j]);
-        acc = j < left ? a2 : acc;
+        for (int j = 0; j < 32; ++j) {
+          const double a2 = __dadd_rn(acc, mine[j]);
+          acc = j < left ? a2 : acc;
+        }
       }
       __syncwarp();
     }
@@ -1928,16 +1933,16 @@ cudaError_t launch_spmv(const CsrDev& A, const double* pg, const double* pown, d
 
 // Mean row length from which a single-GPU CSR block takes a long-row kernel instead of the stream
 // kernel (CGB200_SPMV_ROWGROUP_MIN; 0 = never).  Measured on B200 (tests/rowgroup_sweep.py,
-// profiles/r01f_longrow_sweep.log), matvec time stream / group(G=2) / rowblock:
-//   33 entries per row, n = 1e6:    0.076 / 0.125 / 0.120 ms     (stream at 0.84 of the HBM peak)
-//   65 entries per row, n = 4e5:    0.081 / 0.097 / 0.100 ms
-//   345 entries per row, n = 52269: 0.333 / 0.061 / 0.065 ms     (group at 0.55 of the HBM peak)
+// profiles/r01f_longrow_sweep.log), matvec time stream / group(2 lanes) / row block(16 rows, 256 thr):
+//   33 entries per row, n = 1e6:    0.075 / 0.125 / 0.120 ms     (stream at 0.85 of the HBM peak)
+//   65 entries per row, n = 4e5:    0.080 / 0.097 / 0.078 ms
+//   345 entries per row, n = 52269: 0.333 / 0.061 / 0.049 ms     (row block at 0.67 of the HBM peak)
 // The stream kernel's per-stage hand-over dominates once a 512-row tile needs tens of stages.
 int spmv_rowgroup_min() {
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("CGB200_SPMV_ROWGROUP_MIN");
-    v = e ? atoi(e) : 128;
+    v = e ? atoi(e) : 64;
     if (v < 0) v = 0;
   }
   return v;
@@ -1964,23 +1969,23 @@ static cudaError_t launch_spmv_rowgroup_cfg(const CsrDev& A, const double* pg, c
   return cudaGetLastError();
 }
 
-template <int T>
+template <int T, int ROWS>
 static cudaError_t launch_spmv_rowblock_cfg(const CsrDev& A, const double* pg, const double* pown,
                                             double* s, double* partials, unsigned int* ticket,
                                             CgState* S, int mode, const PeerComm& cm,
                                             cudaStream_t st) {
   static int bps = 0;
   if (!bps) {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowblock<T>, T, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowblock<T, ROWS>, T, 0);
     if (bps < 1) bps = 1;
   }
-  const int nblk = (A.nrows + 31) / 32;
+  const int nblk = (A.nrows + ROWS - 1) / ROWS;
   int grid = sm_count() * bps;
   const int need = (nblk + T / 32 - 1) / (T / 32);
   if (grid > need) grid = need;
   if (grid > MAX_GRID) grid = MAX_GRID;
-  k_spmv_rowblock<T><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s, partials,
-                                         ticket, S, mode, cm);
+  k_spmv_rowblock<T, ROWS><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s,
+                                               partials, ticket, S, mode, cm);
   ++g_launches;
   return cudaGetLastError();
 }
@@ -1989,15 +1994,27 @@ cudaError_t launch_spmv_rowgroup(const CsrDev& A, const double* pg, const double
                                  double* partials, unsigned int* ticket, CgState* S, int mode,
                                  const PeerComm& cm, cudaStream_t st) {
   if (A.nrows <= 0) return cudaSuccess;
-  // CGB200_SPMV_LONGROW: group = the shuffle-chain kernel, block / block64 = the shared-memory
-  // transposition with 4 / 2 warps per CTA
+  // CGB200_SPMV_LONGROW: group = the shuffle-chain kernel; block, block16, block8 (optionally
+  // followed by "x256": threads per CTA) = the shared-memory transposition with 32 / 16 / 8 rows
+  // per warp and work unit
   static int form = -1;
   if (form < 0) {
     const char* e = getenv("CGB200_SPMV_LONGROW");
-    form = !e ? 0 : !strcmp(e, "group") ? 0 : !strcmp(e, "block64") ? 64 : !strncmp(e, "block", 5) ? 128 : 0;
+    form = 1016;  // block16x256 (tests/rowgroup_sweep.py)
+    if (e && !strcmp(e, "group")) form = 0;
+    if (e && !strncmp(e, "block", 5)) {
+      const int rows = atoi(e + 5) > 0 ? atoi(e + 5) : 32;
+      form = (rows == 8 ? 8 : rows == 16 ? 16 : 32) + (strstr(e, "x256") ? 1000 : 0);
+    }
   }
-  if (form == 128) return launch_spmv_rowblock_cfg<128>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
-  if (form == 64) return launch_spmv_rowblock_cfg<64>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
+#define RB_CASE(F, T, R) \
+  if (form == F) return launch_spmv_rowblock_cfg<T, R>(A, pg, pown, s, partials, ticket, S, mode, cm, st)
+  RB_CASE(32, 128, 32);
+  RB_CASE(16, 128, 16);
+  RB_CASE(8, 128, 8);
+  RB_CASE(1016, 256, 16);
+  RB_CASE(1008, 256, 8);
+#undef RB_CASE
   // lanes per row, entries per lane in flight, threads per CTA (CGB200_SPMV_ROWGROUP_G = "G,UNR,T"):
   // fewer lanes share the addition chain between more rows of a warp, more lanes make the loads
   // of a row wider and give a small matrix more threads

@@ -38,9 +38,10 @@ if len(sys.argv) > 1 and sys.argv[1] == "one":
     print(json.dumps(out))
 else:
     only = sys.argv[1] if len(sys.argv) > 1 else ""
-    cfgs = [(f"group {c}", {"CGB200_SPMV_LONGROW": "group", "CGB200_SPMV_ROWGROUP_G": c, "CGB200_SPMV_ROWGROUP_MIN": "16"})
-            for c in ("2,8,256", "2,16,256", "2,16,128", "2,8,128", "4,8,128", "4,8,256", "4,16,128", "8,8,128")]
-    cfgs += [("block", {"CGB200_SPMV_LONGROW": "block", "CGB200_SPMV_ROWGROUP_MIN": "16"}), ("stream", {"CGB200_SPMV_ROWGROUP_MIN": "0"})]
+    cfgs = [("group 2,8,256", {"CGB200_SPMV_LONGROW": "group", "CGB200_SPMV_ROWGROUP_MIN": "16"})]
+    cfgs += [(f, {"CGB200_SPMV_LONGROW": f, "CGB200_SPMV_ROWGROUP_MIN": "16"})
+             for f in ("block", "block16", "block8", "block16x256", "block8x256")]
+    cfgs += [("stream", {"CGB200_SPMV_ROWGROUP_MIN": "0"})]
     for label, env in cfgs:
         r = subprocess.run([sys.executable, os.path.abspath(__file__), "one", only], env=dict(os.environ, **env),
                            stdout=subprocess.PIPE, text=True)

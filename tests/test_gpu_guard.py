@@ -57,11 +57,14 @@ def test_gpu_suites_pass_with_guard_bands_and_poisoned_buffers(gpu_lib):
 
 @pytest.mark.gpu
 def test_stream_kernel_keeps_its_long_row_coverage(gpu_lib):
-    # single-GPU blocks with a mean row length >= 128 take the group-per-row kernel; multi-rank
-    # systems still run such rows through the stream kernel's chunked-row path, so the same
-    # bit-exactness tests are repeated with the selection switched off -- and once more with the
-    # shared-memory form of the long-row kernel, which is selectable but not the default
-    for extra in ({"CGB200_SPMV_ROWGROUP_MIN": "0"}, {"CGB200_SPMV_LONGROW": "block", "CGB200_SPMV_ROWGROUP_MIN": "16"}):
+    # single-GPU blocks with a mean row length >= 64 take the row-block kernel (16 rows per warp);
+    # multi-rank systems still run such rows through the stream kernel's chunked-row path, so the
+    # same bit-exactness tests are repeated with the selection switched off -- and with the other
+    # selectable long-row forms (the shuffle-chain kernel, 32- and 8-row units)
+    for extra in ({"CGB200_SPMV_ROWGROUP_MIN": "0"},
+                  {"CGB200_SPMV_LONGROW": "group", "CGB200_SPMV_ROWGROUP_MIN": "16"},
+                  {"CGB200_SPMV_LONGROW": "block", "CGB200_SPMV_ROWGROUP_MIN": "16"},
+                  {"CGB200_SPMV_LONGROW": "block8", "CGB200_SPMV_ROWGROUP_MIN": "16"}):
         _long_row_tests(extra)
 
 

@@ -214,10 +214,10 @@ def test_mv_mult_ragged_rows_bit_exact(pkg, gpu_lib):
     gpu_lib.cgb200_invalidate(C.byref(A))
 
 
-def test_mv_mult_long_ragged_rows_take_the_group_per_row_kernel_bit_exact(pkg, gpu_lib):
-    # mean row length >= 128 on one GPU: k_spmv_rowgroup (a group of lanes per row, products added in
-    # ascending column order by a shuffle chain).  Empty rows, lengths around the group size and the
-    # unrolled step, and rows of thousands of entries, all mixed
+def test_mv_mult_long_ragged_rows_take_the_long_row_kernel_bit_exact(pkg, gpu_lib):
+    # mean row length >= 64 on one GPU: a long-row kernel (k_spmv_rowblock by default: 16 rows per
+    # warp, products through a shared-memory tile, added in ascending column order).  Empty rows,
+    # lengths around the slab width (32) and rows of thousands of entries, all mixed
     rng = np.random.default_rng(15)
     n = 6000
     rp, ci = [0], []
