@@ -13,6 +13,7 @@ import json
 import os
 import subprocess
 
+import numpy as np
 import pytest
 
 import helpers as H
@@ -107,3 +108,30 @@ def test_cg_driver_pattern_format_and_variant_flags(pkg, gpu_lib):
     assert j["status"] == pkg.CONVERGED and j["relres"] <= 1e-10
     r = subprocess.run([pkg.CG_DRIVER, INPUT, "30", "--variant", "nope"], stderr=subprocess.PIPE, text=True)
     assert r.returncode != 0
+
+
+def test_cg_driver_dump_writes_a_file_the_readers_accept(pkg, gpu_lib, tmp_path):
+    # --gen system -> the reference's text format (and the binary sidecar) -> back through the
+    # library's reader: the arrays of the oracle generator; and the file solves like the generated system
+    import ctypes as C
+
+    s = H.lap(16, 16)
+    txt, binf = tmp_path / "gen.txt", tmp_path / "gen.bin"
+    a = subprocess.run([pkg.CG_DRIVER, "--gen", "lap2d:16", "20", "--dump", str(txt)], stdout=subprocess.PIPE, text=True, check=True).stdout
+    subprocess.run([pkg.CG_DRIVER, "--gen", "lap2d:16", "20", "y", "--dump-binary", str(binf)], stdout=subprocess.PIPE, check=True)
+    L = pkg.lib()
+    for path in (txt, binf):
+        A, b = L.new_mv_struct(), L.new_mv_struct()
+        assert L.cgb200_read_system(str(path).encode(), A, b) == 0, pkg.last_error()
+        ac = A.contents
+        assert ac.size == s.n and ac.nnz == s.nnz
+        assert np.array_equal(np.ctypeslib.as_array(ac.values, shape=(s.nnz,)), s.vals)
+        assert np.array_equal(np.ctypeslib.as_array(ac.col_indices, shape=(s.nnz,)), s.cols)
+        assert np.array_equal(np.ctypeslib.as_array(ac.row_ptr, shape=(s.n + 1,)), s.row_ptr)
+        assert np.array_equal(np.ctypeslib.as_array(b.contents.values, shape=(s.n,)), s.b)
+        L.cgb200_free_all(A)
+        L.cgb200_free_all(b)
+    b_ = subprocess.run([pkg.CG_DRIVER, str(txt), "20"], stdout=subprocess.PIPE, text=True, check=True).stdout
+    xa = [l for l in a.splitlines() if l.startswith("\t") and ":" not in l]      # the printed x (mv_ops.c:92-93)
+    xb = [l for l in b_.splitlines() if l.startswith("\t") and ":" not in l]
+    assert len(xa) == s.n and xa == xb
