@@ -2029,15 +2029,9 @@ cudaError_t launch_spmv_rowgroup(const CsrDev& A, const double* pg, const double
   case G * 10000 + U * 1000 + T: \
     return launch_spmv_rowgroup_cfg<T, G, U>(A, pg, pown, s, partials, ticket, S, mode, cm, st)
   switch (cfg) {
-    RG_CASE(2, 16, 128);
-    RG_CASE(2, 16, 256);
     RG_CASE(2, 8, 128);
-    RG_CASE(4, 8, 128);
     RG_CASE(4, 8, 256);
-    RG_CASE(4, 16, 128);
     RG_CASE(8, 4, 256);
-    RG_CASE(8, 8, 128);
-    RG_CASE(16, 2, 256);
     RG_CASE(32, 1, 256);
     default: break;
   }
