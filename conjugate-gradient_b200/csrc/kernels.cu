@@ -303,7 +303,7 @@ k_spmv_stream(const double* __restrict__ vals, const int* __restrict__ cols,
 // (mv_ops.c:106-110,192-194), as in the stream kernel.  A warp serves 32/G rows, so the chain's
 // instructions are shared by that many rows.  CTAs own contiguous row ranges; one value per row
 // is stored by the group's first lane, which also carries the fused p.s (and p.p) partial sums.
-// Single GPU only (no halo wait): multi-rank systems keep the stream kernel.
+// Single GPU or NCCL mode only (no halo wait in this form).
 // ---------------------------------------------------------------------------------------------
 
 template <int THREADS, int G, int UNR>
@@ -392,13 +392,17 @@ k_spmv_rowgroup(const double* __restrict__ vals, const int* __restrict__ cols,
 // current one runs, so the DRAM latency of a slab hides behind the additions of the previous one.
 // ---------------------------------------------------------------------------------------------
 
-template <int THREADS, int ROWS>
+template <int THREADS, int ROWS, bool COHERENT>
 __global__ void __launch_bounds__(THREADS)
 k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
                 const int* __restrict__ rowptr, const int nrows, const double* __restrict__ pg,
                 const double* __restrict__ pown, double* __restrict__ s,
                 double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
                 const int mode, const __grid_constant__ PeerComm cm) {
+  // COHERENT (several GPUs, peer-memory mode): part of the gather vector is stored by the peers'
+  // direction updates while this kernel may already be running, so every CTA first waits for
+  // their completion flags and the gathers bypass L1.  (The stream kernel overlaps that wait with
+  // its interior tiles; here the whole launch sits behind it.)
   // ROWS rows per warp and work unit (lane i < ROWS owns row i of the unit): fewer rows mean
   // fewer registers for the prefetched slab, hence more warps per SM, and finer units -- both
   // matter while a unit's time is set by latencies rather than by its bytes
@@ -411,6 +415,10 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
   const uint64_t pol_keep = policy_evict_last();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double* const tw = tile[warp];
+  if (COHERENT) {
+    if (threadIdx.x == 0) wait_halo(cm, S);
+    __syncthreads();
+  }
   const int nblk = (nrows + ROWS - 1) / ROWS;
   const int cta = rev ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
   const int b0 = (int)((long long)nblk * cta / gridDim.x);
@@ -441,7 +449,8 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
       // products of the slab in registers -> tile
       double t[ROWS];
 #pragma unroll
-      for (int i = 0; i < ROWS; ++i) t[i] = ld_keep_if(pg + c[i], pol_keep, (ok >> i) & 1u);
+      for (int i = 0; i < ROWS; ++i)
+        t[i] = COHERENT ? ld_l2_if(pg + c[i], (ok >> i) & 1u) : ld_keep_if(pg + c[i], pol_keep, (ok >> i) & 1u);
 #pragma unroll
       for (int i = 0; i < ROWS; ++i) tw[i * LD + lane] = __dmul_rn(v[i], t[i]);
       __syncwarp();
@@ -1969,14 +1978,14 @@ static cudaError_t launch_spmv_rowgroup_cfg(const CsrDev& A, const double* pg, c
   return cudaGetLastError();
 }
 
-template <int T, int ROWS>
+template <int T, int ROWS, bool COH = false>
 static cudaError_t launch_spmv_rowblock_cfg(const CsrDev& A, const double* pg, const double* pown,
                                             double* s, double* partials, unsigned int* ticket,
                                             CgState* S, int mode, const PeerComm& cm,
                                             cudaStream_t st) {
   static int bps = 0;
   if (!bps) {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowblock<T, ROWS>, T, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowblock<T, ROWS, COH>, T, 0);
     if (bps < 1) bps = 1;
   }
   const int nblk = (A.nrows + ROWS - 1) / ROWS;
@@ -1984,10 +1993,18 @@ static cudaError_t launch_spmv_rowblock_cfg(const CsrDev& A, const double* pg, c
   const int need = (nblk + T / 32 - 1) / (T / 32);
   if (grid > need) grid = need;
   if (grid > MAX_GRID) grid = MAX_GRID;
-  k_spmv_rowblock<T, ROWS><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s,
-                                               partials, ticket, S, mode, cm);
+  k_spmv_rowblock<T, ROWS, COH><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s,
+                                                    partials, ticket, S, mode, cm);
   ++g_launches;
   return cudaGetLastError();
+}
+
+// The default long-row kernel behind the peers' completion flags (several GPUs, peer-memory mode).
+cudaError_t launch_spmv_longrow_coherent(const CsrDev& A, const double* pg, const double* pown,
+                                         double* s, double* partials, unsigned int* ticket,
+                                         CgState* S, int mode, const PeerComm& cm, cudaStream_t st) {
+  if (A.nrows <= 0) return cudaSuccess;
+  return launch_spmv_rowblock_cfg<256, 16, true>(A, pg, pown, s, partials, ticket, S, mode, cm, st);
 }
 
 cudaError_t launch_spmv_rowgroup(const CsrDev& A, const double* pg, const double* pown, double* s,

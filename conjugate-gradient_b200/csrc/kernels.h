@@ -139,6 +139,11 @@ cudaError_t launch_spmv_rowgroup(const CsrDev& A, const double* pg, const double
                                  double* partials, unsigned int* ticket, CgState* S, int mode,
                                  const PeerComm& cm, cudaStream_t st);
 int spmv_rowgroup_min();
+// Several GPUs in peer-memory mode: the default long-row kernel, every CTA first waiting for the
+// peers' halo flags, gathers bypassing L1 (the other forms are single-GPU / NCCL-mode only).
+cudaError_t launch_spmv_longrow_coherent(const CsrDev& A, const double* pg, const double* pown,
+                                         double* s, double* partials, unsigned int* ticket,
+                                         CgState* S, int mode, const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_push(const double* p, const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_finish(CgState* S, int which, cudaStream_t st);
 cudaError_t launch_dot(const double* a, const double* b, long long n, double* partials,

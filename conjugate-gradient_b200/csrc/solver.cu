@@ -817,6 +817,20 @@ static const PeerComm& comm_of(const System* S) { return S->p2p ? S->cm : S->cm_
 //   exchange the gather vector's halo / remote blocks take part: in peer-memory mode they were
 //            pushed by the kernel that wrote the vector and this kernel waits for the flags at
 //            its first boundary tile; in NCCL mode the exchange is enqueued here.
+// Multi-rank systems take the long-row matvec too (tools/dist_check.py: neighbour-halo and
+// all-gather systems, both exchange modes); CGB200_SPMV_LONGROW_MULTI=0 keeps them on the stream
+// kernel, whose interior tiles overlap the exchange.
+static bool longrow_multi_ok(const System* S, bool multi) {
+  if (S->world == 1) return true;
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("CGB200_SPMV_LONGROW_MULTI");
+    on = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  (void)multi;
+  return on == 1;
+}
+
 static int enqueue_matvec(System* S, double* out, int fin, bool dual, bool exchange,
                           bool rev = false) {
   Ctx& c = g_ctx;
@@ -840,16 +854,35 @@ static int enqueue_matvec(System* S, double* out, int fin, bool dual, bool excha
     return launch_spmv(S->A, S->p_ext, S->p_own, out, tr, wait_from, partials, &st->ticket[0], st,
                        md, cm, c.stream);
   };
+  // long rows: a warp per unit of 16 rows instead of a thread per row (kernels.cu)
+  const int rg = spmv_rowgroup_min();
+  const bool longrow = !S->pat_active && rg > 0 && S->A.nrows > 0 &&
+                       S->A.nnz >= (long long)rg * S->A.nrows && longrow_multi_ok(S, multi);
   if (!multi) {
-    // long rows on one GPU: a group of lanes per row instead of a thread per row (kernels.cu)
-    const int rg = spmv_rowgroup_min();
-    if (S->world == 1 && !S->pat_active && rg > 0 && S->A.nrows > 0 &&
-        S->A.nnz >= (long long)rg * S->A.nrows) {
+    if (longrow) {
       CUDA_OK(launch_spmv_rowgroup(S->A, S->p_ext, S->p_own, out, S->partials, &st->ticket[0], st,
                                    mode, cm, c.stream));
       return 0;
     }
     CUDA_OK(spmv(all_tiles, NO_WAIT, S->partials, mode));
+    return 0;
+  }
+  if (longrow) {
+    // several GPUs: the whole launch behind the exchange (no interior/boundary split: these
+    // matrices gather from most of the vector anyway)
+    if (S->p2p) {
+      if (cm.nwait > 0)
+        CUDA_OK(launch_spmv_longrow_coherent(S->A, S->p_ext, S->p_own, out, S->partials,
+                                             &st->ticket[0], st, mode, cm, c.stream));
+      else
+        CUDA_OK(launch_spmv_rowgroup(S->A, S->p_ext, S->p_own, out, S->partials, &st->ticket[0],
+                                     st, mode, cm, c.stream));
+      return 0;
+    }
+    if (enqueue_exchange_begin(S)) return -1;
+    if (enqueue_exchange_end(S)) return -1;
+    CUDA_OK(launch_spmv_rowgroup(S->A, S->p_ext, S->p_own, out, S->partials, &st->ticket[0], st,
+                                 mode, cm, c.stream));
     return 0;
   }
   const bool has_interior = !S->allgather && S->tb_hi > S->tb_lo;

@@ -213,7 +213,9 @@ report("dense dynamic tail run-to-run bits", tt.item() == 1.0, "")
 d.free()
 
 # 4) host CSR row blocks, uneven, banded (neighbour mode) and wide band (all-gather fallback)
-for hb, name in ((7, "banded neighbour"), (900, "banded wide")):
+# (hb = 60: 121 entries per row, the long-row matvec kernel behind a neighbour halo; hb = 900 the same
+# kernel in all-gather mode)
+for hb, name in ((7, "banded neighbour"), (60, "banded neighbour long rows"), (900, "banded wide")):
     s = H.banded(3001, hb)
     cnt = blocks(s.n)
     row0 = sum(cnt[:rank])
