@@ -153,9 +153,9 @@ class Runner:
         self.seed = 1000
 
     def calibrate(self):
-        if self.info["kind"] == "dense":
+        if self.info["kind"] == "dense" or self.info.get("short_solves"):
             r = self.d.solve(200, tol=1e-10, variant=self.variant)
-            assert r.status == self.pkg.CONVERGED, f"dense warm-up did not converge: status {r.status}"
+            assert r.status == self.pkg.CONVERGED, f"warm-up solve did not converge: status {r.status}"
             self.J = r.iterations
         return self.J
 
@@ -229,6 +229,60 @@ def timed_steps(pkg, runner, K, W, world, sampler=None):
     assert done == K, (done, K)
     ms_max = max_over_ranks(ms.value, world)
     return {"ms": ms_max, "steps": done, "warmup": w_done, "launches": int(launches), "t0": t0, "t1": t1}
+
+
+def banded_host_system(n, hb, seed=3):
+    """Banded SPD system in host CSR arrays (numpy only): A_ij = A_ji = U(-1/2, 1/2) from a counter-based
+    hash of (min(i,j), max(i,j)) for 0 < |i-j| <= hb, diagonal = sum of the row's |off-diagonals| + 1."""
+    import numpy as np
+
+    i = np.arange(n, dtype=np.int64)[:, None]
+    j = i + np.arange(-hb, hb + 1, dtype=np.int64)[None, :]
+    mask = (j >= 0) & (j < n)
+    lo, hi = np.minimum(i, j), np.maximum(i, j)
+    with np.errstate(over="ignore"):
+        h = (lo.astype(np.uint64) * np.uint64(n) + hi.astype(np.uint64) + np.uint64(seed)) * np.uint64(0x9E3779B97F4A7C15)
+        h ^= h >> np.uint64(30)
+        h *= np.uint64(0xBF58476D1CE4E5B9)
+        h ^= h >> np.uint64(27)
+        h *= np.uint64(0x94D049BB133111EB)
+        h ^= h >> np.uint64(31)
+    v = (h >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0) - 0.5
+    v[~mask] = 0.0
+    v[:, hb] = 0.0
+    v[:, hb] = np.abs(v).sum(axis=1) + 1.0
+    vals = np.ascontiguousarray(v[mask])
+    cols = np.ascontiguousarray(j[mask].astype(np.int32))
+    rp = np.zeros(n + 1, dtype=np.int32)
+    rp[1:] = np.cumsum(mask.sum(axis=1))
+    rng = np.random.default_rng(seed)
+    return rp, cols, vals, rng.random(n) - 0.5
+
+
+def long_row_leg(pkg, peak, peak_src, variant, K=300):
+    """CSR rows of hundreds of entries (the reference's course matrix is of this kind, cg.c:231-232,260):
+    banded SPD n = 52269, 345 entries per row, 18.0 M non-zeros -- the long-row matvec kernel."""
+    n, hb = 52269, 172
+    rp, cols, vals, b = banded_host_system(n, hb)
+    d = pkg.DeviceSystem.from_csr(n, 0, rp, cols, vals, b)
+    info = {"kind": "banded", "n": n, "scaling": "strong", "short_solves": True}
+    rx = Runner(pkg, d, info, variant)
+    tx = timed_steps(pkg, rx, K, 5, 1)
+    ib, k1b = d.bytes()
+    ms = tx["ms"] / tx["steps"]
+    k1 = d.time_kernel(1, 30)
+    out = {"value": round(tx["steps"] / (tx["ms"] * 1e-3), 2), "unit": UNIT, "steps": tx["steps"],
+           "ms_per_step": round(ms, 5), "scaling": "strong", "iterations_per_solve": rx.J,
+           "achieved_gbs_per_gpu": round(ib / (ms * 1e-3) / 1e9, 1), "frac_of_peak": round(ib / (ms * 1e-3) / 1e9 / peak, 4),
+           "config": {"workload": "banded SPD n=52269, 345 entries per row, 18.0 M non-zeros, CSR fp64 (course-sized; not a "
+                                  "BASELINE config)", "n": n, "nnz": int(len(vals)), "matvec": "CSR long-row SpMV (k_spmv_rowblock)",
+                      "l2": "inputs larger than L2 (217 MB matrix streamed every iteration)"},
+           "roofline": {"bound": "hbm", "kernel": "k_spmv_rowblock", "achieved": round(k1b / (k1 * 1e-3) / 1e9, 1),
+                        "peak": peak, "unit": "GB/s", "frac": round(k1b / (k1 * 1e-3) / 1e9 / peak, 4), "traffic": 233068032,
+                        "algorithmic_bytes_per_launch": k1b, "avg_launch_ms": round(k1, 5), "peak_source": peak_src,
+                        "traffic_source": "profiles/r01f_ncu_longrow.md (32-row form of the same kernel)"}}
+    d.free()
+    return out
 
 
 def time_to_solution(pkg, d, info, world, variant=0, tol=1e-10, fixed=None, cap=60000):
@@ -751,6 +805,11 @@ def main():
                 dx.free()
             except Exception as e:
                 extras[nm] = {"error": repr(e)}
+        if world == 1:
+            try:
+                extras["banded52269"] = long_row_leg(pkg, peak, peak_src, variant)
+            except Exception as e:  # noqa: BLE001
+                extras["banded52269"] = {"error": repr(e)}
         line["workloads"] = extras
 
     if sampler:
