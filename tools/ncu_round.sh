@@ -3,7 +3,7 @@
 # launch list of a bench run.  Run on the GPU box from the repo root; writes under gpurun_out/.
 # Every profiled command is first run without ncu and must exit 0.
 set -u
-K='regex:k_gemv|k_spmv|k_update|k_cg_dense'
+K='regex:k_gemv|k_spmv|k_update|k_cg_dense'   # k_spmv also matches k_spmv_rowblock (spec "banded 6 classic")
 # usage: ncu_round.sh ["dense 6 classic" "lap2d 6 classic" ...]   (default: all four)
 if [ $# -gt 0 ]; then SPECS=("$@"); else SPECS=("dense 6 classic" "lap2d 6 classic" "lap3d512 6 classic" "lap3d512 6 sr"); fi
 for spec in "${SPECS[@]}"; do

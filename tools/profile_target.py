@@ -1,5 +1,6 @@
 """Small fixed workload for ncu captures: a few CG iterations of one BASELINE config on 1 GPU.
-usage: profile_target.py {dense|lap2d|lap3d512|lap3d384} [iterations] [classic|sr] [pattern]"""
+usage: profile_target.py {dense|lap2d|lap3d512|lap3d384|banded} [iterations] [classic|sr] [pattern]
+(banded: the course-sized long-row system of bench.py's `banded52269` line, n = 52269, 345 per row)"""
 import os
 import sys
 
@@ -12,7 +13,17 @@ L = pkg.lib()
 assert L.cgb200_init(-1) == 0, pkg.last_error()
 w = sys.argv[1]
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+
+
+def _banded():
+    import bench
+
+    rp, cols, vals, b = bench.banded_host_system(52269, 172)
+    return pkg.DeviceSystem.from_csr(52269, 0, rp, cols, vals, b)
+
+
 d = {
+    "banded": _banded,
     "dense": lambda: pkg.DeviceSystem.dense(32768),
     "lap2d": lambda: pkg.DeviceSystem.lap(4096, 4096, 1),
     "lap3d512": lambda: pkg.DeviceSystem.lap(512, 512, 512),
