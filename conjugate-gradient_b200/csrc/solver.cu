@@ -817,7 +817,7 @@ static const PeerComm& comm_of(const System* S) { return S->p2p ? S->cm : S->cm_
 //   exchange the gather vector's halo / remote blocks take part: in peer-memory mode they were
 //            pushed by the kernel that wrote the vector and this kernel waits for the flags at
 //            its first boundary tile; in NCCL mode the exchange is enqueued here.
-// Multi-rank systems take the long-row matvec too (tools/dist_check.py: neighbour-halo and
+// Multi-rank systems take the long-row matvec too (tests/dist_check.py: neighbour-halo and
 // all-gather systems, both exchange modes); CGB200_SPMV_LONGROW_MULTI=0 keeps them on the stream
 // kernel, whose interior tiles overlap the exchange.
 static bool longrow_multi_ok(const System* S, bool multi) {

@@ -1,5 +1,5 @@
 """Multi-rank parity check, launched as
-    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/dist_check.py
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tests/dist_check.py
 Every rank builds its row block through the C ABI, the ranks solve together (NCCL), rank 0 gathers x
 and compares with the CPU oracle on the whole system (tests/helpers.py; checker only)."""
 import ctypes as C

@@ -1,4 +1,4 @@
-"""Multi-GPU parity on the box: tools/dist_check.py under torch.distributed.run, one process per
+"""Multi-GPU parity on the box: tests/dist_check.py under torch.distributed.run, one process per
 GPU, in both exchange modes (peer memory over NVLink, and NCCL between the kernels).  Needs at
 least two visible GPUs; with one GPU only the single-rank pass runs (the N > 1 host logic is
 covered on CPU by tests/test_partition_gloo.py)."""
@@ -30,7 +30,7 @@ def _run(nproc, comm):
     env = dict(os.environ, CGB200_COMM=comm)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
-           os.path.join(H.ROOT, "tools", "dist_check.py")]
+           os.path.join(H.ROOT, "tests", "dist_check.py")]
     out = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     return out.returncode, out.stdout
 
