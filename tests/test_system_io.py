@@ -158,3 +158,38 @@ def test_writer_refuses_non_systems(pkg, tmp_path):
     A = pkg.MvSparse(s.n, s.nnz, H.dptr(s.vals), H.iptr(s.cols), H.iptr(s.row_ptr))
     short = pkg.MvSparse(3, 3, H.dptr(v), None, None)
     assert L.cgb200_write_system(str(tmp_path / "x.txt").encode(), C.byref(A), C.byref(short), 0) == -1
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_real_spellings_fuzz_against_python_float(pkg, tmp_path, seed):
+    # every spelling printf / numpy / MATLAB-style exporters produce for a double must come back as
+    # the double Python's float() (correctly rounded, like the reference's strtod) reads from it
+    rng = np.random.default_rng(100 + seed)
+    n = 1500
+    mags = rng.choice([1e-310, 1e-300, 1e-20, 1e-3, 1.0, 1e3, 1e17, 1e300], size=n)
+    x = rng.standard_normal(n) * mags
+    x[:6] = [0.0, -0.0, 5e-324, 1.7976931348623157e308, 0.1, -1 / 3]
+    fmts = ["%.17g", "%.16e", "%.6f", "%r", "%.3g", "%+.17g", "%.17E", "%.0f"]
+    toks = []
+    for k, v in enumerate(x):
+        f = fmts[int(rng.integers(len(fmts)))]
+        t = repr(float(v)) if f == "%r" else f % v
+        if len(t) > 400:
+            t = "%.17g" % v
+        pad_l, pad_r = " " * int(rng.integers(0, 3)), " " * int(rng.integers(0, 3))
+        toks.append(pad_l + t + pad_r)
+    want = np.array([float(t) for t in toks])
+    # a 1-row "matrix" whose values line carries the tokens; b holds them once more on the fourth line
+    cols = ",".join(str(i) for i in range(n))
+    p = tmp_path / "fuzz.txt"
+    p.write_text(f"{cols}\n0,{n}\n{','.join(toks)}\n{toks[0]}\n")
+    for threads in ("1", "7"):
+        os.environ["CGB200_IO_THREADS"] = threads
+        try:
+            rc, got = _read(pkg, p)
+        finally:
+            del os.environ["CGB200_IO_THREADS"]
+        assert rc == 0, got
+        assert got["n"] == 1 and got["nnz"] == n
+        assert np.array_equal(got["vals"].view(np.uint64), want.view(np.uint64))
+        assert got["b"].view(np.uint64)[0] == want.view(np.uint64)[0]
