@@ -193,3 +193,23 @@ def test_real_spellings_fuzz_against_python_float(pkg, tmp_path, seed):
         assert got["n"] == 1 and got["nnz"] == n
         assert np.array_equal(got["vals"].view(np.uint64), want.view(np.uint64))
         assert got["b"].view(np.uint64)[0] == want.view(np.uint64)[0]
+
+
+@pytest.mark.skipif(not H.have_ref(), reason="oracle/_ref not built")
+def test_reference_cli_solves_a_file_our_writer_wrote(pkg, tmp_path):
+    # golden input -> our reader -> our writer -> the unmodified reference command line: the stdout the
+    # reference printed for the golden input itself (tests/golden/config1_cg_stdout.txt)
+    L = pkg.lib()
+    A, b = L.new_mv_struct(), L.new_mv_struct()
+    assert L.cgb200_read_system(os.path.join(H.GOLDEN, "config1_lap2d_32x32.txt").encode(), A, b) == 0
+    p = tmp_path / "rewritten.txt"
+    assert L.cgb200_write_system(str(p).encode(), A, b, 0) == 0, pkg.last_error()
+    L.cgb200_free_all(A)
+    L.cgb200_free_all(b)
+    out = subprocess.run([H.REF_CG, str(p), "30"], stdout=subprocess.PIPE, text=True, check=True).stdout
+
+    def x_lines(txt):   # the printed vector (mv_ops.c:92-93); not the timing line or the pointer
+        return [l for l in txt.splitlines() if l.startswith("\t") and ":" not in l]
+
+    want = x_lines(open(os.path.join(H.GOLDEN, "config1_cg_stdout.txt")).read())
+    assert len(want) == 1024 and x_lines(out) == want
