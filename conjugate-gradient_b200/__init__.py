@@ -71,6 +71,7 @@ RUNNING, MAXITER, CONVERGED, BREAKDOWN, EXACT, COMM_TIMEOUT = 0, 1, 2, 3, 4, 5
 CLASSIC, SINGLE_REDUCTION = 0, 1
 EAGER, RESIDENT = 0, 1
 OPT_JACOBI, OPT_X0 = 1, 2
+CACHE_STRICT, CACHE_SAMPLED, CACHE_OFF = 0, 1, 2
 
 # every symbol include/mv_ops.h and include/cgb200.h declare (checked by tests/test_abi_symbols.py)
 MV_OPS_SYMBOLS = [
@@ -139,6 +140,9 @@ def lib():
     L.cgb200_guard_selftest.restype = C.c_int
     L.cgb200_guard_selftest.argtypes = []
     L.cgb200_set_mode.argtypes = [C.c_int]
+    L.cgb200_set_matrix_cache.argtypes = [C.c_int]
+    L.cgb200_content_hash.restype = C.c_ulonglong
+    L.cgb200_content_hash.argtypes = [MvSparseP]
     for name in ("cgb200_to_device", "cgb200_to_host", "cgb200_invalidate"):
         getattr(L, name).argtypes = [MvSparseP]
     L.cgb200_free_all.restype = None

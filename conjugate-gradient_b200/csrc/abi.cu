@@ -14,6 +14,7 @@
 
 #include <map>
 #include <mutex>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -54,13 +55,20 @@ struct MatrixEntry {
   const int* cols = nullptr;
   const int* rowptr = nullptr;
   int size = 0, nnz = 0;
-  uint64_t fp = 0;
+  uint64_t fp = 0;       // sampled fingerprint (cheap; every call)
+  uint64_t content = 0;  // hash of every byte of the three arrays (strict policy)
+  bool has_content = false;
+  bool pinned = false;   // the caller declared the device copy current (cgb200_to_device / resident mode)
 };
 
 struct VectorEntry {
   double* d = nullptr;
   int cap = 0;
   int n = 0;
+  // host array the mirror was last validated against: a struct that was released with plain free()
+  // (the reference's free_mv_struct is just that, mv_ops.c:39-42) and whose address malloc hands
+  // out again comes back with another values pointer -- the stale mirror is then not trusted
+  const double* host_ptr = nullptr;
   bool dev_valid = false;   // device copy holds the current values
   bool host_valid = false;  // host array holds the current values
   // resident mode: v.v of the current device values, once a dot_product(v, v) has computed it.
@@ -100,12 +108,34 @@ int scratch(int slot, size_t n, double** out) {
   return 0;
 }
 
-// Sampled fingerprint of a matrix's host arrays: catches a caller that rebuilt the matrix behind an
-// unchanged struct address (not a proof; cgb200_invalidate() is the contract).  It runs on every
-// mv_mult / solve, and on a multi-gigabyte matrix every sample is a cache and TLB miss: 64 + 32
-// samples cost ~15 us where the first version's 2048 + 1024 cost ~0.5 ms per operator call --
-// more than a third of a dense n = 32768 matvec -- without seeing more of a 10^9-entry array in
-// any way that matters (either figure is a vanishing fraction).
+// ---- is the device copy of a caller's matrix still the caller's matrix? ------------------------
+//
+// The reference reads the caller's arrays on every call (mv_ops.c:187-197), so an unmodified
+// caller may edit values[] in place between two mv_mult / conj_grad calls and expects the new
+// product.  The device copy is therefore re-validated on EVERY call that takes a matrix:
+//   strict  (default)  a hash of every byte of values[], col_indices[], row_ptr[] (several host
+//                      threads; one pass over host memory, an order of magnitude cheaper than
+//                      the upload from pageable memory it saves).  A change confined to one
+//                      8-byte word is always seen (every step of the hash is a bijection of its
+//                      state); anything else with probability 1 - 2^-64.
+//   sampled            96 samples + the array addresses: constant time, sees a rebuilt matrix,
+//                      misses a small in-place edit -- cgb200_invalidate() is then the contract.
+//   off                no cache: every call uploads.
+// CGB200_MATRIX_CACHE=strict|sampled|off, cgb200_set_matrix_cache().  A matrix the caller has
+// handed over explicitly -- cgb200_to_device(A) -- and every matrix in resident mode is PINNED:
+// the caller has stated that the device copy is current until cgb200_invalidate / free, and only
+// the sampled check runs (a rebuilt matrix behind the same struct is still noticed).
+int g_cache_policy = -1;  // CGB200_CACHE_*
+int cache_policy() {
+  if (g_cache_policy < 0) {
+    const char* e = getenv("CGB200_MATRIX_CACHE");
+    g_cache_policy = CGB200_CACHE_STRICT;
+    if (e && strcmp(e, "sampled") == 0) g_cache_policy = CGB200_CACHE_SAMPLED;
+    if (e && strcmp(e, "off") == 0) g_cache_policy = CGB200_CACHE_OFF;
+  }
+  return g_cache_policy;
+}
+
 uint64_t mix(uint64_t h, uint64_t v) {
   h ^= v + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
   return h;
@@ -131,10 +161,79 @@ uint64_t fingerprint(const struct __mv_sparse* A) {
   return h;
 }
 
+// Hash of one byte range: four independent lanes of (h ^ word) * odd constant, so the loop is
+// bound by memory, not by the multiplier's latency.
+uint64_t hash_range(const unsigned char* p, size_t bytes) {
+  const uint64_t P0 = 0x9E3779B97F4A7C15ull, P1 = 0xC2B2AE3D27D4EB4Full, P2 = 0x165667B19E3779F9ull,
+                 P3 = 0xD6E8FEB86659FD93ull;
+  uint64_t h0 = 0x243F6A8885A308D3ull, h1 = 0x13198A2E03707344ull, h2 = 0xA4093822299F31D0ull,
+           h3 = 0x082EFA98EC4E6C89ull;
+  size_t i = 0;
+  for (; i + 32 <= bytes; i += 32) {
+    uint64_t w[4];
+    memcpy(w, p + i, 32);
+    h0 = (h0 ^ w[0]) * P0;
+    h1 = (h1 ^ w[1]) * P1;
+    h2 = (h2 ^ w[2]) * P2;
+    h3 = (h3 ^ w[3]) * P3;
+  }
+  for (; i < bytes; i += 8) {
+    uint64_t w = 0;
+    memcpy(&w, p + i, bytes - i < 8 ? bytes - i : 8);
+    h0 = (h0 ^ w) * P0;
+    h0 = (h0 << 29) | (h0 >> 35);
+  }
+  uint64_t h = h0;
+  h = (h ^ ((h1 << 17) | (h1 >> 47))) * P1;
+  h = (h ^ ((h2 << 31) | (h2 >> 33))) * P2;
+  h = (h ^ ((h3 << 43) | (h3 >> 21))) * P3;
+  return h ^ (h >> 32);
+}
+
+// Hash of a whole array, cut into 4 MiB pieces dealt to up to 32 threads; the pieces' hashes are
+// chained in order, so the result does not depend on the thread count.
+uint64_t hash_array(const void* ptr, size_t bytes, uint64_t seed) {
+  if (!ptr || bytes == 0) return seed * 0x9E3779B97F4A7C15ull + 1;
+  const size_t PIECE = 4u << 20;
+  const size_t npieces = (bytes + PIECE - 1) / PIECE;
+  std::vector<uint64_t> hp(npieces);
+  const unsigned char* p = (const unsigned char*)ptr;
+  auto work = [&](size_t t, size_t nt) {
+    for (size_t k = t; k < npieces; k += nt) {
+      const size_t off = k * PIECE;
+      hp[k] = hash_range(p + off, bytes - off < PIECE ? bytes - off : PIECE);
+    }
+  };
+  size_t nt = std::thread::hardware_concurrency();
+  if (const char* e = getenv("CGB200_HASH_THREADS")) nt = (size_t)atoi(e);
+  if (nt > 32) nt = 32;
+  if (nt > npieces) nt = npieces;
+  if (nt <= 1) {
+    work(0, 1);
+  } else {
+    std::vector<std::thread> th;
+    for (size_t t = 1; t < nt; ++t) th.emplace_back(work, t, nt);
+    work(0, nt);
+    for (auto& x : th) x.join();
+  }
+  uint64_t h = seed ^ (uint64_t)bytes;
+  for (size_t k = 0; k < npieces; ++k) h = (h ^ hp[k]) * 0xD6E8FEB86659FD93ull + 0x9E3779B97F4A7C15ull;
+  return h;
+}
+
+uint64_t content_hash(const struct __mv_sparse* A) {
+  const size_t nnz = A->nnz > 0 ? (size_t)A->nnz : 0;
+  uint64_t h = hash_array(A->values, nnz * sizeof(double), 1);
+  h = hash_array(A->col_indices, A->col_indices ? nnz * sizeof(int) : 0, h);
+  h = hash_array(A->row_ptr, ((size_t)A->size + 1) * sizeof(int), h);
+  return h;
+}
+
 bool is_vector(const struct __mv_sparse* v) { return v->col_indices == NULL && v->row_ptr == NULL; }
 
-// Device system for a host CSR struct, uploaded on first use and whenever the struct changed.
-System* matrix_system(struct __mv_sparse* A) {
+// Device system for a host CSR struct, uploaded on first use and whenever the struct's arrays no
+// longer hold what was uploaded (policy above).  pin: the caller hands the matrix over explicitly.
+System* matrix_system(struct __mv_sparse* A, bool pin = false) {
   if (!A->row_ptr || !A->values || (!A->col_indices && A->nnz > 0)) {
     set_error("matrix struct lacks CSR arrays");
     return nullptr;
@@ -143,17 +242,37 @@ System* matrix_system(struct __mv_sparse* A) {
     set_error("host-struct entry points are single-rank; use the cgb200_system_* API when distributed");
     return nullptr;
   }
+  const int policy = cache_policy();
   const uint64_t fp = fingerprint(A);
+  uint64_t content = 0;
+  bool have_content = false;
   auto it = g_mats.find(A);
   if (it != g_mats.end()) {
     MatrixEntry& e = it->second;
-    if (e.values == A->values && e.cols == A->col_indices && e.rowptr == A->row_ptr &&
-        e.size == A->size && e.nnz == A->nnz && e.fp == fp)
+    bool same = policy != CGB200_CACHE_OFF && e.values == A->values && e.cols == A->col_indices &&
+                e.rowptr == A->row_ptr && e.size == A->size && e.nnz == A->nnz && e.fp == fp;
+    const bool trusted = e.pinned || g_mode == CGB200_RESIDENT || policy == CGB200_CACHE_SAMPLED;
+    if (same && !trusted) {
+      content = content_hash(A);
+      have_content = true;
+      same = e.has_content && e.content == content;
+    }
+    if (same) {
+      if (pin) e.pinned = true;
       return e.sys;
+    }
     delete e.sys;
     g_mats.erase(it);
   }
+  // the hash for the next call's comparison is taken while the upload runs
+  std::thread hasher;
+  if (policy == CGB200_CACHE_STRICT && !have_content)
+    hasher = std::thread([&]() { content = content_hash(A); });
   System* sys = system_from_csr(A->size, 0, A->size, A->row_ptr, A->col_indices, A->values, nullptr);
+  if (hasher.joinable()) {
+    hasher.join();
+    have_content = true;
+  }
   if (!sys) return nullptr;
   MatrixEntry e;
   e.sys = sys;
@@ -163,6 +282,9 @@ System* matrix_system(struct __mv_sparse* A) {
   e.size = A->size;
   e.nnz = A->nnz;
   e.fp = fp;
+  e.content = content;
+  e.has_content = have_content;
+  e.pinned = pin;
   g_mats[A] = e;
   return sys;
 }
@@ -287,7 +409,7 @@ int dev_input(struct __mv_sparse* v, int slot, const double** out) {
   const int n = v->size;
   if (g_mode == CGB200_RESIDENT) {
     VectorEntry& e = g_vecs[v];
-    if (e.dev_valid && e.n == n) {
+    if (e.dev_valid && e.n == n && e.host_ptr == v->values) {
       if (e.lazy && materialize(v)) return -1;
       *out = e.d;
       return 0;
@@ -303,6 +425,7 @@ int dev_input(struct __mv_sparse* v, int slot, const double** out) {
     e.dev_valid = true;
     e.host_valid = true;
     e.sd_valid = false;
+    e.host_ptr = v->values;
     *out = e.d;
     return 0;
   }
@@ -364,6 +487,7 @@ int finish_output(struct __mv_sparse* o, double* d) {
     e.dev_valid = true;
     e.host_valid = false;
     e.sd_valid = false;
+    e.host_ptr = o->values;
     return 0;
   }
   if (o->size > 0)
@@ -377,7 +501,7 @@ int sync_to_host(struct __mv_sparse* o) {
   if (it == g_vecs.end()) return 0;
   VectorEntry& e = it->second;
   if (e.lazy && materialize(o)) return -1;
-  if (e.dev_valid && !e.host_valid && e.n == o->size && o->values) {
+  if (e.dev_valid && !e.host_valid && e.n == o->size && o->values && e.host_ptr == o->values) {
     Ctx& c = ctx();
     if (e.n > 0)
       CU_OK(cudaMemcpyAsync(o->values, e.d, sizeof(double) * e.n, cudaMemcpyDeviceToHost, c.stream));
@@ -408,6 +532,7 @@ int ewise_resident(int op, double sca, struct __mv_sparse* a, struct __mv_sparse
     e.dev_valid = true;
     e.host_valid = false;
     e.sd_valid = false;
+    e.host_ptr = (*out)->values;
     e.lazy = true;
     e.lazy_s = sca;
     e.lazy_src = a;
@@ -562,7 +687,8 @@ struct __mv_sparse* mv_deep_copy(struct __mv_sparse* orig) {
     auto it = g_vecs.find(orig);
     if (it != g_vecs.end() && it->second.lazy && materialize(orig)) return NULL;
     if (g_mode == CGB200_RESIDENT && !orig->col_indices && !orig->row_ptr && it != g_vecs.end() &&
-        it->second.dev_valid && !it->second.host_valid && it->second.n == orig->size) {
+        it->second.dev_valid && !it->second.host_valid && it->second.n == orig->size &&
+        it->second.host_ptr == orig->values) {
       struct __mv_sparse* cp = new_mv_struct();
       if (!cp) return NULL;
       cp->size = orig->size;
@@ -590,6 +716,7 @@ struct __mv_sparse* mv_deep_copy(struct __mv_sparse* orig) {
       e.host_valid = false;
       e.sd_valid = sd_valid;
       e.sd = sd;
+      e.host_ptr = cp->values;
       return cp;
     }
     if (sync_to_host(orig)) return NULL;
@@ -772,11 +899,27 @@ int cgb200_set_mode(int mode) {
   return 0;
 }
 
+int cgb200_set_matrix_cache(int policy) {
+  if (policy != CGB200_CACHE_STRICT && policy != CGB200_CACHE_SAMPLED && policy != CGB200_CACHE_OFF)
+    return -1;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  g_cache_policy = policy;
+  return 0;
+}
+
+unsigned long long cgb200_content_hash(const struct __mv_sparse* A) {
+  if (!A || !A->values) return 0ull;
+  if (!A->row_ptr) {  // a vector: its values only
+    return hash_array(A->values, (A->size > 0 ? (size_t)A->size : 0) * sizeof(double), 1);
+  }
+  return content_hash(A);
+}
+
 int cgb200_to_device(struct __mv_sparse* obj) {
   if (!obj) return -1;
   if (ensure_init(-1)) return -1;
   std::lock_guard<std::mutex> lk(g_tab_mu);
-  if (!is_vector(obj)) return matrix_system(obj) ? 0 : -1;
+  if (!is_vector(obj)) return matrix_system(obj, true) ? 0 : -1;  // pinned until invalidate / free
   if (before_write(obj)) return -1;
   VectorEntry& e = g_vecs[obj];
   if (e.lazy) {
@@ -791,6 +934,7 @@ int cgb200_to_device(struct __mv_sparse* obj) {
   e.dev_valid = true;
   e.host_valid = true;
   e.sd_valid = false;
+  e.host_ptr = obj->values;
   return 0;
 }
 
@@ -855,46 +999,55 @@ int cgb200_solve(struct __mv_sparse* A, struct __mv_sparse* b, struct __mv_spars
 }
 
 cgb200_system* cgb200_system_lap(int nx, int ny, int nz, int z0, int nzl, uint64_t bseed) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   return (cgb200_system*)system_lap(nx, ny, nz, z0, nzl, bseed);
 }
 
 cgb200_system* cgb200_system_dense(int n, int row0, int nrows, uint64_t aseed, uint64_t bseed) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   return (cgb200_system*)system_dense(n, row0, nrows, aseed, bseed);
 }
 
 cgb200_system* cgb200_system_from_csr(long long n_global, long long row0, int nrows,
                                       const int* row_ptr, const int* cols, const double* vals,
                                       const double* b) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   return (cgb200_system*)system_from_csr(n_global, row0, nrows, row_ptr, cols, vals, b);
 }
 
 void cgb200_system_free(cgb200_system* sys) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys) return;
   cudaStreamSynchronize(ctx().stream);
   delete (System*)sys;
 }
 
 int cgb200_system_set_rhs(cgb200_system* sys, const double* b_host) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys || !b_host) return -1;
   return system_set_rhs((System*)sys, b_host);
 }
 
 int cgb200_system_gen_rhs(cgb200_system* sys, uint64_t bseed) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys) return -1;
   return system_gen_rhs((System*)sys, bseed);
 }
 
 int cgb200_system_set_x(cgb200_system* sys, const double* x_host) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys || !x_host) return -1;
   return system_set_x((System*)sys, x_host);
 }
 
 int cgb200_system_get_x(cgb200_system* sys, double* x_host) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys || !x_host) return -1;
   return system_get_x((System*)sys, x_host);
 }
 
 int cgb200_system_solve(cgb200_system* sys, const cgb200_opts* opts, cgb200_result* res) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   SolveResult r;
   memset(&r, 0, sizeof(r));
   const int rc = system_solve((System*)sys, to_opts(opts), &r);
@@ -903,10 +1056,12 @@ int cgb200_system_solve(cgb200_system* sys, const cgb200_opts* opts, cgb200_resu
 }
 
 int cgb200_system_solve_async(cgb200_system* sys, const cgb200_opts* opts, long long* ticket) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   return system_solve_async((System*)sys, to_opts(opts), ticket);
 }
 
 int cgb200_solve_wait(long long ticket, cgb200_result* res) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   SolveResult r;
   memset(&r, 0, sizeof(r));
   const int rc = system_solve_wait(ticket, &r);
@@ -915,26 +1070,31 @@ int cgb200_solve_wait(long long ticket, cgb200_result* res) {
 }
 
 int cgb200_system_matvec(cgb200_system* sys, const double* v_host, double* s_host) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys || !v_host || !s_host) return -1;
   return system_matvec((System*)sys, v_host, s_host);
 }
 
 int cgb200_system_true_relres(cgb200_system* sys, double* relres) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys || !relres) return -1;
   return system_true_relres((System*)sys, relres);
 }
 
 int cgb200_system_time_kernel(cgb200_system* sys, int which, int reps, double* ms) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys || !ms || reps < 1 || which < 1 || which > 6) return -1;
   return system_time_kernel((System*)sys, which, reps, ms);
 }
 
 int cgb200_system_download(cgb200_system* sys, double* vals, int* cols, int* row_ptr) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys) return -1;
   return system_download((System*)sys, vals, cols, row_ptr);
 }
 
 int cgb200_system_get_b(cgb200_system* sys, double* b_host) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys || !b_host) return -1;
   return system_get_b((System*)sys, b_host);
 }
@@ -1013,10 +1173,12 @@ int cgb200_dist_world(void) { return ctx().world; }
 int cgb200_dist_barrier(void) { return dist_barrier(); }
 const char* cgb200_dist_comm_mode(void) { return comm_mode_name(); }
 int cgb200_system_use_pattern_format(cgb200_system* sys, int on) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   return system_use_pattern((System*)sys, on);
 }
 
 int cgb200_system_trace(cgb200_system* sys, int on, unsigned long long* out16) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys) return -1;
   return system_trace((System*)sys, on, out16);
 }

@@ -478,13 +478,16 @@ __device__ __forceinline__ bool grid_wait(const unsigned long long* epoch, unsig
 // ---------------------------------------------------------------------------------------------
 
 // After p.s is known (reference cg.c:113).  Breakdown policy: the reference divides regardless
-// and poisons x with NaN once r is exactly zero; here the loop stops before the update.
+// and poisons x with NaN once r is exactly zero; here the loop stops before the update -- but only
+// where the division has no finite result (r.r == 0, p.s == 0, p.s not finite).  A NEGATIVE p.s is
+// let through exactly as the reference lets it: on a negative-definite system (a Laplacian
+// assembled with the other sign) the recurrence produces the iterates of (-A, -b).
 __device__ __forceinline__ void finish_ps(CgState* S, double ps) {
   S->ps = ps;
   if (S->rr == 0.0) {
     S->done = 1;
     S->status = CGB200_ST_EXACT;
-  } else if (!(ps > 0.0) || isinf(ps)) {
+  } else if (ps == 0.0 || !isfinite(ps)) {
     S->done = 1;
     S->status = CGB200_ST_BREAKDOWN;
   } else {
@@ -537,7 +540,7 @@ __device__ __forceinline__ void finish_sr(CgState* S, double rw, double rr) {
     if (rr == 0.0) {
       S->done = 1;
       S->status = CGB200_ST_EXACT;
-    } else if (!(rw > 0.0) || isinf(rw)) {
+    } else if (rw == 0.0 || !isfinite(rw)) {
       S->done = 1;
       S->status = CGB200_ST_BREAKDOWN;
     } else {
@@ -561,7 +564,7 @@ __device__ __forceinline__ void finish_sr(CgState* S, double rw, double rr) {
   } else {
     const double beta = rr / S->rr;
     const double denom = rw - beta * rr / S->alpha;
-    if (!(denom > 0.0) || isinf(denom)) {
+    if (denom == 0.0 || !isfinite(denom)) {
       S->done = 1;
       S->status = CGB200_ST_BREAKDOWN;
     } else {

@@ -1783,11 +1783,14 @@ __global__ void k_gen_dense(int n, int row0, int nloc, unsigned long long seed,
 }
 
 // min / max column index over all stored entries (halo discovery) and the "every row is full"
-// test (row_ptr[i] == i*ncols).  out[0] = min col, out[1] = max col, out[2] = #rows not full.
+// test (row_ptr[i] == i*ncols).  out[0] = min col, out[1] = max col, out[2] = #rows not full,
+// out[3] = #decreasing steps of row_ptr (a valid CSR has none).
 __global__ void k_analyze(const int* __restrict__ rowptr, const int* __restrict__ cols, int nrows,
                           long long nnz, int ncols, int* __restrict__ out) {
   const long long stride = (long long)gridDim.x * blockDim.x;
-  int mn = 0x7fffffff, mx = -0x7fffffff - 1, bad = 0;
+  int mn = 0x7fffffff, mx = -0x7fffffff - 1, bad = 0, dec = 0;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nrows; i += stride)
+    if (rowptr[i + 1] < rowptr[i]) ++dec;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += stride) {
     const int c = cols[i];
     mn = min(mn, c);
@@ -1799,11 +1802,13 @@ __global__ void k_analyze(const int* __restrict__ rowptr, const int* __restrict_
     mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
     mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     bad += __shfl_xor_sync(0xffffffffu, bad, o);
+    dec += __shfl_xor_sync(0xffffffffu, dec, o);
   }
   if ((threadIdx.x & 31) == 0) {
     atomicMin(out + 0, mn);
     atomicMax(out + 1, mx);
     if (bad) atomicAdd(out + 2, bad);
+    if (dec) atomicAdd(out + 3, dec);
   }
 }
 
@@ -2356,7 +2361,7 @@ cudaError_t launch_gen_dense(int n, int row0, int nloc, unsigned long long seed,
 
 cudaError_t launch_analyze(const int* rowptr, const int* cols, int nrows, long long nnz, int ncols,
                            int* out3, cudaStream_t st) {
-  static const int init[3] = {0x7fffffff, -0x7fffffff - 1, 0};
+  static const int init[4] = {0x7fffffff, -0x7fffffff - 1, 0, 0};
   cudaError_t e = cudaMemcpyAsync(out3, init, sizeof(init), cudaMemcpyHostToDevice, st);
   if (e != cudaSuccess) return e;
   k_analyze<<<sm_count() * 4, 256, 0, st>>>(rowptr, cols, nrows, nnz, ncols, out3);

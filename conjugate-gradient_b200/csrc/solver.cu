@@ -729,17 +729,32 @@ System* system_from_csr(long long n_global, long long row0, int nrows, const int
           cudaStreamSynchronize(c.stream) != cudaSuccess)
         return fail("row_ptr pad");
     }
-    // column span (needed for the halo plan only when distributed)
-    if (c.world > 1 && nnz > 0) {
-      int* d3 = (int*)c.d_scratch;
-      if (launch_analyze(S->A.rowptr, S->A.cols, nrows, nnz, (int)n_global, d3, c.stream) !=
+    // Column span and validity, one pass over the uploaded index arrays.  The span feeds the halo
+    // plan; the checks keep a malformed matrix (a 1-based file, a non-monotone row_ptr) from
+    // reaching the gather and bulk-copy kernels, where it would read out of bounds and leave the
+    // CUDA context in an error state for the rest of the process.  (The reference, which expands
+    // rows on the host, simply ignores such entries: mv_ops.c:106-110.)
+    if (nnz > 0) {
+      int* d4 = (int*)c.d_scratch;
+      if (launch_analyze(S->A.rowptr, S->A.cols, nrows, nnz, (int)n_global, d4, c.stream) !=
               cudaSuccess ||
-          cudaMemcpyAsync(c.h_scratch, d3, 3 * sizeof(int), cudaMemcpyDeviceToHost, c.stream) !=
+          cudaMemcpyAsync(c.h_scratch, d4, 4 * sizeof(int), cudaMemcpyDeviceToHost, c.stream) !=
               cudaSuccess ||
           cudaStreamSynchronize(c.stream) != cudaSuccess)
         return fail("analyze");
-      mincol = ((int*)c.h_scratch)[0];
-      maxcol = ((int*)c.h_scratch)[1];
+      const int* h4 = (const int*)c.h_scratch;
+      if (h4[0] < 0 || (long long)h4[1] >= n_global || h4[3] != 0) {
+        char msg[200];
+        snprintf(msg, sizeof msg,
+                 "system_from_csr: malformed CSR (column range [%d, %d] for %lld columns, %d "
+                 "decreasing row_ptr step(s)); indices are 0-based and row_ptr non-decreasing",
+                 h4[0], h4[1], n_global, h4[3]);
+        set_error(msg);
+        delete S;
+        return nullptr;
+      }
+      mincol = h4[0];
+      maxcol = h4[1];
     }
   }
   if (plan_and_alloc(S, mincol, maxcol, true)) { delete S; return nullptr; }
@@ -1216,7 +1231,7 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
   bool stop = false;
   while (enq < total_updates && !stop) {
     int nb = batch;
-    if (nb > total_updates) nb = (int)total_updates;
+    if (nb > total_updates - enq) nb = (int)(total_updates - enq);  // a tail graph, not early-exit launches
     cudaGraphExec_t exec = nullptr;
     if (get_graph(S, nb, variant, &exec)) return -1;
     CUDA_OK(cudaGraphLaunch(exec, c.stream));
@@ -1327,8 +1342,10 @@ int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out) {
   const long long total_updates = (long long)max_iter + 1;
   int batch = o.check_every > 0 ? o.check_every : 32;
   if (batch > total_updates) batch = (int)total_updates;
-  cudaGraphExec_t exec = nullptr;
+  cudaGraphExec_t exec = nullptr, exec_tail = nullptr;
   if (get_graph(S, batch, variant, &exec)) return -1;
+  const int tail = (int)(total_updates % batch);  // exactly max_iter + 1 updates are enqueued
+  if (tail > 0 && get_graph(S, tail, variant, &exec_tail)) return -1;
   const int kpi = kernels_per_iteration(S, variant);
 
   CUDA_OK(cudaMemcpyAsync(S->state, a.up, sizeof(CgState), cudaMemcpyHostToDevice, c.stream));
@@ -1340,9 +1357,13 @@ int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out) {
     if (nccl && enqueue_nccl_finish(S, 2, FIN_SR)) return -1;
   }
   CUDA_OK(cudaEventRecord(a.t0, c.stream));
-  for (long long enq = 0; enq < total_updates; enq += batch) {
+  for (long long enq = 0; enq + batch <= total_updates; enq += batch) {
     CUDA_OK(cudaGraphLaunch(exec, c.stream));
     add_launches((long long)kpi * batch);
+  }
+  if (tail > 0) {
+    CUDA_OK(cudaGraphLaunch(exec_tail, c.stream));
+    add_launches((long long)kpi * tail);
   }
   CUDA_OK(cudaEventRecord(a.t1, c.stream));
   CUDA_OK(cudaMemcpyAsync(a.down, S->state, sizeof(CgState), cudaMemcpyDeviceToHost, c.stream));

@@ -7,7 +7,7 @@
 #define CGB200_ST_RUNNING 0
 #define CGB200_ST_MAXITER 1    /* fixed count reached (the reference's only exit, cg.c:125-127) */
 #define CGB200_ST_CONVERGED 2  /* r.r <= tol^2 * b.b (extension) */
-#define CGB200_ST_BREAKDOWN 3  /* p.Ap not a positive finite number */
+#define CGB200_ST_BREAKDOWN 3  /* p.Ap zero or not finite (negative is let through, cg.c:113) */
 #define CGB200_ST_EXACT 4      /* r.r == 0 exactly: stopped where the reference would divide 0/0 */
 #define CGB200_ST_COMM 5       /* a peer-memory exchange between GPUs timed out */
 

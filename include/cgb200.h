@@ -20,7 +20,8 @@ extern "C" {
 #define CGB200_RUNNING 0
 #define CGB200_MAXITER 1   /* ran the fixed count (the reference's only exit, cg.c:125-127) */
 #define CGB200_CONVERGED 2 /* r.r <= tol^2 * b.b */
-#define CGB200_BREAKDOWN 3 /* p.Ap not positive and finite: stopped, last finite x kept */
+#define CGB200_BREAKDOWN 3 /* p.Ap zero or not finite: stopped, last finite x kept (a negative p.Ap
+                              is let through as the reference lets it, cg.c:113) */
 #define CGB200_EXACT 4     /* r.r == 0: stopped where the reference would compute 0/0 = NaN */
 #define CGB200_COMM_TIMEOUT 5 /* multi-GPU: a peer-memory exchange timed out (the call returns -1) */
 
@@ -102,7 +103,27 @@ int cgb200_guard_selftest(void);
  * CGB200_MODE=resident selects resident mode at start-up for callers that cannot be edited (the
  * reference's own cg.c loop: tests/test_gpu_dropin.py). */
 int cgb200_set_mode(int mode);
-int cgb200_to_device(struct __mv_sparse *obj); /* upload now; the mirror becomes valid */
+/* Device copies of caller matrices (mv_mult, conj_grad, cgb200_solve on host structs).  The
+ * reference reads the caller's arrays on every call (mv_ops.c:187-197), so a caller may edit
+ * values[] in place between two calls; the device copy is re-validated on every call:
+ *   CGB200_CACHE_STRICT  (default) hash of every byte of values / col_indices / row_ptr, several
+ *                        host threads: any in-place edit is seen and causes a fresh upload;
+ *   CGB200_CACHE_SAMPLED 96 samples + the array addresses (constant time): notices a rebuilt
+ *                        matrix, can miss a small in-place edit -- call cgb200_invalidate;
+ *   CGB200_CACHE_OFF     every call uploads.
+ * Environment: CGB200_MATRIX_CACHE=strict|sampled|off.  A matrix handed over explicitly with
+ * cgb200_to_device(A), and every matrix while in CGB200_RESIDENT mode, is pinned: the caller has
+ * declared the device copy current until cgb200_invalidate(A) / free_mv_struct(A), and only the
+ * sampled check runs.  That is the fast path for repeated solves with one matrix. */
+#define CGB200_CACHE_STRICT 0
+#define CGB200_CACHE_SAMPLED 1
+#define CGB200_CACHE_OFF 2
+int cgb200_set_matrix_cache(int policy);
+/* The content hash CGB200_CACHE_STRICT compares (host only, needs no device; 0 for NULL): every
+ * byte of values / col_indices / row_ptr (a vector: its values).  Independent of the number of
+ * hashing threads (CGB200_HASH_THREADS). */
+unsigned long long cgb200_content_hash(const struct __mv_sparse *A);
+int cgb200_to_device(struct __mv_sparse *obj); /* upload now; the mirror becomes valid (matrices: pinned) */
 int cgb200_to_host(struct __mv_sparse *obj);   /* bring values back if the device copy is newer */
 int cgb200_invalidate(struct __mv_sparse *obj); /* caller changed host arrays in place */
 void cgb200_free_all(struct __mv_sparse *obj);  /* struct + its host arrays + device mirror */
@@ -113,6 +134,10 @@ int cgb200_solve(struct __mv_sparse *A, struct __mv_sparse *b, struct __mv_spars
                  const cgb200_opts *opts, cgb200_result *res);
 
 /* ---- device-resident systems (one row block of A, b, x and the work vectors) -------------- */
+/* Threading: the library has one context per process (one device, one solve stream).  Every entry
+ * point of this header and of mv_ops.h may be called from any thread; calls are serialised by one
+ * process-wide lock (the reference's operators are stateless, mv_ops.c has no globals -- here the
+ * state is the device).  cgb200_solve_wait holds the lock while it waits. */
 typedef struct cgb200_system cgb200_system;
 
 /* Rows [z0*nx*ny, (z0+nzl)*nx*ny) of the Dirichlet 5-point (nz == 1) or 7-point Laplacian on an

@@ -65,7 +65,13 @@ int mat_get_row(struct __mv_sparse *mat_A, int row_id, double *p_row);
 double dot_product(struct __mv_sparse *vec_a, struct __mv_sparse *vec_b);
 /* *out = s * a                                              replaces reference mv_ops.c:134-158 */
 int sv_mult(double s, struct __mv_sparse *vec_a, struct __mv_sparse **out);
-/* *out = A * b; -1 when A->size != b->size                  replaces reference mv_ops.c:160-201 */
+/* *out = A * b; -1 when A->size != b->size                  replaces reference mv_ops.c:160-201
+ * CSR rows: each row's stored entries are multiplied and added in ascending column order, unfused,
+ * so *out has the reference's bits.  A matrix whose every row is full (row_ptr[i] == i*size) takes
+ * the dense GEMV kernel, which accumulates with fma over a fixed tree: agrees with the reference
+ * to <= 4 n eps |A||b| per row, not bit for bit.  A's arrays are re-validated on every call
+ * (cgb200.h: CGB200_CACHE_STRICT), so in-place edits of values[] are seen as the reference sees
+ * them. */
 int mv_mult(struct __mv_sparse *mat_A, struct __mv_sparse *vec_b, struct __mv_sparse **out);
 /* *out = a + b                                              replaces reference mv_ops.c:203-230 */
 int vec_add(struct __mv_sparse *vec_a, struct __mv_sparse *vec_b, struct __mv_sparse **out);
@@ -78,7 +84,10 @@ int vec_sub(struct __mv_sparse *vec_a, struct __mv_sparse *vec_b, struct __mv_sp
  * max_iter = M performs M+1 matrix-vector products and x/r updates and M direction updates,
  * no tolerance test.  *x receives a freshly allocated vector.  Returns 0 (the reference always
  * does); -1 on NULL arguments or a CUDA failure.  Unlike the reference, iterating past exact
- * convergence stops instead of producing NaN (cgb200.h, CGB200_BREAKDOWN).
+ * convergence (r.r == 0, or p.Ap zero / not finite) stops instead of producing NaN (cgb200.h,
+ * CGB200_EXACT / CGB200_BREAKDOWN); a negative p.Ap is divided by as the reference does, so
+ * negative-definite systems solve like (-A, -b).  Structs should be released through
+ * free_mv_struct / cgb200_free_all so that their device mirrors go with them.
  *                                                               replaces reference cg.c:88-141 */
 int conj_grad(int max_iter, struct __mv_sparse *mat_A, struct __mv_sparse *vec_b,
               struct __mv_sparse **x);

@@ -210,6 +210,12 @@ def toeplitz(n, coeffs, bseed=7):
     return System(rp, ci, va, rhs(n, bseed), name=f"toeplitz_{n}_{h}")
 
 
+def negated(sysm):
+    """(-A, -b): a negative-definite system with the same solution.  The reference divides by p.Ap
+    whatever its sign (cg.c:113), so its iterates are those of (A, b) with r, p, s negated."""
+    return System(sysm.row_ptr, sysm.cols, -sysm.vals, -sysm.b, name="neg_" + sysm.name)
+
+
 def tridiag4():
     """The 4x4 known-answer system: tridiag(-1,2,-1), b = 1."""
     rp = [0, 2, 5, 8, 10]

@@ -138,3 +138,36 @@ def test_product_sources_never_touch_the_oracle():
     assert not bad, bad
     ldd = subprocess.run(["ldd", os.path.join(pk, "libcgb200.so")], stdout=subprocess.PIPE, text=True).stdout
     assert "oracle" not in ldd and "cgref" not in ldd
+
+
+def test_content_hash_sees_any_single_edit_and_ignores_thread_count(pkg, monkeypatch):
+    """The strict matrix-cache policy (include/cgb200.h) rests on this hash: host only."""
+    L = pkg.lib()
+    s = H.banded(3000, 40)      # ~240k entries: several words per hashing lane, one 4 MiB piece
+    A = pkg.MvSparse(s.n, s.nnz, H.dptr(s.vals), H.iptr(s.cols), H.iptr(s.row_ptr))
+    h0 = L.cgb200_content_hash(C.byref(A))
+    assert h0 != 0 and L.cgb200_content_hash(C.byref(A)) == h0
+    rng = np.random.default_rng(5)
+    for k in list(rng.integers(0, s.nnz, 40)) + [0, s.nnz - 1]:
+        old = s.vals[k]
+        s.vals[k] = np.nextafter(old, 2 * old + 1)      # one ulp
+        assert L.cgb200_content_hash(C.byref(A)) != h0, k
+        s.vals[k] = old
+    for k in (0, s.nnz // 3, s.nnz - 1):
+        s.cols[k] ^= 1
+        assert L.cgb200_content_hash(C.byref(A)) != h0
+        s.cols[k] ^= 1
+    s.row_ptr[s.n // 2] += 1
+    assert L.cgb200_content_hash(C.byref(A)) != h0
+    s.row_ptr[s.n // 2] -= 1
+    assert L.cgb200_content_hash(C.byref(A)) == h0
+    # a matrix larger than one piece: the same hash with 1 and with many threads
+    big = H.lap(700, 700)       # 2.4 M entries: 19 MB of values, 5 pieces
+    B = pkg.MvSparse(big.n, big.nnz, H.dptr(big.vals), H.iptr(big.cols), H.iptr(big.row_ptr))
+    monkeypatch.setenv("CGB200_HASH_THREADS", "1")
+    h1 = L.cgb200_content_hash(C.byref(B))
+    monkeypatch.setenv("CGB200_HASH_THREADS", "7")
+    assert L.cgb200_content_hash(C.byref(B)) == h1
+    big.vals[big.nnz - 5] = 3.0
+    assert L.cgb200_content_hash(C.byref(B)) != h1
+    assert L.cgb200_content_hash(None) == 0

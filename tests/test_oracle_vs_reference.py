@@ -32,6 +32,20 @@ def test_loop_bitwise(mk, M):
     assert np.array_equal(_bits(H.ref_cg(s, M)), _bits(H.oracle_cg(s, M)[0]))
 
 
+@pytest.mark.parametrize("mk,M", [(lambda: H.lap(16, 16), 40), (lambda: H.lap(6, 5, 4), 12), (lambda: H.banded(200, 9), 8)])
+def test_negative_definite_system_is_not_a_breakdown(mk, M):
+    # the reference divides by p.Ap regardless of its sign (cg.c:113): on (-A, -b) it walks the
+    # iterates of (A, b).  The product's breakdown guard (oracle guard = 1 restates it) must let a
+    # negative p.Ap through and stop only where the division has no finite result.
+    s = mk()
+    neg = H.negated(s)
+    x_ref = H.ref_cg(neg, M)
+    x_g, it, _, st = H.oracle_cg(neg, M, guard=1)
+    assert st == 0 and it == M + 1
+    assert np.array_equal(_bits(x_ref), _bits(x_g))
+    assert np.array_equal(_bits(x_ref), _bits(H.ref_cg(s, M)))  # same x, bit for bit: signs cancel
+
+
 def test_reference_runs_its_own_operators():
     # libcgb200.so exports the same symbol names by design; the reference library must not bind to
     # them (oracle/Makefile links it -Bsymbolic).  A CPU-only box proves it: the product's
