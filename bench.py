@@ -27,6 +27,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+PARITY_MAX_ITER = 4   # conj_grad(4, ...) = 5 iterations: what the dense system needs to reach 1e-10
 METRIC = "cg_iterations_per_second"
 UNIT = "it/s"
 
@@ -48,7 +49,7 @@ def traffic_from_profiles(kernel, workload, world):
     launch shape (same workload, 1 GPU), or None."""
     if world != 1:
         return None
-    key = {"dense32768": "dense", "lap3d512": "lap3d512", "lap2d4096": "lap2d"}.get(workload)
+    key = {"dense32768": "dense", "lap3d512": "lap3d512", "lap2d4096": "lap2d", "banded52269": "banded52269"}.get(workload)
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             return json.load(f)["_by_workload"][key][kernel]
@@ -278,9 +279,9 @@ def long_row_leg(pkg, peak, peak_src, variant, K=300):
                                   "BASELINE config)", "n": n, "nnz": int(len(vals)), "matvec": "CSR long-row SpMV (k_spmv_rowblock)",
                       "l2": "inputs larger than L2 (217 MB matrix streamed every iteration)"},
            "roofline": {"bound": "hbm", "kernel": "k_spmv_rowblock", "achieved": round(k1b / (k1 * 1e-3) / 1e9, 1),
-                        "peak": peak, "unit": "GB/s", "frac": round(k1b / (k1 * 1e-3) / 1e9 / peak, 4), "traffic": 233068032,
-                        "algorithmic_bytes_per_launch": k1b, "avg_launch_ms": round(k1, 5), "peak_source": peak_src,
-                        "traffic_source": "profiles/r01f_ncu_longrow.md (32-row form of the same kernel)"}}
+                        "peak": peak, "unit": "GB/s", "frac": round(k1b / (k1 * 1e-3) / 1e9 / peak, 4),
+                        "traffic": traffic_from_profiles("k_spmv_rowblock", "banded52269", 1),
+                        "algorithmic_bytes_per_launch": k1b, "avg_launch_ms": round(k1, 5), "peak_source": peak_src}}
     d.free()
     return out
 
@@ -310,25 +311,37 @@ def time_to_solution(pkg, d, info, world, variant=0, tol=1e-10, fixed=None, cap=
     return out
 
 
+DENSE_ITERS_PER_TIMED_LAUNCH = 5   # csrc/solver.cu: TIME_KERNEL_DENSE_ITERS
+
+
 def roofline_for(pkg, d, peak, peak_src, kernel_name, workload, world, variant=0):
     it_b, k1_b = d.bytes()
+    extra = {}
     if variant == 0 and d.one_kernel_iteration():
-        # dense path: the whole classic iteration is ONE launch (k_cg_dense_iter) -- its algorithmic
-        # bytes are the contract bytes of an iteration (A + 88 n)
-        kernel_name, alg, which = "k_cg_dense_iter", it_b, 6
-        what = "the one-kernel iteration (matvec, both reductions, both vector updates)"
+        # dense path: a whole classic solve is ONE persistent launch (k_cg_dense_solve); timed as launches
+        # of 5 iterations each (what a 1e-10 solve of this system takes); time_kernel returns ms per
+        # iteration.  Algorithmic bytes of a launch = 5 x the contract bytes of an iteration (A + 88 n).
+        m = DENSE_ITERS_PER_TIMED_LAUNCH
+        kernel_name, which = "k_cg_dense_solve", 6
+        t_it = d.time_kernel(which, 12)
+        alg, t1 = it_b * m, t_it * m
+        extra = {"iterations_per_launch": m, "ms_per_iteration": round(t_it, 5)}
+        what = f"the persistent dense solve kernel, {m} iterations per launch (matvec, both reductions, both vector updates each), cross-GPU steps switched off"
+        reps = 12
     else:
-        alg, which, what = k1_b, 1, "the matvec kernel"
-    t1 = d.time_kernel(which, 30)
+        alg, which, what, reps = k1_b, 1, "the matvec kernel", 30
+        t1 = d.time_kernel(which, reps)
     ach = alg / (t1 * 1e-3) / 1e9
-    return {
+    out = {
         "bound": "hbm", "kernel": kernel_name, "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
         "frac": round(ach / peak, 4), "traffic": traffic_from_profiles(kernel_name, workload, world),
         "algorithmic_bytes_per_launch": alg, "avg_launch_ms": round(t1, 5),
         "peak_source": peak_src,
-        "how": "CUDA events on the library's solve stream around 30 back-to-back launches of "
+        "how": f"CUDA events on the library's solve stream around {reps} back-to-back launches of "
                + what + " (this rank's block), after 3 warm-ups",
     }
+    out.update(extra)
+    return out
 
 
 # -------------------------------------------------------------------------------------------------
@@ -429,11 +442,25 @@ def e2e_host_structs(pkg, d, info, J, solves=8):
         L.cgb200_free_all(xp)
         return res.iterations, chk
 
+    b0 = bnp.copy()
     t = time.perf_counter()
     it_cold, _ = one()                       # uploads A (8 B/nnz on the dense path) + b
     cold_s = time.perf_counter() - t
     rng = np.random.default_rng(3)
     bs = [rng.random(n) - 0.5 for _ in range(solves)]
+    # (a) an unmodified caller: default policy CGB200_CACHE_STRICT -- every call re-validates the device
+    #     copy against every byte of the host arrays (a caller may have edited them in place)
+    it_strict = 0
+    t = time.perf_counter()
+    for i in range(2):
+        bnp[:] = bs[i]
+        it, _ = one()
+        it_strict += it
+    strict_s = time.perf_counter() - t
+    # (b) a caller that solves repeatedly with one matrix hands it over once: cgb200_to_device(A) pins
+    #     the device copy until cgb200_invalidate (include/cgb200.h); the headline e2e figure
+    assert L.cgb200_to_device(C.byref(A)) == 0, pkg.last_error()
+    one()
     iters = 0
     t = time.perf_counter()
     for i in range(solves):
@@ -441,6 +468,15 @@ def e2e_host_structs(pkg, d, info, J, solves=8):
         it, _ = one()
         iters += it
     warm_s = time.perf_counter() - t
+    # parity: the reference's own entry point with the reference's fixed count on the SAME host
+    # arrays the CPU legs use (device generator == oracle generator, tests/test_gpu_parity.py)
+    x_par = None
+    if info["kind"] == "dense":
+        bnp[:] = b0
+        xp = pkg.MvSparseP()
+        assert L.conj_grad(PARITY_MAX_ITER, C.byref(A), C.byref(b), C.byref(xp)) == 0, pkg.last_error()
+        x_par = np.ctypeslib.as_array(xp.contents.values, shape=(n,)).copy()
+        L.cgb200_free_all(xp)
     try:
         ops = operator_api_loop(pkg, A, b, bnp, bs, int(round(iters / solves)))
     except Exception as e:  # noqa: BLE001
@@ -452,14 +488,20 @@ def e2e_host_structs(pkg, d, info, J, solves=8):
         "value": round(iters / warm_s, 2), "unit": UNIT,
         "h2d_bytes_per_step": round(8 * n / per_solve_iters, 1),
         "d2h_bytes_per_step": round(8 * n / per_solve_iters, 1),
-        "api": "cgb200_solve(struct __mv_sparse* A, b, &x) == conj_grad with tol 1e-10; host arrays pinned",
+        "api": "cgb200_to_device(A) once, then cgb200_solve(struct __mv_sparse* A, b, &x) == conj_grad with tol 1e-10 per solve; host arrays pinned; b in and x out every solve",
         "solves": solves, "iterations_per_solve": per_solve_iters,
+        "strict_cache_value": round(it_strict / strict_s, 3),
+        "cold_first_call_value": round(it_cold / cold_s, 3),
         "per_solve": {"h2d_bytes": 8 * n, "d2h_bytes": 8 * n, "ms": round(warm_s / solves * 1e3, 3)},
+        "strict_cache": {"value": round(it_strict / strict_s, 3), "unit": UNIT, "solves": 2,
+                         "note": "default policy for an unmodified caller: every call hashes every byte of A's host arrays "
+                                 "(several host threads) before trusting the device copy"},
         "cold_first_call": {"value": round(it_cold / cold_s, 3), "unit": UNIT, "seconds": round(cold_s, 3),
-                            "h2d_bytes": a_bytes + 8 * n, "note": "includes uploading A"},
-        "note": "A stays device-resident between calls while its struct is unchanged (fingerprinted); every solve copies b in and x out",
+                            "h2d_bytes": a_bytes + 8 * n, "note": "includes uploading A and hashing it"},
+        "note": "value: A pinned on the device by cgb200_to_device (the documented path for repeated solves); "
+                "strict_cache_value: no such call, A re-validated byte for byte on every call; cold_first_call_value: A uploaded",
         "operator_api": ops,
-    }
+    }, x_par
 
 
 def e2e_row_blocks(pkg, name, rank, world, J, solves=8):
@@ -518,7 +560,10 @@ def e2e_row_blocks(pkg, name, rank, world, J, solves=8):
 # -------------------------------------------------------------------------------------------------
 
 
-def cpu_reference_run(workload, budget_s, want_steps, host_arrays=None):
+REF_X_FILE = "/tmp/cgb200_reference_x_dense32768_maxiter4.npy"
+
+
+def cpu_reference_run(workload, budget_s, want_steps, host_arrays=None, x_out=None):
     """Times the reference's own CPU implementation on the host cores.
 
     oracle/_ref/libcgref.so (the UNMODIFIED reference, gcc -g as its Makefile builds it) when
@@ -540,7 +585,7 @@ def cpu_reference_run(workload, budget_s, want_steps, host_arrays=None):
     have_ref = H.have_ref()
     kind = "reference" if have_ref else "port"
 
-    def run(max_iter):
+    def run(max_iter, keep=False):
         t = time.perf_counter()
         if have_ref:
             R = H.ref()
@@ -548,18 +593,34 @@ def cpu_reference_run(workload, budget_s, want_steps, host_arrays=None):
             bv = H.MvSparse(n, n, H.dptr(b), None, None)
             xp = H.MvSparseP()
             assert R.conj_grad(max_iter, C.byref(A), C.byref(bv), C.byref(xp)) == 0
+            dt = time.perf_counter() - t
+            x = np.ctypeslib.as_array(xp.contents.values, shape=(n,)).copy() if keep else None
             x0 = float(xp.contents.values[0])
         else:
             x = np.empty(n)
             H.oracle().oracle_conj_grad(n, H.iptr(rp), H.iptr(ci), H.dptr(va), H.dptr(b), max_iter, 0.0, 1,
                                         H.dptr(x), None, None)
+            dt = time.perf_counter() - t
             x0 = float(x[0])
-        return time.perf_counter() - t, x0
+        return dt, x0, x
 
-    t1, _ = run(0)  # one iteration: calibration and warm-up
-    m = int(max(1, min(want_steps, budget_s // max(t1, 1e-3))))
-    m = min(m, 5)   # fixed-count CG on this matrix is past convergence after ~6 iterations
-    tm, _ = run(m - 1)
+    if x_out:
+        # b200 arm's cpu_baseline leg: ONE run of max_iter = 4 (5 iterations, the count a 1e-10 solve
+        # needs) serves as the timed sample and as the reference solution of the parity check
+        t1 = 0.0
+        m = 5
+        tm, _, xr = run(m - 1, keep=True)
+        np.save(x_out, xr)
+    else:
+        t1, _, _ = run(0)  # one iteration: calibration and warm-up
+        m = int(max(1, min(want_steps, budget_s // max(t1, 1e-3))))
+        m = min(m, 5)   # fixed-count CG on this matrix is past convergence after ~6 iterations
+        tm, _, xr = run(m - 1, keep=True)
+        if m == 5:      # the reference arm leaves its x where the b200 arm of the same lease finds it
+            try:
+                np.save(REF_X_FILE, xr)
+            except Exception:  # noqa: BLE001
+                pass
     val = m / tm
     # beside it, for context: the same loop as a tuned CPU program would run it -- O(nnz) CSR matvec,
     # fused passes, OpenMP over all host cores (oracle_cg_iterations_mt; timing only, its reduction
@@ -583,9 +644,12 @@ def cpu_reference_run(workload, budget_s, want_steps, host_arrays=None):
         port = {"error": repr(e)}
     cb = {
         "value": round(val, 5), "unit": UNIT, "cores": 1, "kind": kind, "tuned_port_all_cores": port,
-        "sample": f"{m} iteration(s) (max_iter={m - 1}) of {'the unmodified reference conj_grad (oracle/_ref, gcc -g as its Makefile)' if have_ref else 'the oracle port (oracle/cg_oracle.c, -O2)'} on the full dense n=32768 CSR system, after a 1-iteration warm-up ({t1:.1f} s)",
+        "sample": f"{m} iteration(s) (max_iter={m - 1}) of {'the unmodified reference conj_grad (oracle/_ref, gcc -g as its Makefile)' if have_ref else 'the oracle port (oracle/cg_oracle.c, -O2)'} on the full dense n=32768 CSR system"
+                  + (f", after a 1-iteration warm-up ({t1:.1f} s)" if t1 else "; the x it returns is the reference solution of the bench line's parity check"),
         "seconds": round(tm, 2),
     }
+    if xr is not None:
+        cb["x_l2"] = float(np.linalg.norm(xr))
     return cb, m, tm
 
 
@@ -608,23 +672,132 @@ def reference_arm(args):
     return 0
 
 
-def workload_config(name, world):
+def workload_config(name, world=1):
+    """The workload, named the same way by both arms (the driver compares the two `config` dicts);
+    how a run was partitioned and which kernels it took is reported beside it under `run`."""
     cfgs = {
         "dense32768": {"workload": "dense SPD n=32768 fp64 (diagonally dominant, synthetic), CG to rel. residual 1e-10 (BASELINE configs[1])",
-                       "n": 32768, "nnz": 32768 ** 2, "matvec": "values-only row-block GEMV", "partition": f"row blocks x{world}",
+                       "n": 32768, "nnz": 32768 ** 2, "matvec": "values-only row-block GEMV",
                        "l2": "inputs larger than L2 (8.6 GB matrix streamed every iteration)"},
         "lap2d4096": {"workload": "2D 5-point Poisson 4096x4096 CSR fp64 (BASELINE configs[2])", "n": 4096 ** 2,
                       "matvec": "CSR stream SpMV", "l2": "inputs larger than L2 (2.5 GB per iteration)"},
         "lap3d512": {"workload": "3D 7-point Laplacian 512^3 CSR fp64 (BASELINE configs[3])", "n": 512 ** 3,
-                     "matvec": "CSR stream SpMV", "partition": f"z-slabs x{world}, halo exchange", "l2": "inputs larger than L2"},
+                     "matvec": "CSR stream SpMV", "l2": "inputs larger than L2"},
         "lap3d384w": {"workload": "3D 7-point Laplacian 384^3 per GPU, weak scaling (BASELINE configs[4])",
-                      "n": 384 ** 3 * world, "matvec": "CSR stream SpMV", "partition": f"z-slabs x{world}, halo exchange",
-                      "l2": "inputs larger than L2"},
+                      "n_per_gpu": 384 ** 3, "matvec": "CSR stream SpMV", "l2": "inputs larger than L2"},
     }
     return cfgs[name]
 
 
+PARTITION = {"dense32768": "row blocks", "lap2d4096": "one block", "lap3d512": "z-slabs, halo exchange",
+             "lap3d384w": "z-slabs, halo exchange"}
+
+
 # -------------------------------------------------------------------------------------------------
+
+
+def comm_report(pkg, d, info, world, ms_per_step, roof, comm_mode):
+    """Row R of the scope table: what crosses NVLink per iteration and how much of an iteration is
+    communication that nothing hides.  exposed = device time per iteration of the real loop minus
+    the device time of the same kernels run back to back with every cross-GPU step disabled
+    (cgb200_system_time_kernel: no push, no wait, no sum) -- it therefore also contains the
+    per-solve set-up (right-hand side, loop entry) of the short dense solves."""
+    if world <= 1:
+        return None
+    out_b = d.comm_bytes()
+    it_us = ms_per_step * 1e3
+    if roof["kernel"] == "k_cg_dense_solve":
+        alone_us = roof["ms_per_iteration"] * 1e3
+        kernels = "k_cg_dense_solve with the cross-GPU steps switched off"
+    else:
+        alone_us = sum(d.time_kernel(w, 30) for w in (1, 2, 3)) * 1e3
+        kernels = "K1 + K2 + K3 alone"
+    gbs = out_b / (it_us * 1e-6) / 1e9
+    wire_us = out_b / 900e9 * 1e6
+    return {
+        "mode": comm_mode, "nvlink_bytes_out_per_iter_per_gpu": out_b, "nvlink_gbs_per_gpu": round(gbs, 3),
+        "frac_of_900": round(gbs / 900.0, 6), "wire_us_at_900": round(wire_us, 3),
+        "iter_us": round(it_us, 2), "compute_only_us": round(alone_us, 2),
+        "exposed_us_per_iter": round(it_us - alone_us, 2), "compute_only": kernels,
+        "note": "latency-bound: the messages are tiny against 900 GB/s/direction, what matters is exposed_us_per_iter "
+                "(rank 0's block; loop time minus the same kernels with the exchange switched off)",
+    }
+
+
+def dense_phase_trace(pkg, d, world, sm_mhz):
+    """Phase trace of the dense one-kernel iteration (cgb200_system_trace) over 40 short solves: where
+    the cross-GPU steps sit inside the launch, in microseconds (SM cycles / sampled SM clock)."""
+    L = pkg.lib()
+    if not d.one_kernel_iteration() or not sm_mhz:
+        return None
+    out = (C.c_ulonglong * (16 + 2048))()
+    if L.cgb200_system_trace(d.h, 1, None) != 0:
+        return None
+    for k in range(40):
+        d.gen_rhs(300 + k)
+        d.solve(4, check_every=5)
+    if L.cgb200_system_trace(d.h, 0, out) != 0:
+        return None
+    cnt = max(int(out[7]), 1)
+    us = lambda i: out[i] / cnt / sm_mhz  # noqa: E731
+    return {"launches": cnt, "wait_for_peers_p_us": round(us(0), 2), "gemv_done_us": round(us(1), 2),
+            "sum1_alpha_us": round(us(3) - us(1), 2), "xr_update_us": round(us(4) - us(3), 2),
+            "sum2_beta_us": round(us(5) - us(4), 2), "p_update_push_us": round(us(6) - us(5), 2),
+            "note": "closing CTA's clock64 per phase / sampled SM MHz; sums include the grid reduction and, with several GPUs, the cross-GPU exchange"}
+
+
+def parity_multi(pkg, rank, world, comm_mode):
+    """N > 1: the ranks solve mid-size systems together, rank 0 gathers x and compares it with the CPU
+    oracle's x for the whole system (oracle/: checker only, rank 0 only)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    cases = []
+
+    def gather(d, nloc):
+        xl = torch.from_numpy(d.x()).cuda()
+        parts = [torch.empty(nloc, dtype=torch.float64, device="cuda") for _ in range(world)]
+        dist.all_gather(parts, xl)
+        return torch.cat(parts).cpu().numpy()
+
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import helpers as H
+    # (1) 3D 7-point Laplacian, z-slabs with halo exchange, fixed count (the reference's semantics)
+    nx, ny, nzl, K = 96, 96, 12, 60
+    d = pkg.DeviceSystem.lap(nx, ny, nzl * world, rank * nzl, nzl)
+    r = d.solve(K - 1)
+    x = gather(d, nx * ny * nzl)
+    d.free()
+    if rank == 0:
+        sm = H.lap(nx, ny, nzl * world)
+        xo, it, _, _ = H.oracle_cg(sm, K - 1)
+        cases.append({"system": f"lap3d {nx}x{ny}x{nzl * world}", "K": int(r.iterations), "K_oracle": int(it),
+                      "rel_l2": float(np.linalg.norm(x - xo) / np.linalg.norm(xo))})
+    # (2) dense SPD, row blocks with an all-gather of p, tolerance stop
+    n = 2048
+    nl = n // world
+    d = pkg.DeviceSystem.dense(n, rank * nl, nl)
+    r = d.solve(200, tol=1e-10)
+    x = gather(d, nl)
+    d.free()
+    if rank == 0:
+        sm = H.dense(n)
+        xo, it, _, _ = H.oracle_cg(sm, 200, tol=1e-10, guard=1)
+        cases.append({"system": f"dense {n}", "K": int(r.iterations), "K_oracle": int(it),
+                      "rel_l2": float(np.linalg.norm(x - xo) / np.linalg.norm(xo)),
+                      "relres_true": float(H.true_relres(sm, x))})
+    if rank != 0:
+        return None
+    worst = max(c["rel_l2"] for c in cases)
+    return {"world": world, "comm": comm_mode, "rel_l2": worst, "tol": 1e-8, "ok": bool(worst <= 1e-8),
+            "iterations_equal": all(abs(c["K"] - c["K_oracle"]) <= 2 for c in cases), "cases": cases,
+            "checker": "oracle/cg_oracle.c restatement (pinned bitwise to the reference), whole system on rank 0"}
+
+
+def compact(v, nd=4):
+    return None if v is None else float(f"{v:.{nd}g}")
 
 
 def main():
@@ -640,12 +813,16 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-tts", action="store_true", help="skip the time-to-solution solves (profiling runs)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity legs")
+    ap.add_argument("--with-other-variant", action="store_true",
+                    help="also time the other recurrence on every workload (it wins nowhere: DESIGN.md section 4)")
     ap.add_argument("--cpu-leg", action="store_true", help="internal: print the cpu_baseline object only")
+    ap.add_argument("--x-out", default=None, help="internal: where the cpu leg leaves the reference's x")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
     if args.cpu_leg:
-        cb, _, _ = cpu_reference_run(args.workload, budget_s=20.0, want_steps=2)
+        cb, _, _ = cpu_reference_run(args.workload, budget_s=20.0, want_steps=2, x_out=args.x_out)
         print(json.dumps(cb), flush=True)
         return 0
 
@@ -667,6 +844,7 @@ def main():
     pkg = g.load_package()
     L = pkg.lib()
     assert L.cgb200_init(local_rank) == 0, pkg.last_error()
+
     if world > 1:
         import torch.distributed as dist
 
@@ -693,17 +871,18 @@ def main():
     clocks = sampler.summary(tm["t0"], tm["t1"]) if sampler else None
     it_b, k1_b = d.bytes()
     value = tm["steps"] / (tm["ms"] * 1e-3)
+    ms_step = tm["ms"] / tm["steps"]
     kname = "k_gemv_units" if info["kind"] == "dense" else "k_spmv_stream"
     roof = roofline_for(pkg, d, peak, peak_src, kname, args.workload, world, variant)
-    iter_gbs = it_b / (tm["ms"] / tm["steps"] * 1e-3) / 1e9
-    true_rr = d.true_relres() if info["kind"] != "dense" else None
+    iter_gbs = it_b / (ms_step * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": tm["steps"],
-        "warmup": tm["warmup"], "ms_per_step": round(tm["ms"] / tm["steps"], 5), "higher_is_better": True,
+        "warmup": tm["warmup"], "ms_per_step": round(ms_step, 5), "higher_is_better": True,
         "scaling": info["scaling"], "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": dict(workload_config(args.workload, world), iterations_per_solve=runner.J,
-                       variant=args.variant, comm=comm,
-                       kernels_per_iteration=1 if roof["kernel"] == "k_cg_dense_iter" else (3 if variant == 0 else 2)),
+        "config": workload_config(args.workload),
+        "run": {"iterations_per_solve": runner.J, "variant": args.variant, "comm": comm,
+                "partition": f"{PARTITION[args.workload]} x{world}",
+                "kernels_per_iteration": 1 if roof["kernel"].startswith("k_cg_dense") else (3 if variant == 0 else 2)},
         "roofline": roof,
         "iteration": {"contract_bytes_per_rank": it_b, "achieved_gbs_per_gpu": round(iter_gbs, 1),
                       "frac_of_peak": round(iter_gbs / peak, 4),
@@ -711,6 +890,30 @@ def main():
         "gpu_launches": tm["launches"],
         "clocks": clocks,
     }
+    summary = {}
+
+    def summarise(name, it_s, frac_iter, frac_k1, tts):
+        e = {"it_s": compact(it_s), "frac_iter": compact(frac_iter), "frac_k1": compact(frac_k1)}
+        if tts and "iterations" in tts:
+            e["tts_s"], e["iters"] = compact(tts["seconds"]), tts["iterations"]
+            if tts.get("relres_true") is not None:
+                e["relres"] = compact(tts["relres_true"], 3)
+        summary[name] = e
+
+    comm_obj = None
+    try:
+        comm_obj = comm_report(pkg, d, info, world, ms_step, roof, comm)
+        if comm_obj is not None:
+            tr = dense_phase_trace(pkg, d, world, (clocks or {}).get("sm_mhz"))
+            if tr:
+                comm_obj["dense_phase_trace"] = tr
+            line["comm"] = comm_obj
+            # flat copies inside an object the driver keeps whole
+            roof["nvlink_bytes_out_per_iter_per_gpu"] = comm_obj["nvlink_bytes_out_per_iter_per_gpu"]
+            roof["nvlink_frac_of_900"] = comm_obj["frac_of_900"]
+            roof["exposed_comm_us_per_iter"] = comm_obj["exposed_us_per_iter"]
+    except Exception as e:  # noqa: BLE001
+        line["comm"] = {"error": repr(e)}
     J = runner.J
     try:
         if not args.no_tts:
@@ -718,6 +921,7 @@ def main():
                                                         fixed=500 if args.workload == "lap3d384w" else None)
     except Exception as e:  # noqa: BLE001
         line["time_to_solution"] = {"error": repr(e)}
+    summarise(args.workload, value, iter_gbs / peak, roof["frac"], line.get("time_to_solution"))
     # the other recurrence on the same system, same K (explains, does not replace, the headline)
     try:
         other = Runner(pkg, d, info, 1 - variant)
@@ -730,18 +934,28 @@ def main():
     d.free()
 
     # ---- end to end with host buffers ----
+    x_par = None
     if not args.no_e2e:
         try:
             if world == 1:
                 d2, info2 = make_system(pkg, args.workload, 0, 1)
                 J2 = J if J else 50
-                line["e2e"] = e2e_host_structs(pkg, d2, info2, J2)
-                host_arrays = None
+                line["e2e"], x_par = e2e_host_structs(pkg, d2, info2, J2)
                 d2.free()
             else:
                 line["e2e"] = e2e_row_blocks(pkg, args.workload, rank, world, J if J else 50)
         except Exception as e:  # an honest gap beats a crashed bench line
             line["e2e"] = {"value": None, "unit": UNIT, "error": repr(e)}
+
+    # ---- parity with the CPU checker on mid-size systems, all ranks (N > 1) ----
+    pm = None
+    if world > 1 and not args.no_parity:
+        try:
+            pm = parity_multi(pkg, rank, world, comm)
+        except Exception as e:  # noqa: BLE001
+            pm = {"error": repr(e), "ok": False}
+        if pm is not None:
+            line["parity_multi"] = pm
 
     # ---- the other BASELINE configs, same run ----
     if not args.no_extras:
@@ -756,23 +970,34 @@ def main():
                 k = 300 if nm == "lap2d4096" else 100
                 tx = timed_steps(pkg, rx, k, 5, world)
                 ib, _ = dx.bytes()
-                gbs = ib / (tx["ms"] / tx["steps"] * 1e-3) / 1e9
+                msx = tx["ms"] / tx["steps"]
+                gbs = ib / (msx * 1e-3) / 1e9
                 ex = {"value": round(tx["steps"] / (tx["ms"] * 1e-3), 2), "unit": UNIT, "steps": tx["steps"],
-                      "ms_per_step": round(tx["ms"] / tx["steps"], 5), "scaling": ix["scaling"],
+                      "ms_per_step": round(msx, 5), "scaling": ix["scaling"],
                       "achieved_gbs_per_gpu": round(gbs, 1), "frac_of_peak": round(gbs / peak, 4),
-                      "config": workload_config(nm, world)}
+                      "config": workload_config(nm), "partition": f"{PARTITION[nm]} x{world}"}
                 ex["roofline"] = roofline_for(pkg, dx, peak, peak_src, "k_spmv_stream", nm, world)
+                try:
+                    cx = comm_report(pkg, dx, ix, world, msx, ex["roofline"], comm)
+                    if cx is not None:
+                        ex["comm"] = cx
+                except Exception as e:  # noqa: BLE001
+                    ex["comm"] = {"error": repr(e)}
                 try:
                     if not args.no_tts:
                         ex["time_to_solution"] = time_to_solution(pkg, dx, ix, world, variant,
                                                                   fixed=500 if nm == "lap3d384w" else None)
                 except Exception as e:  # noqa: BLE001
                     ex["time_to_solution"] = {"error": repr(e)}
-                ry = Runner(pkg, dx, ix, 1 - variant)
-                ty = timed_steps(pkg, ry, k, 5, world)
-                ex["other_variant"] = {"variant": "classic" if variant else "single-reduction",
-                                       "value": round(ty["steps"] / (ty["ms"] * 1e-3), 2),
-                                       "ms_per_step": round(ty["ms"] / ty["steps"], 5)}
+                summarise(nm, ex["value"], gbs / peak, ex["roofline"]["frac"], ex.get("time_to_solution"))
+                if ex.get("comm") and "exposed_us_per_iter" in ex["comm"]:
+                    summary[nm]["exposed_us"] = ex["comm"]["exposed_us_per_iter"]
+                if args.with_other_variant:
+                    ry = Runner(pkg, dx, ix, 1 - variant)
+                    ty = timed_steps(pkg, ry, k, 5, world)
+                    ex["other_variant"] = {"variant": "classic" if variant else "single-reduction",
+                                           "value": round(ty["steps"] / (ty["ms"] * 1e-3), 2),
+                                           "ms_per_step": round(ty["ms"] / ty["steps"], 5)}
                 # the same system in the row-pattern dictionary format: reported beside,
                 # never instead of, the contract figures above -- its iteration streams fewer bytes
                 try:
@@ -786,7 +1011,7 @@ def main():
                         ex["pattern_format"] = {
                             "value": round(tp["steps"] / (tp["ms"] * 1e-3), 2), "unit": UNIT,
                             "ms_per_step": round(ms_p, 5),
-                            "speedup_vs_csr": round((tx["ms"] / tx["steps"]) / ms_p, 3),
+                            "speedup_vs_csr": round(msx / ms_p, 3),
                             "bytes_per_iteration": pb, "csr_contract_bytes_per_iteration": csr_bytes,
                             "achieved_gbs_per_gpu": round(pb / (ms_p * 1e-3) / 1e9, 1),
                             "frac_of_peak": round(pb / (ms_p * 1e-3) / 1e9 / peak, 4),
@@ -796,6 +1021,7 @@ def main():
                             "note": "one byte per row + shared-memory dictionary instead of 12 bytes per entry; same "
                                     "arithmetic, s = A p bit-identical to the CSR kernel (tests/test_gpu_parity.py)",
                         }
+                        summary[nm]["pattern_it_s"] = compact(ex["pattern_format"]["value"])
                         dx.use_pattern_format(False)
                     else:
                         ex["pattern_format"] = {"applicable": False, "why": pkg.last_error()}
@@ -808,6 +1034,8 @@ def main():
         if world == 1:
             try:
                 extras["banded52269"] = long_row_leg(pkg, peak, peak_src, variant)
+                bx = extras["banded52269"]
+                summarise("banded52269", bx["value"], bx["frac_of_peak"], bx["roofline"]["frac"], None)
             except Exception as e:  # noqa: BLE001
                 extras["banded52269"] = {"error": repr(e)}
         line["workloads"] = extras
@@ -815,15 +1043,64 @@ def main():
     if sampler:
         sampler.stop()
 
-    # ---- CPU baseline (rank 0, N = 1 only; the one leg that runs oracle/) ----
+    # ---- CPU baseline (rank 0, N = 1 only; the one leg that runs oracle/) and parity against its x ----
+    x_ref_path = None
     if world == 1 and not args.no_cpu and args.workload == "dense32768":
+        x_ref_path = f"/tmp/cgb200_cpu_leg_x_{os.getpid()}.npy"
         try:
             # a fresh process that never loads libcgb200.so: the reference must run its own operators
-            out = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-leg", "--workload", args.workload],
-                                 stdout=subprocess.PIPE, text=True, timeout=900)
+            out = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-leg", "--workload", args.workload,
+                                  "--x-out", x_ref_path], stdout=subprocess.PIPE, text=True, timeout=900)
             line["cpu_baseline"] = json.loads(out.stdout.strip().splitlines()[-1])
         except Exception as e:
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "error": repr(e)}
+    if world == 1 and not args.no_parity and x_par is not None:
+        import numpy as np
+
+        par = {"config": "dense SPD n=32768 (BASELINE configs[1]), same host arrays", "K": PARITY_MAX_ITER + 1,
+               "call": f"conj_grad({PARITY_MAX_ITER}, A, b, &x) through libcgb200.so vs the unmodified reference's conj_grad",
+               "tol": 1e-8}
+        srcs = []
+        if x_ref_path and os.path.exists(x_ref_path):
+            srcs.append(("cpu_baseline leg of this run (oracle/_ref)", x_ref_path))
+        if os.path.exists(REF_X_FILE):
+            srcs.append(("--impl reference arm of this lease", REF_X_FILE))
+        for what, path in srcs:
+            try:
+                xr = np.load(path)
+                rel = float(np.linalg.norm(x_par - xr) / np.linalg.norm(xr))
+                par.setdefault("against", []).append({"x_from": what, "rel_l2": rel})
+                par["rel_l2"] = max(par.get("rel_l2", 0.0), rel)
+            except Exception as e:  # noqa: BLE001
+                par.setdefault("against", []).append({"x_from": what, "error": repr(e)})
+        if "rel_l2" in par:
+            par["ok"] = bool(par["rel_l2"] <= 1e-8)
+            line["parity"] = par
+            if isinstance(line.get("e2e"), dict):
+                line["e2e"]["parity_rel_l2_vs_reference"] = par["rel_l2"]
+            if isinstance(line.get("cpu_baseline"), dict):
+                line["cpu_baseline"]["parity_rel_l2_gpu_vs_this_x"] = par["rel_l2"]
+        try:
+            if x_ref_path:
+                os.remove(x_ref_path)
+        except OSError:
+            pass
+
+    # ---- compact tail: what the driver's 1500-character window must still show ----
+    tail = {"n_gpus": world, "workloads": summary}
+    if isinstance(line.get("e2e"), dict) and line["e2e"].get("value") is not None:
+        e = line["e2e"]
+        tail["e2e"] = {"pinned": e["value"], "strict": e.get("strict_cache_value"), "cold": e.get("cold_first_call_value")}
+    if "parity" in line:
+        tail["parity"] = {"dense32768_K5_vs_reference_rel_l2": compact(line["parity"]["rel_l2"], 3), "tol": 1e-8}
+    if pm is not None:
+        tail["parity_multi"] = {"world": world, "comm": comm, "rel_l2": compact(pm.get("rel_l2"), 3) if "rel_l2" in pm else None,
+                                "ok": pm.get("ok")}
+    if comm_obj is not None:
+        tail["comm"] = {"nvlink_bytes_per_iter": comm_obj["nvlink_bytes_out_per_iter_per_gpu"],
+                        "nvlink_gbs": comm_obj["nvlink_gbs_per_gpu"], "frac_of_900": comm_obj["frac_of_900"],
+                        "exposed_us_per_iter": comm_obj["exposed_us_per_iter"]}
+    line["summary"] = tail
 
     if world > 1:
         import torch.distributed as dist

@@ -167,6 +167,9 @@ def lib():
     L.cgb200_system_true_relres.argtypes = [C.c_void_p, c_double_p]
     L.cgb200_system_time_kernel.argtypes = [C.c_void_p, C.c_int, C.c_int, c_double_p]
     L.cgb200_system_bytes.argtypes = [C.c_void_p, c_double_p, c_double_p]
+    L.cgb200_system_comm_bytes.restype = C.c_double
+    L.cgb200_system_comm_bytes.argtypes = [C.c_void_p]
+    L.cgb200_system_trace.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_ulonglong)]
     L.cgb200_system_download.argtypes = [C.c_void_p, c_double_p, c_int_p, c_int_p]
     L.cgb200_system_get_b.argtypes = [C.c_void_p, c_double_p]
     L.cgb200_timer_stop.argtypes = [c_double_p]
@@ -324,6 +327,10 @@ class DeviceSystem:
     def one_kernel_iteration(self):
         """True when a classic iteration of this system is one cooperative launch (dense path)."""
         return bool(lib().cgb200_system_one_kernel_iteration(self.h))
+
+    def comm_bytes(self):
+        """Bytes this rank sends to its peers per classic iteration (0 on one GPU)."""
+        return lib().cgb200_system_comm_bytes(self.h)
 
     def bytes(self):
         a, b = C.c_double(0.0), C.c_double(0.0)

@@ -1109,6 +1109,10 @@ int cgb200_system_bytes(cgb200_system* sys, double* iter_bytes, double* k1_bytes
   return 0;
 }
 
+double cgb200_system_comm_bytes(cgb200_system* sys) {
+  return sys ? ((System*)sys)->comm_bytes_per_iter() : -1.0;
+}
+
 long long cgb200_system_rows(cgb200_system* sys) { return sys ? ((System*)sys)->nloc : -1; }
 long long cgb200_system_nnz(cgb200_system* sys) { return sys ? ((System*)sys)->A.nnz : -1; }
 

@@ -83,6 +83,17 @@ __device__ __forceinline__ double4_t ld_stream4(const double* ptr) {
   return v;
 }
 
+// Operand that other CTAs (or peer GPUs) rewrite between two reads of the SAME launch (the search
+// direction inside the persistent dense solve kernel): 256 bit, served by L2, never by this SM's L1,
+// which is not coherent and is only invalidated at launch boundaries.
+__device__ __forceinline__ double4_t ld_l2_4(const double* ptr) {
+  double4_t v;
+  asm volatile("ld.global.cg.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w)
+               : "l"(ptr));
+  return v;
+}
+
 // ---------------------------------------------------------------------------------------------
 // mbarrier + bulk async copy (global -> shared, completes on an mbarrier)
 // ---------------------------------------------------------------------------------------------

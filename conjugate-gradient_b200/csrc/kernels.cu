@@ -392,20 +392,30 @@ k_spmv_rowgroup(const double* __restrict__ vals, const int* __restrict__ cols,
 // current one runs, so the DRAM latency of a slab hides behind the additions of the previous one.
 // ---------------------------------------------------------------------------------------------
 
+// Work split.  Every warp of a persistent grid (CTAs per SM x SMs, so every SM holds the same
+// number of warps) owns ONE contiguous run of rows, cut so that all runs hold the same number of
+// stored entries (`wbound`, computed once per system by k_row_bounds; null = equal row counts), and
+// walks it in units of at most ROWS rows of equal size.  The first version dealt whole 16-row units
+// round-robin: 3267 units over 2368 resident warps is 1.38 units per warp on average and 2 for the
+// slowest -- 0.69 of the launch was the best it could do, and 0.67 is what it measured.
+//
+// L2 residency.  The loop streams the same matrix every iteration; on a matrix of a few hundred MB
+// a fixed share of it can simply stay in the 126 MB L2.  The first `res1024`/1024 of every unit's
+// slabs are loaded with the default priority, the rest evict-first, so the streamed part passes
+// through without pushing the resident part out (tools/exp/l2_resident.cu: an 80 MB head of a
+// 217 MB buffer turns 6.2 TB/s into 8.1 TB/s; at 1 GB the effect is gone, and res1024 is 0).
 template <int THREADS, int ROWS, bool COHERENT>
 __global__ void __launch_bounds__(THREADS)
 k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
-                const int* __restrict__ rowptr, const int nrows, const double* __restrict__ pg,
-                const double* __restrict__ pown, double* __restrict__ s,
-                double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
-                const int mode, const __grid_constant__ PeerComm cm) {
+                const int* __restrict__ rowptr, const int nrows, const int* __restrict__ wbound,
+                const int res1024, const double* __restrict__ pg, const double* __restrict__ pown,
+                double* __restrict__ s, double* __restrict__ partials,
+                unsigned int* __restrict__ ticket, CgState* S, const int mode,
+                const __grid_constant__ PeerComm cm) {
   // COHERENT (several GPUs, peer-memory mode): part of the gather vector is stored by the peers'
   // direction updates while this kernel may already be running, so every CTA first waits for
   // their completion flags and the gathers bypass L1.  (The stream kernel overlaps that wait with
   // its interior tiles; here the whole launch sits behind it.)
-  // ROWS rows per warp and work unit (lane i < ROWS owns row i of the unit): fewer rows mean
-  // fewer registers for the prefetched slab, hence more warps per SM, and finer units -- both
-  // matter while a unit's time is set by latencies rather than by its bytes
   constexpr int WARPS = THREADS / 32;
   constexpr int LD = 33;  // tile row stride in doubles: lane i reads bank pair 2i + 2j (mod 32)
   __shared__ double tile[WARPS][ROWS * LD];
@@ -419,30 +429,44 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
     if (threadIdx.x == 0) wait_halo(cm, S);
     __syncthreads();
   }
-  const int nblk = (nrows + ROWS - 1) / ROWS;
   const int cta = rev ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
-  const int b0 = (int)((long long)nblk * cta / gridDim.x);
-  const int b1 = (int)((long long)nblk * (cta + 1) / gridDim.x);
+  const int W = (int)gridDim.x * WARPS, gw = cta * WARPS + warp;
+  int r0, r1;
+  if (wbound) {
+    r0 = __ldg(wbound + gw);
+    r1 = __ldg(wbound + gw + 1);
+  } else {
+    r0 = (int)((long long)nrows * gw / W);
+    r1 = (int)((long long)nrows * (gw + 1) / W);
+  }
+  const int nr = r1 - r0;
+  const int nunits = (nr + ROWS - 1) / ROWS;
   double dot = 0.0, dot2 = 0.0;
 #pragma unroll 1
-  for (int blk = b0 + warp; blk < b1; blk += WARPS) {
-    const int row = blk * ROWS + lane;
-    const bool rv = lane < ROWS && row < nrows;
+  for (int u = 0; u < nunits; ++u) {
+    const int ub = r0 + (int)((long long)nr * u / nunits);
+    const int ue = r0 + (int)((long long)nr * (u + 1) / nunits);  // ue - ub <= ROWS
+    const int row = ub + lane;
+    const bool rv = lane < ue - ub;
     const int rs = rv ? __ldg(rowptr + row) : 0;
     const int re = rv ? __ldg(rowptr + row + 1) : 0;
     const int maxlen = __reduce_max_sync(0xffffffffu, re - rs);
+    const int res_off = (int)(((long long)maxlen * res1024) >> 10);  // slabs below this offset stay in L2
     double acc = 0.0;
     int c[ROWS];
     double v[ROWS];
     unsigned ok = 0u;  // bit i: this lane holds an entry of row i in the slab in registers
     // slab 0 into registers
+    {
+      const bool keep = 0 < res_off;
 #pragma unroll
-    for (int i = 0; i < ROWS; ++i) {
-      const int k = __shfl_sync(0xffffffffu, rs, i) + lane;
-      const bool o = k < __shfl_sync(0xffffffffu, re, i);
-      ok |= (o ? 1u : 0u) << i;
-      c[i] = o ? __ldcs(cols + k) : 0;
-      v[i] = o ? __ldcs(vals + k) : 0.0;
+      for (int i = 0; i < ROWS; ++i) {
+        const int k = __shfl_sync(0xffffffffu, rs, i) + lane;
+        const bool o = k < __shfl_sync(0xffffffffu, re, i);
+        ok |= (o ? 1u : 0u) << i;
+        c[i] = o ? (keep ? __ldg(cols + k) : __ldcs(cols + k)) : 0;
+        v[i] = o ? (keep ? __ldg(vals + k) : __ldcs(vals + k)) : 0.0;
+      }
     }
 #pragma unroll 1
     for (int off = 0; off < maxlen; off += 32) {
@@ -457,13 +481,14 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
       // next slab's indices and values on their way while this slab is added up
       ok = 0u;
       if (off + 32 < maxlen) {
+        const bool keep = off + 32 < res_off;
 #pragma unroll
         for (int i = 0; i < ROWS; ++i) {
           const int k = __shfl_sync(0xffffffffu, rs, i) + off + 32 + lane;
           const bool o = k < __shfl_sync(0xffffffffu, re, i);
           ok |= (o ? 1u : 0u) << i;
-          c[i] = o ? __ldcs(cols + k) : 0;
-          v[i] = o ? __ldcs(vals + k) : 0.0;
+          c[i] = o ? (keep ? __ldg(cols + k) : __ldcs(cols + k)) : 0;
+          v[i] = o ? (keep ? __ldg(vals + k) : __ldcs(vals + k)) : 0.0;
         }
       }
       if (lane < ROWS) {
@@ -498,6 +523,25 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
     v2[1] = 0.0;
   }
   if (last) finish_block<THREADS>(S, cm, fin, v2[0], v2[1]);
+}
+
+// wbound[k], k = 0..W: first row of warp k's run; runs hold equal shares of the stored entries.
+__global__ void k_row_bounds(const int* __restrict__ rowptr, int nrows, int W, int* __restrict__ wbound) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > W) return;
+  if (k == 0 || k == W) {
+    wbound[k] = k == 0 ? 0 : nrows;
+    return;
+  }
+  const long long nnz = rowptr[nrows];
+  const long long target = nnz * k / W;
+  int lo = 0, hi = nrows;  // first row whose start offset is >= target
+  while (lo < hi) {
+    const int mid = lo + ((hi - lo) >> 1);
+    if (rowptr[mid] < target) lo = mid + 1;
+    else hi = mid;
+  }
+  wbound[k] = lo;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -708,7 +752,7 @@ __device__ __noinline__ void gemv_units_shared_groups(int nrows, int ncols, cons
       if (dots) {
         double d1 = 0.0, d2 = 0.0;
         if (lane < RB && row < nrows) {
-          const double gv = pown[row];
+          const double gv = __ldcg(pown + row);
           d1 = gv * t;
           d2 = gv * gv;
         }
@@ -776,7 +820,7 @@ __device__ __forceinline__ void gemv_units_stream(const double* __restrict__ A, 
     const int cend = min(kb * CW, ncols);
 #pragma unroll 2
     for (int c = ka * CW + tid * 4; c < cend; c += CW) {
-      const double4_t pv = *reinterpret_cast<const double4_t*>(pg + c);
+      const double4_t pv = ld_l2_4(pg + c);
       double4_t a[RB];
 #pragma unroll
       for (int r = 0; r < RB; ++r) a[r] = ld_stream4(rowp[r] + c);
@@ -805,7 +849,7 @@ __device__ __forceinline__ void gemv_units_stream(const double* __restrict__ A, 
         if (row0 + tid < nrows) {
           s[row0 + tid] = t;
           if (dots) {
-            const double gv = pown[row0 + tid];
+            const double gv = __ldcg(pown + row0 + tid);
             dot += gv * t;
             dot2 += gv * gv;
           }
@@ -902,14 +946,14 @@ __device__ __forceinline__ void gemv_pool_phase(const double* __restrict__ A, lo
 #pragma unroll
     for (int r = 0; r < RB; ++r) rowp[r] = A + (long long)min(row0 + r, nrows - 1) * ld;
     double gv = 0.0;
-    if (tid < RB && row0 + tid < nrows) gv = pown[row0 + tid];
+    if (tid < RB && row0 + tid < nrows) gv = __ldcg(pown + row0 + tid);
     double acc[RB];
 #pragma unroll
     for (int r = 0; r < RB; ++r) acc[r] = 0.0;
     const int cend = min((k + 1) * GEMV_PCH * CW, ncols);
 #pragma unroll 2
     for (int c = k * GEMV_PCH * CW + tid * 4; c < cend; c += CW) {
-      const double4_t pv = *reinterpret_cast<const double4_t*>(pg + c);
+      const double4_t pv = ld_l2_4(pg + c);
       double4_t a[RB];
 #pragma unroll
       for (int r = 0; r < RB; ++r) a[r] = ld_stream4(rowp[r] + c);
@@ -947,151 +991,251 @@ __device__ __forceinline__ void gemv_pool_phase(const double* __restrict__ A, lo
 }
 
 // ---------------------------------------------------------------------------------------------
-// Dense path, the whole iteration in ONE launch (classic recurrence, cg.c:111-132).
+// Dense path: the whole SOLVE in one launch (classic recurrence, cg.c:104-135).
 //
 // On the dense path the vectors are n doubles against n^2 of matrix: K2 and K3 are pure latency
 // (5-9 us each plus two launch boundaries), which is 2 % of an iteration on one GPU and 25 % on
 // an eighth of the matrix.  The persistent GEMV grid is co-resident (cooperative launch), so the
-// iteration continues behind two grid barriers instead of two more launches:
+// loop continues behind grid barriers instead of launches -- loop entry and every iteration:
+//   phase I  (init != 0) x = 0, r = p = b, b.b; p pushed to the peers   -> last CTA: [sum] state
+//   per iteration, up to `iters` of them:
 //   phase A  s = A p, p.s (unit-range GEMV as above)         -> last CTA: [cross-GPU sum] alpha
 //   barrier  (the CTA that drew the last ticket releases the grid)
+//            while the reductions and vector phases run HBM is idle: every CTA asks L2 to fetch
+//            the head of its matrix range for the NEXT iteration (the matrix does not depend on p)
 //   phase B  x += alpha p ; r -= alpha s ; r.r  (each CTA a slice) -> last CTA: [sum] beta, stop
 //   barrier
-//   phase C  p = r + beta p, pushed into the peers' gather vectors, flags raised
+//   phase C  p = r + beta p, pushed into the peers' gather vectors
+//   barrier  (arrival count: the last CTA raises the peers' flags and releases the grid)
 // The barriers are epochs in CgState (grid_epoch): a CTA reads the epoch when it starts -- nobody
-// can have released yet, a release needs every CTA's ticket -- and waits for epoch + 1, + 2.
+// can have released yet, a release needs every CTA's arrival -- and waits for epoch + 1, + 2, ...
+// A stop (fixed count reached, tolerance met, breakdown) is seen by every CTA behind the barrier
+// that follows the decision, and the launch ends: a tolerance solve needs no host in the loop.
 // `timing` != 0 leaves the scalars alone (alpha = beta = 0 state of system_time_kernel).
 // ---------------------------------------------------------------------------------------------
 
+struct DenseSolveArgs {
+  int iters;        // iterations this launch may run (it stops earlier when the loop is done)
+  int init;         // run the loop entry first (a new solve); 0 = continue the solve in CgState
+  int max_iter;     // init only: reference semantics, stop after the update at k == max_iter
+  double tol;       // init only
+  int wait;         // the peers' slices of p take part (all-gather by push)
+  int timing;
+  int pool_groups;
+  int prefetch_bytes;  // matrix bytes per CTA asked into L2 ahead of the next iteration (0 = none)
+};
+
+// Every thread of every CTA calls this after its last store of a phase: the CTA that arrives last
+// (optionally after raising the peers' halo flags: the pushes of this rank are complete) releases
+// epoch e.  Replaces a launch boundary between p's update and the next matvec.
+template <int THREADS>
+__device__ __forceinline__ void grid_arrive(CgState* S, const PeerComm& cm, const bool pushed,
+                                            const unsigned long long e) {
+  if (pushed) __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int tk = atomicAdd(&S->ticket[3], 1u);
+    if (tk == gridDim.x - 1) {
+      S->ticket[3] = 0u;
+      __threadfence();
+      if (pushed) {
+        __threadfence_system();
+        const unsigned long long pe = cm.local->push_epoch + 1;
+        cm.local->push_epoch = pe;
+        for (int t = 0; t < cm.npush; ++t)
+          st_release_sys(&cm.mbox[cm.push[t].peer]->halo_flag[cm.rank], pe);
+      }
+      st_release_gpu(&S->grid_epoch, e);
+    }
+  }
+}
+
 // `trace` (normally null): cycle counts of the phases, accumulated by thread 0 of the CTA that
-// closes each phase, relative to that CTA's own start (tools/dense_trace.py).
+// closes each phase, relative to that CTA's own start of the iteration (tools/dense_trace.py).
 template <int THREADS, int RB>
 __global__ void __launch_bounds__(THREADS, 4)
-k_cg_dense_iter(const double* __restrict__ A, long long ld, int nrows, int ncols,
-                const double* pg, double* pown, double* __restrict__ x, double* __restrict__ r,
-                double* s, double* __restrict__ partials, CgState* S, const int wait,
-                const int timing, unsigned long long* __restrict__ trace, const int pool_groups,
-                double* __restrict__ pool, const __grid_constant__ PeerComm cm) {
-  if (S->done) return;
+k_cg_dense_solve(const double* __restrict__ A, long long ld, int nrows, int ncols,
+                 const double* pg, double* pown, double* __restrict__ x, double* __restrict__ r,
+                 double* s, const double* __restrict__ b, double* __restrict__ partials, CgState* S,
+                 unsigned long long* __restrict__ trace, double* __restrict__ pool,
+                 const DenseSolveArgs a, const __grid_constant__ PeerComm cm) {
   const int tid = threadIdx.x;
+  if (!a.init && S->done) return;
   __shared__ unsigned long long sh_e0, sh_t0;
   long long c0 = 0;
-  if (tid == 0) {
-    sh_e0 = ld_acquire_gpu(&S->grid_epoch);
-    if (trace) {
-      c0 = clock64();
-      sh_t0 = global_ns();
-    }
-    if (wait) wait_halo(cm, S);  // the peers' slices of p have landed (all-gather by push)
-    if (trace && blockIdx.x == 0) atomicAdd(trace + 0, (unsigned long long)(clock64() - c0));
-  }
-  // (the __syncthreads at the top of gemv_units_stream publishes sh_e0 and orders the wait)
-
-  // ---- phase A -------------------------------------------------------------------------------
-  double dot = 0.0, dot2 = 0.0;
-  const int ngs = (nrows + RB - 1) / RB - pool_groups;  // statically dealt row groups
-  gemv_units_stream<THREADS, RB>(A, ld, nrows, ncols, ngs, pg, pown, s, partials, true, dot, dot2);
-  if (pool_groups > 0) gemv_pool_phase<THREADS, RB>(A, ld, nrows, ncols, ngs, pool_groups, pg, pown, pool);
-  const unsigned long long e0 = sh_e0;
-  if (trace && tid == 0) {  // spread of the CTAs' start and stream-end times (ns, global timer)
-    atomicMin(trace + 8, sh_t0);
-    atomicMax(trace + 9, sh_t0);
-    const unsigned long long t1 = global_ns();
-    atomicMin(trace + 10, t1);
-    atomicMax(trace + 11, t1);
-    atomicAdd(trace + 12, t1 - sh_t0);
-    trace[16 + blockIdx.x] += t1 - sh_t0;  // per-CTA sum of GEMV durations (this CTA is the only writer)
-    unsigned int smid;
-    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    trace[16 + 1024 + blockIdx.x] = smid;
-  }
-  {
-    double v[1] = {dot};
-    if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[0], partials + GEMV_GDOT_OFFSET,
-                                (int)gridDim.x - 1)) {
-      if (trace && tid == 0) {
-        atomicAdd(trace + 1, (unsigned long long)(clock64() - c0));
-        // per-launch spreads (ns): CTA starts, ends of the CTAs' GEMV shares, first start -> first end
-        volatile unsigned long long* tv = trace;
-        const unsigned long long s0 = tv[8], s1 = tv[9], f0 = tv[10], f1 = tv[11];
-        tv[13] += s1 - s0;
-        tv[14] += f1 - f0;
-        tv[15] += f0 - s0;
-        tv[2] += f1 - s0;  // first start -> last end
-        tv[8] = ~0ull;
-        tv[10] = ~0ull;
-        tv[9] = 0ull;
-        tv[11] = 0ull;
-      }
-      if (pool_groups > 0) {  // the pool's shares of p.s, in chunk order
-        const int cpc = gemv_chunks_per_group(ncols, THREADS);
-        const int nchunks = pool_groups * cpc;
-        const double* cdot = pool + (size_t)cpc * pool_groups * RB;
-        double cd = 0.0;
-        for (int i = tid; i < nchunks; i += THREADS) cd += __ldcg(cdot + i);
-        __shared__ double sm_cd[THREADS / 32];
-        cd = block_sum<THREADS>(cd, sm_cd);
-        if (tid == 0) {
-          v[0] += cd;
-          *reinterpret_cast<unsigned int*>(pool + (size_t)cpc * pool_groups * RB + nchunks) = 0u;
-        }
-      }
-      if (!timing) finish_block<THREADS>(S, cm, FIN_PS, v[0], 0.0);
-      if (trace && tid == 0) {
-        atomicAdd(trace + 3, (unsigned long long)(clock64() - c0));
-        atomicAdd(trace + 7, 1ull);
-      }
-      grid_release<THREADS>(&S->grid_epoch, e0 + 1);
-    }
-  }
-  if (!grid_wait(&S->grid_epoch, e0 + 1, S)) return;
-  if (ld_volatile_int(&S->done)) return;
-
-  // ---- phase B -------------------------------------------------------------------------------
-  const double alpha = ld_volatile_f64(&S->alpha);
+  if (tid == 0) sh_e0 = ld_acquire_gpu(&S->grid_epoch);
+  __syncthreads();
+  unsigned long long e = sh_e0;
   const long long gstride = (long long)gridDim.x * THREADS;
-  const long long pool_row0 = pool_groups > 0 ? (long long)ngs * RB : (long long)nrows;
-  double acc = 0.0;
-  for (long long i = (long long)blockIdx.x * THREADS + tid; i < nrows; i += gstride) {
-    const double pv = pown[i];
-    double sv;
-    if (i >= pool_row0) {  // a pool row: its chunks' partial sums, in chunk order
-      const int cpc = gemv_chunks_per_group(ncols, THREADS);
-      const size_t jr = (size_t)(i - pool_row0);  // == j * RB + r
-      sv = 0.0;
-      for (int k = 0; k < cpc; ++k) sv += __ldcg(pool + (size_t)k * pool_groups * RB + jr);
-      s[i] = sv;
-    } else {
-      sv = __ldcg(s + i);  // written by other CTAs of this launch: read at L2
-    }
-    const double xn = __dadd_rn(x[i], __dmul_rn(alpha, pv));
-    const double rn = __dsub_rn(r[i], __dmul_rn(alpha, sv));
-    x[i] = xn;
-    r[i] = rn;
-    acc = fma(rn, rn, acc);
-  }
-  {
-    double v[1] = {acc};
-    if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[1])) {
-      if (trace && tid == 0) atomicAdd(trace + 4, (unsigned long long)(clock64() - c0));
-      if (!timing) finish_block<THREADS>(S, cm, FIN_RR, v[0], 0.0);
-      if (trace && tid == 0) atomicAdd(trace + 5, (unsigned long long)(clock64() - c0));
-      grid_release<THREADS>(&S->grid_epoch, e0 + 2);
-    }
-  }
-  if (!grid_wait(&S->grid_epoch, e0 + 2, S)) return;
-  if (ld_volatile_int(&S->done)) return;
-
-  // ---- phase C -------------------------------------------------------------------------------
-  const double beta = ld_volatile_f64(&S->beta);
   const bool pushing = cm.npush > 0;
-  for (long long i = (long long)blockIdx.x * THREADS + tid; i < nrows; i += gstride) {
-    const double pn = __dadd_rn(r[i], __dmul_rn(beta, pown[i]));
-    pown[i] = pn;
-    if (pushing) push_elem(cm, i, pn);
+  const int pool_groups = a.pool_groups;
+  const int ngs = (nrows + RB - 1) / RB - pool_groups;  // statically dealt row groups
+
+  // ---- phase I: loop entry (cg.c:104-108) -----------------------------------------------------
+  if (a.init) {
+    double acc = 0.0;
+    for (long long i = (long long)blockIdx.x * THREADS + tid; i < nrows; i += gstride) {
+      const double v = b[i];
+      x[i] = 0.0;
+      r[i] = v;
+      pown[i] = v;
+      if (pushing) push_elem(cm, i, v);
+      acc = fma(v, v, acc);
+    }
+    double v[1] = {acc};
+    if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[2])) {
+      if (tid == 0) {  // a fresh solve: the scalars of the previous one are void
+        S->tol = a.tol > 0.0 ? a.tol : 0.0;
+        S->max_iter = a.max_iter;
+        S->variant = 0;
+      }
+      finish_block<THREADS>(S, cm, FIN_INIT, v[0], 0.0);
+    }
+    // (the reduction's partials are consumed before anyone can pass the barrier below)
+    grid_arrive<THREADS>(S, cm, pushing, e + 1);
+    if (!grid_wait(&S->grid_epoch, e + 1, S)) return;
+    e += 1;
+    if (ld_volatile_int(&S->done)) return;
   }
-  push_finish(cm);
-  if (trace && tid == 0 && blockIdx.x == 0) atomicAdd(trace + 6, (unsigned long long)(clock64() - c0));
+
+#pragma unroll 1
+  for (int it = 0; it < a.iters; ++it) {
+    if (tid == 0) {
+      if (trace) {
+        c0 = clock64();
+        sh_t0 = global_ns();
+      }
+      if (a.wait) wait_halo(cm, S);  // the peers' slices of p have landed (all-gather by push)
+      if (trace && blockIdx.x == 0) atomicAdd(trace + 0, (unsigned long long)(clock64() - c0));
+    }
+    // (the __syncthreads at the top of gemv_units_stream orders the wait before the block's loads)
+
+    // ---- phase A -----------------------------------------------------------------------------
+    double dot = 0.0, dot2 = 0.0;
+    gemv_units_stream<THREADS, RB>(A, ld, nrows, ncols, ngs, pg, pown, s, partials, true, dot, dot2);
+    if (pool_groups > 0)
+      gemv_pool_phase<THREADS, RB>(A, ld, nrows, ncols, ngs, pool_groups, pg, pown, pool);
+    if (trace && tid == 0) {  // spread of the CTAs' start and stream-end times (ns, global timer)
+      atomicMin(trace + 8, sh_t0);
+      atomicMax(trace + 9, sh_t0);
+      const unsigned long long t1 = global_ns();
+      atomicMin(trace + 10, t1);
+      atomicMax(trace + 11, t1);
+      atomicAdd(trace + 12, t1 - sh_t0);
+      trace[16 + blockIdx.x] += t1 - sh_t0;  // per-CTA sum of GEMV durations (this CTA is the only writer)
+      unsigned int smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      trace[16 + 1024 + blockIdx.x] = smid;
+    }
+    {
+      double v[1] = {dot};
+      if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[0], partials + GEMV_GDOT_OFFSET,
+                                  (int)gridDim.x - 1)) {
+        if (trace && tid == 0) {
+          atomicAdd(trace + 1, (unsigned long long)(clock64() - c0));
+          // per-launch spreads (ns): CTA starts, ends of the CTAs' GEMV shares, first start -> first end
+          volatile unsigned long long* tv = trace;
+          const unsigned long long s0 = tv[8], s1 = tv[9], f0 = tv[10], f1 = tv[11];
+          tv[13] += s1 - s0;
+          tv[14] += f1 - f0;
+          tv[15] += f0 - s0;
+          tv[2] += f1 - s0;  // first start -> last end
+          tv[8] = ~0ull;
+          tv[10] = ~0ull;
+          tv[9] = 0ull;
+          tv[11] = 0ull;
+        }
+        if (pool_groups > 0) {  // the pool's shares of p.s, in chunk order
+          const int cpc = gemv_chunks_per_group(ncols, THREADS);
+          const int nchunks = pool_groups * cpc;
+          const double* cdot = pool + (size_t)cpc * pool_groups * RB;
+          double cd = 0.0;
+          for (int i = tid; i < nchunks; i += THREADS) cd += __ldcg(cdot + i);
+          __shared__ double sm_cd[THREADS / 32];
+          cd = block_sum<THREADS>(cd, sm_cd);
+          if (tid == 0) {
+            v[0] += cd;
+            *reinterpret_cast<unsigned int*>(pool + (size_t)cpc * pool_groups * RB + nchunks) = 0u;
+          }
+        }
+        if (!a.timing) finish_block<THREADS>(S, cm, FIN_PS, v[0], 0.0);
+        if (trace && tid == 0) {
+          atomicAdd(trace + 3, (unsigned long long)(clock64() - c0));
+          atomicAdd(trace + 7, 1ull);
+        }
+        grid_release<THREADS>(&S->grid_epoch, e + 1);
+      }
+    }
+    if (!grid_wait(&S->grid_epoch, e + 1, S)) return;
+    if (ld_volatile_int(&S->done)) return;
+
+    // HBM has nothing to do until the next matvec: have L2 fetch the head of this CTA's matrix
+    // range (the first row group it will stream) -- evict-first loads then find it there
+    if (a.prefetch_bytes > 0 && it + 1 < a.iters && tid < RB) {
+      constexpr int CW = THREADS * 4;
+      const int cpg = (ncols + CW - 1) / CW;
+      const long long U = (long long)ngs * cpg;
+      const long long ubeg = U * blockIdx.x / gridDim.x, uend = U * (blockIdx.x + 1) / gridDim.x;
+      const int g0 = (int)(ubeg / cpg), ka = (int)(ubeg % cpg);
+      const int row = g0 * RB + tid;
+      long long cols_ahead = min((long long)(cpg - ka), uend - ubeg) * CW;
+      cols_ahead = min(cols_ahead, (long long)ncols - (long long)ka * CW);
+      long long bytes = min(cols_ahead * 8, (long long)(a.prefetch_bytes / RB)) & ~15ll;
+      if (row < nrows && bytes > 0)
+        bulk_prefetch_l2(A + (long long)row * ld + (long long)ka * CW, (uint32_t)bytes);
+    }
+
+    // ---- phase B -----------------------------------------------------------------------------
+    const double alpha = ld_volatile_f64(&S->alpha);
+    const long long pool_row0 = pool_groups > 0 ? (long long)ngs * RB : (long long)nrows;
+    double acc = 0.0;
+    for (long long i = (long long)blockIdx.x * THREADS + tid; i < nrows; i += gstride) {
+      const double pv = pown[i];
+      double sv;
+      if (i >= pool_row0) {  // a pool row: its chunks' partial sums, in chunk order
+        const int cpc = gemv_chunks_per_group(ncols, THREADS);
+        const size_t jr = (size_t)(i - pool_row0);  // == j * RB + r
+        sv = 0.0;
+        for (int k = 0; k < cpc; ++k) sv += __ldcg(pool + (size_t)k * pool_groups * RB + jr);
+        s[i] = sv;
+      } else {
+        sv = __ldcg(s + i);  // written by other CTAs of this launch: read at L2
+      }
+      const double xn = __dadd_rn(x[i], __dmul_rn(alpha, pv));
+      const double rn = __dsub_rn(r[i], __dmul_rn(alpha, sv));
+      x[i] = xn;
+      r[i] = rn;
+      acc = fma(rn, rn, acc);
+    }
+    {
+      double v[1] = {acc};
+      if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[1])) {
+        if (trace && tid == 0) atomicAdd(trace + 4, (unsigned long long)(clock64() - c0));
+        if (!a.timing) finish_block<THREADS>(S, cm, FIN_RR, v[0], 0.0);
+        if (trace && tid == 0) atomicAdd(trace + 5, (unsigned long long)(clock64() - c0));
+        grid_release<THREADS>(&S->grid_epoch, e + 2);
+      }
+    }
+    if (!grid_wait(&S->grid_epoch, e + 2, S)) return;
+    if (ld_volatile_int(&S->done)) return;
+
+    // ---- phase C -----------------------------------------------------------------------------
+    const double beta = ld_volatile_f64(&S->beta);
+    for (long long i = (long long)blockIdx.x * THREADS + tid; i < nrows; i += gstride) {
+      const double pn = __dadd_rn(__ldcg(r + i), __dmul_rn(beta, pown[i]));
+      pown[i] = pn;
+      if (pushing) push_elem(cm, i, pn);
+    }
+    grid_arrive<THREADS>(S, cm, pushing, e + 3);
+    if (it + 1 == a.iters) {  // nothing of this launch reads p any more: the next launch will
+      if (trace && tid == 0 && blockIdx.x == 0) atomicAdd(trace + 6, (unsigned long long)(clock64() - c0));
+      return;
+    }
+    if (!grid_wait(&S->grid_epoch, e + 3, S)) return;
+    if (trace && tid == 0 && blockIdx.x == 0) atomicAdd(trace + 6, (unsigned long long)(clock64() - c0));
+    e += 3;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1983,23 +2127,55 @@ static cudaError_t launch_spmv_rowgroup_cfg(const CsrDev& A, const double* pg, c
   return cudaGetLastError();
 }
 
-template <int T, int ROWS, bool COH = false>
-static cudaError_t launch_spmv_rowblock_cfg(const CsrDev& A, const double* pg, const double* pown,
-                                            double* s, double* partials, unsigned int* ticket,
-                                            CgState* S, int mode, const PeerComm& cm,
-                                            cudaStream_t st) {
+// Share of a matrix of `matrix_bytes` that the loop keeps in L2 across iterations, in 1/1024:
+// CGB200_L2_RESIDENT_MB (default 80) minus the loop's vectors, and nothing for matrices beyond
+// 600 MB, where a resident head no longer pays (tools/exp/l2_resident.cu).
+int l2_resident_1024(double matrix_bytes, double vector_bytes) {
+  static double mb = -1.0;
+  if (mb < 0.0) {
+    const char* e = getenv("CGB200_L2_RESIDENT_MB");
+    mb = e ? atof(e) : 80.0;
+    if (mb < 0.0) mb = 0.0;
+  }
+  const double budget = mb * 1e6 - vector_bytes;
+  if (budget <= 0.0 || matrix_bytes <= 0.0 || matrix_bytes > 600e6) return 0;
+  const double f = budget / matrix_bytes;
+  return f >= 1.0 ? 1024 : (int)(f * 1024.0);
+}
+
+template <int T, int ROWS, bool COH>
+static int rowblock_grid() {
   static int bps = 0;
   if (!bps) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowblock<T, ROWS, COH>, T, 0);
     if (bps < 1) bps = 1;
   }
-  const int nblk = (A.nrows + ROWS - 1) / ROWS;
-  int grid = sm_count() * bps;
-  const int need = (nblk + T / 32 - 1) / (T / 32);
-  if (grid > need) grid = need;
+  int grid = sm_count() * bps;  // every SM holds the same number of warps
   if (grid > MAX_GRID) grid = MAX_GRID;
-  k_spmv_rowblock<T, ROWS, COH><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s,
-                                                    partials, ticket, S, mode, cm);
+  return grid;
+}
+
+// Warps of the default long-row launch (the run bounds of a system are computed for this count).
+int spmv_longrow_warps(bool coherent) {
+  return (coherent ? rowblock_grid<256, 16, true>() : rowblock_grid<256, 16, false>()) * (256 / 32);
+}
+
+cudaError_t launch_row_bounds(const int* rowptr, int nrows, int W, int* wbound, cudaStream_t st) {
+  k_row_bounds<<<(W + 1 + 127) / 128, 128, 0, st>>>(rowptr, nrows, W, wbound);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+template <int T, int ROWS, bool COH = false>
+static cudaError_t launch_spmv_rowblock_cfg(const CsrDev& A, const double* pg, const double* pown,
+                                            double* s, double* partials, unsigned int* ticket,
+                                            CgState* S, int mode, const PeerComm& cm,
+                                            cudaStream_t st) {
+  const int grid = rowblock_grid<T, ROWS, COH>();
+  const int W = grid * (T / 32);
+  const int* wb = (A.wbound && A.wbound_w == W) ? A.wbound : nullptr;  // else: equal row counts
+  k_spmv_rowblock<T, ROWS, COH><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, wb, A.res1024,
+                                                    pg, pown, s, partials, ticket, S, mode, cm);
   ++g_launches;
   return cudaGetLastError();
 }
@@ -2174,14 +2350,26 @@ size_t dense_pool_doubles(int nrows, int ncols) {
   return cpc * P * GV_RB + cpc * P + 8;
 }
 
-cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int ncols,
-                                 const double* pg, double* pown, double* x, double* r, double* s,
-                                 double* partials, CgState* S, int wait, int timing,
-                                 unsigned long long* trace, double* pool, const PeerComm& cm,
-                                 cudaStream_t st) {
+// CGB200_DENSE_PREFETCH_KB: matrix bytes per CTA asked into L2 ahead of the next iteration's matvec.
+static int dense_prefetch_bytes() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("CGB200_DENSE_PREFETCH_KB");
+    v = (e ? atoi(e) : 96) * 1024;
+    if (v < 0) v = 0;
+  }
+  return v;
+}
+
+cudaError_t launch_cg_dense_solve(const double* A, long long ld, int nrows, int ncols,
+                                  const double* pg, double* pown, double* x, double* r, double* s,
+                                  const double* b, double* partials, CgState* S, int iters,
+                                  int init, int max_iter, double tol, int wait, int timing,
+                                  unsigned long long* trace, double* pool, const PeerComm& cm,
+                                  cudaStream_t st) {
   static int bps = 0;
   if (!bps) {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_cg_dense_iter<GV_T, GV_RB>, GV_T, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_cg_dense_solve<GV_T, GV_RB>, GV_T, 0);
     if (bps < 1) bps = 1;
     const char* e = getenv("CGB200_GEMV_BPS");  // fewer CTAs per SM (experiments)
     if (e && atoi(e) > 0 && atoi(e) < bps) bps = atoi(e);
@@ -2194,6 +2382,15 @@ cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int n
   const long long cap = GEMV_MAX_GRID;  // room for two records per CTA
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
+  DenseSolveArgs a;
+  a.iters = iters;
+  a.init = init;
+  a.max_iter = max_iter;
+  a.tol = tol;
+  a.wait = wait;
+  a.timing = timing;
+  a.pool_groups = P;
+  a.prefetch_bytes = dense_prefetch_bytes();
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid);
   cfg.blockDim = dim3(GV_T);
@@ -2204,9 +2401,8 @@ cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int n
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  const cudaError_t e = cudaLaunchKernelEx(&cfg, k_cg_dense_iter<GV_T, GV_RB>, A, ld, nrows, ncols, pg,
-                                           pown, x, r, s, partials, S, wait, timing, trace, P, pool,
-                                           cm);
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, k_cg_dense_solve<GV_T, GV_RB>, A, ld, nrows, ncols,
+                                           pg, pown, x, r, s, b, partials, S, trace, pool, a, cm);
   ++g_launches;
   return e != cudaSuccess ? e : cudaGetLastError();
 }

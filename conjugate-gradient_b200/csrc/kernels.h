@@ -20,6 +20,11 @@ struct CsrDev {
   // banded matrices: gather index of the upper band edge = local row + lead (-1: no prefetch);
   // plen = length of the gather vector
   long long lead = -1, plen = 0;
+  // long-row matvec (k_spmv_rowblock): first row of every warp's run for a launch of wbound_w warps
+  // (runs of equal stored entries), and the share of the matrix kept in L2 across iterations (1/1024)
+  int* wbound = nullptr;
+  int wbound_w = 0;
+  int res1024 = 0;
 };
 
 // Row-pattern dictionary format (pattern.cu): one byte per row naming the row's pattern
@@ -93,15 +98,18 @@ void free_pattern(PatDev* P);
 cudaError_t launch_gemv(const double* A, long long ld, int nrows, int ncols, const double* pg,
                         const double* pown, double* s, double* partials, unsigned int* ticket,
                         CgState* S, int mode, int wait, const PeerComm& cm, cudaStream_t st);
-// dense path: the whole classic iteration in one cooperative launch (kernels.cu: k_cg_dense_iter)
+// dense path: the whole classic solve in one cooperative launch (kernels.cu: k_cg_dense_solve)
 void set_dense_iter_enabled(int on);
 bool dense_iter_enabled();
 bool dense_iter_supported(const double* A, long long ld, int ncols, const double* pg);
-cudaError_t launch_cg_dense_iter(const double* A, long long ld, int nrows, int ncols,
-                                 const double* pg, double* pown, double* x, double* r, double* s,
-                                 double* partials, CgState* S, int wait, int timing,
-                                 unsigned long long* trace, double* pool, const PeerComm& cm,
-                                 cudaStream_t st);
+// One cooperative launch runs the loop entry (init != 0) and up to `iters` iterations; it ends by
+// itself when the loop stops.  max_iter / tol are read at the loop entry only.
+cudaError_t launch_cg_dense_solve(const double* A, long long ld, int nrows, int ncols,
+                                  const double* pg, double* pown, double* x, double* r, double* s,
+                                  const double* b, double* partials, CgState* S, int iters,
+                                  int init, int max_iter, double tol, int wait, int timing,
+                                  unsigned long long* trace, double* pool, const PeerComm& cm,
+                                  cudaStream_t st);
 int dense_pool_groups(int nrows, int ncols);       // row groups dealt dynamically (0 = none)
 size_t dense_pool_doubles(int nrows, int ncols);   // size of the zero-initialised pool buffer
 // rev != 0: the vector kernels sweep from the last element to the first (see solver.cu: sweep_dir)
@@ -139,6 +147,9 @@ cudaError_t launch_spmv_rowgroup(const CsrDev& A, const double* pg, const double
                                  double* partials, unsigned int* ticket, CgState* S, int mode,
                                  const PeerComm& cm, cudaStream_t st);
 int spmv_rowgroup_min();
+int spmv_longrow_warps(bool coherent);
+int l2_resident_1024(double matrix_bytes, double vector_bytes);
+cudaError_t launch_row_bounds(const int* rowptr, int nrows, int W, int* wbound, cudaStream_t st);
 // Several GPUs in peer-memory mode: the default long-row kernel, every CTA first waiting for the
 // peers' halo flags, gathers bypassing L1 (the other forms are single-GPU / NCCL-mode only).
 cudaError_t launch_spmv_longrow_coherent(const CsrDev& A, const double* pg, const double* pown,

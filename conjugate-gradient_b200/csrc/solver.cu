@@ -295,6 +295,7 @@ System::~System() {
   dev_free(A.vals);
   dev_free(A.cols);
   dev_free(A.rowptr);
+  dev_free(A.wbound);
   dev_free(b);
   dev_free(x);
   dev_free(r);
@@ -509,6 +510,16 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
       // worth it only for a band that is wide enough to fall out of the tile's own footprint and
       // narrow enough to be a band at all
       if (lead > 4 * spmv_rows_per_tile() && lead < S->ext_len) S->A.lead = lead;
+    }
+    // long rows (k_spmv_rowblock): the warps' runs of equal stored entries, and the L2-resident share
+    const int rgm = spmv_rowgroup_min();
+    if (rgm > 0 && S->nloc > 0 && S->A.nnz >= (long long)rgm * S->nloc) {
+      const bool coherent = c.world > 1 && S->p2p && S->cm.nwait > 0;
+      const int W = spmv_longrow_warps(coherent);
+      CUDA_OK(DEV_ALLOC(&S->A.wbound, ((size_t)W + 1) * sizeof(int)));
+      CUDA_OK(launch_row_bounds(S->A.rowptr, S->nloc, W, S->A.wbound, c.stream));
+      S->A.wbound_w = W;
+      S->A.res1024 = l2_resident_1024(12.0 * (double)S->A.nnz, 5.0 * 8.0 * (double)S->ext_len);
     }
     const int R = spmv_rows_per_tile();
     S->ntiles = (S->nloc + R - 1) / R;
@@ -948,12 +959,22 @@ static int ensure_w(System* S) {
   return 0;
 }
 
-// Dense row block on one GPU or with the peer-memory exchange: one cooperative launch per
-// classic iteration (kernels.cu: k_cg_dense_iter).  NCCL mode keeps the three-kernel form (its
-// sums happen between launches).
+// Dense row block on one GPU or with the peer-memory exchange: one cooperative launch per classic
+// SOLVE -- loop entry and all iterations behind grid barriers (kernels.cu: k_cg_dense_solve).  NCCL
+// mode keeps the three-kernel form (its sums happen between launches).
 bool dense_one_kernel(const System* S) {
   return S->dense && S->nloc > 0 && !S->pc_loop && (S->world == 1 || S->p2p) &&
          dense_iter_supported(S->A.vals, S->n_global, (int)S->n_global, S->p_ext);
+}
+
+static int launch_dense_solve(System* S, int iters, int init, int max_iter, double tol, int timing) {
+  Ctx& c = g_ctx;
+  const bool peers = S->world > 1 && S->p2p && !timing;
+  CUDA_OK(launch_cg_dense_solve(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext, S->p_own,
+                                S->x, S->r, S->s, S->b, S->partials, S->state, iters, init, max_iter,
+                                tol, peers ? 1 : 0, timing, timing ? nullptr : S->trace, S->gemv_pool,
+                                peers ? S->cm : S->cm_off, c.stream));
+  return 0;
 }
 
 // Classic recurrence (the reference's, cg.c:110-135): K1, K2, K3.
@@ -994,13 +1015,6 @@ static int enqueue_iteration(System* S, int variant, int it = 0) {
     CUDA_OK(launch_update_p_pc(S->p_own, S->r, S->dinv, S->nloc, st, cm, c.stream));
     return 0;
   }
-  if (dense_one_kernel(S)) {  // dense path: the whole iteration behind two grid barriers
-    CUDA_OK(launch_cg_dense_iter(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext,
-                                 S->p_own, S->x, S->r, S->s, S->partials, st,
-                                 (S->world > 1 && S->p2p) ? 1 : 0, 0, S->trace, S->gemv_pool, cm,
-                                 c.stream));
-    return 0;
-  }
   // three kernels per iteration, alternating: K1, K2, K3 of iteration `it` are kernels 3 it + 0..2
   const bool d1 = sw && ((3 * it) & 1), d2 = sw && ((3 * it + 1) & 1), d3 = sw && ((3 * it + 2) & 1);
   if (enqueue_matvec(S, S->s, nccl ? FIN_LOCAL : FIN_PS, false, true, d1)) return -1;
@@ -1014,7 +1028,6 @@ static int enqueue_iteration(System* S, int variant, int it = 0) {
 
 // Kernel nodes per captured iteration (for the launch counter)
 static int kernels_per_iteration(const System* S, int variant) {
-  if (variant == 0 && dense_one_kernel(S)) return 1;
   int k = variant == 1 ? 2 : 3;
   if (S->world > 1 && !S->p2p) {
     k += variant == 1 ? 1 : 2;  // bookkeeping kernels
@@ -1027,7 +1040,7 @@ static int kernels_per_iteration(const System* S, int variant) {
 
 static int get_graph(System* S, int iters, int variant, cudaGraphExec_t* out) {
   Ctx& c = g_ctx;
-  const int key = 8 * iters + 4 * (S->pc_loop ? 1 : 0) + 2 * (dense_one_kernel(S) ? 1 : 0) + variant;
+  const int key = 8 * iters + 4 * (S->pc_loop ? 1 : 0) + variant;
   auto it = S->graphs.find(key);
   if (it != S->graphs.end()) {
     *out = it->second;
@@ -1070,6 +1083,23 @@ double System::matrix_bytes() const {
 }
 double System::iter_bytes() const { return matrix_bytes() + 88.0 * (double)nloc; }
 double System::k1_bytes() const { return matrix_bytes() + 16.0 * (double)nloc; }
+
+// Bytes this rank sends to its peers per classic iteration (NVLink, one direction): its share of
+// the search-direction exchange (peer-memory mode: the rows it stores into the peers' gather
+// vectors; NCCL mode: the halo rows it sends, or its block to every peer for an all-gather) plus
+// the two scalar sums (one 32-byte flagged slot per peer and sum; NCCL mode: counted alike).
+double System::comm_bytes_per_iter() const {
+  if (world <= 1) return 0.0;
+  double rows = 0.0;
+  if (p2p) {
+    for (int t = 0; t < cm.npush; ++t) rows += (double)(cm.push[t].end - cm.push[t].begin);
+  } else if (allgather) {
+    rows = (double)nloc * (world - 1);
+  } else {
+    rows = (double)send_lo * (rank > 0 ? 1 : 0) + (double)send_hi * (rank + 1 < world ? 1 : 0);
+  }
+  return 8.0 * rows + 2.0 * 32.0 * (world - 1);
+}
 
 // Switches the matvec of a CSR system between the stream kernel and the row-pattern kernel.
 int system_use_pattern(System* S, int on) {
@@ -1171,13 +1201,20 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
   const long long launches0 = launch_count();
   const int max_iter = o.max_iter < 0 ? 0 : o.max_iter;
 
+  // dense row block, classic recurrence: one persistent launch runs the loop entry and every
+  // iteration; it reads max_iter / tol from its arguments, so not even the scalars are uploaded
+  const bool dense1 = variant == 0 && !jacobi && dense_one_kernel(S);
+  const bool fused_entry = dense1 && !warm;
+
   // device scalars for this solve
   CgState* h = &c.h_state[2];
-  memset(h, 0, sizeof(CgState));
-  h->tol = o.tol > 0.0 ? o.tol : 0.0;
-  h->max_iter = max_iter;
-  h->variant = variant;
-  CUDA_OK(cudaMemcpyAsync(S->state, h, sizeof(CgState), cudaMemcpyHostToDevice, c.stream));
+  if (!fused_entry) {
+    memset(h, 0, sizeof(CgState));
+    h->tol = o.tol > 0.0 ? o.tol : 0.0;
+    h->max_iter = max_iter;
+    h->variant = variant;
+    CUDA_OK(cudaMemcpyAsync(S->state, h, sizeof(CgState), cudaMemcpyHostToDevice, c.stream));
+  }
 
   if (S->nloc == 0 && !multi) {
     if (res) {
@@ -1205,7 +1242,7 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
                           S->nloc, S->partials, &S->state->ticket[1], S->state,
                           nccl ? FIN_LOCAL : FIN_INIT2, cm, c.stream));
     if (nccl && enqueue_nccl_finish(S, 2, FIN_INIT2)) return -1;
-  } else {
+  } else if (!fused_entry) {
   // loop entry: x = 0, r = p = b, rr = bb = b.b                         (cg.c:104-108)
   CUDA_OK(launch_init(S->x, S->r, S->p_own, S->s, S->b, S->nloc, variant == 1 ? 1 : 0, S->partials,
                       &S->state->ticket[2], S->state, nccl ? FIN_LOCAL : FIN_INIT, cm, c.stream));
@@ -1226,6 +1263,12 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
   const int kpi = kernels_per_iteration(S, variant);
 
   CUDA_OK(cudaEventRecord(c.t0, c.stream));
+  if (dense1) {
+    // the launch ends by itself when the loop stops (count, tolerance, breakdown): no polling
+    if (launch_dense_solve(S, (int)std::min<long long>(total_updates, 0x7fffffff), fused_entry ? 1 : 0,
+                           max_iter, o.tol > 0.0 ? o.tol : 0.0, 0))
+      return -1;
+  } else {
   long long enq = 0;
   int k = 0;
   bool stop = false;
@@ -1246,6 +1289,7 @@ int system_solve(System* S, const SolveOpts& o, SolveResult* res) {
       if (c.h_state[(k - 1) & 1].done) stop = true;
     }
     ++k;
+  }
   }
   CUDA_OK(cudaEventRecord(c.t1, c.stream));
   CUDA_OK(cudaMemcpyAsync(&c.h_state[3], S->state, sizeof(CgState), cudaMemcpyDeviceToHost,
@@ -1342,6 +1386,12 @@ int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out) {
   const long long total_updates = (long long)max_iter + 1;
   int batch = o.check_every > 0 ? o.check_every : 32;
   if (batch > total_updates) batch = (int)total_updates;
+  if (variant == 0 && dense_one_kernel(S)) {
+    // dense row block: the whole solve is one persistent launch (loop entry included)
+    CUDA_OK(cudaEventRecord(a.t0, c.stream));
+    if (launch_dense_solve(S, (int)std::min<long long>(total_updates, 0x7fffffff), 1, max_iter, 0.0, 0))
+      return -1;
+  } else {
   cudaGraphExec_t exec = nullptr, exec_tail = nullptr;
   if (get_graph(S, batch, variant, &exec)) return -1;
   const int tail = (int)(total_updates % batch);  // exactly max_iter + 1 updates are enqueued
@@ -1364,6 +1414,7 @@ int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out) {
   if (tail > 0) {
     CUDA_OK(cudaGraphLaunch(exec_tail, c.stream));
     add_launches((long long)kpi * tail);
+  }
   }
   CUDA_OK(cudaEventRecord(a.t1, c.stream));
   CUDA_OK(cudaMemcpyAsync(a.down, S->state, sizeof(CgState), cudaMemcpyDeviceToHost, c.stream));
@@ -1567,6 +1618,14 @@ int timer_start() {
     CUDA_OK(cudaEventCreate(&c.t3));
   }
   CUDA_OK(cudaStreamSynchronize(c.stream));
+  if (c.world > 1 && c.comm) {
+    // several ranks: the start event sits behind a device-side rendezvous (a 4-byte all-reduce on
+    // the solve stream, not waited for by the host), so every rank's timed region begins when the
+    // last rank's stream gets there and not when its host process happened to be scheduled
+    CUDA_OK(cudaMemsetAsync(c.d_scratch, 0, 8, c.stream));
+    NCCL_OK(g_nccl.AllReduce(c.d_scratch, c.d_scratch, 1, ncclInt32, ncclSum, (ncclComm_t)c.comm,
+                             c.stream));
+  }
   CUDA_OK(cudaEventRecord(c.t2, c.stream));
   return 0;
 }
@@ -1585,6 +1644,8 @@ int timer_stop(double* ms_out) {
   return 0;
 }
 
+constexpr int TIME_KERNEL_DENSE_ITERS = 5;  // iterations per launch when the dense solve kernel is timed
+
 int system_time_kernel(System* S, int which, int reps, double* ms_out) {
   Ctx& c = g_ctx;
   // a benign state: alpha = beta = 0 keeps x, r, p finite however often the kernels run
@@ -1602,14 +1663,12 @@ int system_time_kernel(System* S, int which, int reps, double* ms_out) {
                                &S->state->ticket[1], S->state, FIN_LOCAL, 0, S->cm_off, c.stream));
     } else if (which == 3) {
       CUDA_OK(launch_update_p(S->p_own, S->r, S->nloc, S->state, 0, S->cm_off, c.stream));
-    } else if (which == 6) {  // the one-kernel dense iteration, scalars left alone
+    } else if (which == 6) {  // the persistent dense solve kernel, scalars left alone
       if (!dense_one_kernel(S)) {
-        set_error("system_time_kernel: this system does not run the one-kernel iteration");
+        set_error("system_time_kernel: this system does not run the one-kernel solve");
         return -1;
       }
-      CUDA_OK(launch_cg_dense_iter(S->A.vals, S->n_global, S->nloc, (int)S->n_global, S->p_ext,
-                                   S->p_own, S->x, S->r, S->s, S->partials, S->state, 0, 1,
-                                   nullptr, S->gemv_pool, S->cm_off, c.stream));
+      if (launch_dense_solve(S, TIME_KERNEL_DENSE_ITERS, 0, 0, 0.0, 1)) return -1;
     } else if (which == 4) {
       CUDA_OK(launch_update_sr(S->x, S->p_own, S->r, S->s, S->w, S->nloc, S->state, 0, S->cm_off,
                                c.stream));
@@ -1628,6 +1687,7 @@ int system_time_kernel(System* S, int which, int reps, double* ms_out) {
   float ms = 0.f;
   CUDA_OK(cudaEventElapsedTime(&ms, c.t0, c.t1));
   *ms_out = (double)ms / reps;
+  if (which == 6) *ms_out /= TIME_KERNEL_DENSE_ITERS;  // per iteration
   return 0;
 }
 

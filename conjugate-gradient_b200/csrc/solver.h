@@ -95,6 +95,7 @@ struct System {
   double matrix_bytes() const;  // bytes of A the matvec streams per launch in the current format
   double iter_bytes() const;  // contract bytes per iteration: A + 88 n
   double k1_bytes() const;    // share of the matvec kernel: A + 16 n
+  double comm_bytes_per_iter() const;  // bytes this rank sends to peers per classic iteration
   ~System();
 };
 

@@ -172,11 +172,13 @@ int cgb200_system_true_relres(cgb200_system *sys, double *relres);
 /* Average device time (ms, CUDA events on the launching stream) of `reps` back-to-back launches
  * of one kernel of the loop on this system's buffers.  which: 1 = matvec+dot (K1),
  * 2 = x/r update + r.r (K2), 3 = direction update (K3); single-reduction variant: 4 = the fused
- * vector update, 5 = matvec with both dot products; 6 = the one-kernel classic iteration of the
- * dense path (only where cgb200_system_one_kernel_iteration() is 1). */
+ * vector update, 5 = matvec with both dot products; 6 = the dense path's persistent solve kernel
+ * (only where cgb200_system_one_kernel_iteration() is 1): launches of 5 iterations each, and the
+ * figure returned is the time per ITERATION (launch duration / 5). */
 int cgb200_system_time_kernel(cgb200_system *sys, int which, int reps, double *ms);
-/* 1 if a classic iteration of this system is ONE cooperative launch (dense row block, one GPU or
- * peer-memory mode): matvec, both reductions and both vector updates behind two grid barriers. */
+/* 1 if a classic solve of this system is ONE cooperative launch (dense row block, one GPU or
+ * peer-memory mode): loop entry and every iteration -- matvec, both reductions, both vector
+ * updates -- behind grid barriers; the launch ends by itself when the loop stops. */
 int cgb200_system_one_kernel_iteration(cgb200_system *sys);
 /* Process-wide switch for the above (default on; CGB200_DENSE_FUSED=0 also turns it off): with 0 the
  * dense path runs the same three kernels per iteration as the CSR path.  For comparison runs. */
@@ -207,6 +209,10 @@ int cgb200_system_use_pattern_format(cgb200_system *sys, int on);
 int cgb200_system_trace(cgb200_system *sys, int on, unsigned long long *out16);
 /* Contract bytes per iteration for this rank and the share of the matvec kernel. */
 int cgb200_system_bytes(cgb200_system *sys, double *iter_bytes, double *k1_bytes);
+/* Bytes this rank sends to its peers over NVLink per classic iteration: its share of the
+ * search-direction exchange (halo rows, or its whole block to every peer for a dense system) plus
+ * the two scalar sums.  0 on one GPU. */
+double cgb200_system_comm_bytes(cgb200_system *sys);
 /* Copies the matrix block to host arrays (any may be NULL): vals[nnz], cols[nnz] (global column
  * indices), row_ptr[rows+1] (local, from 0).  Lets a device-generated system be handed to code
  * that wants the reference's host structs (the cg driver's --gen, bench.py's end-to-end leg). */

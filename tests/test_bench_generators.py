@@ -37,3 +37,12 @@ def test_banded_host_system_is_deterministic():
     a = bench.banded_host_system(500, 7)
     b = bench.banded_host_system(500, 7)
     assert all(np.array_equal(u, v) for u, v in zip(a, b))
+
+
+def test_both_arms_name_the_workload_identically():
+    # the driver compares the `config` dict of the b200 arm with the reference arm's: nothing in it
+    # may depend on how a run was partitioned (that lives under `run`)
+    for nm in ("dense32768", "lap2d4096", "lap3d512", "lap3d384w"):
+        assert bench.workload_config(nm) == bench.workload_config(nm, 8)
+        assert "partition" not in bench.workload_config(nm)
+

@@ -499,8 +499,8 @@ def _dev(pkg, s):
 
 @pytest.mark.parametrize("n", [256, 1000, 2052, 4096])
 def test_dense_one_kernel_iteration_matches_three_kernel_form(pkg, gpu_lib, n):
-    # dense path: matvec, both reductions and both vector updates in ONE cooperative launch
-    # (k_cg_dense_iter) against the K1/K2/K3 form of the same recurrence, and against the oracle
+    # dense path: loop entry and every iteration in ONE cooperative launch per solve
+    # (k_cg_dense_solve) against the K1/K2/K3 form of the same recurrence, and against the oracle
     s = H.dense(n)
     xo, it_o, _, _ = H.oracle_cg(s, 4)
     got = {}
@@ -513,7 +513,7 @@ def test_dense_one_kernel_iteration_matches_three_kernel_form(pkg, gpu_lib, n):
             r = d.solve(4, check_every=5)
             launches = gpu_lib.cgb200_launch_count() - l0
             assert r.iterations == it_o == 5 and r.status == pkg.MAXITER
-            assert launches == 1 + (5 if on else 15), launches      # k_init + kernels of 5 iterations
+            assert launches == (1 if on else 1 + 15), launches      # one launch per solve | k_init + 5 x (K1, K2, K3)
             rt = d.solve(500, tol=1e-10)
             got[on] = (d.x(), r.rr, rt.iterations, rt.status, d.true_relres())
             d.gen_rhs(3)
@@ -925,3 +925,120 @@ def test_full_size_dense_32768(pkg, gpu_lib):
     assert r.status == pkg.CONVERGED and r.iterations <= 12
     assert d.true_relres() <= TOL_RES * 1.05
     d.free()
+
+
+# ---------------------------------------------------------------------------------------------
+# full-size configurations against the ORACLE itself (north_star: "results must match the
+# reference's CPU solve on the same inputs"): x after a fixed small K at BASELINE sizes (SURVEY
+# H9), the matvec bit for bit on all rows, and the device generator against the oracle's.
+# ---------------------------------------------------------------------------------------------
+
+
+def _host_ram_gb():
+    try:
+        import psutil
+
+        return psutil.virtual_memory().available / 1e9
+    except Exception:  # noqa: BLE001
+        return 0.0
+
+
+def test_full_size_lap2d_4096_x_matches_the_oracle_after_20_iterations(pkg, gpu_lib):
+    L = gpu_lib
+    nx = ny = 4096
+    n = nx * ny
+    s = H.lap(nx, ny)                                  # the oracle's own generator, 83.9 M entries
+    d = pkg.DeviceSystem.lap(nx, ny, 1)
+    # the device-generated system IS the oracle's, bit for bit
+    vals = np.empty(d.nnz)
+    cols = np.empty(d.nnz, dtype=np.int32)
+    rp = np.empty(n + 1, dtype=np.int32)
+    assert L.cgb200_system_download(d.h, H.dptr(vals), H.iptr(cols), H.iptr(rp)) == 0, pkg.last_error()
+    assert np.array_equal(rp, s.row_ptr) and np.array_equal(cols, s.cols) and np.array_equal(_bits(vals), _bits(s.vals))
+    del vals, cols, rp
+    # the matvec on all 16.7 M rows, bit-exact
+    v = H.rhs(n, 77)
+    want = np.empty(n)
+    H.oracle().oracle_spmv(n, H.iptr(s.row_ptr), H.iptr(s.cols), H.dptr(s.vals), H.dptr(v), H.dptr(want))
+    assert np.array_equal(_bits(d.matvec(v)), _bits(want))
+    # the loop: K = 20 iterations, device-resident system and the reference's own entry point
+    K = 20
+    xo, it, rr_o, _ = H.oracle_cg(s, K - 1)
+    assert it == K
+    r = d.solve(K - 1)
+    assert r.iterations == K and r.status == pkg.MAXITER
+    x = d.x()
+    assert np.linalg.norm(x - xo) / np.linalg.norm(xo) <= TOL_X
+    assert abs(r.rr - rr_o) <= 1e-10 * rr_o
+    d.free()
+    x2 = gpu_cg(pkg, L, s, K - 1)                      # conj_grad(19, A, b, &x) on the oracle's host arrays
+    assert np.linalg.norm(x2 - xo) / np.linalg.norm(xo) <= TOL_X
+    assert np.array_equal(_bits(x2), _bits(x))         # same kernels, same bits, whichever way A arrived
+
+
+def test_full_size_lap3d_512_x_matches_the_oracle_after_5_iterations(pkg, gpu_lib):
+    if _host_ram_gb() < 48:
+        pytest.skip("needs ~25 GB of host memory for the 512^3 CSR system and the oracle's vectors")
+    nx = 512
+    n = nx ** 3
+    s = H.lap(nx, nx, nx)                              # 938 M entries, 11.8 GB
+    d = pkg.DeviceSystem.lap(nx, nx, nx)
+    assert d.rows == n and d.nnz == s.nnz
+    v = H.rhs(n, 78)
+    want = np.empty(n)
+    H.oracle().oracle_spmv(n, H.iptr(s.row_ptr), H.iptr(s.cols), H.dptr(s.vals), H.dptr(v), H.dptr(want))
+    assert np.array_equal(_bits(d.matvec(v)), _bits(want))   # generator + kernel on all 134 M rows
+    del v, want
+    K = 5
+    xo, it, rr_o, _ = H.oracle_cg(s, K - 1)
+    assert it == K
+    r = d.solve(K - 1)
+    assert r.iterations == K and r.status == pkg.MAXITER
+    x = d.x()
+    assert np.linalg.norm(x - xo) / np.linalg.norm(xo) <= TOL_X
+    assert abs(r.rr - rr_o) <= 1e-10 * rr_o
+    if d.use_pattern_format(True):                     # the row-pattern format on the same system
+        d.solve(K - 1)                                 # same row sums bit for bit; the dot products are
+        xp = d.x()                                     # summed over another grid shape
+        assert np.linalg.norm(xp - xo) / np.linalg.norm(xo) <= TOL_X
+        assert np.linalg.norm(xp - x) / np.linalg.norm(x) <= 1e-12
+    d.free()
+
+
+def test_full_size_dense_32768_block_matches_the_oracle(pkg, gpu_lib):
+    # the dense generator and GEMV against the oracle on a row block of the n = 32768 system that the
+    # oracle can hold (rows 20000..20511): A[rows, :] p for a random p, within the dense path's bar
+    n, r0, nr = 32768, 20000, 512
+    O = H.oracle()
+    d = pkg.DeviceSystem.dense(n)
+    p = H.rhs(n, 79)
+    got = d.matvec(p)[r0:r0 + nr]
+    blk = np.empty((nr, n))
+    for i in range(nr):
+        gi = r0 + i
+        for j in (0, gi - 1, gi, gi + 1, n - 1):
+            blk[i, j] = 0.5 * n + 1.0 if j == gi else O.oracle_uniform(1, min(gi, j) * n + max(gi, j))
+    # full rows through a vectorised restatement of the same hash (splitmix64, as oracle_uniform)
+    def u(ctr):
+        with np.errstate(over="ignore"):
+            def sm64(z):
+                z = z + np.uint64(0x9E3779B97F4A7C15)
+                z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+                z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+                return z ^ (z >> np.uint64(31))
+            h = sm64(sm64(np.uint64(1)) ^ (ctr * np.uint64(0xD1342543DE82EF95) + np.uint64(1)))
+        return (h >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0) - 0.5
+    j = np.arange(n, dtype=np.uint64)
+    for i in range(nr):
+        gi = np.uint64(r0 + i)
+        lo, hi = np.minimum(gi, j), np.maximum(gi, j)
+        row = u(lo * np.uint64(n) + hi)
+        row[r0 + i] = 0.5 * n + 1.0
+        for jj in (0, r0 + i - 1, r0 + i, r0 + i + 1, n - 1):   # the vectorised hash IS oracle_uniform
+            assert row[jj] == blk[i, jj]
+        blk[i] = row
+    want = blk @ p
+    scale = np.abs(blk) @ np.abs(p)
+    assert np.all(np.abs(got - want) <= 4 * n * EPS * scale)
+    d.free()
+
