@@ -392,30 +392,32 @@ k_spmv_rowgroup(const double* __restrict__ vals, const int* __restrict__ cols,
 // current one runs, so the DRAM latency of a slab hides behind the additions of the previous one.
 // ---------------------------------------------------------------------------------------------
 
-// Work split.  Every warp of a persistent grid (CTAs per SM x SMs, so every SM holds the same
-// number of warps) owns ONE contiguous run of rows, cut so that all runs hold the same number of
-// stored entries (`wbound`, computed once per system by k_row_bounds; null = equal row counts), and
-// walks it in units of at most ROWS rows of equal size.  The first version dealt whole 16-row units
-// round-robin: 3267 units over 2368 resident warps is 1.38 units per warp on average and 2 for the
-// slowest -- 0.69 of the launch was the best it could do, and 0.67 is what it measured.
-//
-// L2 residency.  The loop streams the same matrix every iteration; on a matrix of a few hundred MB
-// a fixed share of it can simply stay in the 126 MB L2.  The first `res1024`/1024 of every unit's
-// slabs are loaded with the default priority, the rest evict-first, so the streamed part passes
-// through without pushing the resident part out (tools/exp/l2_resident.cu: an 80 MB head of a
-// 217 MB buffer turns 6.2 TB/s into 8.1 TB/s; at 1 GB the effect is gone, and res1024 is 0).
+// Round 2 (ncu --set full on the shipped <256,16> form, profiles/r02_ncu_longrow.md): DRAM traffic equals
+// the algorithmic bytes, DRAM at 54 % of its peak, 16 warps per SM (119 registers), 1.1 warp
+// instructions per stored entry; top stalls long scoreboard (the gathers behind the slab's loads),
+// barrier (the launch tail: 3267 blocks over 2368 warps) and wait.  The kernel streams at 0.84 of
+// the HBM peak on a matrix four times the size (869 MB) and 0.68 on the course-sized one (217 MB,
+// 49 us per product): what is missing there is a fixed ~20 us of ramp and tail, not bandwidth.
+// Tried against it and dropped, each measured slower on the course-sized matrix: equal runs of
+// stored entries per warp with 8-row units (0.53), an L2-resident head of the matrix (no gain: the
+// launch is not DRAM-bound), a ring of 16-byte asynchronous copies with gather-ahead (0.45), a
+// thread per row fed by per-row bulk copies (0.31), blocks drawn from an atomic counter with a
+// predicate-free path for full slabs (0.64), paired 128-bit loads covering two rows per
+// instruction (0.61), three CTAs per SM at 80 registers (0.34, spills).
 template <int THREADS, int ROWS, bool COHERENT>
 __global__ void __launch_bounds__(THREADS)
 k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
-                const int* __restrict__ rowptr, const int nrows, const int* __restrict__ wbound,
-                const int res1024, const double* __restrict__ pg, const double* __restrict__ pown,
-                double* __restrict__ s, double* __restrict__ partials,
-                unsigned int* __restrict__ ticket, CgState* S, const int mode,
-                const __grid_constant__ PeerComm cm) {
+                const int* __restrict__ rowptr, const int nrows, const double* __restrict__ pg,
+                const double* __restrict__ pown, double* __restrict__ s,
+                double* __restrict__ partials, unsigned int* __restrict__ ticket, CgState* S,
+                const int mode, const __grid_constant__ PeerComm cm) {
   // COHERENT (several GPUs, peer-memory mode): part of the gather vector is stored by the peers'
   // direction updates while this kernel may already be running, so every CTA first waits for
   // their completion flags and the gathers bypass L1.  (The stream kernel overlaps that wait with
   // its interior tiles; here the whole launch sits behind it.)
+  // ROWS rows per warp and work unit (lane i < ROWS owns row i of the unit): fewer rows mean
+  // fewer registers for the prefetched slab, hence more warps per SM, and finer units -- both
+  // matter while a unit's time is set by latencies rather than by its bytes
   constexpr int WARPS = THREADS / 32;
   constexpr int LD = 33;  // tile row stride in doubles: lane i reads bank pair 2i + 2j (mod 32)
   __shared__ double tile[WARPS][ROWS * LD];
@@ -429,44 +431,30 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
     if (threadIdx.x == 0) wait_halo(cm, S);
     __syncthreads();
   }
+  const int nblk = (nrows + ROWS - 1) / ROWS;
   const int cta = rev ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
-  const int W = (int)gridDim.x * WARPS, gw = cta * WARPS + warp;
-  int r0, r1;
-  if (wbound) {
-    r0 = __ldg(wbound + gw);
-    r1 = __ldg(wbound + gw + 1);
-  } else {
-    r0 = (int)((long long)nrows * gw / W);
-    r1 = (int)((long long)nrows * (gw + 1) / W);
-  }
-  const int nr = r1 - r0;
-  const int nunits = (nr + ROWS - 1) / ROWS;
+  const int b0 = (int)((long long)nblk * cta / gridDim.x);
+  const int b1 = (int)((long long)nblk * (cta + 1) / gridDim.x);
   double dot = 0.0, dot2 = 0.0;
 #pragma unroll 1
-  for (int u = 0; u < nunits; ++u) {
-    const int ub = r0 + (int)((long long)nr * u / nunits);
-    const int ue = r0 + (int)((long long)nr * (u + 1) / nunits);  // ue - ub <= ROWS
-    const int row = ub + lane;
-    const bool rv = lane < ue - ub;
+  for (int blk = b0 + warp; blk < b1; blk += WARPS) {
+    const int row = blk * ROWS + lane;
+    const bool rv = lane < ROWS && row < nrows;
     const int rs = rv ? __ldg(rowptr + row) : 0;
     const int re = rv ? __ldg(rowptr + row + 1) : 0;
     const int maxlen = __reduce_max_sync(0xffffffffu, re - rs);
-    const int res_off = (int)(((long long)maxlen * res1024) >> 10);  // slabs below this offset stay in L2
     double acc = 0.0;
     int c[ROWS];
     double v[ROWS];
     unsigned ok = 0u;  // bit i: this lane holds an entry of row i in the slab in registers
     // slab 0 into registers
-    {
-      const bool keep = 0 < res_off;
 #pragma unroll
-      for (int i = 0; i < ROWS; ++i) {
-        const int k = __shfl_sync(0xffffffffu, rs, i) + lane;
-        const bool o = k < __shfl_sync(0xffffffffu, re, i);
-        ok |= (o ? 1u : 0u) << i;
-        c[i] = o ? (keep ? __ldg(cols + k) : __ldcs(cols + k)) : 0;
-        v[i] = o ? (keep ? __ldg(vals + k) : __ldcs(vals + k)) : 0.0;
-      }
+    for (int i = 0; i < ROWS; ++i) {
+      const int k = __shfl_sync(0xffffffffu, rs, i) + lane;
+      const bool o = k < __shfl_sync(0xffffffffu, re, i);
+      ok |= (o ? 1u : 0u) << i;
+      c[i] = o ? __ldcs(cols + k) : 0;
+      v[i] = o ? __ldcs(vals + k) : 0.0;
     }
 #pragma unroll 1
     for (int off = 0; off < maxlen; off += 32) {
@@ -481,14 +469,13 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
       // next slab's indices and values on their way while this slab is added up
       ok = 0u;
       if (off + 32 < maxlen) {
-        const bool keep = off + 32 < res_off;
 #pragma unroll
         for (int i = 0; i < ROWS; ++i) {
           const int k = __shfl_sync(0xffffffffu, rs, i) + off + 32 + lane;
           const bool o = k < __shfl_sync(0xffffffffu, re, i);
           ok |= (o ? 1u : 0u) << i;
-          c[i] = o ? (keep ? __ldg(cols + k) : __ldcs(cols + k)) : 0;
-          v[i] = o ? (keep ? __ldg(vals + k) : __ldcs(vals + k)) : 0.0;
+          c[i] = o ? __ldcs(cols + k) : 0;
+          v[i] = o ? __ldcs(vals + k) : 0.0;
         }
       }
       if (lane < ROWS) {
@@ -523,25 +510,6 @@ k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
     v2[1] = 0.0;
   }
   if (last) finish_block<THREADS>(S, cm, fin, v2[0], v2[1]);
-}
-
-// wbound[k], k = 0..W: first row of warp k's run; runs hold equal shares of the stored entries.
-__global__ void k_row_bounds(const int* __restrict__ rowptr, int nrows, int W, int* __restrict__ wbound) {
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k > W) return;
-  if (k == 0 || k == W) {
-    wbound[k] = k == 0 ? 0 : nrows;
-    return;
-  }
-  const long long nnz = rowptr[nrows];
-  const long long target = nnz * k / W;
-  int lo = 0, hi = nrows;  // first row whose start offset is >= target
-  while (lo < hi) {
-    const int mid = lo + ((hi - lo) >> 1);
-    if (rowptr[mid] < target) lo = mid + 1;
-    else hi = mid;
-  }
-  wbound[k] = lo;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -2127,55 +2095,23 @@ static cudaError_t launch_spmv_rowgroup_cfg(const CsrDev& A, const double* pg, c
   return cudaGetLastError();
 }
 
-// Share of a matrix of `matrix_bytes` that the loop keeps in L2 across iterations, in 1/1024:
-// CGB200_L2_RESIDENT_MB (default 80) minus the loop's vectors, and nothing for matrices beyond
-// 600 MB, where a resident head no longer pays (tools/exp/l2_resident.cu).
-int l2_resident_1024(double matrix_bytes, double vector_bytes) {
-  static double mb = -1.0;
-  if (mb < 0.0) {
-    const char* e = getenv("CGB200_L2_RESIDENT_MB");
-    mb = e ? atof(e) : 80.0;
-    if (mb < 0.0) mb = 0.0;
-  }
-  const double budget = mb * 1e6 - vector_bytes;
-  if (budget <= 0.0 || matrix_bytes <= 0.0 || matrix_bytes > 600e6) return 0;
-  const double f = budget / matrix_bytes;
-  return f >= 1.0 ? 1024 : (int)(f * 1024.0);
-}
-
-template <int T, int ROWS, bool COH>
-static int rowblock_grid() {
-  static int bps = 0;
-  if (!bps) {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowblock<T, ROWS, COH>, T, 0);
-    if (bps < 1) bps = 1;
-  }
-  int grid = sm_count() * bps;  // every SM holds the same number of warps
-  if (grid > MAX_GRID) grid = MAX_GRID;
-  return grid;
-}
-
-// Warps of the default long-row launch (the run bounds of a system are computed for this count).
-int spmv_longrow_warps(bool coherent) {
-  return (coherent ? rowblock_grid<256, 16, true>() : rowblock_grid<256, 16, false>()) * (256 / 32);
-}
-
-cudaError_t launch_row_bounds(const int* rowptr, int nrows, int W, int* wbound, cudaStream_t st) {
-  k_row_bounds<<<(W + 1 + 127) / 128, 128, 0, st>>>(rowptr, nrows, W, wbound);
-  ++g_launches;
-  return cudaGetLastError();
-}
-
 template <int T, int ROWS, bool COH = false>
 static cudaError_t launch_spmv_rowblock_cfg(const CsrDev& A, const double* pg, const double* pown,
                                             double* s, double* partials, unsigned int* ticket,
                                             CgState* S, int mode, const PeerComm& cm,
                                             cudaStream_t st) {
-  const int grid = rowblock_grid<T, ROWS, COH>();
-  const int W = grid * (T / 32);
-  const int* wb = (A.wbound && A.wbound_w == W) ? A.wbound : nullptr;  // else: equal row counts
-  k_spmv_rowblock<T, ROWS, COH><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, wb, A.res1024,
-                                                    pg, pown, s, partials, ticket, S, mode, cm);
+  static int bps = 0;
+  if (!bps) {
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_spmv_rowblock<T, ROWS, COH>, T, 0);
+    if (bps < 1) bps = 1;
+  }
+  const int nblk = (A.nrows + ROWS - 1) / ROWS;
+  int grid = sm_count() * bps;
+  const int need = (nblk + T / 32 - 1) / (T / 32);
+  if (grid > need) grid = need;
+  if (grid > MAX_GRID) grid = MAX_GRID;
+  k_spmv_rowblock<T, ROWS, COH><<<grid, T, 0, st>>>(A.vals, A.cols, A.rowptr, A.nrows, pg, pown, s,
+                                                    partials, ticket, S, mode, cm);
   ++g_launches;
   return cudaGetLastError();
 }

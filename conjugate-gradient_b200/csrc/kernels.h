@@ -20,11 +20,6 @@ struct CsrDev {
   // banded matrices: gather index of the upper band edge = local row + lead (-1: no prefetch);
   // plen = length of the gather vector
   long long lead = -1, plen = 0;
-  // long-row matvec (k_spmv_rowblock): first row of every warp's run for a launch of wbound_w warps
-  // (runs of equal stored entries), and the share of the matrix kept in L2 across iterations (1/1024)
-  int* wbound = nullptr;
-  int wbound_w = 0;
-  int res1024 = 0;
 };
 
 // Row-pattern dictionary format (pattern.cu): one byte per row naming the row's pattern
@@ -147,9 +142,6 @@ cudaError_t launch_spmv_rowgroup(const CsrDev& A, const double* pg, const double
                                  double* partials, unsigned int* ticket, CgState* S, int mode,
                                  const PeerComm& cm, cudaStream_t st);
 int spmv_rowgroup_min();
-int spmv_longrow_warps(bool coherent);
-int l2_resident_1024(double matrix_bytes, double vector_bytes);
-cudaError_t launch_row_bounds(const int* rowptr, int nrows, int W, int* wbound, cudaStream_t st);
 // Several GPUs in peer-memory mode: the default long-row kernel, every CTA first waiting for the
 // peers' halo flags, gathers bypassing L1 (the other forms are single-GPU / NCCL-mode only).
 cudaError_t launch_spmv_longrow_coherent(const CsrDev& A, const double* pg, const double* pown,

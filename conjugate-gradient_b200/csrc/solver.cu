@@ -295,7 +295,6 @@ System::~System() {
   dev_free(A.vals);
   dev_free(A.cols);
   dev_free(A.rowptr);
-  dev_free(A.wbound);
   dev_free(b);
   dev_free(x);
   dev_free(r);
@@ -510,16 +509,6 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
       // worth it only for a band that is wide enough to fall out of the tile's own footprint and
       // narrow enough to be a band at all
       if (lead > 4 * spmv_rows_per_tile() && lead < S->ext_len) S->A.lead = lead;
-    }
-    // long rows (k_spmv_rowblock): the warps' runs of equal stored entries, and the L2-resident share
-    const int rgm = spmv_rowgroup_min();
-    if (rgm > 0 && S->nloc > 0 && S->A.nnz >= (long long)rgm * S->nloc) {
-      const bool coherent = c.world > 1 && S->p2p && S->cm.nwait > 0;
-      const int W = spmv_longrow_warps(coherent);
-      CUDA_OK(DEV_ALLOC(&S->A.wbound, ((size_t)W + 1) * sizeof(int)));
-      CUDA_OK(launch_row_bounds(S->A.rowptr, S->nloc, W, S->A.wbound, c.stream));
-      S->A.wbound_w = W;
-      S->A.res1024 = l2_resident_1024(12.0 * (double)S->A.nnz, 5.0 * 8.0 * (double)S->ext_len);
     }
     const int R = spmv_rows_per_tile();
     S->ntiles = (S->nloc + R - 1) / R;

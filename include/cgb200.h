@@ -145,8 +145,14 @@ typedef struct cgb200_system cgb200_system;
 cgb200_system *cgb200_system_lap(int nx, int ny, int nz, int z0, int nzl, uint64_t bseed);
 /* Rows [row0, row0+nrows) of the dense SPD test matrix, values only. */
 cgb200_system *cgb200_system_dense(int n, int row0, int nrows, uint64_t aseed, uint64_t bseed);
-/* Rows [row0, row0+nrows) of a CSR matrix held in host arrays: row_ptr[nrows+1] local (starts at
- * 0), cols global, b local.  A full-row matrix (row_ptr[i] == i*n_global) takes the dense path. */
+/* Rows [row0, row0+nrows) of a CSR matrix held in host arrays.  row_ptr[nrows+1] are this block's
+ * row offsets INTO cols[] / vals[]: either a local array that starts at 0 with the block's own
+ * cols / vals, or a slice of the global row_ptr (row_ptr = global_row_ptr + row0, starting at any
+ * offset) with the GLOBAL cols / vals arrays -- the block's entries are then
+ * cols[row_ptr[0] .. row_ptr[nrows]).  Column indices are global, 0-based and ascending within a
+ * row; b holds the block's nrows right-hand-side entries (may be NULL: set later).  The arrays are
+ * checked on upload (column range, non-decreasing row_ptr): a malformed matrix is refused with
+ * NULL and a message.  A full-row matrix (row_ptr[i] == i*n_global) takes the dense path. */
 cgb200_system *cgb200_system_from_csr(long long n_global, long long row0, int nrows,
                                       const int *row_ptr, const int *cols, const double *vals,
                                       const double *b);
