@@ -72,6 +72,7 @@ CLASSIC, SINGLE_REDUCTION = 0, 1
 EAGER, RESIDENT = 0, 1
 OPT_JACOBI, OPT_X0 = 1, 2
 CACHE_STRICT, CACHE_SAMPLED, CACHE_OFF = 0, 1, 2
+DOT_STATIC_MAX_N = 1 << 28
 
 # every symbol include/mv_ops.h and include/cgb200.h declare (checked by tests/test_abi_symbols.py)
 MV_OPS_SYMBOLS = [
@@ -139,6 +140,7 @@ def lib():
     L.cgb200_guard_check.argtypes = []
     L.cgb200_guard_selftest.restype = C.c_int
     L.cgb200_guard_selftest.argtypes = []
+    L.cgb200_dot_static.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]
     L.cgb200_set_mode.argtypes = [C.c_int]
     L.cgb200_set_matrix_cache.argtypes = [C.c_int]
     L.cgb200_content_hash.restype = C.c_ulonglong

@@ -230,6 +230,23 @@ int cgb200_timer_stop(double *ms);
 long long cgb200_system_rows(cgb200_system *sys);
 long long cgb200_system_nnz(cgb200_system *sys);
 
+/* ---- an entry point that allocates nothing ---------------------------------------------------- */
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  *result_dev = sum_i a_dev[i] * b_dev[i] for DEVICE vectors of n doubles, on the current
+ * device, enqueued on `stream` (a cudaStream_t; NULL = the default stream) and not waited for.  The
+ * reduction's scratch (one partial sum per 2^18 elements and a ticket) lives in a file-scope static
+ * __device__ array of 8.5 KB that every GPU which loads the library holds until exit, hence the
+ * limit: n <= CGB200_DOT_STATIC_MAX_N, larger n is refused with -1 and a message.  Neither this call
+ * nor anything it calls allocates or frees device memory, and it does not create the library's
+ * context.  Every call on a device shares the one array: calls that overlap on the same GPU (two
+ * streams, two threads) race -- serialise them.  The result has the same bits on every GPU and for
+ * every grid size (partials belong to chunks of the vectors and are added in chunk order); it
+ * agrees with dot_product to the summation-order bound 4 n eps sum|a_i b_i|.  0 / -1. */
+#define CGB200_DOT_STATIC_MAX_N 268435456LL /* 2^28 */
+int cgb200_dot_static(const double *a_dev, const double *b_dev, long long n, double *result_dev,
+                      void *stream);
+
 /* ---- systems on disk (host only) ------------------------------------------ */
 /* Replaces read_input_file (reference cg.c:146-218): fills caller-created A and b (new_mv_struct)
  * from the reference's 4-line comma-separated text format -- line 0 column indices, 1 row
