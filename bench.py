@@ -725,25 +725,26 @@ def comm_report(pkg, d, info, world, ms_per_step, roof, comm_mode):
 
 
 def dense_phase_trace(pkg, d, world, sm_mhz):
-    """Phase trace of the dense one-kernel iteration (cgb200_system_trace) over 40 short solves: where
-    the cross-GPU steps sit inside the launch, in microseconds (SM cycles / sampled SM clock)."""
+    """Phase trace of the dense one-kernel solve (cgb200_system_trace) over 40 short solves: where
+    the cross-GPU steps sit inside the launch, in microseconds (SM cycles / sampled SM clock).
+    Collective: EVERY rank runs the traced solves; the rank without a clock sample returns None."""
     L = pkg.lib()
-    if not d.one_kernel_iteration() or not sm_mhz:
+    if not d.one_kernel_iteration():      # (the same answer on every rank)
         return None
     out = (C.c_ulonglong * (16 + 2048))()
-    if L.cgb200_system_trace(d.h, 1, None) != 0:
-        return None
+    ok = L.cgb200_system_trace(d.h, 1, None) == 0
     for k in range(40):
         d.gen_rhs(300 + k)
         d.solve(4, check_every=5)
-    if L.cgb200_system_trace(d.h, 0, out) != 0:
+    ok = (L.cgb200_system_trace(d.h, 0, out) == 0) and ok
+    if not ok or not sm_mhz:
         return None
     cnt = max(int(out[7]), 1)
     us = lambda i: out[i] / cnt / sm_mhz  # noqa: E731
     return {"launches": cnt, "wait_for_peers_p_us": round(us(0), 2), "gemv_done_us": round(us(1), 2),
             "sum1_alpha_us": round(us(3) - us(1), 2), "xr_update_us": round(us(4) - us(3), 2),
             "sum2_beta_us": round(us(5) - us(4), 2), "p_update_push_us": round(us(6) - us(5), 2),
-            "note": "closing CTA's clock64 per phase / sampled SM MHz; sums include the grid reduction and, with several GPUs, the cross-GPU exchange"}
+            "note": "closing CTA's clock64 per phase / sampled SM MHz, per iteration; sums include the grid reduction and, with several GPUs, the cross-GPU exchange"}
 
 
 def parity_multi(pkg, rank, world, comm_mode):
