@@ -63,12 +63,16 @@ ALG = {  # algorithmic bytes per launch
     "dense": {"n": 32768, "nnz": 32768 ** 2, "dense": True},
     "lap2d": {"n": 4096 ** 2, "nnz": 5 * 4096 ** 2 - 4 * 4096},
     "lap3d512": {"n": 512 ** 3, "nnz": 7 * 512 ** 3 - 6 * 512 ** 2},
+    "banded": {"n": 52269, "nnz": 18003049},   # course-sized long-row system (bench.py: banded52269)
 }
+DENSE_ITERS_PER_LAUNCH = 5   # tools/ncu_round.sh profiles one persistent launch: loop entry + 5 iterations
 
 
 def alg_bytes(w, kernel):
     a = ALG[w]
     n, nnz = a["n"], a["nnz"]
+    if kernel.startswith("k_cg_dense_solve"):  # loop entry (32 n) + 5 whole iterations (A + 88 n each)
+        return DENSE_ITERS_PER_LAUNCH * (8.0 * nnz + 88.0 * n) + 32.0 * n
     if kernel.startswith("k_cg_dense"):  # the whole iteration: contract bytes A + 88 n
         return 8.0 * nnz + 88.0 * n
     if kernel.startswith("k_gemv"):
@@ -112,7 +116,10 @@ for path in paths:
                   f"{rd / 1e9:.4f} | {wrt / 1e9:.4f} | {(rd + wrt) / 1e9:.4f} | {alg / 1e9 if alg else 0:.4f} | {(rd + wrt) / alg if alg else 0:.3f} | "
                   f"{(rd + wrt) / t / 1e3:.0f} | {avg('dram_pct'):.1f} | {avg('l2_hit_pct'):.1f} | {avg('l1_hit_pct'):.1f} | {avg('warps_active_pct'):.1f} |")
         if v == "classic" or kname == "k_update_sr" or kname.startswith("k_spmv_pattern"):
-            traffic["_by_workload"].setdefault(w, {})[kname] = round(rd + wrt)
+            key = {"banded": "banded52269"}.get(w, w)
+            traffic["_by_workload"].setdefault(key, {})[kname] = round(rd + wrt)
+            if kname == "k_cg_dense_solve":
+                traffic["_by_workload"][key]["_iterations_per_launch"] = DENSE_ITERS_PER_LAUNCH
 with open(os.path.join(DST, f"{tag}_ncu_summary.md"), "w") as f:
     f.write("\n".join(md) + "\n")
 json.dump(traffic, open(os.path.join(DST, "traffic.json"), "w"), indent=1)
