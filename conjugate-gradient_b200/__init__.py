@@ -141,6 +141,7 @@ def lib():
     L.cgb200_guard_selftest.restype = C.c_int
     L.cgb200_guard_selftest.argtypes = []
     L.cgb200_dot_static.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]
+    L.cgb200_set_gpus.argtypes = [C.c_int]
     L.cgb200_set_mode.argtypes = [C.c_int]
     L.cgb200_set_matrix_cache.argtypes = [C.c_int]
     L.cgb200_content_hash.restype = C.c_ulonglong

@@ -21,6 +21,7 @@
 #include "devmem.h"
 #include "../../include/cgb200.h"
 #include "solver.h"
+#include "team.h"
 
 using namespace cgb;
 
@@ -50,7 +51,8 @@ int g_mode = initial_mode();
 // ---- device mirrors of caller structs (keyed by struct address) -----------------------------
 
 struct MatrixEntry {
-  System* sys = nullptr;
+  System* sys = nullptr;       // single-GPU copy (mv_mult, and solves without a GPU team)
+  TeamSystem* team = nullptr;  // row blocks over the GPU team (solves with CGB200_GPUS > 1)
   const double* values = nullptr;
   const int* cols = nullptr;
   const int* rowptr = nullptr;
@@ -233,12 +235,21 @@ bool is_vector(const struct __mv_sparse* v) { return v->col_indices == NULL && v
 
 // Device system for a host CSR struct, uploaded on first use and whenever the struct's arrays no
 // longer hold what was uploaded (policy above).  pin: the caller hands the matrix over explicitly.
-System* matrix_system(struct __mv_sparse* A, bool pin = false) {
+void release_entry(MatrixEntry& e) {
+  delete e.sys;
+  e.sys = nullptr;
+  if (e.team) team_destroy(e.team);  // collective with the workers
+  e.team = nullptr;
+}
+
+// The cache entry of a caller's matrix with the requested device copy in it: one GPU (want_team
+// false) or row blocks over the GPU team.  Validation is the same for both (policy above).
+MatrixEntry* matrix_entry(struct __mv_sparse* A, bool pin, bool want_team) {
   if (!A->row_ptr || !A->values || (!A->col_indices && A->nnz > 0)) {
     set_error("matrix struct lacks CSR arrays");
     return nullptr;
   }
-  if (ctx().world > 1) {
+  if (ctx().world > 1 && !ctx().team_primary) {
     set_error("host-struct entry points are single-rank; use the cgb200_system_* API when distributed");
     return nullptr;
   }
@@ -246,47 +257,85 @@ System* matrix_system(struct __mv_sparse* A, bool pin = false) {
   const uint64_t fp = fingerprint(A);
   uint64_t content = 0;
   bool have_content = false;
+  MatrixEntry* e = nullptr;
   auto it = g_mats.find(A);
   if (it != g_mats.end()) {
-    MatrixEntry& e = it->second;
-    bool same = policy != CGB200_CACHE_OFF && e.values == A->values && e.cols == A->col_indices &&
-                e.rowptr == A->row_ptr && e.size == A->size && e.nnz == A->nnz && e.fp == fp;
-    const bool trusted = e.pinned || g_mode == CGB200_RESIDENT || policy == CGB200_CACHE_SAMPLED;
+    MatrixEntry& old = it->second;
+    bool same = policy != CGB200_CACHE_OFF && old.values == A->values && old.cols == A->col_indices &&
+                old.rowptr == A->row_ptr && old.size == A->size && old.nnz == A->nnz && old.fp == fp;
+    const bool trusted = old.pinned || g_mode == CGB200_RESIDENT || policy == CGB200_CACHE_SAMPLED;
     if (same && !trusted) {
       content = content_hash(A);
       have_content = true;
-      same = e.has_content && e.content == content;
+      same = old.has_content && old.content == content;
     }
     if (same) {
-      if (pin) e.pinned = true;
-      return e.sys;
+      e = &old;
+      if (pin) e->pinned = true;
+    } else {
+      release_entry(old);
+      g_mats.erase(it);
     }
-    delete e.sys;
-    g_mats.erase(it);
   }
-  // the hash for the next call's comparison is taken while the upload runs
-  std::thread hasher;
-  if (policy == CGB200_CACHE_STRICT && !have_content)
-    hasher = std::thread([&]() { content = content_hash(A); });
-  System* sys = system_from_csr(A->size, 0, A->size, A->row_ptr, A->col_indices, A->values, nullptr);
+  std::thread hasher;  // the hash for the next call's comparison is taken while the upload runs
+  bool fresh = false;
+  if (!e) {
+    MatrixEntry ne;
+    ne.values = A->values;
+    ne.cols = A->col_indices;
+    ne.rowptr = A->row_ptr;
+    ne.size = A->size;
+    ne.nnz = A->nnz;
+    ne.fp = fp;
+    ne.content = content;
+    ne.has_content = have_content;
+    ne.pinned = pin;
+    e = &(g_mats[A] = ne);
+    fresh = true;
+    if (policy == CGB200_CACHE_STRICT && !have_content)
+      hasher = std::thread([&]() { content = content_hash(A); });
+  }
+  bool ok = true;
+  if (want_team && !e->team) {
+    e->team = team_create(A);
+    ok = e->team != nullptr;
+  } else if (!want_team && !e->sys) {
+    SoloScope solo;  // (the primary of a GPU team is in a multi-rank world: this copy is not)
+    e->sys = system_from_csr(A->size, 0, A->size, A->row_ptr, A->col_indices, A->values, nullptr);
+    ok = e->sys != nullptr;
+  }
   if (hasher.joinable()) {
     hasher.join();
-    have_content = true;
+    e->content = content;
+    e->has_content = true;
   }
-  if (!sys) return nullptr;
-  MatrixEntry e;
-  e.sys = sys;
-  e.values = A->values;
-  e.cols = A->col_indices;
-  e.rowptr = A->row_ptr;
-  e.size = A->size;
-  e.nnz = A->nnz;
-  e.fp = fp;
-  e.content = content;
-  e.has_content = have_content;
-  e.pinned = pin;
-  g_mats[A] = e;
-  return sys;
+  if (!ok) {
+    if (fresh || (!e->sys && !e->team)) g_mats.erase(A);
+    return nullptr;
+  }
+  return e;
+}
+
+// Device system for a host CSR struct, uploaded on first use and whenever the struct's arrays no
+// longer hold what was uploaded (policy above).  pin: the caller hands the matrix over explicitly.
+System* matrix_system(struct __mv_sparse* A, bool pin = false) {
+  MatrixEntry* e = matrix_entry(A, pin, false);
+  return e ? e->sys : nullptr;
+}
+
+// Several GPUs behind the host-struct solve (team.h): asked for, worth it, and the team is up.
+bool want_team(const struct __mv_sparse* A) {
+  const int g = team_requested();
+  if (g <= 1 || A->size < 64 * g || !A->row_ptr) return false;
+  if (ctx().world > 1 && !ctx().team_primary) return false;
+  if (team_active()) return true;
+  static bool warned = false;
+  if (team_start() == 0) return true;
+  if (!warned) {
+    warned = true;
+    fprintf(stderr, "[cgb200] CGB200_GPUS=%d: %s -- solving on one GPU\n", g, last_error());
+  }
+  return false;
 }
 
 std::vector<const void*> g_lazy;  // structs whose mirror is a deferred scale (a handful at most)
@@ -364,7 +413,7 @@ void vec_release(double* d, int cap) {
 void drop_mirror(const void* obj) {
   auto im = g_mats.find(obj);
   if (im != g_mats.end()) {
-    delete im->second.sys;
+    release_entry(im->second);
     g_mats.erase(im);
   }
   if (!g_lazy.empty()) {
@@ -614,6 +663,36 @@ int solve_host(struct __mv_sparse* A, struct __mv_sparse* b, struct __mv_sparse*
   if (ensure_init(-1)) return -1;
   std::lock_guard<std::mutex> lk(g_tab_mu);
   Ctx& c = ctx();
+  if (want_team(A)) {  // CGB200_GPUS > 1: the same call, the matrix cut into row blocks over the GPU team
+    MatrixEntry* e = matrix_entry(A, false, true);
+    if (e && e->team) {
+      if (sync_to_host(b)) return -1;
+      const int n = b->size;
+      const double* x0 = nullptr;
+      if (o.flags & CGB200_OPT_X0) {
+        if (!*x || (*x)->size != n || !(*x)->values) {
+          set_error("CGB200_OPT_X0: *x must be a vector of A's size holding the initial guess");
+          return -1;
+        }
+        if (sync_to_host(*x)) return -1;
+        x0 = (*x)->values;
+      }
+      struct __mv_sparse* xv = (struct __mv_sparse*)calloc(1, sizeof(struct __mv_sparse));
+      if (!xv) return -1;
+      xv->size = n;
+      xv->nnz = n;
+      xv->values = (double*)calloc(n > 0 ? n : 1, sizeof(double));
+      if (!xv->values || team_solve(e->team, b->values, x0, xv->values, o, res)) {
+        free(xv->values);
+        free(xv);
+        return -1;
+      }
+      *x = xv;
+      return 0;
+    }
+    if (team_active()) return -1;  // the team is fine, this matrix was refused: the reason is in last_error
+    // (the team broke while taking the matrix: fall through to one GPU)
+  }
   System* sys = matrix_system(A);
   if (!sys) return -1;
   if (sync_to_host(b)) return -1;
@@ -851,8 +930,9 @@ int cgb200_init(int device) { return ensure_init(device); }
 
 void cgb200_shutdown(void) {
   std::lock_guard<std::mutex> lk(g_tab_mu);
-  for (auto& kv : g_mats) delete kv.second.sys;
+  for (auto& kv : g_mats) release_entry(kv.second);
   g_mats.clear();
+  team_stop();  // the workers leave with the last matrix
   for (auto& kv : g_vecs) dev_free(kv.second.d);
   vec_pool_flush();
   g_vecs.clear();
@@ -915,11 +995,31 @@ unsigned long long cgb200_content_hash(const struct __mv_sparse* A) {
   return content_hash(A);
 }
 
+int cgb200_set_gpus(int gpus) {
+  if (gpus < 1 || gpus > MAX_RANKS) return -1;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  if (gpus != team_requested() && team_active()) {  // another team size: the old team's copies go first
+    for (auto& kv : g_mats)
+      if (kv.second.team) {
+        team_destroy(kv.second.team);
+        kv.second.team = nullptr;
+      }
+    team_stop();
+  }
+  team_request(gpus);
+  return 0;
+}
+
+int cgb200_gpus_in_use(void) { return team_active() ? ctx().world : 1; }
+
+int cgb200_worker_main(int argc, char** argv) { return worker_main(argc, argv); }
+
 int cgb200_to_device(struct __mv_sparse* obj) {
   if (!obj) return -1;
   if (ensure_init(-1)) return -1;
   std::lock_guard<std::mutex> lk(g_tab_mu);
-  if (!is_vector(obj)) return matrix_system(obj, true) ? 0 : -1;  // pinned until invalidate / free
+  if (!is_vector(obj))  // pinned until invalidate / free; with a GPU team the blocks go to their GPUs now
+    return matrix_entry(obj, true, want_team(obj)) ? 0 : -1;
   if (before_write(obj)) return -1;
   VectorEntry& e = g_vecs[obj];
   if (e.lazy) {

@@ -219,11 +219,20 @@ static int allreduce_sum_f64(void* buf, size_t count, cudaStream_t st) {
   return 0;
 }
 
+// A process that belongs to a multi-rank world (the primary of a GPU team, team.cu) still serves
+// the single-rank entry points of mv_ops.h: systems created inside a SoloScope ignore the world.
+static thread_local int t_solo = 0;
+SoloScope::SoloScope() { ++t_solo; }
+SoloScope::~SoloScope() { --t_solo; }
+static int eff_world() { return t_solo > 0 ? 1 : g_ctx.world; }
+static int eff_rank() { return t_solo > 0 ? 0 : g_ctx.rank; }
+
 // host-side all-gather / max of a few 64-bit integers through a device bounce buffer (set-up only)
-static int allgather_i64(const long long* mine, int count, std::vector<long long>& all) {
+static int allgather_i64(const long long* mine, int count, std::vector<long long>& all, int world = -1) {
   Ctx& c = g_ctx;
-  all.assign((size_t)count * c.world, 0);
-  if (c.world == 1) {
+  if (world < 0) world = eff_world();
+  all.assign((size_t)count * world, 0);
+  if (world == 1) {
     for (int i = 0; i < count; ++i) all[i] = mine[i];
     return 0;
   }
@@ -292,11 +301,15 @@ System::~System() {
     dist_barrier();
   }
   free_pattern(&pat);
-  dev_free(A.vals);
-  dev_free(A.cols);
-  dev_free(A.rowptr);
-  dev_free(b);
-  dev_free(x);
+  if (!ext_matrix) {
+    dev_free(A.vals);
+    dev_free(A.cols);
+    dev_free(A.rowptr);
+  }
+  if (!ext_bx) {
+    dev_free(b);
+    dev_free(x);
+  }
   dev_free(r);
   dev_free(s);
   dev_free(w);
@@ -413,32 +426,33 @@ static int setup_peer_comm(System* S, const std::vector<PartInfo>& parts) {
 // `mincol`/`maxcol` are GLOBAL column indices seen in this rank's rows.
 static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool cols_are_global) {
   Ctx& c = g_ctx;
-  S->world = c.world;
-  S->rank = c.rank;
+  const int world = eff_world(), rank = eff_rank();
+  S->world = world;
+  S->rank = rank;
   // every rank learns every rank's (row0, nloc, mincol, maxcol); the plan is pure host logic
   long long mine[4] = {S->row0, (long long)S->nloc, mincol, maxcol};
   std::vector<long long> all;
   if (allgather_i64(mine, 4, all)) return -1;
-  std::vector<PartInfo> parts(c.world);
-  for (int g = 0; g < c.world; ++g)
+  std::vector<PartInfo> parts(world);
+  for (int g = 0; g < world; ++g)
     parts[g] = PartInfo{all[4 * g + 0], all[4 * g + 1], all[4 * g + 2], all[4 * g + 3]};
   // diagnostics (tools/gemv_rows_sweep.py): a lone row block [0, nloc) of a wider matrix, for timing
   // its kernels on one GPU; such a system is not a solvable one
-  if (c.world == 1 && S->row0 == 0 && S->nloc < S->n_global && getenv("CGB200_TIMING_BLOCKS"))
+  if (world == 1 && S->row0 == 0 && S->nloc < S->n_global && getenv("CGB200_TIMING_BLOCKS"))
     parts[0].nloc = S->n_global;
   Plan plan;
   const char* perr = nullptr;
-  if (plan_partition(c.world, c.rank, S->n_global, parts.data(), S->dense ? 1 : 0, &plan, &perr)) {
+  if (plan_partition(world, rank, S->n_global, parts.data(), S->dense ? 1 : 0, &plan, &perr)) {
     set_error(std::string("partition plan: ") + (perr ? perr : "?"));
     return -1;
   }
-  S->part_row0.resize(c.world);
-  S->part_nloc.resize(c.world);
-  for (int g = 0; g < c.world; ++g) {
+  S->part_row0.resize(world);
+  S->part_nloc.resize(world);
+  for (int g = 0; g < world; ++g) {
     S->part_row0[g] = parts[g].row0;
     S->part_nloc[g] = (int)parts[g].nloc;
   }
-  S->allgather = (c.world > 1) && plan.allgather;
+  S->allgather = (world > 1) && plan.allgather;
   S->h_lo = plan.h_lo;
   S->h_hi = plan.h_hi;
   S->send_lo = plan.send_lo;
@@ -454,7 +468,7 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
   CUDA_OK(DEV_ALLOC(&S->s, (nl + 16) * sizeof(double)));
   S->cm_off.world = 1;
   S->cm = S->cm_off;
-  if (c.world > 1 && c.comm_mode == 1 && c.world <= MAX_RANKS) {
+  if (world > 1 && c.comm_mode == 1 && world <= MAX_RANKS) {
     // one exported allocation: [Mailbox | CommLocal | p_ext]; a multiple of 2 MiB so that it is
     // never a sub-allocation of a block shared with other buffers
     size_t bytes = COMM_PEXT_OFFSET + ((size_t)S->ext_len + 16) * sizeof(double);
@@ -517,7 +531,7 @@ static int plan_and_alloc(System* S, long long mincol, long long maxcol, bool co
     // for banded/stencil matrices; verified per tile below for general patterns.
     S->tb_lo = 0;
     S->tb_hi = S->ntiles;
-    if (c.world > 1 && !S->allgather && (S->h_lo > 0 || S->h_hi > 0)) {
+    if (world > 1 && !S->allgather && (S->h_lo > 0 || S->h_hi > 0)) {
       if (classify_tiles(S)) return -1;
     }
   }
@@ -763,6 +777,54 @@ System* system_from_csr(long long n_global, long long row0, int nrows, const int
           cudaSuccess)
     return fail("b H2D");
   if (cudaStreamSynchronize(c.stream) != cudaSuccess) return fail("sync");
+  if (maybe_auto_pattern(S)) { delete S; return nullptr; }
+  return S;
+}
+
+System* system_from_device(long long n_global, long long row0, int nrows, long long nnz, bool dense,
+                           double* vals, int* cols, int* rowptr, double* b, double* x) {
+  if (ensure_init(-1)) return nullptr;
+  Ctx& c = g_ctx;
+  if (n_global < 1 || n_global > 0x7fffffffLL || nrows < 0 || row0 < 0 || row0 + nrows > n_global ||
+      !vals || (!dense && (!cols || !rowptr)) || !b || !x) {
+    set_error("system_from_device: bad arguments");
+    return nullptr;
+  }
+  System* S = new System();
+  S->n_global = n_global;
+  S->row0 = row0;
+  S->nloc = nrows;
+  S->dense = dense;
+  S->ext_matrix = true;
+  S->A.nnz = nnz;
+  S->A.nrows = nrows;
+  S->A.vals = vals;
+  S->A.cols = dense ? nullptr : cols;
+  S->A.rowptr = dense ? nullptr : rowptr;
+  long long mincol = 0, maxcol = n_global - 1;
+  if (!dense && nnz > 0) {  // the column span feeds the halo plan (validity was checked by the primary)
+    int* d4 = (int*)c.d_scratch;
+    if (launch_analyze(S->A.rowptr, S->A.cols, nrows, nnz, (int)n_global, d4, c.stream) != cudaSuccess ||
+        cudaMemcpyAsync(c.h_scratch, d4, 4 * sizeof(int), cudaMemcpyDeviceToHost, c.stream) != cudaSuccess ||
+        cudaStreamSynchronize(c.stream) != cudaSuccess) {
+      set_error(std::string("system_from_device: analyze: ") + cudaGetErrorString(cudaGetLastError()));
+      delete S;
+      return nullptr;
+    }
+    mincol = ((const int*)c.h_scratch)[0];
+    maxcol = ((const int*)c.h_scratch)[1];
+  }
+  if (plan_and_alloc(S, mincol, maxcol, true)) { delete S; return nullptr; }
+  if (cudaStreamSynchronize(c.stream) != cudaSuccess) {
+    set_error("system_from_device: sync failed");
+    delete S;
+    return nullptr;
+  }
+  dev_free(S->b);  // the loop reads b and leaves x where the primary can reach them
+  dev_free(S->x);
+  S->b = b;
+  S->x = x;
+  S->ext_bx = true;
   if (maybe_auto_pattern(S)) { delete S; return nullptr; }
   return S;
 }
@@ -1140,7 +1202,7 @@ static int ensure_dinv(System* S) {
   long long nbad = *(const int*)c.h_scratch;
   if (S->world > 1) {
     std::vector<long long> all;
-    if (allgather_i64(&nbad, 1, all)) {
+    if (allgather_i64(&nbad, 1, all, S->world)) {
       dev_free(d);
       return -1;
     }
@@ -1607,7 +1669,7 @@ int timer_start() {
     CUDA_OK(cudaEventCreate(&c.t3));
   }
   CUDA_OK(cudaStreamSynchronize(c.stream));
-  if (c.world > 1 && c.comm) {
+  if (c.world > 1 && c.comm && !c.team_primary) {
     // several ranks: the start event sits behind a device-side rendezvous (a 4-byte all-reduce on
     // the solve stream, not waited for by the host), so every rank's timed region begins when the
     // last rank's stream gets there and not when its host process happened to be scheduled

@@ -35,6 +35,7 @@ struct Ctx {
   // how the GPUs talk inside the loop: 1 = peer memory over NVLink (kernels store into each
   // other's buffers, comm.h), 0 = NCCL calls between the kernels.  CGB200_COMM=p2p|nccl.
   int comm_mode = 1;
+  bool team_primary = false;  // this process is rank 0 of a GPU team it started itself (team.cu)
 };
 
 Ctx& ctx();
@@ -58,6 +59,9 @@ struct System {
   CsrDev A;
   PatDev pat;               // row-pattern dictionary form of A (pattern.cu), built on request
   bool pat_active = false;  // the matvec runs k_spmv_pattern instead of the CSR stream kernel
+  // GPU team (team.cu): the matrix arrays and b / x live in an allocation that the primary process
+  // made on this device and exported; this system only borrows them
+  bool ext_matrix = false, ext_bx = false;
 
   // gather space of the matvec: p_ext = [ lower halo | owned rows | upper halo ] (neighbour mode)
   // or the whole global vector (single rank, all-gather mode)
@@ -115,10 +119,20 @@ struct SolveResult {
   long long kernel_launches;
 };
 
+// Systems created while a SoloScope is alive are single-rank whatever world the process is in.
+struct SoloScope {
+  SoloScope();
+  ~SoloScope();
+};
+
 System* system_lap(int nx, int ny, int nz, int z0, int nzl, unsigned long long bseed);
 System* system_dense(int n, int row0, int nrows, unsigned long long aseed, unsigned long long bseed);
 System* system_from_csr(long long n_global, long long row0, int nrows, const int* row_ptr,
                         const int* cols, const double* vals, const double* b);
+// A row block whose arrays are already on this device (padded like alloc_matrix pads them; rowptr
+// local from 0, cols global; cols / rowptr null for a full-row block): borrowed, never freed here.
+System* system_from_device(long long n_global, long long row0, int nrows, long long nnz, bool dense,
+                           double* vals, int* cols, int* rowptr, double* b, double* x);
 int classify_tiles(System* S);
 bool dense_one_kernel(const System* S);  // classic iterations of S run as one cooperative launch
 int system_solve(System* S, const SolveOpts& o, SolveResult* res);

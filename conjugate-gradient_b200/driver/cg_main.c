@@ -226,7 +226,10 @@ int main(int argc, char **argv) {
         } else {
           if (read(pipes[r][0], id, 128) != 128) _exit(1);
         }
-        _exit(run_rank(&o, r, o.gpus, id));
+        const int rrc = run_rank(&o, r, o.gpus, id);
+        fflush(stdout); /* _exit does not: rank 0's report would be lost when stdout is a pipe */
+        fflush(stderr);
+        _exit(rrc);
       }
     }
     int rc = 0;

@@ -128,6 +128,23 @@ int cgb200_to_host(struct __mv_sparse *obj);   /* bring values back if the devic
 int cgb200_invalidate(struct __mv_sparse *obj); /* caller changed host arrays in place */
 void cgb200_free_all(struct __mv_sparse *obj);  /* struct + its host arrays + device mirror */
 
+/* ---- several GPUs behind conj_grad / cgb200_solve ------------------------------------------- */
+/* The reference's entry point takes host structs and knows nothing about GPUs (cg.c:24).  With
+ * gpus > 1 -- or the environment variable CGB200_GPUS=N ("all": every visible GPU), for callers
+ * that cannot be edited, e.g. the reference's own cg.c relinked -- conj_grad and cgb200_solve cut
+ * the caller's matrix into N contiguous row blocks of equal stored entries, one per GPU, and run
+ * the same loop over all of them: the calling process becomes rank 0 of a team of N processes (it
+ * starts N-1 `cgb200_worker` processes, found next to the library or through CGB200_WORKER, which
+ * stay up until cgb200_shutdown or exit), puts every block on its GPU itself and copies b in and x
+ * out of every GPU per call.  The matrix cache (above) applies unchanged: an unchanged matrix stays
+ * on its GPUs.  Systems with fewer than 64 rows per GPU, and every call when the team cannot be
+ * started (fewer GPUs visible, worker missing: one line on stderr), run on one GPU.  mv_mult and
+ * the vector operators always run on the calling process's GPU.  0 / -1 (gpus outside 1..8). */
+int cgb200_set_gpus(int gpus);
+int cgb200_gpus_in_use(void); /* ranks of the running team, 1 without one */
+/* Body of the cgb200_worker executable (driver/cgb200_worker.c); not for users. */
+int cgb200_worker_main(int argc, char **argv);
+
 /* ---- solve on host structs with options ---------------------------------------------------- */
 /* conj_grad(M, A, b, &x) == cgb200_solve with {max_iter = M, tol = 0, CGB200_CLASSIC}. */
 int cgb200_solve(struct __mv_sparse *A, struct __mv_sparse *b, struct __mv_sparse **x,
