@@ -76,7 +76,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.FIELDS}",
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "50"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True,
             )
             self.thread = threading.Thread(target=self._pump, daemon=True)
@@ -743,8 +743,9 @@ def dense_phase_trace(pkg, d, world, sm_mhz):
     us = lambda i: out[i] / cnt / sm_mhz  # noqa: E731
     return {"launches": cnt, "wait_for_peers_p_us": round(us(0), 2), "gemv_done_us": round(us(1), 2),
             "sum1_alpha_us": round(us(3) - us(1), 2), "xr_update_us": round(us(4) - us(3), 2),
-            "sum2_beta_us": round(us(5) - us(4), 2), "p_update_push_us": round(us(6) - us(5), 2),
-            "note": "closing CTA's clock64 per phase / sampled SM MHz, per iteration; sums include the grid reduction and, with several GPUs, the cross-GPU exchange"}
+            "sum2_beta_us": round(us(5) - us(4), 2), "cta0_start_to_p_pushed_us": round(us(6), 2),
+            "note": "clock64 / sampled SM MHz, per iteration: gemv_done .. sum2_beta by the CTA that closes each phase (relative to its own "
+                    "iteration start); cta0_start_to_p_pushed by CTA 0; sums include the grid reduction and, with several GPUs, the cross-GPU exchange"}
 
 
 def parity_multi(pkg, rank, world, comm_mode):
@@ -869,12 +870,16 @@ def main():
     comm = "single" if world == 1 else ("p2p" if L.cgb200_system_comm_is_p2p(d.h) else "nccl")
     runner = Runner(pkg, d, info, variant)
     tm = timed_steps(pkg, runner, args.steps, args.warmup, world)
-    clocks = sampler.summary(tm["t0"], tm["t1"]) if sampler else None
     it_b, k1_b = d.bytes()
     value = tm["steps"] / (tm["ms"] * 1e-3)
     ms_step = tm["ms"] / tm["steps"]
     kname = "k_gemv_units" if info["kind"] == "dense" else "k_spmv_stream"
     roof = roofline_for(pkg, d, peak, peak_src, kname, args.workload, world, variant)
+    # clocks: sampled every 50 ms from the start of the timed steps to the end of the roofline timing
+    # (the same kernels on the same system, back to back): the timed region alone is shorter than one period
+    clocks = sampler.summary(tm["t0"], time.time()) if sampler else None
+    if clocks:
+        clocks["window"] = "timed steps + the roofline timing of the same kernels that follows them"
     iter_gbs = it_b / (ms_step * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": tm["steps"],
