@@ -282,6 +282,29 @@ def long_row_leg(pkg, peak, peak_src, variant, K=300):
                         "peak": peak, "unit": "GB/s", "frac": round(k1b / (k1 * 1e-3) / 1e9 / peak, 4),
                         "traffic": traffic_from_profiles("k_spmv_rowblock", "banded52269", 1),
                         "algorithmic_bytes_per_launch": k1b, "avg_launch_ms": round(k1, 5), "peak_source": peak_src}}
+    # the same system in diagonal storage (csrc/banded.cu): reported beside, never
+    # instead of, the CSR contract figures above -- 8 bytes per entry, no indices, no gathers
+    try:
+        if d.use_banded_format(True):
+            rb = Runner(pkg, d, info, variant)
+            tb = timed_steps(pkg, rb, K, 5, 1)
+            bb, bk1 = d.bytes()
+            ms_b = tb["ms"] / tb["steps"]
+            k1d = d.time_kernel(1, 30)
+            out["banded_format"] = {
+                "value": round(tb["steps"] / (tb["ms"] * 1e-3), 2), "unit": UNIT, "ms_per_step": round(ms_b, 5),
+                "speedup_vs_csr": round(ms / ms_b, 3), "bytes_per_iteration": bb, "csr_contract_bytes_per_iteration": ib,
+                "achieved_gbs_per_gpu": round(bb / (ms_b * 1e-3) / 1e9, 1), "frac_of_peak": round(bb / (ms_b * 1e-3) / 1e9 / peak, 4),
+                "matvec": {"kernel": "k_spmv_dia", "algorithmic_bytes_per_launch": bk1, "avg_launch_ms": round(k1d, 5),
+                           "achieved": round(bk1 / (k1d * 1e-3) / 1e9, 1), "unit": "GB/s",
+                           "frac": round(bk1 / (k1d * 1e-3) / 1e9 / peak, 4)},
+                "note": "diagonal storage of the band: same arithmetic in the same order, s = A p bit-identical to the CSR "
+                        "kernel (tests/test_gpu_extensions.py)"}
+            d.use_banded_format(False)
+        else:
+            out["banded_format"] = {"applicable": False, "why": pkg.last_error()}
+    except Exception as e:  # noqa: BLE001
+        out["banded_format"] = {"error": repr(e)}
     d.free()
     return out
 
@@ -1042,6 +1065,8 @@ def main():
                 extras["banded52269"] = long_row_leg(pkg, peak, peak_src, variant)
                 bx = extras["banded52269"]
                 summarise("banded52269", bx["value"], bx["frac_of_peak"], bx["roofline"]["frac"], None)
+                if "value" in bx.get("banded_format", {}):
+                    summary["banded52269"]["banded_it_s"] = compact(bx["banded_format"]["value"])
             except Exception as e:  # noqa: BLE001
                 extras["banded52269"] = {"error": repr(e)}
         line["workloads"] = extras

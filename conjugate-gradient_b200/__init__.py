@@ -188,6 +188,7 @@ def lib():
     L.cgb200_system_comm_is_p2p.argtypes = [C.c_void_p]
     L.cgb200_system_one_kernel_iteration.argtypes = [C.c_void_p]
     L.cgb200_system_use_pattern_format.argtypes = [C.c_void_p, C.c_int]
+    L.cgb200_system_use_banded_format.argtypes = [C.c_void_p, C.c_int]
     _lib = L
     return L
 
@@ -325,6 +326,13 @@ class DeviceSystem:
         rc = lib().cgb200_system_use_pattern_format(self.h, 1 if on else 0)
         if rc < 0:
             raise CgError("cgb200_system_use_pattern_format failed: " + last_error())
+        return rc == 1
+
+    def use_banded_format(self, on=True):
+        """Switch the matvec to diagonal storage; True if the matrix is a mostly full band."""
+        rc = lib().cgb200_system_use_banded_format(self.h, 1 if on else 0)
+        if rc < 0:
+            raise CgError("cgb200_system_use_banded_format failed: " + last_error())
         return rc == 1
 
     def one_kernel_iteration(self):

@@ -1281,6 +1281,11 @@ int cgb200_system_use_pattern_format(cgb200_system* sys, int on) {
   return system_use_pattern((System*)sys, on);
 }
 
+int cgb200_system_use_banded_format(cgb200_system* sys, int on) {
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  return system_use_banded((System*)sys, on);
+}
+
 int cgb200_system_trace(cgb200_system* sys, int on, unsigned long long* out16) {
   std::lock_guard<std::mutex> lk(g_tab_mu);
   if (!sys) return -1;

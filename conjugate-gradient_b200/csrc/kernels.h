@@ -45,6 +45,13 @@ struct PatDev {
   int stage_elems = 0;            // doubles of gather vector per stage
 };
 
+// Diagonal (DIA) storage of a banded block (banded.cu): dia[d * ld + i] = A(i, i + lo + d), D diagonals.
+struct DiaDev {
+  double* dia = nullptr;
+  int D = 0, lo = 0;
+  long long ld = 0;
+};
+
 // `mode` of the matvec kernels: a finish kind (what the last CTA does with the fused dot
 // products) in the low bits plus flags.
 //   FIN_NONE   s = A p only (mv_mult of the operator API)
@@ -90,6 +97,10 @@ cudaError_t launch_spmv_pattern(const PatDev& P, int nrows, const double* pg, co
                                 double* partials, unsigned int* ticket, CgState* S, int mode,
                                 const PeerComm& cm, cudaStream_t st);
 void free_pattern(PatDev* P);
+void free_banded(DiaDev* B);
+cudaError_t launch_spmv_dia(const DiaDev& B, int nrows, const double* pg, long long plen, long long poff,
+                            const double* pown, double* s, double* partials, unsigned int* ticket,
+                            CgState* S, int mode, const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_gemv(const double* A, long long ld, int nrows, int ncols, const double* pg,
                         const double* pown, double* s, double* partials, unsigned int* ticket,
                         CgState* S, int mode, int wait, const PeerComm& cm, cudaStream_t st);

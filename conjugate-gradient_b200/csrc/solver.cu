@@ -301,6 +301,7 @@ System::~System() {
     dist_barrier();
   }
   free_pattern(&pat);
+  free_banded(&dia);
   if (!ext_matrix) {
     dev_free(A.vals);
     dev_free(A.cols);
@@ -585,7 +586,9 @@ int classify_tiles(System* S) {
 // created (for callers that cannot be edited; cgb200_system_use_pattern_format is the API).
 static int maybe_auto_pattern(System* S) {
   const char* f = getenv("CGB200_FORMAT");
-  if (!f || strcmp(f, "pattern") != 0 || S->dense || S->nloc <= 0) return 0;
+  if (!f || S->dense || S->nloc <= 0) return 0;
+  if (strcmp(f, "banded") == 0 && S->world == 1) return system_use_banded(S, 1) < 0 ? -1 : 0;
+  if (strcmp(f, "pattern") != 0) return 0;
   return system_use_pattern(S, 1) < 0 ? -1 : 0;
 }
 
@@ -935,6 +938,11 @@ static int enqueue_matvec(System* S, double* out, int fin, bool dual, bool excha
   const int rg = spmv_rowgroup_min();
   const bool longrow = !S->pat_active && rg > 0 && S->A.nrows > 0 &&
                        S->A.nnz >= (long long)rg * S->A.nrows && longrow_multi_ok(S, multi);
+  if (S->dia_active && S->world == 1) {  // banded block in diagonal storage (banded.cu)
+    CUDA_OK(launch_spmv_dia(S->dia, S->nloc, S->p_ext, S->ext_len, S->off, S->p_own, out, S->partials,
+                            &st->ticket[0], st, mode, cm, c.stream));
+    return 0;
+  }
   if (!multi) {
     if (longrow) {
       CUDA_OK(launch_spmv_rowgroup(S->A, S->p_ext, S->p_own, out, S->partials, &st->ticket[0], st,
@@ -1129,6 +1137,7 @@ static int get_graph(System* S, int iters, int variant, cudaGraphExec_t* out) {
 double System::matrix_bytes() const {
   const double n = (double)nloc;
   if (dense) return 8.0 * (double)A.nnz;
+  if (dia_active) return 8.0 * (double)dia.D * n;  // every diagonal in full, no indices
   if (pat_active) return n;
   return 12.0 * (double)A.nnz + 4.0 * (n + 1.0);
 }
@@ -1176,8 +1185,44 @@ int system_use_pattern(System* S, int on) {
   // every rank must take the same path only in the sense of correctness of its own rows: the
   // exchange, the reductions and the tile classification do not depend on the format
   const bool active = result == 1;
+  if (active) S->dia_active = false;  // one format at a time
   if (active != S->pat_active) {
     S->pat_active = active;
+    for (auto& kv : S->graphs)
+      if (kv.second) cudaGraphExecDestroy(kv.second);
+    S->graphs.clear();
+  }
+  return result;
+}
+
+// Switches the matvec of a banded CSR system between its CSR kernel and the diagonal-storage kernel.
+int system_use_banded(System* S, int on) {
+  Ctx& c = g_ctx;
+  if (!S) {
+    set_error("system_use_banded: NULL system");
+    return -1;
+  }
+  CUDA_OK(cudaSetDevice(c.device));
+  CUDA_OK(cudaStreamSynchronize(c.stream));
+  int result = 0;
+  if (on && !S->dense && S->nloc > 0 && S->world == 1) {
+    if (!S->dia.dia) {
+      std::string why;
+      const int rc = build_banded(S->A, S->off, &S->dia, c.stream, &why);
+      if (rc < 0) {
+        set_error(std::string("system_use_banded: ") + cudaGetErrorString(cudaGetLastError()));
+        return -1;
+      }
+      if (rc == 0) set_error("banded format not applicable: " + why);
+    }
+    result = S->dia.dia ? 1 : 0;
+  } else if (on) {
+    set_error("banded format not applicable: dense, empty or multi-rank row block");
+  }
+  const bool active = result == 1;
+  if (active != S->dia_active) {
+    S->dia_active = active;
+    if (active) S->pat_active = false;  // one format at a time
     for (auto& kv : S->graphs)
       if (kv.second) cudaGraphExecDestroy(kv.second);
     S->graphs.clear();

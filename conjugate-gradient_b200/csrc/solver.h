@@ -59,6 +59,8 @@ struct System {
   CsrDev A;
   PatDev pat;               // row-pattern dictionary form of A (pattern.cu), built on request
   bool pat_active = false;  // the matvec runs k_spmv_pattern instead of the CSR stream kernel
+  DiaDev dia;               // diagonal form of a banded A (banded.cu), built on request
+  bool dia_active = false;  // the matvec runs k_spmv_dia
   // GPU team (team.cu): the matrix arrays and b / x live in an allocation that the primary process
   // made on this device and exported; this system only borrows them
   bool ext_matrix = false, ext_bx = false;
@@ -140,6 +142,9 @@ int system_solve_async(System* S, const SolveOpts& o, long long* ticket_out);
 int system_solve_wait(long long ticket, SolveResult* res);
 // 1 = S now runs the pattern matvec, 0 = not compressible (stays on CSR; reason in last_error), -1 = failure
 int system_use_pattern(System* S, int on);
+// the same for the diagonal (banded) format; single rank only
+int system_use_banded(System* S, int on);
+int build_banded(const CsrDev& A, long long off, DiaDev* out, cudaStream_t st, std::string* why);
 int build_pattern(const CsrDev& A, PatDev* out, cudaStream_t st, std::string* why);
 int system_trace(System* S, int on, unsigned long long* out16);
 int system_set_rhs(System* S, const double* b_host);

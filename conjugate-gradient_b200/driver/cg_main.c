@@ -20,6 +20,7 @@
  *     --gpus G           row-block partition over G GPUs (one process per GPU, NCCL)
  *     --json             one machine-readable line: iterations, relres, seconds, it/s, GB/s
  *     --variant classic|sr   the reference's recurrence (default) or the single-reduction one
+ *     --banded           store a mostly full band as diagonals: 8 bytes per entry, no indices (one GPU)
  *     --pattern          store stencil-like matrices as one byte per row (row-pattern dictionary
  *                        format; same arithmetic, fewer bytes) when the matrix qualifies
  *     --jacobi           diagonal (Jacobi) preconditioner (classic recurrence only)
@@ -63,6 +64,7 @@ typedef struct {
   int json;
   int variant;
   int pattern;
+  int banded;
   int jacobi;
 } options;
 
@@ -70,7 +72,7 @@ static void usage(const char *p) {
   fprintf(stderr,
           "Usage: %s <input-data> <max-iterations> [suppress-output]\n"
           "       %s --gen dense:N|lap2d:N|lap3d:N <max-iterations> [--gpus G]\n"
-          "       options: --tol T  --check-every M  --json  --variant classic|sr  --pattern  --jacobi\n"
+          "       options: --tol T  --check-every M  --json  --variant classic|sr  --pattern  --banded  --jacobi\n"
           "                --dump FILE | --dump-binary FILE   (write the system before solving)\n", p, p);
 }
 
@@ -89,6 +91,7 @@ static int parse(int argc, char **argv, options *o) {
     else if (!strcmp(a, "--gpus") && i + 1 < argc) o->gpus = atoi(argv[++i]);
     else if (!strcmp(a, "--json")) o->json = 1;
     else if (!strcmp(a, "--pattern")) o->pattern = 1;
+    else if (!strcmp(a, "--banded")) o->banded = 1;
     else if (!strcmp(a, "--jacobi")) o->jacobi = 1;
     else if (!strcmp(a, "--variant") && i + 1 < argc) {
       const char *v = argv[++i];
@@ -107,6 +110,7 @@ static int parse(int argc, char **argv, options *o) {
   }
   if ((!o->input && !o->gen) || o->max_iter < 0 || o->gpus < 1) return -1;
   if (o->pattern) setenv("CGB200_FORMAT", "pattern", 1); /* read by the library when a system is created */
+  if (o->banded) setenv("CGB200_FORMAT", "banded", 1);   /* diagonal storage for mostly full bands (one GPU) */
   return 0;
 }
 

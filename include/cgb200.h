@@ -218,6 +218,17 @@ void cgb200_set_one_kernel_iteration(int on);
  * The environment variable CGB200_FORMAT=pattern makes every CSR system try the format when it is
  * created (callers that cannot be edited; `cg --pattern`). */
 int cgb200_system_use_pattern_format(cgb200_system *sys, int on);
+/* Diagonal (DIA) storage for banded matrices with arbitrary coefficients (not in the
+ * reference).  A CSR block whose entries lie in a band lo <= column - row <= hi that is at least
+ * 70 % full (the reference's course matrix: 345 entries per row, cg.c:231-232,260) is re-stored as
+ * hi - lo + 1 diagonals of one value per row; the matvec of the loop then streams 8 bytes per entry
+ * instead of 12, without index loads or gathers.  Row sums are formed in ascending column order
+ * with unfused multiply and add and padding contributes exact zeros: s = A p is bit-identical to
+ * the CSR kernels' for finite p.  Same return convention as cgb200_system_use_pattern_format (1 = now
+ * active, 0 = does not qualify and stays on CSR, -1 = CUDA failure; on == 0 switches back).  One
+ * GPU only (a multi-rank block answers 0).  CGB200_FORMAT=banded tries it on every CSR system at
+ * creation.  Reported beside the CSR contract figures, never instead of them. */
+int cgb200_system_use_banded_format(cgb200_system *sys, int on);
 /* Diagnostics of the one-kernel iteration: SM-cycle counts of its phases, summed over launches by
  * the CTA that closes each phase, relative to that CTA's start.  out16 (may be NULL) receives the
  * counters accumulated so far: [0] wait for the peers' slices of p, [1] GEMV done (last ticket),

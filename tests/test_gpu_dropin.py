@@ -110,6 +110,19 @@ def test_cg_driver_pattern_format_and_variant_flags(pkg, gpu_lib):
     assert r.returncode != 0
 
 
+def test_cg_driver_banded_flag_prints_the_same_solution(pkg, gpu_lib, tmp_path):
+    # --banded: a mostly full band is stored as diagonals (8 bytes per entry, no indices); the printed
+    # solution is the CSR run's, line for line; a stencil file does not qualify and silently stays on CSR
+    s = H.banded(1200, 60)
+    p = tmp_path / "band.txt"
+    H.write_text_format(s, str(p))
+    csr = subprocess.run([pkg.CG_DRIVER, str(p), "12"], stdout=subprocess.PIPE, text=True, check=True).stdout
+    dia = subprocess.run([pkg.CG_DRIVER, str(p), "12", "--banded"], stdout=subprocess.PIPE, text=True, check=True).stdout
+    _close(_filtered(dia), _filtered(csr))
+    out = subprocess.run([pkg.CG_DRIVER, INPUT, "30", "--banded"], stdout=subprocess.PIPE, text=True, check=True).stdout
+    _close(_filtered(out), open(WANT).read().splitlines())
+
+
 def test_cg_driver_dump_writes_a_file_the_readers_accept(pkg, gpu_lib, tmp_path):
     # --gen system -> the reference's text format (and the binary sidecar) -> back through the
     # library's reader: the arrays of the oracle generator; and the file solves like the generated system

@@ -219,3 +219,72 @@ def test_struct_api_with_initial_guess(pkg, gpu_lib):
     null = pkg.MvSparseP()
     assert gpu_lib.cgb200_solve(C.byref(A), C.byref(b), C.byref(null), C.byref(o), C.byref(r)) == -1
     gpu_lib.cgb200_invalidate(C.byref(A))
+
+
+# ---------------------------------------------------------------------------------------------
+# diagonal (DIA) storage for banded matrices with arbitrary coefficients (csrc/banded.cu)
+# ---------------------------------------------------------------------------------------------
+
+
+def _holey_band(n, hb, drop, seed=11):
+    """Symmetric banded SPD system with a fraction `drop` of its off-diagonal pairs missing (the band
+    stays mostly full, rows have different lengths, the chain i -- i+1 is kept: irreducible)."""
+    rng = np.random.default_rng(seed)
+    s = H.banded(n, hb)
+    keep = np.ones(s.nnz, dtype=bool)
+    rows = np.repeat(np.arange(n), np.diff(s.row_ptr))
+    off = s.cols - rows
+    pair_lo, pair_hi = np.minimum(rows, s.cols), np.maximum(rows, s.cols)
+    h = (pair_lo.astype(np.int64) * 1000003 + pair_hi) % 1000
+    keep &= ~((np.abs(off) > 1) & (h < int(drop * 1000)))
+    rp = np.zeros(n + 1, dtype=np.int64)
+    np.add.at(rp, rows[keep] + 1, 1)
+    return H.System(np.cumsum(rp), s.cols[keep], s.vals[keep], s.b, "holey_band")
+
+
+BANDED_SYSTEMS = [lambda: H.banded(3000, 40), lambda: H.banded(700, 300), lambda: H.banded(4097, 5),
+                  lambda: _holey_band(2500, 60, 0.2), lambda: H.lap(1, 2000)]
+
+
+@pytest.mark.parametrize("mk", BANDED_SYSTEMS)
+def test_banded_format_matvec_bit_exact_and_solves(pkg, gpu_lib, mk):
+    s = mk()
+    d = pkg.DeviceSystem.from_csr(s.n, 0, s.row_ptr, s.cols, s.vals, s.b)
+    it_b0, k1_b0 = d.bytes()
+    assert d.use_banded_format(True), pkg.last_error()
+    it_b1, _ = d.bytes()
+    assert it_b1 < it_b0                                     # fewer bytes per iteration than CSR
+    want = np.empty(s.n)
+    for seed in (3, 4):
+        v = H.rhs(s.n, seed)
+        H.oracle().oracle_spmv(s.n, H.iptr(s.row_ptr), H.iptr(s.cols), H.dptr(s.vals), H.dptr(v), H.dptr(want))
+        assert np.array_equal(d.matvec(v).view(np.uint64), want.view(np.uint64))
+    K = 12
+    xo, it, _, _ = H.oracle_cg(s, K)
+    r = d.solve(K)
+    assert r.iterations == it
+    x_dia = d.x()
+    assert np.linalg.norm(x_dia - xo) <= 1e-8 * np.linalg.norm(xo)
+    rt = d.solve(5000, tol=1e-10)
+    assert rt.status == pkg.CONVERGED and d.true_relres() <= 1.05e-10
+    rj = d.solve(5000, tol=1e-10, jacobi=True)               # the preconditioned loop takes the same matvec
+    assert rj.status == pkg.CONVERGED
+    assert not d.use_banded_format(False)                    # back on CSR: same x to the last bits of the dots
+    d.solve(K)
+    assert np.linalg.norm(d.x() - x_dia) <= 1e-12 * np.linalg.norm(x_dia)
+    d.free()
+
+
+def test_banded_format_refuses_what_is_not_a_mostly_full_band(pkg, gpu_lib):
+    s = H.lap(64, 64)                                        # 5 entries in a band of 129 diagonals
+    d = pkg.DeviceSystem.from_csr(s.n, 0, s.row_ptr, s.cols, s.vals, s.b)
+    assert not d.use_banded_format(True)
+    assert "not applicable" in pkg.last_error() and "full" in pkg.last_error()
+    xo, it, _, _ = H.oracle_cg(s, 30)                        # it stays on CSR and keeps working
+    d.solve(30)
+    assert np.linalg.norm(d.x() - xo) <= 1e-8 * np.linalg.norm(xo)
+    d.free()
+    dd = pkg.DeviceSystem.dense(256)                         # the dense path has no use for it
+    assert not dd.use_banded_format(True)
+    dd.free()
+

@@ -17,4 +17,5 @@ peak, src = bench.measured_peak()
 out = bench.long_row_leg(pkg, peak, src, 0)
 tag = {k: v for k, v in os.environ.items() if k.startswith("CGB200_")}
 print(json.dumps({"env": tag, "it_s": out["value"], "ms_per_step": out["ms_per_step"], "frac_iter": out["frac_of_peak"],
-                  "k1_ms": out["roofline"]["avg_launch_ms"], "k1_frac": out["roofline"]["frac"]}))
+                  "k1_ms": out["roofline"]["avg_launch_ms"], "k1_frac": out["roofline"]["frac"],
+                  "banded_format": out.get("banded_format")}))
