@@ -196,7 +196,10 @@ template <int THREADS, int NV>
 __device__ __forceinline__ bool grid_reduce(double (&v)[NV], double* __restrict__ partials,
                                             unsigned int* __restrict__ ticket,
                                             const double* __restrict__ extra = nullptr,
-                                            int n_extra = 0) {
+                                            int n_extra = 0, int nparts = -1) {
+  // nparts >= 0: only CTAs 0 .. nparts-1 call this (the others have no share in the sum and go
+  // straight to the barrier that follows): nparts tickets, nparts partials
+  const int np = nparts < 0 ? (int)gridDim.x : nparts;
   __shared__ double sm[THREADS / 32];
   __shared__ int is_last;
 #pragma unroll
@@ -207,7 +210,7 @@ __device__ __forceinline__ bool grid_reduce(double (&v)[NV], double* __restrict_
   if (threadIdx.x == 0) {
     __threadfence();
     unsigned int tk = atomicAdd(ticket, 1u);
-    is_last = (tk == gridDim.x - 1);
+    is_last = (tk == (unsigned int)np - 1);
   }
   __syncthreads();
   if (!is_last) return false;
@@ -215,7 +218,7 @@ __device__ __forceinline__ bool grid_reduce(double (&v)[NV], double* __restrict_
 #pragma unroll
   for (int k = 0; k < NV; ++k) {
     double acc = 0.0;
-    for (int i = threadIdx.x; i < (int)gridDim.x; i += THREADS)
+    for (int i = threadIdx.x; i < np; i += THREADS)
       acc += __ldcg(partials + k * PART_STRIDE + i);
     for (int i = threadIdx.x; i < n_extra; i += THREADS) acc += __ldcg(extra + k * PART_STRIDE + i);
     v[k] = block_sum<THREADS>(acc, sm);

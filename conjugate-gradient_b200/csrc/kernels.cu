@@ -1002,13 +1002,13 @@ struct DenseSolveArgs {
 // epoch e.  Replaces a launch boundary between p's update and the next matvec.
 template <int THREADS>
 __device__ __forceinline__ void grid_arrive(CgState* S, const PeerComm& cm, const bool pushed,
-                                            const unsigned long long e) {
+                                            const unsigned long long e, const int nparts) {
   if (pushed) __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
     const unsigned int tk = atomicAdd(&S->ticket[3], 1u);
-    if (tk == gridDim.x - 1) {
+    if (tk == (unsigned int)nparts - 1) {  // only the CTAs that own rows arrive
       S->ticket[3] = 0u;
       __threadfence();
       if (pushed) {
@@ -1043,6 +1043,12 @@ k_cg_dense_solve(const double* __restrict__ A, long long ld, int nrows, int ncol
   const bool pushing = cm.npush > 0;
   const int pool_groups = a.pool_groups;
   const int ngs = (nrows + RB - 1) / RB - pool_groups;  // statically dealt row groups
+  // The vector phases hand row i to thread i of the grid: only the first `nact` CTAs own rows (16 of
+  // 592 on an eighth of the n = 32768 system).  Only they take part in those phases' reductions and
+  // arrival barrier -- the others would each add a zero partial, a fence and a ticket to the
+  // critical path -- and everybody meets at the epoch wait.
+  const int nact = (int)min((long long)gridDim.x, ((long long)nrows + THREADS - 1) / THREADS);
+  const bool active = (int)blockIdx.x < nact;
 
   // ---- phase I: loop entry (cg.c:104-108) -----------------------------------------------------
   if (a.init) {
@@ -1055,17 +1061,19 @@ k_cg_dense_solve(const double* __restrict__ A, long long ld, int nrows, int ncol
       if (pushing) push_elem(cm, i, v);
       acc = fma(v, v, acc);
     }
-    double v[1] = {acc};
-    if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[2])) {
-      if (tid == 0) {  // a fresh solve: the scalars of the previous one are void
-        S->tol = a.tol > 0.0 ? a.tol : 0.0;
-        S->max_iter = a.max_iter;
-        S->variant = 0;
+    if (active) {
+      double v[1] = {acc};
+      if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[2], nullptr, 0, nact)) {
+        if (tid == 0) {  // a fresh solve: the scalars of the previous one are void
+          S->tol = a.tol > 0.0 ? a.tol : 0.0;
+          S->max_iter = a.max_iter;
+          S->variant = 0;
+        }
+        finish_block<THREADS>(S, cm, FIN_INIT, v[0], 0.0);
       }
-      finish_block<THREADS>(S, cm, FIN_INIT, v[0], 0.0);
+      // (the reduction's partials are consumed before anyone can pass the barrier below)
+      grid_arrive<THREADS>(S, cm, pushing, e + 1, nact);
     }
-    // (the reduction's partials are consumed before anyone can pass the barrier below)
-    grid_arrive<THREADS>(S, cm, pushing, e + 1);
     if (!grid_wait(&S->grid_epoch, e + 1, S)) return;
     e += 1;
     if (ld_volatile_int(&S->done)) return;
@@ -1180,9 +1188,9 @@ k_cg_dense_solve(const double* __restrict__ A, long long ld, int nrows, int ncol
       r[i] = rn;
       acc = fma(rn, rn, acc);
     }
-    {
+    if (active) {
       double v[1] = {acc};
-      if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[1])) {
+      if (grid_reduce<THREADS, 1>(v, partials, &S->ticket[1], nullptr, 0, nact)) {
         if (trace && tid == 0) atomicAdd(trace + 4, (unsigned long long)(clock64() - c0));
         if (!a.timing) finish_block<THREADS>(S, cm, FIN_RR, v[0], 0.0);
         if (trace && tid == 0) atomicAdd(trace + 5, (unsigned long long)(clock64() - c0));
@@ -1199,7 +1207,7 @@ k_cg_dense_solve(const double* __restrict__ A, long long ld, int nrows, int ncol
       pown[i] = pn;
       if (pushing) push_elem(cm, i, pn);
     }
-    grid_arrive<THREADS>(S, cm, pushing, e + 3);
+    if (active) grid_arrive<THREADS>(S, cm, pushing, e + 3, nact);
     if (it + 1 == a.iters) {  // nothing of this launch reads p any more: the next launch will
       if (trace && tid == 0 && blockIdx.x == 0) atomicAdd(trace + 6, (unsigned long long)(clock64() - c0));
       return;
