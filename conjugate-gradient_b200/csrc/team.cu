@@ -473,6 +473,16 @@ int team_solve(TeamSystem* T, const double* b_host, const double* x0_host, doubl
     set_error("GPU team: not running");
     return -1;
   }
+  // what any rank would refuse on its own is refused HERE, before the request goes out: a rank that
+  // backs out of a collective solve alone leaves the others waiting for it
+  if ((o.variant != 0 && o.variant != 1) || ((o.flags & 3) != 0 && o.variant != 0) || (o.flags & ~3) != 0) {
+    set_error("GPU team: unknown variant / flags, or CGB200_OPT_JACOBI / CGB200_OPT_X0 with the single-reduction variant");
+    return -1;
+  }
+  if (((o.flags & 2) != 0) != (x0_host != nullptr)) {
+    set_error("GPU team: CGB200_OPT_X0 and the initial guess must come together");
+    return -1;
+  }
   Ctx& c = ctx();
   const int G = c.world;
   bool ok = true;
