@@ -71,7 +71,7 @@ RUNNING, MAXITER, CONVERGED, BREAKDOWN, EXACT, COMM_TIMEOUT = 0, 1, 2, 3, 4, 5
 CLASSIC, SINGLE_REDUCTION = 0, 1
 EAGER, RESIDENT = 0, 1
 OPT_JACOBI, OPT_X0 = 1, 2
-CACHE_STRICT, CACHE_SAMPLED, CACHE_OFF = 0, 1, 2
+CACHE_STRICT, CACHE_SAMPLED, CACHE_OFF, CACHE_TRACKED = 0, 1, 2, 3
 DOT_STATIC_MAX_N = 1 << 28
 
 # every symbol include/mv_ops.h and include/cgb200.h declare (checked by tests/test_abi_symbols.py)
@@ -144,6 +144,7 @@ def lib():
     L.cgb200_set_gpus.argtypes = [C.c_int]
     L.cgb200_set_mode.argtypes = [C.c_int]
     L.cgb200_set_matrix_cache.argtypes = [C.c_int]
+    L.cgb200_cache_stats.argtypes = [C.POINTER(C.c_longlong)]
     L.cgb200_content_hash.restype = C.c_ulonglong
     L.cgb200_content_hash.argtypes = [MvSparseP]
     for name in ("cgb200_to_device", "cgb200_to_host", "cgb200_invalidate"):
@@ -191,6 +192,13 @@ def lib():
     L.cgb200_system_use_banded_format.argtypes = [C.c_void_p, C.c_int]
     _lib = L
     return L
+
+
+def cache_stats():
+    """{uploads, hashes, tracked_clean, tracked_dirty, tracking_available} of the matrix cache."""
+    out = (C.c_longlong * 5)()
+    lib().cgb200_cache_stats(out)
+    return dict(zip(("uploads", "hashes", "tracked_clean", "tracked_dirty", "tracking_available"), [int(v) for v in out]))
 
 
 def last_error():

@@ -12,6 +12,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <chrono>
 #include <map>
 #include <mutex>
 #include <thread>
@@ -22,6 +23,7 @@
 #include "../../include/cgb200.h"
 #include "solver.h"
 #include "team.h"
+#include "writewatch.h"
 
 using namespace cgb;
 
@@ -61,7 +63,15 @@ struct MatrixEntry {
   uint64_t content = 0;  // hash of every byte of the three arrays (strict policy)
   bool has_content = false;
   bool pinned = false;   // the caller declared the device copy current (cgb200_to_device / resident mode)
+  // tracked policy: the page-aligned interiors of the three arrays are watched for writes
+  // (writewatch.cpp); their partial first / last pages are hashed instead (edge)
+  bool watched = false;
+  uint64_t seen[3] = {0, 0, 0};  // epoch of each watched range at this entry's last validation
+  uint64_t edge = 0;
 };
+
+// what the cache did, for tests and the bench line (cgb200_cache_stats)
+long long g_stat_uploads = 0, g_stat_hashes = 0, g_stat_tracked_clean = 0, g_stat_tracked_dirty = 0;
 
 struct VectorEntry {
   double* d = nullptr;
@@ -131,7 +141,8 @@ int g_cache_policy = -1;  // CGB200_CACHE_*
 int cache_policy() {
   if (g_cache_policy < 0) {
     const char* e = getenv("CGB200_MATRIX_CACHE");
-    g_cache_policy = CGB200_CACHE_STRICT;
+    g_cache_policy = CGB200_CACHE_TRACKED;
+    if (e && strcmp(e, "strict") == 0) g_cache_policy = CGB200_CACHE_STRICT;
     if (e && strcmp(e, "sampled") == 0) g_cache_policy = CGB200_CACHE_SAMPLED;
     if (e && strcmp(e, "off") == 0) g_cache_policy = CGB200_CACHE_OFF;
   }
@@ -235,7 +246,166 @@ bool is_vector(const struct __mv_sparse* v) { return v->col_indices == NULL && v
 
 // Device system for a host CSR struct, uploaded on first use and whenever the struct's arrays no
 // longer hold what was uploaded (policy above).  pin: the caller hands the matrix over explicitly.
+// The three host arrays of a matrix struct.
+struct HostArr {
+  const void* p;
+  size_t bytes;
+};
+void host_arrays(const struct __mv_sparse* A, HostArr out[3]) {
+  const size_t nnz = A->nnz > 0 ? (size_t)A->nnz : 0;
+  out[0] = HostArr{A->values, nnz * sizeof(double)};
+  out[1] = HostArr{A->col_indices, A->col_indices ? nnz * sizeof(int) : 0};
+  out[2] = HostArr{A->row_ptr, ((size_t)A->size + 1) * sizeof(int)};
+}
+void host_arrays(const MatrixEntry& e, HostArr out[3]) {
+  const size_t nnz = e.nnz > 0 ? (size_t)e.nnz : 0;
+  out[0] = HostArr{e.values, nnz * sizeof(double)};
+  out[1] = HostArr{e.cols, e.cols ? nnz * sizeof(int) : 0};
+  out[2] = HostArr{e.rowptr, ((size_t)e.size + 1) * sizeof(int)};
+}
+
+constexpr size_t WATCH_MIN_BYTES = 1u << 20;  // smaller arrays are hashed: cheaper than a page-table walk is worth
+
+// Hash of what write tracking does not cover: the partial first and last pages of the watched
+// arrays, and the whole of the arrays too small to watch.  A few KB to a few MB per call.
+uint64_t edge_hash(const HostArr a[3]) {
+  const size_t pg = ww_page();
+  uint64_t h = 7;
+  for (int k = 0; k < 3; ++k) {
+    const unsigned char* p = (const unsigned char*)a[k].p;
+    if (!p || a[k].bytes == 0) continue;
+    if (a[k].bytes < WATCH_MIN_BYTES) {
+      h = hash_array(p, a[k].bytes, h);
+      continue;
+    }
+    const uintptr_t lo = ((uintptr_t)p + pg - 1) / pg * pg, hi = ((uintptr_t)p + a[k].bytes) / pg * pg;
+    h = hash_array(p, lo - (uintptr_t)p, h);
+    h = hash_array((const void*)hi, (uintptr_t)p + a[k].bytes - hi, h);
+  }
+  return h;
+}
+
+// Pageable memory only: device DMA into page-locked memory (cudaHostAlloc, cudaHostRegister) does
+// not go through the CPU's page tables and would not be seen.
+bool plain_pageable(const void* p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeUnregistered;
+}
+
+// Watched ranges are shared between cache entries: two matrix structs may point at the same arrays,
+// and re-arming a range for one of them erases the "written" marks the other has not looked at yet.
+// So every range carries an epoch that is bumped whenever its marks are cleared, and an entry trusts
+// "no page written" only while the epoch is the one it saw at its own last validation.  Ranges that
+// overlap without being identical are not watched (those entries hash).
+struct WatchedRange {
+  size_t bytes = 0;
+  int refs = 0;
+  uint64_t epoch = 0;
+};
+std::map<uintptr_t, WatchedRange> g_ranges;  // by start address; guarded by g_tab_mu like the cache
+
+bool watchable(const HostArr& h) { return h.p && h.bytes >= WATCH_MIN_BYTES; }
+
+bool range_acquire(const HostArr& h, uint64_t* seen) {
+  const uintptr_t lo = (uintptr_t)h.p, hi = lo + h.bytes;
+  auto nx = g_ranges.lower_bound(lo);
+  if (nx != g_ranges.end() && nx->first == lo && nx->second.bytes == h.bytes) {
+    ++nx->second.refs;  // marks left by writes before now stay: this entry's first check hashes
+    *seen = nx->second.epoch;
+    return true;
+  }
+  if (nx != g_ranges.end() && nx->first < hi) return false;
+  if (nx != g_ranges.begin()) {
+    auto pv = std::prev(nx);
+    if (pv->first + pv->second.bytes > lo) return false;
+  }
+  if (!plain_pageable(h.p) || !ww_arm(h.p, h.bytes)) return false;
+  WatchedRange r;
+  r.bytes = h.bytes;
+  r.refs = 1;
+  g_ranges[lo] = r;
+  *seen = 0;
+  return true;
+}
+
+void range_release(const HostArr& h) {
+  auto it = g_ranges.find((uintptr_t)h.p);
+  if (it == g_ranges.end() || it->second.bytes != h.bytes) return;
+  if (--it->second.refs > 0) return;
+  ww_disarm(h.p, h.bytes);
+  g_ranges.erase(it);
+}
+
+void watch_release(const HostArr a[3]) {
+  for (int k = 0; k < 3; ++k)
+    if (watchable(a[k])) range_release(a[k]);
+}
+
+bool watch_acquire(const HostArr a[3], uint64_t seen[3]) {
+  if (!ww_available()) return false;
+  bool any = false;
+  for (int k = 0; k < 3; ++k) {
+    if (!watchable(a[k])) continue;
+    if (!range_acquire(a[k], &seen[k])) {
+      for (int j = 0; j < k; ++j)
+        if (watchable(a[j])) range_release(a[j]);
+      return false;
+    }
+    any = true;
+  }
+  if (!any) return false;  // (nothing large enough to watch: the caller just hashes, which is cheap then)
+  return true;
+}
+
+// 0 = no watched array was written since this entry last validated, 1 = one was (or its marks
+// were cleared on behalf of another entry), -1 = cannot tell
+int watch_state(const HostArr a[3], const uint64_t seen[3]) {
+  int out = 0;
+  for (int k = 0; k < 3; ++k) {
+    if (!watchable(a[k])) continue;
+    auto it = g_ranges.find((uintptr_t)a[k].p);
+    if (it == g_ranges.end() || it->second.bytes != a[k].bytes) return -1;
+    if (!plain_pageable(a[k].p)) return -1;  // page-locked since (cudaHostRegister): DMA writes are invisible
+    const int w = ww_written(a[k].p, a[k].bytes);
+    if (w < 0) return -1;
+    out |= w | (it->second.epoch != seen[k] ? 1 : 0);
+  }
+  return out;
+}
+
+// Before the arrays are re-read for the deciding hash: clear the marks of the ranges that carry
+// any (bumping their epoch for the other entries that share them) and note the epochs.  false =
+// tracking lost (the entry has released its ranges and hashes from now on).
+bool watch_refresh(const HostArr a[3], uint64_t seen[3]) {
+  bool ok = true;
+  for (int k = 0; k < 3 && ok; ++k) {
+    if (!watchable(a[k])) continue;
+    auto it = g_ranges.find((uintptr_t)a[k].p);
+    if (it == g_ranges.end() || it->second.bytes != a[k].bytes || !plain_pageable(a[k].p)) {
+      ok = false;
+      break;
+    }
+    if (ww_written(a[k].p, a[k].bytes) != 0) {
+      ++it->second.epoch;
+      if (!ww_rearm(a[k].p, a[k].bytes)) ok = false;
+    }
+    seen[k] = it->second.epoch;
+  }
+  if (!ok) watch_release(a);
+  return ok;
+}
+
 void release_entry(MatrixEntry& e) {
+  if (e.watched) {
+    HostArr a[3];
+    host_arrays(e, a);
+    watch_release(a);
+    e.watched = false;
+  }
   delete e.sys;
   e.sys = nullptr;
   if (e.team) team_destroy(e.team);  // collective with the workers
@@ -265,9 +435,39 @@ MatrixEntry* matrix_entry(struct __mv_sparse* A, bool pin, bool want_team) {
                 old.rowptr == A->row_ptr && old.size == A->size && old.nnz == A->nnz && old.fp == fp;
     const bool trusted = old.pinned || g_mode == CGB200_RESIDENT || policy == CGB200_CACHE_SAMPLED;
     if (same && !trusted) {
-      content = content_hash(A);
-      have_content = true;
-      same = old.has_content && old.content == content;
+      bool settled = false;
+      if (policy == CGB200_CACHE_TRACKED && old.watched) {
+        // nothing written to the watched interiors and the unwatched edges hash alike: unchanged,
+        // exactly, without reading the arrays
+        HostArr a[3];
+        host_arrays(A, a);
+        const int w = watch_state(a, old.seen);
+        if (w == 0 && edge_hash(a) == old.edge) {
+          ++g_stat_tracked_clean;
+          settled = true;
+        } else if (w != 0) {
+          // written (perhaps with the same values) or unknown: the hash decides.  The marks are
+          // cleared BEFORE the arrays are read, so a write racing with the hash is seen next time.
+          ++g_stat_tracked_dirty;
+          old.watched = watch_refresh(a, old.seen);
+          if (old.watched) old.edge = edge_hash(a);
+        }
+      }
+      if (!settled) {
+        content = content_hash(A);
+        have_content = true;
+        ++g_stat_hashes;
+        same = old.has_content && old.content == content;
+        if (same && policy == CGB200_CACHE_TRACKED && !old.watched) {  // try to watch from here on
+          HostArr a[3];
+          host_arrays(A, a);
+          old.watched = watch_acquire(a, old.seen);
+          if (old.watched) {  // armed after the hash read the arrays: one more look at them settles it
+            old.edge = edge_hash(a);
+            if (content_hash(A) != content) same = false;
+          }
+        }
+      }
     }
     if (same) {
       e = &old;
@@ -279,6 +479,12 @@ MatrixEntry* matrix_entry(struct __mv_sparse* A, bool pin, bool want_team) {
   }
   std::thread hasher;  // the hash for the next call's comparison is taken while the upload runs
   bool fresh = false;
+  const bool trace = getenv("CGB200_TRACE_UPLOAD") != nullptr;  // first-call timing to stderr
+  const auto t0 = std::chrono::steady_clock::now();
+  auto ms_since = [&](std::chrono::steady_clock::time_point a) {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - a).count();
+  };
+  double t_arm = 0.0, t_up = 0.0;
   if (!e) {
     MatrixEntry ne;
     ne.values = A->values;
@@ -292,8 +498,20 @@ MatrixEntry* matrix_entry(struct __mv_sparse* A, bool pin, bool want_team) {
     ne.pinned = pin;
     e = &(g_mats[A] = ne);
     fresh = true;
-    if (policy == CGB200_CACHE_STRICT && !have_content)
+    ++g_stat_uploads;
+    if (policy == CGB200_CACHE_TRACKED) {
+      // armed BEFORE the arrays are read for the upload and the hash: a write that races with them
+      // is seen at the next call (and costs a re-upload) instead of being missed
+      HostArr a[3];
+      host_arrays(A, a);
+      e->watched = watch_acquire(a, e->seen);
+      if (e->watched) e->edge = edge_hash(a);
+      t_arm = ms_since(t0);
+    }
+    if ((policy == CGB200_CACHE_STRICT || policy == CGB200_CACHE_TRACKED) && !have_content) {
+      ++g_stat_hashes;
       hasher = std::thread([&]() { content = content_hash(A); });
+    }
   }
   bool ok = true;
   if (want_team && !e->team) {
@@ -304,13 +522,21 @@ MatrixEntry* matrix_entry(struct __mv_sparse* A, bool pin, bool want_team) {
     e->sys = system_from_csr(A->size, 0, A->size, A->row_ptr, A->col_indices, A->values, nullptr);
     ok = e->sys != nullptr;
   }
+  t_up = ms_since(t0);
   if (hasher.joinable()) {
     hasher.join();
     e->content = content;
     e->has_content = true;
   }
+  if (trace && fresh)
+    fprintf(stderr, "[cgb200] matrix %lld x %lld, %lld entries: write tracking armed %.1f ms, on the device %.1f ms, "
+                    "content hash joined %.1f ms%s\n", (long long)A->size, (long long)A->size, (long long)A->nnz, t_arm,
+            t_up, ms_since(t0), e->watched ? " (watched)" : "");
   if (!ok) {
-    if (fresh || (!e->sys && !e->team)) g_mats.erase(A);
+    if (fresh || (!e->sys && !e->team)) {
+      release_entry(*e);
+      g_mats.erase(A);
+    }
     return nullptr;
   }
   return e;
@@ -980,10 +1206,24 @@ int cgb200_set_mode(int mode) {
 }
 
 int cgb200_set_matrix_cache(int policy) {
-  if (policy != CGB200_CACHE_STRICT && policy != CGB200_CACHE_SAMPLED && policy != CGB200_CACHE_OFF)
+  if (policy != CGB200_CACHE_STRICT && policy != CGB200_CACHE_SAMPLED && policy != CGB200_CACHE_OFF &&
+      policy != CGB200_CACHE_TRACKED)
     return -1;
   std::lock_guard<std::mutex> lk(g_tab_mu);
   g_cache_policy = policy;
+  return 0;
+}
+
+int cgb200_write_tracking_available(void) { return ww_available() ? 1 : 0; }
+
+int cgb200_cache_stats(long long* out5) {
+  if (!out5) return -1;
+  std::lock_guard<std::mutex> lk(g_tab_mu);
+  out5[0] = g_stat_uploads;
+  out5[1] = g_stat_hashes;
+  out5[2] = g_stat_tracked_clean;
+  out5[3] = g_stat_tracked_dirty;
+  out5[4] = ww_available() ? 1 : 0;
   return 0;
 }
 

@@ -106,18 +106,33 @@ int cgb200_set_mode(int mode);
 /* Device copies of caller matrices (mv_mult, conj_grad, cgb200_solve on host structs).  The
  * reference reads the caller's arrays on every call (mv_ops.c:187-197), so a caller may edit
  * values[] in place between two calls; the device copy is re-validated on every call:
- *   CGB200_CACHE_STRICT  (default) hash of every byte of values / col_indices / row_ptr, several
- *                        host threads: any in-place edit is seen and causes a fresh upload;
+ *   CGB200_CACHE_TRACKED (default) the kernel is asked whether the arrays were WRITTEN since the
+ *                        upload (userfaultfd asynchronous write-protection + PAGEMAP_SCAN, Linux
+ *                        >= 6.7: the page-aligned interior of each array of >= 1 MiB; their partial
+ *                        first / last pages and smaller arrays are hashed): exact for every write
+ *                        that goes through the CPU, ~1 ms per 10 GB instead of a pass over the
+ *                        arrays.  Written, or the kernel cannot tell (no support, page-locked
+ *                        memory -- device DMA bypasses the page tables --, any error): the full
+ *                        hash below decides.  The caller pays one minor fault per 4 KiB page it
+ *                        rewrites.  CGB200_WRITE_TRACKING=0 disables the tracking.
+ *   CGB200_CACHE_STRICT  hash of every byte of values / col_indices / row_ptr on every call,
+ *                        several host threads: any in-place edit is seen and causes a fresh upload;
  *   CGB200_CACHE_SAMPLED 96 samples + the array addresses (constant time): notices a rebuilt
  *                        matrix, can miss a small in-place edit -- call cgb200_invalidate;
  *   CGB200_CACHE_OFF     every call uploads.
- * Environment: CGB200_MATRIX_CACHE=strict|sampled|off.  A matrix handed over explicitly with
- * cgb200_to_device(A), and every matrix while in CGB200_RESIDENT mode, is pinned: the caller has
- * declared the device copy current until cgb200_invalidate(A) / free_mv_struct(A), and only the
- * sampled check runs.  That is the fast path for repeated solves with one matrix. */
+ * Environment: CGB200_MATRIX_CACHE=tracked|strict|sampled|off.  A matrix handed over explicitly
+ * with cgb200_to_device(A), and every matrix while in CGB200_RESIDENT mode, is pinned: the caller
+ * has declared the device copy current until cgb200_invalidate(A) / free_mv_struct(A), and only the
+ * sampled check runs.  cgb200_cache_stats: {uploads, full hashes, calls settled by write tracking
+ * alone, calls where tracking reported a write or could not tell, tracking available (0/1)}. */
 #define CGB200_CACHE_STRICT 0
 #define CGB200_CACHE_SAMPLED 1
 #define CGB200_CACHE_OFF 2
+#define CGB200_CACHE_TRACKED 3
+int cgb200_cache_stats(long long *out5);
+/* 1 if the kernel's write tracking is usable in this process (probed and self-tested on first use;
+ * host only, needs no GPU), 0 if CGB200_CACHE_TRACKED will hash like CGB200_CACHE_STRICT. */
+int cgb200_write_tracking_available(void);
 int cgb200_set_matrix_cache(int policy);
 /* The content hash CGB200_CACHE_STRICT compares (host only, needs no device; 0 for NULL): every
  * byte of values / col_indices / row_ptr (a vector: its values).  Independent of the number of

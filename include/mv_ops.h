@@ -70,7 +70,7 @@ int sv_mult(double s, struct __mv_sparse *vec_a, struct __mv_sparse **out);
  * so *out has the reference's bits.  A matrix whose every row is full (row_ptr[i] == i*size) takes
  * the dense GEMV kernel, which accumulates with fma over a fixed tree: agrees with the reference
  * to <= 4 n eps |A||b| per row, not bit for bit.  A's arrays are re-validated on every call
- * (cgb200.h: CGB200_CACHE_STRICT), so in-place edits of values[] are seen as the reference sees
+ * (cgb200.h: CGB200_CACHE_TRACKED), so in-place edits of values[] are seen as the reference sees
  * them. */
 int mv_mult(struct __mv_sparse *mat_A, struct __mv_sparse *vec_b, struct __mv_sparse **out);
 /* *out = a + b                                              replaces reference mv_ops.c:203-230 */

@@ -171,3 +171,12 @@ def test_content_hash_sees_any_single_edit_and_ignores_thread_count(pkg, monkeyp
     big.vals[big.nnz - 5] = 3.0
     assert L.cgb200_content_hash(C.byref(B)) != h1
     assert L.cgb200_content_hash(None) == 0
+
+
+def test_write_tracking_probe_needs_no_gpu(pkg):
+    # the default matrix-cache policy asks the kernel whether the caller's arrays were written
+    # (userfaultfd async write-protection + PAGEMAP_SCAN); where that is missing it hashes instead
+    L = pkg.lib()
+    a = L.cgb200_write_tracking_available()
+    assert a in (0, 1) and L.cgb200_write_tracking_available() == a
+

@@ -48,7 +48,7 @@ def _off_grid_index(nnz):
 def strict(pkg, gpu_lib):
     assert gpu_lib.cgb200_set_matrix_cache(pkg.CACHE_STRICT) == 0
     yield gpu_lib
-    gpu_lib.cgb200_set_matrix_cache(pkg.CACHE_STRICT)
+    gpu_lib.cgb200_set_matrix_cache(pkg.CACHE_TRACKED)
 
 
 def test_in_place_edit_between_two_mv_mult_calls_is_seen(pkg, strict):
@@ -98,6 +98,134 @@ def test_in_place_edit_between_two_conj_grad_calls_is_seen(pkg, strict):
     assert np.linalg.norm(x2 - xo) <= TOL_X * np.linalg.norm(xo)
     assert np.linalg.norm(x2 - x1) > 1e-3 * np.linalg.norm(x1)
     L.cgb200_invalidate(C.byref(A))
+
+
+def test_tracked_policy_sees_every_edit_without_reading_unchanged_arrays(pkg, gpu_lib):
+    # the default policy: the kernel tells whether the caller wrote to the arrays (csrc/writewatch.cpp)
+    L = gpu_lib
+    assert L.cgb200_set_matrix_cache(pkg.CACHE_TRACKED) == 0
+    s = H.lap(420, 400)                       # values 6.7 MB, indices 3.4 MB: watched; row_ptr 0.7 MB: hashed
+    A, _ = _structs(pkg, s)
+    v = H.rhs(s.n, 33)
+    vv = pkg.MvSparse(s.n, s.n, H.dptr(v), None, None)
+    out = pkg.MvSparseP()
+
+    def product_is_current():
+        assert L.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0, pkg.last_error()
+        assert np.array_equal(_bits(_take(out, s.n)), _bits(_spmv(s, v)))
+
+    st0 = pkg.cache_stats()
+    product_is_current()                      # upload (+ one hash, taken while the upload runs)
+    st1 = pkg.cache_stats()
+    assert st1["uploads"] == st0["uploads"] + 1
+    for _ in range(3):
+        product_is_current()                  # unchanged: settled by the kernel's answer alone
+    st2 = pkg.cache_stats()
+    assert st2["uploads"] == st1["uploads"]
+    if st2["tracking_available"]:
+        assert st2["tracked_clean"] == st1["tracked_clean"] + 3 and st2["hashes"] == st1["hashes"]
+    else:
+        assert st2["hashes"] == st1["hashes"] + 3          # no kernel support: the full hash, every call
+    # edits: deep inside values, in the first bytes (a partial page: hashed, not watched), in the last
+    # entry, in a column index, in row_ptr -- each is seen, without cgb200_invalidate
+    k_mid = _off_grid_index(s.nnz)
+    edits = [("values mid", lambda: s.vals.__setitem__(k_mid, 17.5)),
+             ("values first", lambda: s.vals.__setitem__(1, -3.25)),
+             ("values last", lambda: s.vals.__setitem__(s.nnz - 2, 0.125)),
+             ("col index", lambda: s.cols.__setitem__(s.row_ptr[7] + 1, s.cols[s.row_ptr[7] + 1] + 1)),
+             ("same values rewritten", lambda: s.vals.__setitem__(slice(1000, 200000), s.vals[1000:200000].copy()))]
+    for name, edit in edits:
+        before = pkg.cache_stats()
+        edit()
+        product_is_current()
+        after = pkg.cache_stats()
+        if name == "same values rewritten":
+            assert after["uploads"] == before["uploads"], name      # written, hashed, found equal: no upload
+            if after["tracking_available"]:
+                assert after["hashes"] == before["hashes"] + 1 and after["tracked_dirty"] == before["tracked_dirty"] + 1
+        else:
+            assert after["uploads"] == before["uploads"] + 1, name
+        product_is_current()                  # and the call after that is clean again
+        again = pkg.cache_stats()
+        assert again["uploads"] == after["uploads"]
+        if again["tracking_available"]:
+            assert again["tracked_clean"] == after["tracked_clean"] + 1 and again["hashes"] == after["hashes"], name
+    # conj_grad goes through the same cache
+    A2, b2 = _structs(pkg, s)
+    xp = pkg.MvSparseP()
+    assert L.conj_grad(10, C.byref(A2), C.byref(b2), C.byref(xp)) == 0
+    x1 = _take(xp, s.n)
+    s.vals[s.row_ptr[1:] - 1] *= 1.0
+    d = np.flatnonzero(s.cols == np.repeat(np.arange(s.n), np.diff(s.row_ptr)))
+    s.vals[d] = 4.75                           # the diagonal, in place
+    assert L.conj_grad(10, C.byref(A2), C.byref(b2), C.byref(xp)) == 0
+    x2 = _take(xp, s.n)
+    xo = H.oracle_cg(s, 10)[0]
+    assert np.linalg.norm(x2 - xo) <= TOL_X * np.linalg.norm(xo) and np.linalg.norm(x2 - x1) > 1e-3 * np.linalg.norm(x1)
+    L.cgb200_invalidate(C.byref(A))
+    L.cgb200_invalidate(C.byref(A2))
+    L.cgb200_free_all(out)
+
+
+def test_tracked_policy_with_two_structs_over_the_same_arrays(pkg, gpu_lib):
+    # re-validating one struct clears the kernel's "written" marks of the shared arrays; the other
+    # struct must not take the cleared marks for "unchanged" (abi.cu: WatchedRange.epoch)
+    L = gpu_lib
+    assert L.cgb200_set_matrix_cache(pkg.CACHE_TRACKED) == 0
+    s = H.lap(400, 380)
+    A1, _ = _structs(pkg, s)
+    A2, _ = _structs(pkg, s)
+    v = H.rhs(s.n, 4)
+    vv = pkg.MvSparse(s.n, s.n, H.dptr(v), None, None)
+    out = pkg.MvSparseP()
+
+    def check(A):
+        assert L.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0, pkg.last_error()
+        assert np.array_equal(_bits(_take(out, s.n)), _bits(_spmv(s, v)))
+
+    check(A1)
+    check(A2)
+    k = _off_grid_index(s.nnz)
+    for first, second, val in ((A2, A1, 3.5), (A1, A2, -8.25), (A2, A1, 0.75)):
+        s.vals[k] = val
+        check(first)                           # sees the write, re-uploads, re-arms the shared range
+        check(second)                          # the marks are gone; the epoch says: look again
+        check(first)
+        check(second)
+    st0 = pkg.cache_stats()
+    check(A1)
+    check(A2)
+    st1 = pkg.cache_stats()
+    assert st1["uploads"] == st0["uploads"]
+    if st1["tracking_available"]:
+        assert st1["tracked_clean"] == st0["tracked_clean"] + 2 and st1["hashes"] == st0["hashes"]
+    L.cgb200_invalidate(C.byref(A1))
+    check(A2)                                  # releasing one struct leaves the other's watch intact
+    s.vals[k + 1] = 9.0
+    check(A2)
+    L.cgb200_invalidate(C.byref(A2))
+    L.cgb200_free_all(out)
+
+
+def test_large_pageable_arrays_upload_through_the_staged_copy(pkg, gpu_lib, monkeypatch):
+    # arrays of 64 MiB and more in ordinary memory go to the device in 4 MiB pieces from several host
+    # threads (solver.cu: upload_host); the device copy is the same as the driver's own single copy
+    L = gpu_lib
+    s = H.lap(112, 110, 110)                  # 9.4 M entries: values 75 MB (staged), indices 38 MB (plain)
+    assert 8 * s.nnz >= 64 << 20
+    rng = np.random.default_rng(5)
+    s.vals[:] = rng.random(s.nnz) - 0.5       # every piece distinguishable
+    v = H.rhs(s.n, 12)
+    want = _bits(_spmv(s, v))
+    vv = pkg.MvSparse(s.n, s.n, H.dptr(v), None, None)
+    for staged in ("1", "0"):
+        monkeypatch.setenv("CGB200_STAGED_UPLOAD", staged)
+        A, _ = _structs(pkg, s)
+        out = pkg.MvSparseP()
+        assert L.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0, pkg.last_error()
+        assert np.array_equal(_bits(_take(out, s.n)), want), staged
+        L.cgb200_invalidate(C.byref(A))
+        L.cgb200_free_all(out)
 
 
 def test_pinned_and_sampled_matrices_follow_the_documented_contract(pkg, strict):
