@@ -696,7 +696,7 @@ int dev_input(struct __mv_sparse* v, int slot, const double** out) {
     }
     if (ensure_vec_capacity(e, n)) return -1;
     if (n > 0)
-      CU_OK(cudaMemcpyAsync(e.d, v->values, sizeof(double) * n, cudaMemcpyHostToDevice, c.stream));
+      CU_OK(upload_host(e.d, v->values, sizeof(double) * n, c.stream));
     e.dev_valid = true;
     e.host_valid = true;
     e.sd_valid = false;
@@ -707,7 +707,7 @@ int dev_input(struct __mv_sparse* v, int slot, const double** out) {
   double* d;
   if (scratch(slot, n, &d)) return -1;
   if (n > 0)
-    CU_OK(cudaMemcpyAsync(d, v->values, sizeof(double) * n, cudaMemcpyHostToDevice, c.stream));
+    CU_OK(upload_host(d, v->values, sizeof(double) * n, c.stream));
   *out = d;
   return 0;
 }
@@ -766,7 +766,7 @@ int finish_output(struct __mv_sparse* o, double* d) {
     return 0;
   }
   if (o->size > 0)
-    CU_OK(cudaMemcpyAsync(o->values, d, sizeof(double) * o->size, cudaMemcpyDeviceToHost, c.stream));
+    CU_OK(download_host(o->values, d, sizeof(double) * o->size, c.stream));
   CU_OK(cudaStreamSynchronize(c.stream));
   return 0;
 }
@@ -779,7 +779,7 @@ int sync_to_host(struct __mv_sparse* o) {
   if (e.dev_valid && !e.host_valid && e.n == o->size && o->values && e.host_ptr == o->values) {
     Ctx& c = ctx();
     if (e.n > 0)
-      CU_OK(cudaMemcpyAsync(o->values, e.d, sizeof(double) * e.n, cudaMemcpyDeviceToHost, c.stream));
+      CU_OK(download_host(o->values, e.d, sizeof(double) * e.n, c.stream));
     CU_OK(cudaStreamSynchronize(c.stream));
     e.host_valid = true;
   }
@@ -923,14 +923,14 @@ int solve_host(struct __mv_sparse* A, struct __mv_sparse* b, struct __mv_sparse*
   if (!sys) return -1;
   if (sync_to_host(b)) return -1;
   const int n = b->size;
-  if (n > 0) CU_OK(cudaMemcpyAsync(sys->b, b->values, sizeof(double) * n, cudaMemcpyHostToDevice, c.stream));
+  if (n > 0) CU_OK(upload_host(sys->b, b->values, sizeof(double) * n, c.stream));
   if (o.flags & CGB200_OPT_X0) {  // extension: *x holds the initial guess (the reference starts at 0)
     if (!*x || (*x)->size != n || !(*x)->values) {
       set_error("CGB200_OPT_X0: *x must be a vector of A's size holding the initial guess");
       return -1;
     }
     if (sync_to_host(*x)) return -1;
-    if (n > 0) CU_OK(cudaMemcpyAsync(sys->x, (*x)->values, sizeof(double) * n, cudaMemcpyHostToDevice, c.stream));
+    if (n > 0) CU_OK(upload_host(sys->x, (*x)->values, sizeof(double) * n, c.stream));
   }
   if (system_solve(sys, o, res)) return -1;
   // the reference hands back a freshly allocated vector (cg.c:104,138)

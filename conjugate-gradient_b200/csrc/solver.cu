@@ -170,6 +170,7 @@ void shutdown() {
   cudaFreeHost(c.h_state);
   dev_free(c.d_scratch);
   cudaFreeHost(c.h_scratch);
+  stage_release();
   cudaStreamDestroy(c.stream);
   cudaStreamDestroy(c.comm_stream);
   c = Ctx();
@@ -682,70 +683,130 @@ System* system_dense(int n, int row0, int nrows, unsigned long long aseed,
   return S;
 }
 
-// Host -> device copy of a large array.  From page-locked memory: one cudaMemcpyAsync.  From ordinary
-// (pageable) memory -- what a caller of the reference has, cg.c:231-262 -- the driver's own staging
-// reaches ~10 GB/s (measured: 8.6 GB in 0.8 s); here a few host threads copy 4 MiB pieces into
-// page-locked buffers and send each on its own stream, so the host-side copy of one piece overlaps
-// the PCIe transfer of the others.  Returns with the data on the device.
-static cudaError_t upload_host(void* dst, const void* src, size_t bytes, cudaStream_t st) {
-  constexpr size_t PIECE = 4u << 20;
-  constexpr int NBUF = 2;
-  cudaPointerAttributes at;
-  bool pageable = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeUnregistered;
-  cudaGetLastError();
+// Copies of large arrays between the caller's ordinary (pageable) memory and the device.  The
+// driver's own staging reaches ~10 GB/s there (measured: 8.6 GB up in 0.8 s); here a few host
+// threads move 4 MiB pieces through page-locked buffers, each thread on its own stream, so the
+// host-side copy of one piece overlaps the PCIe transfer of the others (8.6 GB up in 0.22 s).
+// Page-locked sources / destinations and small arrays take one cudaMemcpyAsync on st.  The staged
+// forms synchronise st first (the device buffer is theirs from then on) and return with the data
+// in place.  The staging buffer (64 MiB, usable from every device) is allocated on first use and
+// kept until shutdown: allocating page-locked memory costs more than a 100 MB copy.
+namespace {
+
+constexpr size_t STAGE_PIECE = 4u << 20;
+constexpr int STAGE_NBUF = 2, STAGE_MAXT = 8;
+constexpr size_t STAGE_MIN_BYTES = 32u << 20;
+char* g_stage = nullptr;
+std::mutex g_stage_mu;  // one staged copy at a time per process
+
+bool staged_copy_wanted(const void* host, size_t bytes) {
+  if (bytes < STAGE_MIN_BYTES) return false;
   if (const char* e = getenv("CGB200_STAGED_UPLOAD"))
-    if (strcmp(e, "0") == 0) pageable = false;
-  if (bytes < (64u << 20) || !pageable) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+    if (strcmp(e, "0") == 0) return false;
+  cudaPointerAttributes at;
+  const bool pageable = cudaPointerGetAttributes(&at, host) == cudaSuccess && at.type == cudaMemoryTypeUnregistered;
+  cudaGetLastError();
+  return pageable;
+}
+
+int stage_threads() {
+  const int t = (int)std::thread::hardware_concurrency() / 2;
+  return t < 2 ? 2 : (t > STAGE_MAXT ? STAGE_MAXT : t);
+}
+
+// dir 0: host -> device, 1: device -> host.  Call with g_stage_mu held and g_stage allocated.
+cudaError_t staged_copy(char* dev_ptr, char* host_ptr, size_t bytes, int dir) {
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
-  int T = (int)std::thread::hardware_concurrency() / 2;
-  T = T < 2 ? 2 : (T > 8 ? 8 : T);
-  char* stage = nullptr;
-  if (cudaHostAlloc((void**)&stage, (size_t)T * NBUF * PIECE, cudaHostAllocDefault) != cudaSuccess) {
-    cudaGetLastError();
-    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
-  }
-  e = cudaStreamSynchronize(st);  // dst is ours from here on
+  const int T = stage_threads();
   std::vector<cudaError_t> err((size_t)T, cudaSuccess);
   std::atomic<size_t> next(0);
   auto work = [&](int t) {
     cudaError_t& er = err[(size_t)t];
     cudaStream_t s = nullptr;
-    cudaEvent_t ev[NBUF] = {nullptr, nullptr};
+    cudaEvent_t ev[STAGE_NBUF] = {nullptr, nullptr};
+    size_t p_off[STAGE_NBUF] = {0, 0}, p_len[STAGE_NBUF] = {0, 0};  // dir 1: piece waiting in each buffer
     if ((er = cudaSetDevice(dev)) != cudaSuccess) return;
     if ((er = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)) != cudaSuccess) return;
-    for (int k = 0; k < NBUF && er == cudaSuccess; ++k) er = cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming);
+    for (int k = 0; k < STAGE_NBUF && er == cudaSuccess; ++k)
+      er = cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming);
+    auto buffer = [&](int b) { return g_stage + ((size_t)t * STAGE_NBUF + b) * STAGE_PIECE; };
+    auto drain = [&](int b) {  // dir 1: the piece that arrived in buffer b goes to the caller's array
+      if (p_len[b] == 0 || er != cudaSuccess) return;
+      er = cudaEventSynchronize(ev[b]);
+      if (er == cudaSuccess) memcpy(host_ptr + p_off[b], buffer(b), p_len[b]);
+      p_len[b] = 0;
+    };
     for (size_t k = 0; er == cudaSuccess; ++k) {
-      const size_t off = next.fetch_add(1) * PIECE;
+      const size_t off = next.fetch_add(1) * STAGE_PIECE;
       if (off >= bytes) break;
-      const size_t len = bytes - off < PIECE ? bytes - off : PIECE;
-      const int buf = (int)(k % NBUF);
-      char* h = stage + ((size_t)t * NBUF + buf) * PIECE;
-      if (k >= NBUF) er = cudaEventSynchronize(ev[buf]);  // the transfer that last used this buffer
-      if (er != cudaSuccess) break;
-      memcpy(h, (const char*)src + off, len);
-      er = cudaMemcpyAsync((char*)dst + off, h, len, cudaMemcpyHostToDevice, s);
-      if (er == cudaSuccess) er = cudaEventRecord(ev[buf], s);
+      const size_t len = bytes - off < STAGE_PIECE ? bytes - off : STAGE_PIECE;
+      const int b = (int)(k % STAGE_NBUF);
+      if (dir == 0) {
+        if (k >= STAGE_NBUF) er = cudaEventSynchronize(ev[b]);  // the transfer that last used this buffer
+        if (er != cudaSuccess) break;
+        memcpy(buffer(b), host_ptr + off, len);
+        er = cudaMemcpyAsync(dev_ptr + off, buffer(b), len, cudaMemcpyHostToDevice, s);
+      } else {
+        drain(b);
+        if (er != cudaSuccess) break;
+        er = cudaMemcpyAsync(buffer(b), dev_ptr + off, len, cudaMemcpyDeviceToHost, s);
+        p_off[b] = off;
+        p_len[b] = len;
+      }
+      if (er == cudaSuccess) er = cudaEventRecord(ev[b], s);
     }
+    if (dir == 1)
+      for (int b = 0; b < STAGE_NBUF; ++b) drain(b);
     if (s) {
       const cudaError_t e2 = cudaStreamSynchronize(s);
       if (er == cudaSuccess) er = e2;
       cudaStreamDestroy(s);
     }
-    for (int k = 0; k < NBUF; ++k)
+    for (int k = 0; k < STAGE_NBUF; ++k)
       if (ev[k]) cudaEventDestroy(ev[k]);
   };
-  if (e == cudaSuccess) {
-    std::vector<std::thread> th;
-    for (int t = 1; t < T; ++t) th.emplace_back(work, t);
-    work(0);
-    for (auto& x : th) x.join();
-    for (cudaError_t x : err)
-      if (x != cudaSuccess) e = x;
-  }
-  cudaFreeHost(stage);
+  std::vector<std::thread> th;
+  for (int t = 1; t < T; ++t) th.emplace_back(work, t);
+  work(0);
+  for (auto& x : th) x.join();
+  for (cudaError_t x : err)
+    if (x != cudaSuccess) e = x;
   return e;
+}
+
+cudaError_t host_copy(void* dev_ptr, void* host_ptr, size_t bytes, int dir, cudaStream_t st) {
+  const cudaMemcpyKind kind = dir == 0 ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+  void* dst = dir == 0 ? dev_ptr : host_ptr;
+  const void* src = dir == 0 ? host_ptr : dev_ptr;
+  if (!staged_copy_wanted(host_ptr, bytes)) return cudaMemcpyAsync(dst, src, bytes, kind, st);
+  std::lock_guard<std::mutex> lk(g_stage_mu);
+  if (!g_stage &&
+      cudaHostAlloc((void**)&g_stage, (size_t)STAGE_MAXT * STAGE_NBUF * STAGE_PIECE, cudaHostAllocPortable) != cudaSuccess) {
+    cudaGetLastError();
+    g_stage = nullptr;
+    return cudaMemcpyAsync(dst, src, bytes, kind, st);
+  }
+  const cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return e;
+  return staged_copy((char*)dev_ptr, (char*)host_ptr, bytes, dir);
+}
+
+}  // namespace
+
+cudaError_t upload_host(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+  return host_copy(dst, const_cast<void*>(src), bytes, 0, st);
+}
+
+cudaError_t download_host(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+  return host_copy(const_cast<void*>(src), dst, bytes, 1, st);
+}
+
+void stage_release() {
+  std::lock_guard<std::mutex> lk(g_stage_mu);
+  if (g_stage) cudaFreeHost(g_stage);
+  g_stage = nullptr;
 }
 
 System* system_from_csr(long long n_global, long long row0, int nrows, const int* row_ptr,
@@ -1649,7 +1710,7 @@ int system_trace(System* S, int on, unsigned long long* out) {
 
 int system_set_rhs(System* S, const double* b_host) {
   Ctx& c = g_ctx;
-  CUDA_OK(cudaMemcpyAsync(S->b, b_host, sizeof(double) * S->nloc, cudaMemcpyHostToDevice, c.stream));
+  CUDA_OK(upload_host(S->b, b_host, sizeof(double) * S->nloc, c.stream));
   CUDA_OK(cudaStreamSynchronize(c.stream));
   return 0;
 }
@@ -1662,14 +1723,14 @@ int system_gen_rhs(System* S, unsigned long long seed) {
 
 int system_set_x(System* S, const double* x_host) {
   Ctx& c = g_ctx;
-  CUDA_OK(cudaMemcpyAsync(S->x, x_host, sizeof(double) * S->nloc, cudaMemcpyHostToDevice, c.stream));
+  CUDA_OK(upload_host(S->x, x_host, sizeof(double) * S->nloc, c.stream));
   CUDA_OK(cudaStreamSynchronize(c.stream));
   return 0;
 }
 
 int system_get_x(System* S, double* x_host) {
   Ctx& c = g_ctx;
-  CUDA_OK(cudaMemcpyAsync(x_host, S->x, sizeof(double) * S->nloc, cudaMemcpyDeviceToHost, c.stream));
+  CUDA_OK(download_host(x_host, S->x, sizeof(double) * S->nloc, c.stream));
   CUDA_OK(cudaStreamSynchronize(c.stream));
   return 0;
 }

@@ -129,6 +129,13 @@ struct SoloScope {
 
 System* system_lap(int nx, int ny, int nz, int z0, int nzl, unsigned long long bseed);
 System* system_dense(int n, int row0, int nrows, unsigned long long aseed, unsigned long long bseed);
+// Copies of large arrays between ordinary (pageable) host memory and the CURRENT device, staged
+// through page-locked buffers by a few host threads (solver.cu).  In that case st is synchronised
+// first and the data is in place on return; otherwise they are a cudaMemcpyAsync on st.
+cudaError_t upload_host(void* dst_dev, const void* src_host, size_t bytes, cudaStream_t st);
+cudaError_t download_host(void* dst_host, const void* src_dev, size_t bytes, cudaStream_t st);
+void stage_release();  // frees the staging buffer (shutdown)
+
 System* system_from_csr(long long n_global, long long row0, int nrows, const int* row_ptr,
                         const int* cols, const double* vals, const double* b);
 // A row block whose arrays are already on this device (padded like alloc_matrix pads them; rowptr

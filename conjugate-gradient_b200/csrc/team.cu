@@ -404,9 +404,9 @@ TeamSystem* team_create(const struct __mv_sparse* A) {
          cudaMemset(base, 0, m.bytes) == cudaSuccess;
     if (ok) {
       T->base[g] = base;
-      ok = cudaMemcpy(base + m.off_vals, A->values + k0, sizeof(double) * bn, cudaMemcpyHostToDevice) == cudaSuccess;
+      ok = upload_host(base + m.off_vals, A->values + k0, sizeof(double) * bn, nullptr) == cudaSuccess;
       if (ok && !full) {
-        ok = cudaMemcpy(base + m.off_cols, A->col_indices + k0, sizeof(int) * bn, cudaMemcpyHostToDevice) == cudaSuccess;
+        ok = upload_host(base + m.off_cols, A->col_indices + k0, sizeof(int) * bn, nullptr) == cudaSuccess;
         std::vector<int> lrp(rpad, (int)bn);  // local offsets; the padding repeats the end offset
         for (int i = 0; i <= nr; ++i) lrp[i] = (int)((long long)rp[r0 + i] - k0);
         ok = ok && cudaMemcpy(base + m.off_rowptr, lrp.data(), sizeof(int) * rpad, cudaMemcpyHostToDevice) == cudaSuccess;
@@ -486,12 +486,17 @@ int team_solve(TeamSystem* T, const double* b_host, const double* x0_host, doubl
   Ctx& c = ctx();
   const int G = c.world;
   bool ok = true;
-  for (int g = 1; g < G && ok; ++g) {  // every rank's slice of b (and of the guess) onto its GPU
+  // every rank's slice of b (and of the guess) onto its GPU, with that GPU current (the staged copy
+  // of a large slice from pageable memory runs on streams of the current device, solver.cu)
+  for (int g = 1; g < G && ok; ++g) {
     char* base = (char*)T->base[g];
-    ok = cudaMemcpy(base + T->off_b[g], b_host + T->row0[g], sizeof(double) * T->nrows[g], cudaMemcpyHostToDevice) == cudaSuccess;
-    if (ok && x0_host)
-      ok = cudaMemcpy(base + T->off_x[g], x0_host + T->row0[g], sizeof(double) * T->nrows[g], cudaMemcpyHostToDevice) == cudaSuccess;
+    const size_t bytes = sizeof(double) * (size_t)T->nrows[g];
+    ok = cudaSetDevice(g_workers[g - 1].device) == cudaSuccess &&
+         upload_host(base + T->off_b[g], b_host + T->row0[g], bytes, nullptr) == cudaSuccess;
+    if (ok && x0_host) ok = upload_host(base + T->off_x[g], x0_host + T->row0[g], bytes, nullptr) == cudaSuccess;
+    if (ok) ok = cudaStreamSynchronize(nullptr) == cudaSuccess;
   }
+  cudaSetDevice(c.device);
   if (ok) ok = system_set_rhs(T->mine, b_host) == 0 && (!x0_host || system_set_x(T->mine, x0_host) == 0);
   if (!ok) {
     set_error(std::string("GPU team: copying the right-hand side in failed: ") + cudaGetErrorString(cudaGetLastError()));
@@ -506,12 +511,17 @@ int team_solve(TeamSystem* T, const double* b_host, const double* x0_host, doubl
   }
   if (team_round(msgs, [&]() -> int { return system_solve(T->mine, o, res); }) != 0) return -1;
   if (system_get_x(T->mine, x_host)) return -1;
-  for (int g = 1; g < G; ++g)
-    if (cudaMemcpy(x_host + T->row0[g], (char*)T->base[g] + T->off_x[g], sizeof(double) * T->nrows[g],
-                   cudaMemcpyDeviceToHost) != cudaSuccess) {
+  for (int g = 1; g < G; ++g) {
+    const bool got = cudaSetDevice(g_workers[g - 1].device) == cudaSuccess &&
+                     download_host(x_host + T->row0[g], (char*)T->base[g] + T->off_x[g],
+                                   sizeof(double) * T->nrows[g], nullptr) == cudaSuccess &&
+                     cudaStreamSynchronize(nullptr) == cudaSuccess;
+    cudaSetDevice(c.device);
+    if (!got) {
       set_error(std::string("GPU team: copying x out failed: ") + cudaGetErrorString(cudaGetLastError()));
       return -1;
     }
+  }
   return 0;
 }
 

@@ -228,6 +228,31 @@ def test_large_pageable_arrays_upload_through_the_staged_copy(pkg, gpu_lib, monk
         L.cgb200_free_all(out)
 
 
+def test_large_vectors_move_through_the_staged_copy_in_both_directions(pkg, gpu_lib, monkeypatch):
+    # b in and x out of 32 MiB and more (pageable) are staged like the matrix arrays; same results
+    L = gpu_lib
+    s = H.lap(2100, 2048)                     # 4.3 M unknowns: 34 MB per vector
+    assert 8 * s.n >= 32 << 20
+    v = H.rhs(s.n, 9)
+    want = _bits(_spmv(s, v))
+    xo = H.oracle_cg(s, 6)[0]
+    vv = pkg.MvSparse(s.n, s.n, H.dptr(v), None, None)
+    got = {}
+    for staged in ("1", "0"):
+        monkeypatch.setenv("CGB200_STAGED_UPLOAD", staged)
+        A, b = _structs(pkg, s)
+        out, xp = pkg.MvSparseP(), pkg.MvSparseP()
+        assert L.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0, pkg.last_error()
+        assert np.array_equal(_bits(_take(out, s.n)), want), staged
+        assert L.conj_grad(6, C.byref(A), C.byref(b), C.byref(xp)) == 0, pkg.last_error()
+        got[staged] = _take(xp, s.n)
+        assert np.linalg.norm(got[staged] - xo) <= TOL_X * np.linalg.norm(xo)
+        L.cgb200_invalidate(C.byref(A))
+        L.cgb200_free_all(out)
+        L.cgb200_free_all(xp)
+    assert np.array_equal(_bits(got["1"]), _bits(got["0"]))
+
+
 def test_pinned_and_sampled_matrices_follow_the_documented_contract(pkg, strict):
     L = strict
     s = H.lap(40, 30)
