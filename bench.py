@@ -520,12 +520,13 @@ def e2e_host_structs(pkg, d, info, J, solves=8):
     a_bytes = 8 * nnz if info["kind"] == "dense" else 12 * nnz + 4 * (n + 1)
     per_solve_iters = iters / solves
     return {
-        "value": round(iters / warm_s, 2), "unit": UNIT,
+        "value": round(it_def / def_s, 2), "unit": UNIT,
         "h2d_bytes_per_step": round(8 * n / per_solve_iters, 1),
         "d2h_bytes_per_step": round(8 * n / per_solve_iters, 1),
-        "api": "cgb200_to_device(A) once, then cgb200_solve(struct __mv_sparse* A, b, &x) == conj_grad with tol 1e-10 per solve; A pageable, b pinned; b in and x out every solve",
+        "api": "cgb200_solve(struct __mv_sparse* A, b, &x) == conj_grad with tol 1e-10, per solve, by an unmodified caller (default cache policy, no hand-over call); A in pageable memory, b pinned; b in and x out every solve",
         "solves": solves, "iterations_per_solve": per_solve_iters,
         "default_policy_value": round(it_def / def_s, 2),
+        "pinned_value": round(iters / warm_s, 2),
         "strict_cache_value": round(it_strict / strict_s, 3),
         "cold_first_call_value": round(it_cold / cold_s, 3),
         "default_policy": {"value": round(it_def / def_s, 2), "unit": UNIT, "solves": solves, "policy": "CGB200_CACHE_TRACKED",
@@ -534,14 +535,14 @@ def e2e_host_structs(pkg, d, info, J, solves=8):
                            "content_hashes": st1["hashes"] - st0["hashes"], "uploads": st1["uploads"] - st0["uploads"],
                            "note": "an unmodified caller of the reference's API (no cgb200_to_device): per call the kernel is asked "
                                    "whether A's pageable host arrays were written since the upload; exact, reads nothing of A"},
-        "per_solve": {"h2d_bytes": 8 * n, "d2h_bytes": 8 * n, "ms": round(warm_s / solves * 1e3, 3)},
+        "per_solve": {"h2d_bytes": 8 * n, "d2h_bytes": 8 * n, "ms": round(def_s / solves * 1e3, 3)},
         "strict_cache": {"value": round(it_strict / strict_s, 3), "unit": UNIT, "solves": 2,
                          "note": "CGB200_CACHE_STRICT (the fallback without kernel write tracking, and for page-locked arrays): "
                                  "every call hashes every byte of A's host arrays (several host threads)"},
         "cold_first_call": {"value": round(it_cold / cold_s, 3), "unit": UNIT, "seconds": round(cold_s, 3),
                             "h2d_bytes": a_bytes + 8 * n, "note": "includes uploading A and hashing it"},
-        "note": "value: A pinned on the device by cgb200_to_device (the documented path for repeated solves); "
-                "default_policy_value: no such call (unmodified caller), A validated per call by kernel write tracking; "
+        "note": "value = default_policy_value: an unmodified caller, A validated per call by kernel write tracking (asked while "
+                "the device already works); pinned_value: A handed over once with cgb200_to_device (no per-call validation); "
                 "strict_cache_value: A re-validated byte for byte on every call; cold_first_call_value: A uploaded from pageable memory",
         "operator_api": ops,
     }, x_par
@@ -1141,7 +1142,7 @@ def main():
     tail = {"n_gpus": world, "workloads": summary}
     if isinstance(line.get("e2e"), dict) and line["e2e"].get("value") is not None:
         e = line["e2e"]
-        tail["e2e"] = {"pinned": e["value"], "default": e.get("default_policy_value"), "strict": e.get("strict_cache_value"),
+        tail["e2e"] = {"default": e["value"], "pinned": e.get("pinned_value"), "strict": e.get("strict_cache_value"),
                        "cold": e.get("cold_first_call_value")}
     if "parity" in line:
         tail["parity"] = {"dense32768_K5_vs_reference_rel_l2": compact(line["parity"]["rel_l2"], 3), "tol": 1e-8}

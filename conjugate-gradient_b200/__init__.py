@@ -145,6 +145,8 @@ def lib():
     L.cgb200_set_mode.argtypes = [C.c_int]
     L.cgb200_set_matrix_cache.argtypes = [C.c_int]
     L.cgb200_cache_stats.argtypes = [C.POINTER(C.c_longlong)]
+    L.cgb200_write_tracking_op.argtypes = [C.c_void_p, C.c_size_t, C.c_int]
+    L.cgb200_write_tracking_op.restype = C.c_int
     L.cgb200_content_hash.restype = C.c_ulonglong
     L.cgb200_content_hash.argtypes = [MvSparseP]
     for name in ("cgb200_to_device", "cgb200_to_host", "cgb200_invalidate"):

@@ -412,9 +412,37 @@ void release_entry(MatrixEntry& e) {
   e.team = nullptr;
 }
 
+// The tracked policy's question to the kernel takes 0.1-0.5 ms on a multi-GB matrix (a walk over
+// its page tables) -- against a 1.2 ms matvec.  Callers that are about to start device work on the
+// matrix hand in a PendingCheck: the question is then asked on a host thread WHILE the device works
+// on the copy it already has, and settle() says afterwards whether that copy was the current one.
+// If not (the arrays were written, or the kernel cannot tell), nothing has left the library yet:
+// the caller validates the ordinary way and repeats the device work.
+struct PendingCheck {
+  std::thread th;
+  MatrixEntry* entry = nullptr;
+  int w = 0;
+  uint64_t edge = 0;
+  bool started = false;
+  ~PendingCheck() {
+    if (th.joinable()) th.join();
+  }
+  // true = the device copy that was used is the caller's current matrix
+  bool settle() {
+    if (!started) return true;
+    th.join();
+    started = false;
+    if (w == 0 && edge == entry->edge) {
+      ++g_stat_tracked_clean;
+      return true;
+    }
+    return false;
+  }
+};
+
 // The cache entry of a caller's matrix with the requested device copy in it: one GPU (want_team
 // false) or row blocks over the GPU team.  Validation is the same for both (policy above).
-MatrixEntry* matrix_entry(struct __mv_sparse* A, bool pin, bool want_team) {
+MatrixEntry* matrix_entry(struct __mv_sparse* A, bool pin, bool want_team, PendingCheck* pc = nullptr) {
   if (!A->row_ptr || !A->values || (!A->col_indices && A->nnz > 0)) {
     set_error("matrix struct lacks CSR arrays");
     return nullptr;
@@ -441,6 +469,19 @@ MatrixEntry* matrix_entry(struct __mv_sparse* A, bool pin, bool want_team) {
         // exactly, without reading the arrays
         HostArr a[3];
         host_arrays(A, a);
+        if (pc && old.sys && !want_team) {  // asked while the device works: PendingCheck
+          pc->entry = &old;
+          pc->started = true;
+          const HostArr a0 = a[0], a1 = a[1], a2 = a[2];
+          const uint64_t s0 = old.seen[0], s1 = old.seen[1], s2 = old.seen[2];
+          pc->th = std::thread([pc, a0, a1, a2, s0, s1, s2]() {
+            const HostArr aa[3] = {a0, a1, a2};
+            const uint64_t ss[3] = {s0, s1, s2};
+            pc->w = watch_state(aa, ss);
+            pc->edge = pc->w == 0 ? edge_hash(aa) : 0;
+          });
+          return &old;
+        }
         const int w = watch_state(a, old.seen);
         if (w == 0 && edge_hash(a) == old.edge) {
           ++g_stat_tracked_clean;
@@ -544,8 +585,8 @@ MatrixEntry* matrix_entry(struct __mv_sparse* A, bool pin, bool want_team) {
 
 // Device system for a host CSR struct, uploaded on first use and whenever the struct's arrays no
 // longer hold what was uploaded (policy above).  pin: the caller hands the matrix over explicitly.
-System* matrix_system(struct __mv_sparse* A, bool pin = false) {
-  MatrixEntry* e = matrix_entry(A, pin, false);
+System* matrix_system(struct __mv_sparse* A, bool pin = false, PendingCheck* pc = nullptr) {
+  MatrixEntry* e = matrix_entry(A, pin, false, pc);
   return e ? e->sys : nullptr;
 }
 
@@ -919,20 +960,28 @@ int solve_host(struct __mv_sparse* A, struct __mv_sparse* b, struct __mv_sparse*
     if (team_active()) return -1;  // the team is fine, this matrix was refused: the reason is in last_error
     // (the team broke while taking the matrix: fall through to one GPU)
   }
-  System* sys = matrix_system(A);
+  PendingCheck pc;
+  System* sys = matrix_system(A, false, &pc);
   if (!sys) return -1;
   if (sync_to_host(b)) return -1;
   const int n = b->size;
-  if (n > 0) CU_OK(upload_host(sys->b, b->values, sizeof(double) * n, c.stream));
   if (o.flags & CGB200_OPT_X0) {  // extension: *x holds the initial guess (the reference starts at 0)
     if (!*x || (*x)->size != n || !(*x)->values) {
       set_error("CGB200_OPT_X0: *x must be a vector of A's size holding the initial guess");
       return -1;
     }
     if (sync_to_host(*x)) return -1;
-    if (n > 0) CU_OK(upload_host(sys->x, (*x)->values, sizeof(double) * n, c.stream));
   }
-  if (system_solve(sys, o, res)) return -1;
+  for (int attempt = 0;; ++attempt) {
+    if (n > 0) CU_OK(upload_host(sys->b, b->values, sizeof(double) * n, c.stream));
+    if ((o.flags & CGB200_OPT_X0) && n > 0) CU_OK(upload_host(sys->x, (*x)->values, sizeof(double) * n, c.stream));
+    if (system_solve(sys, o, res)) return -1;
+    if (attempt > 0 || pc.settle()) break;
+    // the arrays were written since the upload (or the kernel cannot tell): that solve ran on a
+    // stale copy and is dropped -- validate the ordinary way (hash, upload if different), again
+    sys = matrix_system(A);
+    if (!sys) return -1;
+  }
   // the reference hands back a freshly allocated vector (cg.c:104,138)
   struct __mv_sparse* xv = (struct __mv_sparse*)calloc(1, sizeof(struct __mv_sparse));
   if (!xv) return -1;
@@ -1124,7 +1173,8 @@ int mv_mult(struct __mv_sparse* mat_A, struct __mv_sparse* vec_b, struct __mv_sp
   if (ensure_init(-1)) return -1;
   std::lock_guard<std::mutex> lk(g_tab_mu);
   Ctx& c = ctx();
-  System* sys = matrix_system(mat_A);
+  PendingCheck pc;  // (tracked policy: the kernel is asked about A's arrays while the product runs)
+  System* sys = matrix_system(mat_A, false, &pc);
   if (!sys) return -1;
   const int n = mat_A->size;
   const double* db = nullptr;
@@ -1134,6 +1184,12 @@ int mv_mult(struct __mv_sparse* mat_A, struct __mv_sparse* vec_b, struct __mv_sp
   if (n == 0) return 0;
   double* dout = nullptr;
   if (dev_output(*out, 2, &dout)) return -1;
+  if (system_matvec_into(sys, db, dout)) return -1;
+  if (finish_output(*out, dout)) return -1;
+  if (pc.settle()) return 0;
+  // A was written since its upload: that product is dropped; validate the ordinary way and redo it
+  sys = matrix_system(mat_A);
+  if (!sys) return -1;
   if (system_matvec_into(sys, db, dout)) return -1;
   return finish_output(*out, dout);
 }
@@ -1215,6 +1271,17 @@ int cgb200_set_matrix_cache(int policy) {
 }
 
 int cgb200_write_tracking_available(void) { return ww_available() ? 1 : 0; }
+
+int cgb200_write_tracking_op(const void* p, size_t bytes, int op) {
+  if (!ww_available()) return -1;
+  switch (op) {
+    case 0: return ww_arm(p, bytes) ? 0 : -1;
+    case 1: return ww_written(p, bytes);
+    case 2: return ww_rearm(p, bytes) ? 0 : -1;
+    case 3: ww_disarm(p, bytes); return 0;
+    default: return -1;
+  }
+}
 
 int cgb200_cache_stats(long long* out5) {
   if (!out5) return -1;

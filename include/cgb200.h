@@ -133,6 +133,11 @@ int cgb200_cache_stats(long long *out5);
 /* 1 if the kernel's write tracking is usable in this process (probed and self-tested on first use;
  * host only, needs no GPU), 0 if CGB200_CACHE_TRACKED will hash like CGB200_CACHE_STRICT. */
 int cgb200_write_tracking_available(void);
+/* The mechanism itself, for tests and diagnostics (host only, no GPU; not needed by callers).
+ * [p, p + bytes) is ordinary anonymous memory; only its page-aligned interior is covered.
+ * op 0: start watching (0 / -1); op 1: was any page written since the marks were last cleared?
+ * (1 / 0 / -1 = cannot tell, e.g. not watched); op 2: clear the marks (0 / -1); op 3: stop watching. */
+int cgb200_write_tracking_op(const void *p, size_t bytes, int op);
 int cgb200_set_matrix_cache(int policy);
 /* The content hash CGB200_CACHE_STRICT compares (host only, needs no device; 0 for NULL): every
  * byte of values / col_indices / row_ptr (a vector: its values).  Independent of the number of

@@ -180,3 +180,36 @@ def test_write_tracking_probe_needs_no_gpu(pkg):
     a = L.cgb200_write_tracking_available()
     assert a in (0, 1) and L.cgb200_write_tracking_available() == a
 
+
+def test_write_tracking_sees_writes_and_only_writes(pkg):
+    # csrc/writewatch.cpp on a numpy array, no GPU involved: a read is not a write, one stored byte
+    # anywhere in the interior is, clearing the marks starts over, an unwatched range says "cannot tell"
+    import numpy as np
+
+    L = pkg.lib()
+    if not L.cgb200_write_tracking_available():
+        pytest.skip("this kernel has no userfaultfd async write protection / PAGEMAP_SCAN")
+    a = np.ones(3 << 20)                         # 24 MiB, touched
+    p, nb = a.ctypes.data, a.nbytes
+    op = L.cgb200_write_tracking_op
+    assert op(p, nb, 1) == -1                    # not watched yet
+    assert op(p, nb, 0) == 0
+    assert op(p, nb, 1) == 0
+    assert float(a[12345:99999].sum()) == 99999 - 12345 and op(p, nb, 1) == 0
+    a[(1 << 20) + 17] = 2.0
+    assert op(p, nb, 1) == 1
+    assert op(p, nb, 2) == 0 and op(p, nb, 1) == 0
+    a[-1000] = 3.0                               # the last full page of the interior
+    assert op(p, nb, 1) == 1
+    assert op(p, nb, 2) == 0
+    a[5000:5010] = a[5000:5010].copy()           # the same values are still a write
+    assert op(p, nb, 1) == 1
+    b = np.zeros(1 << 20)                        # a second, independent range
+    assert op(b.ctypes.data, b.nbytes, 0) == 0 and op(b.ctypes.data, b.nbytes, 1) == 0
+    assert op(p, nb, 3) == 0 and op(p, nb, 1) == -1
+    assert op(b.ctypes.data, b.nbytes, 1) == 0
+    b[77] = 1.0
+    assert op(b.ctypes.data, b.nbytes, 1) == 1
+    assert op(b.ctypes.data, b.nbytes, 3) == 0
+    assert op(p, 100, 0) == -1                   # no whole page inside
+
