@@ -372,16 +372,17 @@ def roofline_for(pkg, d, peak, peak_src, kernel_name, workload, world, variant=0
 # -------------------------------------------------------------------------------------------------
 
 
-def operator_api_loop(pkg, A, b, bnp, bs, J):
+def operator_api_loop(pkg, A, b, bnp, bs, J, resident=True):
     """The reference's own loop (cg.c:104-135) kept by the caller and run operator by operator
-    against libcgb200.so in resident mode -- what a user gets who relinks mv_ops but keeps their
-    cg.c.  Per iteration, as the reference issues them: mv_mult, 4 dot_product (2 answered from the
+    against libcgb200.so -- what a user gets who relinks mv_ops but keeps their cg.c: in resident
+    mode (CGB200_MODE=resident: vectors stay on the device between operators) or in the default
+    eager mode (every operator copies its operands in and its result out, and mv_mult re-validates A).  Per iteration, as the reference issues them: mv_mult, 4 dot_product (2 answered from the
     stored v.v of an unchanged vector), 3 sv_mult, 2 vec_add, vec_sub, 2 mv_deep_copy; b in and x out
     every solve.  `value` is wall clock over everything; `loop_only` leaves out the per-solve set-up
     the reference's structure imposes on the host (deep copies of b on the host, cg.c:107-108, and
     the uploads they cause) and the final download."""
     L = pkg.lib()
-    assert L.cgb200_set_mode(pkg.RESIDENT) == 0
+    assert L.cgb200_set_mode(pkg.RESIDENT if resident else pkg.EAGER) == 0
     iters = 0
     loop_s = 0.0
     try:
@@ -429,7 +430,7 @@ def operator_api_loop(pkg, A, b, bnp, bs, J):
     return {"value": round(iters / sec, 2), "unit": UNIT, "solves": len(bs), "iterations_per_solve": J,
             "loop_only": {"value": round((iters - len(bs)) / loop_s, 2), "unit": UNIT,
                           "note": "iterations 2..J of every solve (vectors already on the device)"},
-            "mode": "CGB200_RESIDENT",
+            "mode": "CGB200_RESIDENT" if resident else "CGB200_EAGER (default)",
             "note": "the reference's loop statement by statement through mv_mult / dot_product / sv_mult / vec_add / "
                     "vec_sub / mv_deep_copy; wall clock; b in and x out every solve"}
 
@@ -481,6 +482,11 @@ def e2e_host_structs(pkg, d, info, J, solves=8):
         it_def += it
     def_s = time.perf_counter() - t
     st1 = pkg.cache_stats()
+    # the reference's loop kept by the caller, default (eager) mode, default policy: nothing opted into
+    try:
+        ops_eager = operator_api_loop(pkg, A, b, bnp, bs[:4], int(round(it_def / solves)), resident=False)
+    except Exception as e:  # noqa: BLE001
+        ops_eager = {"error": repr(e)}
     # (a') CGB200_CACHE_STRICT, the fallback where the kernel has no write tracking: every call hashes
     #     every byte of the host arrays
     L.cgb200_set_matrix_cache(pkg.CACHE_STRICT)
@@ -545,6 +551,7 @@ def e2e_host_structs(pkg, d, info, J, solves=8):
                 "the device already works); pinned_value: A handed over once with cgb200_to_device (no per-call validation); "
                 "strict_cache_value: A re-validated byte for byte on every call; cold_first_call_value: A uploaded from pageable memory",
         "operator_api": ops,
+        "operator_api_eager": ops_eager,
     }, x_par
 
 
