@@ -49,7 +49,8 @@ def traffic_from_profiles(kernel, workload, world):
     launch shape (same workload, 1 GPU), or None."""
     if world != 1:
         return None
-    key = {"dense32768": "dense", "lap3d512": "lap3d512", "lap2d4096": "lap2d", "banded52269": "banded52269"}.get(workload)
+    key = {"dense32768": "dense", "lap3d512": "lap3d512", "lap2d4096": "lap2d", "banded52269": "banded52269",
+           "banded52269_dia": "banded52269_dia"}.get(workload)
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             return json.load(f)["_by_workload"][key][kernel]
@@ -297,7 +298,8 @@ def long_row_leg(pkg, peak, peak_src, variant, K=300):
                 "achieved_gbs_per_gpu": round(bb / (ms_b * 1e-3) / 1e9, 1), "frac_of_peak": round(bb / (ms_b * 1e-3) / 1e9 / peak, 4),
                 "matvec": {"kernel": "k_spmv_dia", "algorithmic_bytes_per_launch": bk1, "avg_launch_ms": round(k1d, 5),
                            "achieved": round(bk1 / (k1d * 1e-3) / 1e9, 1), "unit": "GB/s",
-                           "frac": round(bk1 / (k1d * 1e-3) / 1e9 / peak, 4)},
+                           "frac": round(bk1 / (k1d * 1e-3) / 1e9 / peak, 4),
+                           "traffic": traffic_from_profiles("k_spmv_dia", "banded52269_dia", 1)},
                 "note": "diagonal storage of the band: same arithmetic in the same order, s = A p bit-identical to the CSR "
                         "kernel (tests/test_gpu_extensions.py)"}
             d.use_banded_format(False)

@@ -11,7 +11,7 @@ run() {  # name iterations skip count
       -f -o "gpurun_out/prof_${name}_classic" python tools/profile_target.py "$name" "$it" > "gpurun_out/ncu_$name.log" 2>&1
   echo "$name: rc=$? $(tail -1 gpurun_out/plain_$name.log)"
   ncu -i "gpurun_out/prof_${name}_classic.ncu-rep" --page raw --csv > "gpurun_out/prof_${name}_classic_raw.csv" 2>/dev/null
-  if [ "$name" = dense ] || [ "$name" = banded ]; then
+  if [ "$name" = dense ] || [ "$name" = banded ] || [ "$name" = bandeddia ]; then
     ncu -i "gpurun_out/prof_${name}_classic.ncu-rep" --page source --csv > "gpurun_out/prof_${name}_classic_source.csv" 2>/dev/null
   fi
   rm -f "gpurun_out/prof_${name}_classic.ncu-rep"
@@ -20,6 +20,7 @@ run dense 5 0 1          # one persistent launch = loop entry + 5 iterations
 run lap2d 8 3 6          # skip iteration 1, take iterations 2-3 (K1, K2, K3 each)
 run lap3d512 6 3 6
 run banded 8 3 6
+run bandeddia 8 3 6      # the same system stored as diagonals (optional format)
 python bench.py --steps 20 --warmup 3 --no-cpu --no-tts > gpurun_out/plain_bench.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/launches_bench.csv \
     python bench.py --steps 20 --warmup 3 --no-cpu --no-tts > gpurun_out/ncu_bench.log 2>&1

@@ -32,7 +32,7 @@ UNIT_SCALE = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3,
 
 
 def short(name):
-    m = re.match(r"(?:void )?(?:cgb::)?(k_\w+)", name)
+    m = re.search(r"\b(k_[a-z0-9_]+)", name)  # (also inside cgb::<unnamed>::)
     return m.group(1) if m else name[:40]
 
 
@@ -64,6 +64,7 @@ ALG = {  # algorithmic bytes per launch
     "lap2d": {"n": 4096 ** 2, "nnz": 5 * 4096 ** 2 - 4 * 4096},
     "lap3d512": {"n": 512 ** 3, "nnz": 7 * 512 ** 3 - 6 * 512 ** 2},
     "banded": {"n": 52269, "nnz": 18003049},   # course-sized long-row system (bench.py: banded52269)
+    "bandeddia": {"n": 52269, "nnz": 18003049, "dia": 345 * 52288},  # the same as 345 diagonals of ld = 52288 values
 }
 DENSE_ITERS_PER_LAUNCH = 5   # tools/ncu_round.sh profiles one persistent launch: loop entry + 5 iterations
 
@@ -77,6 +78,8 @@ def alg_bytes(w, kernel):
         return 8.0 * nnz + 88.0 * n
     if kernel.startswith("k_gemv"):
         return 8.0 * nnz + 16.0 * n
+    if kernel.startswith("k_spmv_dia"):  # every stored diagonal once (padding included) + p in + s out
+        return 8.0 * a["dia"] + 16.0 * n
     if kernel.startswith("k_spmv_pattern"):  # one byte per row instead of the CSR arrays
         return 1.0 * n + 16.0 * n
     if kernel.startswith("k_spmv"):
@@ -116,7 +119,7 @@ for path in paths:
                   f"{rd / 1e9:.4f} | {wrt / 1e9:.4f} | {(rd + wrt) / 1e9:.4f} | {alg / 1e9 if alg else 0:.4f} | {(rd + wrt) / alg if alg else 0:.3f} | "
                   f"{(rd + wrt) / t / 1e3:.0f} | {avg('dram_pct'):.1f} | {avg('l2_hit_pct'):.1f} | {avg('l1_hit_pct'):.1f} | {avg('warps_active_pct'):.1f} |")
         if v == "classic" or kname == "k_update_sr" or kname.startswith("k_spmv_pattern"):
-            key = {"banded": "banded52269"}.get(w, w)
+            key = {"banded": "banded52269", "bandeddia": "banded52269_dia"}.get(w, w)
             traffic["_by_workload"].setdefault(key, {})[kname] = round(rd + wrt)
             if kname == "k_cg_dense_solve":
                 traffic["_by_workload"][key]["_iterations_per_launch"] = DENSE_ITERS_PER_LAUNCH

@@ -1,6 +1,7 @@
 """Small fixed workload for ncu captures: a few CG iterations of one BASELINE config on 1 GPU.
-usage: profile_target.py {dense|lap2d|lap3d512|lap3d384|banded} [iterations] [classic|sr] [pattern]
-(banded: the course-sized long-row system of bench.py's `banded52269` line, n = 52269, 345 per row)"""
+usage: profile_target.py {dense|lap2d|lap3d512|lap3d384|banded|bandeddia} [iterations] [classic|sr] [pattern]
+(banded: the course-sized long-row system of bench.py's `banded52269` line, n = 52269, 345 per row;
+bandeddia: the same system in the optional diagonal storage, csrc/banded.cu)"""
 import os
 import sys
 
@@ -24,12 +25,15 @@ def _banded():
 
 d = {
     "banded": _banded,
+    "bandeddia": _banded,
     "dense": lambda: pkg.DeviceSystem.dense(32768),
     "lap2d": lambda: pkg.DeviceSystem.lap(4096, 4096, 1),
     "lap3d512": lambda: pkg.DeviceSystem.lap(512, 512, 512),
     "lap3d384": lambda: pkg.DeviceSystem.lap(384, 384, 384),
 }[w]()
 variant = pkg.SINGLE_REDUCTION if (len(sys.argv) > 3 and sys.argv[3] == "sr") else pkg.CLASSIC
+if w == "bandeddia":
+    assert d.use_banded_format(True), pkg.last_error()
 if len(sys.argv) > 4 and sys.argv[4] == "pattern":
     assert d.use_pattern_format(True), pkg.last_error()
 r = d.solve(iters - 1, check_every=iters, variant=variant)
