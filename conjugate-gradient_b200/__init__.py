@@ -190,6 +190,8 @@ def lib():
     L.cgb200_dist_comm_mode.restype = C.c_char_p
     L.cgb200_system_comm_is_p2p.argtypes = [C.c_void_p]
     L.cgb200_system_one_kernel_iteration.argtypes = [C.c_void_p]
+    L.cgb200_set_fused_vector_update.argtypes = [C.c_int]
+    L.cgb200_set_fused_vector_update.restype = None
     L.cgb200_system_use_pattern_format.argtypes = [C.c_void_p, C.c_int]
     L.cgb200_system_use_banded_format.argtypes = [C.c_void_p, C.c_int]
     _lib = L

@@ -1600,6 +1600,7 @@ int cgb200_system_trace(cgb200_system* sys, int on, unsigned long long* out16) {
 }
 
 void cgb200_set_one_kernel_iteration(int on) { set_dense_iter_enabled(on); }
+void cgb200_set_fused_vector_update(int on) { set_fused_vector_update(on); }
 
 int cgb200_system_one_kernel_iteration(cgb200_system* sys) {
   return sys && dense_one_kernel((System*)sys) ? 1 : 0;

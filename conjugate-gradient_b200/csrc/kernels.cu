@@ -1419,6 +1419,100 @@ k_update_p(double* __restrict__ p, const double* __restrict__ r, long long n, co
   push_finish(cm);
 }
 
+// K2 + K3 in one launch for systems whose vectors one wave of CTAs covers (single GPU, 32-byte
+// aligned vectors, at most 8 elements per thread).  On such systems the two vector kernels move a
+// few hundred KB and cost 5-9 us each -- launch, ramp and drain; the matvec of the reference's
+// course-sized matrix takes 49 us.  Here the grid does K2, meets at a grid barrier behind the
+// r.r reduction (the CTA that closes it forms beta, cg.c:129, and releases the epoch) and goes on
+// with K3 on the r and p it still holds in registers: one launch and two L2 round trips less per
+// iteration.  Same element-to-thread mapping and summation order as k_update_xr, so r.r -- and
+// with it every iterate -- has the bits of the three-kernel loop.  Launched co-operatively (all
+// CTAs resident: the barrier cannot starve).
+__global__ void __launch_bounds__(VT)
+k_update_xrp(double* __restrict__ x, double* __restrict__ r, double* __restrict__ p,
+             const double* __restrict__ s, long long n, double* __restrict__ partials,
+             unsigned int* __restrict__ ticket, CgState* S, const int rev,
+             const __grid_constant__ PeerComm cm) {
+  if (S->done) return;
+  __shared__ unsigned long long sh_e0;
+  if (threadIdx.x == 0) sh_e0 = ld_acquire_gpu(&S->grid_epoch);  // nobody can have released yet
+  __syncthreads();
+  const unsigned long long e = sh_e0 + 1;
+  const double alpha = S->alpha;
+  const long long n4 = n >> 2;  // (the launcher checked the alignment)
+  const long long stride = (long long)gridDim.x * VT;
+  const long long i = (long long)blockIdx.x * VT + threadIdx.x;
+  double acc = 0.0;
+  double4_t rv[VU4], pv[VU4];
+  {
+    double4_t xv[VU4], sv[VU4];
+#pragma unroll
+    for (int u = 0; u < VU4; ++u) {
+      const long long jj = i + u * stride;
+      const long long j = rev ? n4 - 1 - jj : jj;
+      if (jj < n4) {
+        xv[u] = ld4(x + 4 * j);
+        pv[u] = ld4(p + 4 * j);
+        rv[u] = ld4(r + 4 * j);
+        sv[u] = ld4(s + 4 * j);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < VU4; ++u) {
+      const long long jj = i + u * stride;
+      const long long j = rev ? n4 - 1 - jj : jj;
+      if (jj < n4) {
+        xv[u].x = __dadd_rn(xv[u].x, __dmul_rn(alpha, pv[u].x));
+        xv[u].y = __dadd_rn(xv[u].y, __dmul_rn(alpha, pv[u].y));
+        xv[u].z = __dadd_rn(xv[u].z, __dmul_rn(alpha, pv[u].z));
+        xv[u].w = __dadd_rn(xv[u].w, __dmul_rn(alpha, pv[u].w));
+        rv[u].x = __dsub_rn(rv[u].x, __dmul_rn(alpha, sv[u].x));
+        rv[u].y = __dsub_rn(rv[u].y, __dmul_rn(alpha, sv[u].y));
+        rv[u].z = __dsub_rn(rv[u].z, __dmul_rn(alpha, sv[u].z));
+        rv[u].w = __dsub_rn(rv[u].w, __dmul_rn(alpha, sv[u].w));
+        st4(x + 4 * j, xv[u]);
+        st4(r + 4 * j, rv[u]);
+        acc = fma(rv[u].x, rv[u].x, acc);
+        acc = fma(rv[u].y, rv[u].y, acc);
+        acc = fma(rv[u].z, rv[u].z, acc);
+        acc = fma(rv[u].w, rv[u].w, acc);
+      }
+    }
+  }
+  // the last n mod 4 elements: one each for the first threads of the grid
+  const long long jt = 4 * n4 + i;
+  double rt = 0.0, pt = 0.0;
+  if (jt < n) {
+    pt = p[jt];
+    const double xn = __dadd_rn(x[jt], __dmul_rn(alpha, pt));
+    rt = __dsub_rn(r[jt], __dmul_rn(alpha, s[jt]));
+    x[jt] = xn;
+    r[jt] = rt;
+    acc = fma(rt, rt, acc);
+  }
+  double v[1] = {acc};
+  if (grid_reduce<VT, 1>(v, partials, ticket)) {
+    finish_block<VT>(S, cm, FIN_RR, v[0], 0.0);
+    grid_release<VT>(&S->grid_epoch, e);
+  }
+  if (!grid_wait(&S->grid_epoch, e, S)) return;
+  if (ld_volatile_int(&S->done)) return;
+  const double beta = ld_volatile_f64(&S->beta);
+#pragma unroll
+  for (int u = 0; u < VU4; ++u) {
+    const long long jj = i + u * stride;
+    const long long j = rev ? n4 - 1 - jj : jj;
+    if (jj < n4) {
+      pv[u].x = __dadd_rn(rv[u].x, __dmul_rn(beta, pv[u].x));
+      pv[u].y = __dadd_rn(rv[u].y, __dmul_rn(beta, pv[u].y));
+      pv[u].z = __dadd_rn(rv[u].z, __dmul_rn(beta, pv[u].z));
+      pv[u].w = __dadd_rn(rv[u].w, __dmul_rn(beta, pv[u].w));
+      st4(p + 4 * j, pv[u]);
+    }
+  }
+  if (jt < n) p[jt] = __dadd_rn(rt, __dmul_rn(beta, pt));
+}
+
 // Single-reduction variant, the whole vector update in one pass (g = residual, held in the gather
 // vector; d = search direction; s = A d; w = A g):
 //   d = g + beta d ; s = w + beta s ; x += alpha d ; g -= alpha s ; push the new g to the peers
@@ -2368,6 +2462,49 @@ cudaError_t launch_update_p(double* p, const double* r, long long n, const CgSta
   k_update_p<<<vec_grid(n), VT, 0, st>>>(p, r, n, S, rev, cm);
   ++g_launches;
   return cudaGetLastError();
+}
+
+// K2 + K3 fused (k_update_xrp) when one resident wave of CTAs covers the vectors; false = not this system
+static int g_fuse_vec = -1;  // -1: CGB200_FUSE_VEC not looked at yet
+void set_fused_vector_update(int on) { g_fuse_vec = on ? 1 : 0; }
+
+bool update_xrp_applies(const double* x, const double* r, const double* p, const double* s, long long n) {
+  static int limit = -1;
+  if (g_fuse_vec < 0) {
+    const char* e = getenv("CGB200_FUSE_VEC");
+    g_fuse_vec = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  const int on = g_fuse_vec;
+  if (limit < 0) {
+    int bps = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_update_xrp, VT, 0) != cudaSuccess) bps = 0;
+    limit = bps * sm_count();
+  }
+  if (!on || n < 1) return false;
+  if ((((uintptr_t)x | (uintptr_t)r | (uintptr_t)p | (uintptr_t)s) & 31) != 0) return false;
+  const long long want = (n / 2 + (long long)VT * VU - 1) / ((long long)VT * VU);
+  // one pass: every thread holds its elements (at most 2 quads + 1) across the barrier.  Worth it up to
+  // half a wave of CTAs (measured, it/s fused vs three kernels: 32x32 grid 87.4k vs 81.0k, course-sized
+  // band 17.46k vs 17.03k, 512x512 grid 59.3k vs 58.8k; at 512 000 unknowns 47.4k vs 48.4k: not there)
+  return want <= limit && want <= (long long)sm_count() / 2;
+}
+
+cudaError_t launch_update_xrp(double* x, double* r, double* p, const double* s, long long n,
+                              double* partials, unsigned int* ticket, CgState* S, int rev,
+                              const PeerComm& cm, cudaStream_t st) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)vec_grid(n));
+  cfg.blockDim = dim3(VT);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, k_update_xrp, x, r, p, s, n, partials, ticket, S, rev, cm);
+  ++g_launches;
+  return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 cudaError_t launch_update_sr(double* x, double* g, double* d, double* s, const double* w,

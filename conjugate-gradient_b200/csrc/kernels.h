@@ -122,6 +122,12 @@ size_t dense_pool_doubles(int nrows, int ncols);   // size of the zero-initialis
 cudaError_t launch_update_xr(double* x, double* r, const double* p, const double* s, long long n,
                              double* partials, unsigned int* ticket, CgState* S, int fin, int rev,
                              const PeerComm& cm, cudaStream_t st);
+// K2 and K3 in one co-operative launch for small single-GPU systems (kernels.cu: k_update_xrp)
+void set_fused_vector_update(int on);  // A/B switch (CGB200_FUSE_VEC), for systems solved afterwards
+bool update_xrp_applies(const double* x, const double* r, const double* p, const double* s, long long n);
+cudaError_t launch_update_xrp(double* x, double* r, double* p, const double* s, long long n,
+                              double* partials, unsigned int* ticket, CgState* S, int rev,
+                              const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_update_p(double* p, const double* r, long long n, const CgState* S, int rev,
                             const PeerComm& cm, cudaStream_t st);
 cudaError_t launch_update_sr(double* x, double* g, double* d, double* s, const double* w,

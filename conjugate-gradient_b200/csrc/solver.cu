@@ -1180,6 +1180,11 @@ static bool sweep_enabled() {
   return on != 0;
 }
 
+// classic recurrence on one GPU without preconditioner, vectors covered by one resident wave of CTAs
+static bool fused_vector_update(const System* S) {
+  return S->world == 1 && !S->pc_loop && update_xrp_applies(S->x, S->r, S->p_own, S->s, S->nloc);
+}
+
 static int enqueue_iteration(System* S, int variant, int it = 0) {
   Ctx& c = g_ctx;
   CgState* st = S->state;
@@ -1205,6 +1210,11 @@ static int enqueue_iteration(System* S, int variant, int it = 0) {
   const bool d1 = sw && ((3 * it) & 1), d2 = sw && ((3 * it + 1) & 1), d3 = sw && ((3 * it + 2) & 1);
   if (enqueue_matvec(S, S->s, nccl ? FIN_LOCAL : FIN_PS, false, true, d1)) return -1;
   if (nccl && enqueue_nccl_finish(S, 1, FIN_PS)) return -1;
+  if (fused_vector_update(S)) {  // small single-GPU system: K2 and K3 in one launch
+    CUDA_OK(launch_update_xrp(S->x, S->r, S->p_own, S->s, S->nloc, S->partials, &st->ticket[1], st,
+                              d2 ? 1 : 0, cm, c.stream));
+    return 0;
+  }
   CUDA_OK(launch_update_xr(S->x, S->r, S->p_own, S->s, S->nloc, S->partials, &st->ticket[1], st,
                            nccl ? FIN_LOCAL : FIN_RR, d2 ? 1 : 0, cm, c.stream));
   if (nccl && enqueue_nccl_finish(S, 1, FIN_RR)) return -1;
@@ -1215,6 +1225,7 @@ static int enqueue_iteration(System* S, int variant, int it = 0) {
 // Kernel nodes per captured iteration (for the launch counter)
 static int kernels_per_iteration(const System* S, int variant) {
   int k = variant == 1 ? 2 : 3;
+  if (variant == 0 && fused_vector_update(S)) k = 2;
   if (S->world > 1 && !S->p2p) {
     k += variant == 1 ? 1 : 2;  // bookkeeping kernels
     if (!S->dense && !S->allgather && S->tb_hi > S->tb_lo &&
@@ -1226,7 +1237,7 @@ static int kernels_per_iteration(const System* S, int variant) {
 
 static int get_graph(System* S, int iters, int variant, cudaGraphExec_t* out) {
   Ctx& c = g_ctx;
-  const int key = 8 * iters + 4 * (S->pc_loop ? 1 : 0) + variant;
+  const int key = 16 * iters + 8 * (fused_vector_update(S) ? 1 : 0) + 4 * (S->pc_loop ? 1 : 0) + variant;
   auto it = S->graphs.find(key);
   if (it != S->graphs.end()) {
     *out = it->second;

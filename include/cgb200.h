@@ -226,6 +226,11 @@ int cgb200_system_one_kernel_iteration(cgb200_system *sys);
 /* Process-wide switch for the above (default on; CGB200_DENSE_FUSED=0 also turns it off): with 0 the
  * dense path runs the same three kernels per iteration as the CSR path.  For comparison runs. */
 void cgb200_set_one_kernel_iteration(int on);
+/* Small single-GPU CSR systems (vectors covered by one resident wave of CTAs, about 600 000 unknowns)
+ * run the two vector kernels of an iteration as ONE co-operative launch with a grid barrier behind
+ * the r.r reduction: 2 launches per iteration instead of 3, same bits.  Process-wide switch (default
+ * on; CGB200_FUSE_VEC=0 also turns it off), for systems solved afterwards.  For comparison runs. */
+void cgb200_set_fused_vector_update(int on);
 /* Row-pattern dictionary format (not in the reference, whose only layout is CSR,
  * mv_ops.h:17-23).  A CSR row block with at most 255 distinct rows -- a row being the list of
  * (column - row, value) pairs, as in constant-coefficient stencil and Toeplitz band matrices -- is

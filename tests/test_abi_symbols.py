@@ -208,7 +208,7 @@ def test_write_tracking_sees_writes_and_only_writes(pkg):
     assert op(b.ctypes.data, b.nbytes, 0) == 0 and op(b.ctypes.data, b.nbytes, 1) == 0
     assert op(p, nb, 3) == 0 and op(p, nb, 1) == -1
     assert op(b.ctypes.data, b.nbytes, 1) == 0
-    b[77] = 1.0
+    b[7700] = 1.0                                # (not in the array's first, partial page: only whole pages are watched)
     assert op(b.ctypes.data, b.nbytes, 1) == 1
     assert op(b.ctypes.data, b.nbytes, 3) == 0
     assert op(p, 100, 0) == -1                   # no whole page inside

@@ -343,15 +343,21 @@ def test_malformed_csr_is_refused_and_the_library_stays_usable(pkg, gpu_lib):
 @pytest.mark.parametrize("M", [0, 3, 31, 32, 40, 70])
 def test_fixed_count_solve_launches_exactly_the_iterations_it_runs(pkg, gpu_lib, M):
     # max_iter = M is M + 1 updates (cg.c:110-135): 3 kernels each + the loop entry, no early-exit
-    # launches behind the last one (the final batch is a tail graph of the right length)
-    d = pkg.DeviceSystem.lap(64, 48)
-    r = d.solve(M)
-    assert r.iterations == M + 1 and r.status == pkg.MAXITER
-    assert r.kernel_launches == 3 * (M + 1) + 1
-    t = d.solve_async(M)
-    ra = d.solve_wait(t)
-    assert ra.iterations == M + 1 and ra.kernel_launches == 3 * (M + 1) + 1
-    d.free()
+    # launches behind the last one (the final batch is a tail graph of the right length); a system this
+    # small runs its two vector kernels as one launch by default (k_update_xrp): 2 per update
+    try:
+        for fused, per in ((0, 3), (1, 2)):
+            gpu_lib.cgb200_set_fused_vector_update(fused)
+            d = pkg.DeviceSystem.lap(64, 48)
+            r = d.solve(M)
+            assert r.iterations == M + 1 and r.status == pkg.MAXITER
+            assert r.kernel_launches == per * (M + 1) + 1
+            t = d.solve_async(M)
+            ra = d.solve_wait(t)
+            assert ra.iterations == M + 1 and ra.kernel_launches == per * (M + 1) + 1
+            d.free()
+    finally:
+        gpu_lib.cgb200_set_fused_vector_update(1)
 
 
 def test_calls_from_several_threads_are_serialised_not_corrupted(pkg, gpu_lib):

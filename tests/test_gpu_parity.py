@@ -497,6 +497,39 @@ def _dev(pkg, s):
     return pkg.DeviceSystem.from_csr(s.n, 0, s.row_ptr, s.cols, s.vals, s.b)
 
 
+@pytest.mark.parametrize("make", [lambda: H.lap(64, 48), lambda: H.lap(37, 29), lambda: H.lap(31, 21, 17),
+                                  lambda: H.banded(1201, 60), lambda: H.banded(3002, 40), lambda: H.lap(1, 1),
+                                  lambda: H.lap(3, 1), lambda: H.lap(500, 600)],
+                         ids=["lap64x48", "lap37x29_n%4=1", "lap3d_n%4=3", "banded1201", "banded3002_n%4=2", "n=1", "n=3",
+                              "lap500x600"])
+def test_fused_vector_update_has_the_bits_of_the_three_kernel_loop(pkg, gpu_lib, make):
+    # small single-GPU systems: K2 and K3 as one co-operative launch (k_update_xrp).  Same element-to-
+    # thread mapping and summation order as k_update_xr, so x, r.r and the iteration count are
+    # bit-identical to the three-kernel loop; and both agree with the oracle
+    s = make()
+    xo = H.oracle_cg(s, 12, guard=1)[0]            # (guard: stop where the reference would divide by r.r = 0)
+    got = {}
+    try:
+        for fused in (1, 0):
+            gpu_lib.cgb200_set_fused_vector_update(fused)
+            d = _dev(pkg, s)
+            r = d.solve(12, check_every=5)
+            x12 = d.x()
+            rt = d.solve(5000, tol=1e-11)
+            got[fused] = (x12, r.rr, r.iterations, r.kernel_launches, d.x(), rt.iterations, rt.status, rt.rr)
+            d.free()
+    finally:
+        gpu_lib.cgb200_set_fused_vector_update(1)
+    f, u = got[1], got[0]
+    assert f[2] == u[2] and f[5] == u[5] and f[6] == u[6]
+    assert np.array_equal(f[0].view(np.uint64), u[0].view(np.uint64))
+    assert np.array_equal(f[4].view(np.uint64), u[4].view(np.uint64))
+    assert f[1] == u[1] and f[7] == u[7]
+    if u[2] == 13:                                   # (tiny systems stop early: exact solution reached)
+        assert f[3] == 2 * 13 + 1 and u[3] == 3 * 13 + 1
+    assert np.linalg.norm(f[0] - xo) <= 1e-8 * max(np.linalg.norm(xo), 1e-300)
+
+
 @pytest.mark.parametrize("n", [256, 1000, 2052, 4096])
 def test_dense_one_kernel_iteration_matches_three_kernel_form(pkg, gpu_lib, n):
     # dense path: loop entry and every iteration in ONE cooperative launch per solve
@@ -513,7 +546,7 @@ def test_dense_one_kernel_iteration_matches_three_kernel_form(pkg, gpu_lib, n):
             r = d.solve(4, check_every=5)
             launches = gpu_lib.cgb200_launch_count() - l0
             assert r.iterations == it_o == 5 and r.status == pkg.MAXITER
-            assert launches == (1 if on else 1 + 15), launches      # one launch per solve | k_init + 5 x (K1, K2, K3)
+            assert launches == (1 if on else 1 + 10), launches      # one launch per solve | k_init + 5 x (K1, K2+K3 fused: small system)
             rt = d.solve(500, tol=1e-10)
             got[on] = (d.x(), r.rr, rt.iterations, rt.status, d.true_relres())
             d.gen_rhs(3)
