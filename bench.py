@@ -1151,8 +1151,9 @@ def main():
     tail = {"n_gpus": world, "workloads": summary}
     if isinstance(line.get("e2e"), dict) and line["e2e"].get("value") is not None:
         e = line["e2e"]
-        tail["e2e"] = {"default": e["value"], "pinned": e.get("pinned_value"), "strict": e.get("strict_cache_value"),
-                       "cold": e.get("cold_first_call_value")}
+        tail["e2e"] = {k: v for k, v in (("default" if world == 1 else "value", e["value"]), ("pinned", e.get("pinned_value")),
+                                            ("strict", e.get("strict_cache_value")), ("cold", e.get("cold_first_call_value")))
+                       if v is not None}
     if "parity" in line:
         tail["parity"] = {"dense32768_K5_vs_reference_rel_l2": compact(line["parity"]["rel_l2"], 3), "tol": 1e-8}
     if pm is not None:
