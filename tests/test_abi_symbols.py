@@ -213,3 +213,42 @@ def test_write_tracking_sees_writes_and_only_writes(pkg):
     assert op(b.ctypes.data, b.nbytes, 3) == 0
     assert op(p, 100, 0) == -1                   # no whole page inside
 
+
+def test_write_tracking_on_transparent_huge_pages(pkg):
+    # multi-GB matrices are backed by 2 MiB pages where the system allows it: one stored byte inside a
+    # huge page is seen, re-arming clears it, and the untouched huge pages stay clean
+    import ctypes as C
+
+    import numpy as np
+
+    L = pkg.lib()
+    if not L.cgb200_write_tracking_available():
+        pytest.skip("this kernel has no userfaultfd async write protection / PAGEMAP_SCAN")
+    a = np.empty(4 << 20)                        # 32 MiB, untouched
+    lo = (a.ctypes.data + 4095) & ~4095
+    ln = (a.ctypes.data + a.nbytes - lo) & ~4095
+    C.CDLL(None, use_errno=True).madvise(C.c_void_p(lo), C.c_size_t(ln), 14)    # MADV_HUGEPAGE
+    a[:] = 1.0                                   # first touch: huge pages where available
+    huge_kb = 0
+    with open("/proc/self/smaps") as f:
+        inside = False
+        for ln_ in f:
+            if "-" in ln_.split(" ")[0] and ln_[0] in "0123456789abcdef":
+                b0, b1 = (int(x, 16) for x in ln_.split(" ")[0].split("-"))
+                inside = b0 <= lo + (8 << 20) < b1       # (the madvise split the mapping: look in its middle)
+            elif inside and ln_.startswith("AnonHugePages:"):
+                huge_kb = int(ln_.split()[1])
+    op = L.cgb200_write_tracking_op
+    p, nb = a.ctypes.data, a.nbytes
+    assert op(p, nb, 0) == 0 and op(p, nb, 1) == 0
+    for k in (300_000, 1_500_000, 2_621_440 + 7, a.size - 600):
+        assert float(a[k - 100:k + 100].sum()) == 200.0 and op(p, nb, 1) == 0     # reads leave it clean
+        a[k] = 2.0
+        assert op(p, nb, 1) == 1, (k, huge_kb)
+        assert op(p, nb, 2) == 0 and op(p, nb, 1) == 0, (k, huge_kb)
+        a[k] = 1.0
+        assert op(p, nb, 1) == 1
+        assert op(p, nb, 2) == 0 and op(p, nb, 1) == 0
+    assert op(p, nb, 3) == 0
+    print("AnonHugePages under the array:", huge_kb, "kB")
+

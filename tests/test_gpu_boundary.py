@@ -226,6 +226,36 @@ def test_large_pageable_arrays_upload_through_the_staged_copy(pkg, gpu_lib, monk
         assert np.array_equal(_bits(_take(out, s.n)), want), staged
         L.cgb200_invalidate(C.byref(A))
         L.cgb200_free_all(out)
+    # arrays this large are usually backed by transparent huge pages: single stores anywhere in them are
+    # still seen by the default (tracked) policy -- at the start, in the middle, at the end of a 2 MiB page
+    monkeypatch.setenv("CGB200_STAGED_UPLOAD", "1")
+    assert L.cgb200_set_matrix_cache(pkg.CACHE_TRACKED) == 0
+    fresh = np.empty(s.nnz)                          # ask for huge pages whatever the system default is
+    lo = (fresh.ctypes.data + 4095) & ~4095
+    C.CDLL(None, use_errno=True).madvise(C.c_void_p(lo), C.c_size_t((fresh.ctypes.data + fresh.nbytes - lo) & ~4095), 14)
+    fresh[:] = s.vals                                # (14 = MADV_HUGEPAGE; first touch happens here)
+    s.vals = fresh
+    want = _bits(_spmv(s, v))
+    A, _ = _structs(pkg, s)
+    out = pkg.MvSparseP()
+    assert L.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0, pkg.last_error()
+    assert np.array_equal(_bits(_take(out, s.n)), want)
+    base = s.vals.ctypes.data
+    first_huge = (-base) % (2 << 20) // 8            # index of the first element on a 2 MiB boundary
+    for k in (first_huge, first_huge + (1 << 18) - 1, first_huge + 5 * (1 << 18) + 12345, s.nnz // 2, s.nnz - 3):
+        u0 = pkg.cache_stats()["uploads"]
+        s.vals[k] += 1.0
+        assert L.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0, pkg.last_error()
+        assert np.array_equal(_bits(_take(out, s.n)), _bits(_spmv(s, v))), k
+        assert pkg.cache_stats()["uploads"] == u0 + 1
+        assert L.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0
+        assert pkg.cache_stats()["uploads"] == u0 + 1   # and clean again
+    c0 = s.cols[s.nnz // 3]
+    s.cols[s.nnz // 3] = c0 + 1 if c0 + 1 < s.n else c0 - 1
+    assert L.mv_mult(C.byref(A), C.byref(vv), C.byref(out)) == 0, pkg.last_error()
+    assert np.array_equal(_bits(_take(out, s.n)), _bits(_spmv(s, v)))
+    L.cgb200_invalidate(C.byref(A))
+    L.cgb200_free_all(out)
 
 
 def test_large_vectors_move_through_the_staged_copy_in_both_directions(pkg, gpu_lib, monkeypatch):
