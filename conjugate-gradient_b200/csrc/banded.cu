@@ -90,7 +90,9 @@ k_spmv_dia(const double* __restrict__ dia, const long long ld, const int D, cons
     // course-sized matrix: a second batch in flight, values double-buffered in registers, is SLOWER --
     // 37.0 against 32.3 us, 149 registers --, and so are 256-thread CTAs (39.0); 32- and 64-thread
     // CTAs are level with 128 (32.9 / 31.9).  At 145 MB per product the launch is ramp and tail
-    // around ~22 us of streaming, like the CSR long-row kernel at this size.)
+    // around ~22 us of streaming, like the CSR long-row kernel at this size.  16 rows per warp -- the
+    // half-warps taking alternate diagonals, products handed over by shuffle, same sums -- doubles the
+    // warps and the loads in flight and is slower still: 41.4 us with 16 loads per lane, 44.1 with 8.)
 #pragma unroll 1
     for (int d = 0; d < D; d += U) {
       double v[U], pv[U];
