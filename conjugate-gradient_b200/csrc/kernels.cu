@@ -403,7 +403,8 @@ k_spmv_rowgroup(const double* __restrict__ vals, const int* __restrict__ cols,
 // launch is not DRAM-bound), a ring of 16-byte asynchronous copies with gather-ahead (0.45), a
 // thread per row fed by per-row bulk copies (0.31), blocks drawn from an atomic counter with a
 // predicate-free path for full slabs (0.64), paired 128-bit loads covering two rows per
-// instruction (0.61), three CTAs per SM at 80 registers (0.34, spills).
+// instruction (0.61), three CTAs per SM at 80 registers (0.34, spills), the next slab's indices
+// requested right behind the gathers instead of after the products (0.65).
 template <int THREADS, int ROWS, bool COHERENT>
 __global__ void __launch_bounds__(THREADS)
 k_spmv_rowblock(const double* __restrict__ vals, const int* __restrict__ cols,
