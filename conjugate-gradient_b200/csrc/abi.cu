@@ -469,7 +469,7 @@ MatrixEntry* matrix_entry(struct __mv_sparse* A, bool pin, bool want_team, Pendi
         // exactly, without reading the arrays
         HostArr a[3];
         host_arrays(A, a);
-        if (pc && old.sys && !want_team) {  // asked while the device works: PendingCheck
+        if (pc && (want_team ? old.team != nullptr : old.sys != nullptr)) {  // asked while the device works: PendingCheck
           pc->entry = &old;
           pc->started = true;
           const HostArr a0 = a[0], a1 = a[1], a2 = a[2];
@@ -931,7 +931,8 @@ int solve_host(struct __mv_sparse* A, struct __mv_sparse* b, struct __mv_sparse*
   std::lock_guard<std::mutex> lk(g_tab_mu);
   Ctx& c = ctx();
   if (want_team(A)) {  // CGB200_GPUS > 1: the same call, the matrix cut into row blocks over the GPU team
-    MatrixEntry* e = matrix_entry(A, false, true);
+    PendingCheck pc;  // (tracked policy: A's arrays are checked while the team already solves)
+    MatrixEntry* e = matrix_entry(A, false, true, &pc);
     if (e && e->team) {
       if (sync_to_host(b)) return -1;
       const int n = b->size;
@@ -949,7 +950,14 @@ int solve_host(struct __mv_sparse* A, struct __mv_sparse* b, struct __mv_sparse*
       xv->size = n;
       xv->nnz = n;
       xv->values = (double*)calloc(n > 0 ? n : 1, sizeof(double));
-      if (!xv->values || team_solve(e->team, b->values, x0, xv->values, o, res)) {
+      bool ok = xv->values != nullptr && team_solve(e->team, b->values, x0, xv->values, o, res) == 0;
+      if (ok && !pc.settle()) {
+        // A was written since it was cut and uploaded: that solve is dropped; validate the ordinary
+        // way (hash, re-cut and upload if different) and solve again
+        e = matrix_entry(A, false, true);
+        ok = e && e->team && team_solve(e->team, b->values, x0, xv->values, o, res) == 0;
+      }
+      if (!ok) {
         free(xv->values);
         free(xv);
         return -1;
