@@ -114,7 +114,13 @@ int cgb200_set_mode(int mode);
  *                        arrays.  Written, or the kernel cannot tell (no support, page-locked
  *                        memory -- device DMA bypasses the page tables --, any error): the full
  *                        hash below decides.  The caller pays one minor fault per 4 KiB page it
- *                        rewrites.  CGB200_WRITE_TRACKING=0 disables the tracking.
+ *                        rewrites.  CGB200_WRITE_TRACKING=0 disables the tracking.  mv_mult and
+ *                        the solves ask the question on a host thread while the device already
+ *                        works on the copy it has, and look at the answer before any result leaves
+ *                        the library: a write means that result is dropped and the call repeats
+ *                        after the ordinary validation.  Two structs over the same arrays share
+ *                        one watch; the arrays must not be written WHILE a call on them runs (the
+ *                        reference reads them during the call too).
  *   CGB200_CACHE_STRICT  hash of every byte of values / col_indices / row_ptr on every call,
  *                        several host threads: any in-place edit is seen and causes a fresh upload;
  *   CGB200_CACHE_SAMPLED 96 samples + the array addresses (constant time): notices a rebuilt
