@@ -252,3 +252,22 @@ def test_write_tracking_on_transparent_huge_pages(pkg):
     assert op(p, nb, 3) == 0
     print("AnonHugePages under the array:", huge_kb, "kB")
 
+
+
+def test_every_environment_variable_the_library_reads_is_documented():
+    # INTEGRATION.md section 7 is the list a maintainer of the reference looks at
+    import glob
+    import re
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pk = os.path.join(root, "conjugate-gradient_b200")
+    read = set()
+    for f in glob.glob(os.path.join(pk, "csrc", "*")) + glob.glob(os.path.join(pk, "driver", "*")) + [os.path.join(pk, "__init__.py")]:
+        with open(f, errors="replace") as fh:
+            t = fh.read()
+        read |= set(re.findall(r'getenv\("(CGB200_[A-Z0-9_]+)"\)', t))
+        read |= set(re.findall(r'environ\.get\("(CGB200_[A-Z0-9_]+)"', t))
+    with open(os.path.join(root, "INTEGRATION.md")) as fh:
+        doc = fh.read()
+    assert len(read) > 20
+    assert sorted(e for e in read if e not in doc) == []
