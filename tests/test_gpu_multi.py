@@ -132,7 +132,7 @@ for name, s, M in [("lap3d", H.lap(40, 36, 30), 60), ("banded", H.banded(3001, 7
     assert L.conj_grad(M, C.byref(A), C.byref(b), C.byref(xp)) == 0, pkg.last_error()
     x = np.ctypeslib.as_array(xp.contents.values, shape=(s.n,)).copy()
     out[name] = {"rel": rel(x, H.oracle_cg(s, M)[0]), "gpus": L.cgb200_gpus_in_use()}
-    # an in-place edit between two calls is seen by the team as by one GPU (strict cache)
+    # an in-place edit between two calls is seen by the team as by one GPU (default cache policy)
     if name == "banded":
         s.vals[s.row_ptr[1:] - 1] *= 1.5
         assert L.conj_grad(M, C.byref(A), C.byref(b), C.byref(xp)) == 0, pkg.last_error()
